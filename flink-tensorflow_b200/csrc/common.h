@@ -1,0 +1,47 @@
+// common.h -- shared declarations of the runner library (host + device).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <string>
+#include "../../include/ftf.h"
+
+namespace ftf {
+
+// Per-thread message of the last failing call that had no runner to attach it to.
+void set_thread_error(const std::string& msg);
+const char* thread_error();
+
+// Formats "<what>: <cudaGetErrorString>" into *err and returns FTF_INTERNAL.
+int cuda_fail(cudaError_t e, const char* what, std::string* err);
+
+#define FTF_CUDA(call, errp)                                                       \
+    do {                                                                           \
+        cudaError_t e__ = (call);                                                  \
+        if (e__ != cudaSuccess) return ::ftf::cuda_fail(e__, #call, (errp));       \
+    } while (0)
+
+// Driver entry points fetched through the runtime (no link-time dependency on libcuda).
+typedef CUresult (*tensor_map_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                               const cuuint64_t*, const cuuint64_t*,
+                                               const cuuint32_t*, const cuuint32_t*,
+                                               CUtensorMapInterleave, CUtensorMapSwizzle,
+                                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+tensor_map_encode_tiled_fn get_tensor_map_encode_tiled();
+
+int device_sm_count(int device);
+
+// ---- kernel launchers (one per .cu file); each returns an FTF status and fills *err. ----------
+int launch_affine_f32(const float* x, float* y, int64_t n, float a, float b, cudaStream_t s,
+                      std::string* err);
+int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out_h, int out_w,
+                       float mean, float scale, void* out, int out_dtype, cudaStream_t s,
+                       std::string* err);
+int launch_softmax_topk(const float* x, int64_t m, int n, int n_labels, int k, int apply_softmax,
+                        float* probs, int32_t* idx, float* score, cudaStream_t s, std::string* err);
+
+// Count of this library's kernel launches (process-wide, relaxed).
+void count_launch(int n = 1);
+uint64_t launches_so_far();
+
+}  // namespace ftf

@@ -1,0 +1,255 @@
+// K2  Cast(u8->f32) -> ResizeBilinear(align_corners=false) -> Sub(mean) -> Div(scale), fused.
+//
+// Reference: flink-tensorflow-examples/src/main/scala/org/apache/flink/contrib/tensorflow/examples/
+// inception/ImageNormalization.scala:57-65 builds Div(Sub(ResizeBilinear(ExpandDims(Cast(DecodeJpeg))))),
+// ops from .../examples/common/GraphBuilder.java:21-39; five materialised fp32 tensors per record on the
+// reference's CPU path, one pass here.  DecodeJpeg sits before this kernel (raw RGB records).
+//
+// Arithmetic follows TF-1.1's CPU ResizeBilinear exactly and in the same order, every operation
+// individually rounded (__f*_rn intrinsics are never fused), so results are bit-identical:
+//   scale = in/(float)out; p = (float)i*scale; lo = (int)p; hi = min(lo+1, in-1); l = p - lo
+//   top = tl + (tr-tl)*xl; bot = bl + (br-bl)*xl; v = top + (bot-top)*yl; out = (v-mean)/scale
+//
+// Layout: in u8 [n,in_h,in_w,3] (HWC rows of in_w*3 bytes), out f32/bf16 [n,out_h,out_w,3].
+// HBM-bound: each input byte and each output element crosses HBM once.  A CTA owns a band of `th`
+// full-width output rows of one image: the input rows the band touches are fetched by TMA
+// (cp.async.bulk.tensor, <=256-byte wide column chunks of a 3-D tensor map) into shared memory, the
+// 4-tap lerp reads shared memory, and the band's output is one contiguous, fully coalesced range.
+#include "common.h"
+#include "ptx.cuh"
+#include <cuda_bf16.h>
+#include <math.h>
+
+namespace ftf {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxBandRows = 64;   // output rows per band upper bound (row tables in smem)
+
+struct ResizeParams {
+    int in_h, in_w, out_h, out_w;
+    float hs, ws;            // in/(float)out
+    float mean, scale, inv_scale;
+    int th;                  // output rows per band
+    int bands;               // bands per image
+    int br;                  // input rows fetched per band (TMA box height)
+    int cw;                  // chunk width in bytes (TMA box width)
+    int n_chunks;
+    int chunk_stride;        // bytes between chunk regions in smem (128-byte multiple)
+    long long n;             // images
+};
+
+template <typename T> __device__ __forceinline__ T to_out(float v);
+template <> __device__ __forceinline__ float to_out<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 to_out<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+template <bool kMulRecip>
+__device__ __forceinline__ float finish(float top, float bot, float yl, const ResizeParams& p) {
+    const float v = __fadd_rn(top, __fmul_rn(__fsub_rn(bot, top), yl));
+    const float d = __fsub_rn(v, p.mean);
+    return kMulRecip ? __fmul_rn(d, p.inv_scale) : __fdiv_rn(d, p.scale);
+}
+
+// ---- TMA-staged band kernel -------------------------------------------------------------------
+template <bool kMulRecip, typename OutT>
+__global__ void __launch_bounds__(kThreads)
+resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ int row_lo[kMaxBandRows], row_hi[kMaxBandRows];
+    __shared__ float row_l[kMaxBandRows];
+
+    const long long blk = blockIdx.x;
+    const long long img = blk / p.bands;
+    const int band = (int)(blk - img * p.bands);
+    const int oy0 = band * p.th;
+    const int rows = min(p.th, p.out_h - oy0);
+    const int iy0 = (int)__fmul_rn((float)oy0, p.hs);  // first input row of the band
+
+    if (threadIdx.x == 0) {
+        ptx::mbar_init(&bar, 1);
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        ptx::mbar_expect_tx(&bar, (uint32_t)(p.n_chunks * p.cw * p.br));
+        for (int k = 0; k < p.n_chunks; ++k)
+            ptx::tma_load_3d(smem + (size_t)k * p.chunk_stride, &tmap, &bar, k * p.cw, iy0, (int)img);
+    }
+    // per-row interpolation table while the copy is in flight
+    if (threadIdx.x < rows) {
+        const float py = __fmul_rn((float)(oy0 + threadIdx.x), p.hs);
+        const int lo = (int)py;
+        const int hi = min(lo + 1, p.in_h - 1);
+        row_lo[threadIdx.x] = (lo - iy0) * p.cw;
+        row_hi[threadIdx.x] = (hi - iy0) * p.cw;
+        row_l[threadIdx.x] = __fsub_rn(py, (float)lo);
+    }
+    __syncthreads();
+
+    const int ow3 = p.out_w * 3;
+    OutT* obase = out + ((size_t)img * p.out_h + oy0) * ow3;
+    bool waited = false;
+    for (int col = threadIdx.x; col < ow3; col += kThreads) {
+        const int px = col / 3, c = col - px * 3;
+        const float fx = __fmul_rn((float)px, p.ws);
+        const int lo = (int)fx;
+        const int hi = min(lo + 1, p.in_w - 1);
+        const float xl = __fsub_rn(fx, (float)lo);
+        const int blo = lo * 3 + c, bhi = hi * 3 + c;
+        const int klo = blo / p.cw, khi = bhi / p.cw;
+        const uint8_t* s_lo = smem + (size_t)klo * p.chunk_stride + (blo - klo * p.cw);
+        const uint8_t* s_hi = smem + (size_t)khi * p.chunk_stride + (bhi - khi * p.cw);
+        if (!waited) { ptx::mbar_wait(&bar, 0); waited = true; }
+#pragma unroll 4
+        for (int r = 0; r < rows; ++r) {
+            const int o0 = row_lo[r], o1 = row_hi[r];
+            const float tl = (float)s_lo[o0], tr = (float)s_hi[o0];
+            const float bl = (float)s_lo[o1], br = (float)s_hi[o1];
+            const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(tr, tl), xl));
+            const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(br, bl), xl));
+            obase[(size_t)r * ow3 + col] = to_out<OutT>(finish<kMulRecip>(top, bot, row_l[r], p));
+        }
+    }
+    if (!waited) ptx::mbar_wait(&bar, 0);  // never leave a copy in flight behind an exiting CTA
+}
+
+// ---- direct kernel: any alignment, any size; one thread per output element ---------------------
+template <bool kMulRecip, typename OutT>
+__global__ void __launch_bounds__(kThreads)
+resize_norm_direct(const uint8_t* __restrict__ in, OutT* __restrict__ out, const ResizeParams p) {
+    const long long ow3 = (long long)p.out_w * 3;
+    const long long per_img = (long long)p.out_h * ow3;
+    const long long total = p.n * per_img;
+    const long long stride = (long long)gridDim.x * kThreads;
+    for (long long e = (long long)blockIdx.x * kThreads + threadIdx.x; e < total; e += stride) {
+        const long long img = e / per_img;
+        const long long rem = e - img * per_img;
+        const int oy = (int)(rem / ow3);
+        const int col = (int)(rem - (long long)oy * ow3);
+        const int px = col / 3, c = col - px * 3;
+        const float py = __fmul_rn((float)oy, p.hs);
+        const int ylo = (int)py, yhi = min(ylo + 1, p.in_h - 1);
+        const float yl = __fsub_rn(py, (float)ylo);
+        const float fx = __fmul_rn((float)px, p.ws);
+        const int xlo = (int)fx, xhi = min(xlo + 1, p.in_w - 1);
+        const float xl = __fsub_rn(fx, (float)xlo);
+        const uint8_t* base = in + (size_t)img * p.in_h * p.in_w * 3;
+        const uint8_t* r0 = base + (size_t)ylo * p.in_w * 3;
+        const uint8_t* r1 = base + (size_t)yhi * p.in_w * 3;
+        const float tl = (float)__ldg(r0 + xlo * 3 + c), tr = (float)__ldg(r0 + xhi * 3 + c);
+        const float bl = (float)__ldg(r1 + xlo * 3 + c), br = (float)__ldg(r1 + xhi * 3 + c);
+        const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(tr, tl), xl));
+        const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(br, bl), xl));
+        out[e] = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
+    }
+}
+
+bool exact_reciprocal(float s, float* inv) {
+    if (!(s > 0.0f) || isinf(s)) return false;
+    int e = 0;
+    const float m = frexpf(s, &e);
+    if (m != 0.5f || e < -60 || e > 60) return false;
+    *inv = 1.0f / s;
+    return true;
+}
+
+// Input rows a band of `th` output rows touches, worst case over the bands of one image.
+int band_input_rows(int th, int in_h, int out_h, float hs) {
+    int worst = 1;
+    for (int oy0 = 0; oy0 < out_h; oy0 += th) {
+        const int last = (oy0 + th < out_h ? oy0 + th : out_h) - 1;
+        const int lo = (int)((float)oy0 * hs);
+        const int l2 = (int)((float)last * hs);
+        const int hi = l2 + 1 < in_h - 1 ? l2 + 1 : in_h - 1;
+        if (hi - lo + 1 > worst) worst = hi - lo + 1;
+    }
+    return worst;
+}
+
+template <typename OutT>
+int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool use_tma, size_t smem,
+                 const CUtensorMap* tmap, int sms, cudaStream_t s, std::string* err) {
+    if (use_tma) {
+        auto kern = recip ? resize_norm_band_tma<true, OutT> : resize_norm_band_tma<false, OutT>;
+        FTF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), err);
+        const long long blocks = p.n * p.bands;
+        kern<<<(unsigned)blocks, kThreads, smem, s>>>(*tmap, out, p);
+    } else {
+        auto kern = recip ? resize_norm_direct<true, OutT> : resize_norm_direct<false, OutT>;
+        const long long total = p.n * p.out_h * p.out_w * 3;
+        long long want = (total + kThreads - 1) / kThreads;
+        const long long cap = (long long)sms * 8 * 4;
+        kern<<<(unsigned)(want < cap ? want : cap), kThreads, 0, s>>>(in, out, p);
+    }
+    count_launch();
+    FTF_CUDA(cudaGetLastError(), err);
+    return FTF_OK;
+}
+
+}  // namespace
+
+int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out_h, int out_w, float mean,
+                       float scale, void* out, int out_dtype, cudaStream_t s, std::string* err) {
+    if (n < 0 || in_h <= 0 || in_w <= 0 || out_h <= 0 || out_w <= 0 || (n > 0 && (!in || !out))) {
+        if (err) *err = "resize_norm: bad shape or null buffer";
+        return FTF_INVALID_ARGUMENT;
+    }
+    if (out_dtype != FTF_FLOAT && out_dtype != FTF_BFLOAT16) {
+        if (err) *err = "resize_norm: output dtype must be FLOAT or BFLOAT16";
+        return FTF_INVALID_ARGUMENT;
+    }
+    if (n == 0) return FTF_OK;
+    int dev = 0;
+    FTF_CUDA(cudaGetDevice(&dev), err);
+    const int sms = device_sm_count(dev);
+
+    ResizeParams p{};
+    p.in_h = in_h; p.in_w = in_w; p.out_h = out_h; p.out_w = out_w;
+    p.hs = (float)in_h / (float)out_h;
+    p.ws = (float)in_w / (float)out_w;
+    p.mean = mean; p.scale = scale; p.inv_scale = 0.0f; p.n = n;
+    const bool recip = exact_reciprocal(scale, &p.inv_scale);
+
+    // TMA path preconditions: 16-byte aligned base and row pitch, dimensions within tensor-map limits.
+    const long long row_bytes = (long long)in_w * 3;
+    bool use_tma = ((uintptr_t)in & 15u) == 0 && row_bytes % 16 == 0 && n * (long long)((out_h + 0)) < (1ll << 31) &&
+                   n <= 0x7fffffffLL;
+    size_t smem = 0;
+    CUtensorMap tmap;
+    if (use_tma) {
+        p.n_chunks = (int)((row_bytes + 255) / 256);
+        p.cw = (int)(((row_bytes + p.n_chunks - 1) / p.n_chunks + 15) / 16 * 16);
+        bool fits = false;
+        for (int th = 8; th >= 1; th /= 2) {
+            p.th = th < out_h ? th : out_h;
+            p.br = band_input_rows(p.th, in_h, out_h, p.hs);
+            p.chunk_stride = (p.cw * p.br + 127) / 128 * 128;
+            smem = (size_t)p.chunk_stride * p.n_chunks;
+            if (p.br <= 256 && smem <= 96 * 1024) { fits = true; break; }
+        }
+        p.bands = (out_h + p.th - 1) / p.th;
+        if (!fits || n * (long long)p.bands > 0x7fffffffLL) use_tma = false;
+    }
+    if (use_tma) {
+        auto encode = get_tensor_map_encode_tiled();
+        if (!encode) { if (err) *err = "cuTensorMapEncodeTiled entry point not found"; return FTF_INTERNAL; }
+        cuuint64_t dims[3] = {(cuuint64_t)row_bytes, (cuuint64_t)in_h, (cuuint64_t)n};
+        cuuint64_t strides[2] = {(cuuint64_t)row_bytes, (cuuint64_t)row_bytes * (cuuint64_t)in_h};
+        cuuint32_t box[3] = {(cuuint32_t)p.cw, (cuuint32_t)p.br, 1};
+        cuuint32_t estr[3] = {1, 1, 1};
+        CUresult rc = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, (void*)in, dims, strides, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (rc != CUDA_SUCCESS) {
+            if (err) *err = "cuTensorMapEncodeTiled failed for the image tensor, code " + std::to_string((int)rc);
+            return FTF_INTERNAL;
+        }
+    }
+    if (out_dtype == FTF_FLOAT)
+        return launch_typed<float>(in, p, (float*)out, recip, use_tma, smem, &tmap, sms, s, err);
+    return launch_typed<__nv_bfloat16>(in, p, (__nv_bfloat16*)out, recip, use_tma, smem, &tmap, sms, s, err);
+}
+
+}  // namespace ftf

@@ -1,0 +1,60 @@
+"""Device-level entry points of the C ABI on torch CUDA tensors (torch only owns the memory and the stream)."""
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _abi
+from .host import _check
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _need_cuda(*ts):
+    for t in ts:
+        if t is not None and (not t.is_cuda or not t.is_contiguous()):
+            raise ValueError("device entry points take contiguous CUDA tensors")
+
+
+def affine_f32(x, a, b, out=None):
+    """K1: y = a*x + b (two roundings) on a CUDA float32 tensor."""
+    _need_cuda(x, out)
+    y = out if out is not None else torch.empty_like(x)
+    _check(_abi.load_library().ftf_affine_f32_dev(x.data_ptr(), y.data_ptr(), x.numel(), a, b, _stream()))
+    return y
+
+
+def resize_norm(images_u8, out_h, out_w, mean, scale, out_dtype=torch.float32, out=None):
+    """K2: u8 [N,H,W,3] -> [N,out_h,out_w,3] float32/bfloat16."""
+    _need_cuda(images_u8, out)
+    n, h, w, c = images_u8.shape
+    if c != 3 or images_u8.dtype != torch.uint8:
+        raise ValueError("images must be uint8 [N,H,W,3]")
+    y = out if out is not None else torch.empty((n, out_h, out_w, 3), dtype=out_dtype, device=images_u8.device)
+    code = _abi.FLOAT if y.dtype == torch.float32 else _abi.BFLOAT16
+    _check(_abi.load_library().ftf_resize_norm_dev(images_u8.data_ptr(), n, h, w, out_h, out_w, mean, scale,
+                                                   y.data_ptr(), code, _stream()))
+    return y
+
+
+def softmax_topk(x, k, n_labels=None, apply_softmax=True, want_probs=True):
+    """K7 on a CUDA float32 [M,N] tensor -> (probs or None, idx int32 [M,k], score float32 [M,k])."""
+    _need_cuda(x)
+    m, n = x.shape
+    probs = torch.empty_like(x) if (want_probs and apply_softmax) else None
+    idx = torch.empty((m, k), dtype=torch.int32, device=x.device)
+    score = torch.empty((m, k), dtype=torch.float32, device=x.device)
+    _check(_abi.load_library().ftf_softmax_topk_dev(
+        x.data_ptr(), m, n, n if n_labels is None else n_labels, k, 1 if apply_softmax else 0,
+        probs.data_ptr() if probs is not None else None, idx.data_ptr(), score.data_ptr(), _stream()))
+    return probs, idx, score
+
+
+def top_labels(scores_np, n_labels, k):
+    """toTextLabels' selection for a host score matrix: upload, K7 without softmax, download."""
+    x = torch.from_numpy(np.ascontiguousarray(scores_np, dtype=np.float32)).cuda()
+    _, idx, score = softmax_topk(x, k, n_labels=n_labels, apply_softmax=False)
+    torch.cuda.synchronize()
+    return idx.cpu().numpy(), score.cpu().numpy()
