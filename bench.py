@@ -1,0 +1,340 @@
+#!/usr/bin/env python
+"""bench.py -- one JSON line per run (see the round contract).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload half_plus_two|normalize|inception]
+  python bench.py --impl reference ...          the reference's CPU path (oracle stand-in) on the host cores
+  torchrun --nproc-per-node N bench.py --gpus N one rank per GPU, records sharded, no collective on the data path
+
+A step is one pass of the hot path over one batch of synthetic input:
+  half_plus_two  BASELINE config 2: y = 0.5x + 2 over 2^28 fp32 (1 GiB in, 1 GiB out), 8 algorithmic B/element
+  normalize      BASELINE config 3: 256 x (480x640 u8 RGB -> 299x299 f32), 1 994 412 algorithmic B/image
+  inception      BASELINE config 4: Inception-v3 random-init bf16, batch 64, top-5 labels
+`value` is device-resident throughput (inputs already in HBM), `e2e` the same metric through ftf_run with host
+buffers (H2D + D2H inside the timed region), `roofline` the dominant kernel against MEASURED_PEAKS.json,
+`cpu_baseline` the CPU oracle timed on this box's cores on a bounded sample.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+HPT_N = 1 << 28
+NORM = dict(batch=256, in_h=480, in_w=640, out_h=299, out_w=299, mean=128.0, scale=128.0)
+NORM_BYTES_PER_IMAGE = 480 * 640 * 3 + 299 * 299 * 3 * 4          # 1 994 412
+INC = dict(batch=64, side=299, classes=1000, top_k=5, seed=2024)
+INC_FLOP_PER_IMAGE = 11.43e9                                       # SURVEY 8d (2*MAC, 94 convs + FC)
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            p = json.load(f)
+        return dict(hbm=float(p["hbm_gbs"]), tf_burst=float(p["bf16_tflops"]),
+                    tf_sustained=float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), src="measured")
+    except Exception:
+        return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _loop(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._loop, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def dist_env():
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    return rank, int(os.environ.get("LOCAL_RANK", rank)), world
+
+
+# ================================================================================================
+# reference arm: the reference's CPU implementation of the path (oracle stand-in for TF-Java Session.run)
+# ================================================================================================
+def run_reference(args):
+    import numpy as np
+    import oracle
+    rank, _, _ = dist_env()
+    if rank != 0:
+        return
+    threads = oracle.num_threads()
+    rng = np.random.default_rng(1234)
+    wl = args.workload
+    if wl == "half_plus_two":
+        n = 1 << 26                                           # bounded sample: 1/4 of the 2^28 workload per step
+        x = (rng.standard_normal(n) * 100).astype(np.float32)
+        step = lambda: oracle.affine_f32(x, 0.5, 2.0, threads=threads)
+        units, unit, metric, sample = 8.0 * n / 1e9, "GB/s", "half_plus_two GB/s", f"2^26 of the 2^28 floats per step"
+        config = {"workload": "half_plus_two y=0.5x+2 over 2^28 fp32 (BASELINE config 2)", "sample_elements": n}
+        dtype = "f32"
+    elif wl == "normalize":
+        b = 32
+        img = rng.integers(0, 256, (b, NORM["in_h"], NORM["in_w"], 3), dtype=np.uint8)
+        step = lambda: oracle.resize_bilinear_norm_u8(img, NORM["out_h"], NORM["out_w"], NORM["mean"], NORM["scale"], threads=threads)
+        units, unit, metric, sample = float(b), "images/s", "ImageNormalization images/sec", "32 of the 256 images per step"
+        config = {"workload": "ImageNormalization 640x480 -> 299x299 batch 256 (BASELINE config 3)", "sample_images": b}
+        dtype = "f32"
+    else:
+        import oracle.inception as oinc                       # noqa: F401  (exists once the conv path lands)
+        net = oinc.Net(INC["classes"], INC["seed"])
+        b = 4
+        img = rng.standard_normal((b, 299, 299, 3)).astype(np.float32)
+        step = lambda: net.forward(img, threads=threads)
+        units, unit, metric, sample = float(b), "images/s", "Inception-v3 images/sec", "4 of the 64 images per step, fp32"
+        config = {"workload": "Inception-v3 random-init batch 64 top-5 (BASELINE config 4)", "sample_images": b}
+        dtype = "f32"
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = units * args.steps / dt
+    line = {"impl": "reference", "metric": metric, "value": value, "unit": unit, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+            "config": config,
+            "cpu_baseline": {"value": value, "unit": unit, "cores": threads, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "note": "CPU oracle (C restatement of the TF-1.1 op sequence) stands in for TF-Java Session.run, which "
+                    "cannot run without a JVM; it omits the reference's per-record JNI/dispatch overhead"}
+    print(json.dumps(line), flush=True)
+
+
+# ================================================================================================
+# our arm
+# ================================================================================================
+def cuda_time(fn, steps, torch):
+    """K back-to-back steps between two events on the current stream; returns total milliseconds."""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1)
+
+
+def pinned_array(lib, np, nbytes, dtype):
+    p = lib.ftf_host_alloc(nbytes)
+    if not p:
+        raise MemoryError("ftf_host_alloc failed")
+    return p, np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,)).view(dtype)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import ftf_loader
+    ftf = ftf_loader.load()
+    from flink_tensorflow_b200 import device
+    import oracle
+    lib = ftf._abi.load_library()
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the runner has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    pk = peaks()
+    wl = args.workload
+    K, Wm = args.steps, max(3, args.warmup)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    launches0 = lib.ftf_launch_count()
+    extra = {}
+    if wl == "half_plus_two":
+        n = HPT_N
+        g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+        x = torch.randn(n, device="cuda", generator=g) * 100
+        y = torch.empty_like(x)
+        step = lambda: device.affine_f32(x, 0.5, 2.0, out=y)
+        units_per_step, unit, metric, dtype = 8.0 * n / 1e9, "GB/s", "half_plus_two GB/s", "f32"
+        algo_bytes = 8.0 * n
+        config = {"workload": "half_plus_two y=0.5x+2 over 2^28 fp32 per GPU (BASELINE config 2)", "elements": n,
+                  "l2": "inputs (1 GiB) larger than L2, no flush", "parallelism": f"dp{world} (records sharded, no collective)"}
+        bound, peak, peak_unit = "hbm", pk["hbm"], "GB/s"
+    elif wl == "normalize":
+        b = NORM["batch"]
+        g = torch.Generator(device="cuda").manual_seed(42 + rank)
+        img = torch.randint(0, 256, (b, NORM["in_h"], NORM["in_w"], 3), dtype=torch.uint8, device="cuda", generator=g)
+        out = torch.empty((b, NORM["out_h"], NORM["out_w"], 3), dtype=torch.float32, device="cuda")
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        step = lambda: device.resize_norm(img, NORM["out_h"], NORM["out_w"], NORM["mean"], NORM["scale"], out=out)
+        units_per_step, unit, metric, dtype = float(b), "images/s", "ImageNormalization images/sec", "f32"
+        algo_bytes = float(NORM_BYTES_PER_IMAGE) * b
+        config = {"workload": "ImageNormalization 640x480 u8 RGB -> ResizeBilinear 299x299 + mean/scale, batch 256 per GPU "
+                              "(BASELINE config 3)", "l2": "input+output 511 MB per step, larger than L2",
+                  "parallelism": f"dp{world} (records sharded, no collective)", **NORM}
+        bound, peak, peak_unit = "hbm", pk["hbm"], "GB/s"
+    else:
+        raise SystemExit(f"workload {wl} not available in this build")
+
+    # ---- device-resident timing ------------------------------------------------------------------
+    for _ in range(Wm):
+        step()
+    barrier()
+    with ClockSampler(local_rank) as clk:
+        ms_total = cuda_time(step, K, torch)
+        barrier()
+    ms_total = max_over_ranks(ms_total)
+    ms_step = ms_total / K
+    value = units_per_step * world / (ms_step / 1e3)
+    achieved = algo_bytes / (ms_step / 1e3) / 1e9
+    gpu_launches = int(lib.ftf_launch_count() - launches0)
+
+    # ---- end to end through ftf_run with host buffers ----------------------------------------------
+    e2e_steps = max(1, min(K, 5))
+    if wl == "half_plus_two":
+        r = ftf.Runner(os.path.join(ROOT, "models", "half_plus_two"), "serving_default", None,
+                       ftf.default_config(device=local_rank))
+        p, hx = pinned_array(lib, np, 4 * HPT_N, np.float32)
+        hx[:] = np.random.default_rng(5 + rank).standard_normal(HPT_N, dtype=np.float32)
+        tv = ftf.TensorValue.__new__(ftf.TensorValue)
+        tv.data_type, tv.shape, tv.buffer = ftf.DataType.FLOAT, (HPT_N, 1), hx.view(np.uint8)
+        in_key, out_key = "x", "y"
+        h2d = d2h = 4 * HPT_N
+    else:
+        r = ftf.Runner("builtin:image_normalization", None, None,
+                       ftf.default_config(device=local_rank, out_h=NORM["out_h"], out_w=NORM["out_w"], mean=NORM["mean"],
+                                          scale=NORM["scale"]))
+        nb = NORM["batch"] * NORM["in_h"] * NORM["in_w"] * 3
+        p, hx = pinned_array(lib, np, nb, np.uint8)
+        hx[:] = np.random.default_rng(5 + rank).integers(0, 256, nb, dtype=np.uint8)
+        tv = ftf.TensorValue.__new__(ftf.TensorValue)
+        tv.data_type, tv.shape, tv.buffer = ftf.DataType.UINT8, (NORM["batch"], NORM["in_h"], NORM["in_w"], 3), hx
+        in_key, out_key = "inputs", "outputs"
+        h2d, d2h = nb, NORM["batch"] * NORM["out_h"] * NORM["out_w"] * 3 * 4
+
+    from flink_tensorflow_b200.host import _as_ftf, FtfTensor, _check
+    t_in, keep = _as_ftf(tv.data_type, tv.shape, tv.buffer)
+    ikeys, okeys = (C.c_char_p * 1)(in_key.encode()), (C.c_char_p * 1)(out_key.encode())
+    tin, tout = (FtfTensor * 1)(t_in), (FtfTensor * 1)()
+
+    def e2e_step():
+        _check(lib.ftf_run(r.handle, 1, ikeys, tin, 1, okeys, tout), r.handle)
+        # the result (runner-owned pinned memory) is read by the host: first and last element
+        res = np.ctypeslib.as_array(C.cast(tout[0].data, C.POINTER(C.c_float)), shape=(tout[0].nbytes // 4,))
+        return float(res[0]) + float(res[-1])
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
+    e2e_value = units_per_step * world / (e2e_ms / 1e3)
+    e2e_launches = r.stats()["kernel_launches"]
+    r.close()
+    lib.ftf_host_free(p)
+
+    if rank != 0:
+        return
+    # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -----------------------------------------
+    cpu = None
+    if world == 1:
+        threads = oracle.num_threads()
+        rng = np.random.default_rng(1234)
+        if wl == "half_plus_two":
+            n = 1 << 26
+            cx = (rng.standard_normal(n) * 100).astype(np.float32)
+            oracle.affine_f32(cx, 0.5, 2.0, threads=threads)
+            t0, reps = time.perf_counter(), 0
+            while time.perf_counter() - t0 < 5.0:
+                oracle.affine_f32(cx, 0.5, 2.0, threads=threads)
+                reps += 1
+            cpu = {"value": 8.0 * n * reps / 1e9 / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
+                   "sample": f"{reps} passes over 2^26 floats (1/4 of the workload), all host threads"}
+        else:
+            b = 32
+            cimg = rng.integers(0, 256, (b, NORM["in_h"], NORM["in_w"], 3), dtype=np.uint8)
+            oracle.resize_bilinear_norm_u8(cimg, NORM["out_h"], NORM["out_w"], NORM["mean"], NORM["scale"], threads=threads)
+            t0, reps = time.perf_counter(), 0
+            while time.perf_counter() - t0 < 5.0:
+                oracle.resize_bilinear_norm_u8(cimg, NORM["out_h"], NORM["out_w"], NORM["mean"], NORM["scale"], threads=threads)
+                reps += 1
+            cpu = {"value": b * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
+                   "sample": f"{reps} passes over 32 images (1/8 of the batch), all host threads"}
+
+    line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
+            "data": "synthetic", "config": config,
+            "roofline": {"bound": bound, "achieved": achieved, "peak": peak, "unit": peak_unit, "frac": achieved / peak,
+                         "traffic": None, "peak_source": pk["src"], "frac_of_nominal_8TBps": achieved / 8000.0,
+                         "kernel_ms": ms_step},
+            "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": e2e_ms, "steps": e2e_steps, "gpu_launches": int(e2e_launches),
+                    "api": "ftf_run (C ABI) with pinned host buffers, chunked H2D/kernel/D2H pipeline"},
+            "gpu_launches": gpu_launches, "clocks": clk.summary(), "cpu_baseline": cpu}
+    line.update(extra)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="half_plus_two", choices=["half_plus_two", "normalize", "inception"])
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -68,6 +68,7 @@ SYMBOLS = {
     "ftf_label_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p]),
     "ftf_runner_stream": (C.c_void_p, [C.c_void_p]),
+    "ftf_launch_count": (C.c_uint64, []),
     "ftf_version": (C.c_char_p, []),
 }
 

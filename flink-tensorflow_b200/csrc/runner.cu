@@ -278,6 +278,8 @@ extern "C" void ftf_default_config(ftf_config* c) {
     c->num_classes = 1000; c->seed = 2024;
 }
 
+extern "C" uint64_t ftf_launch_count(void) { return launches_so_far(); }
+
 extern "C" const char* ftf_version(void) { return "flink-tensorflow_b200 0.1 (sm_100a)"; }
 
 extern "C" int ftf_create(const char* model, const char* signature_key, const char* method_name,

@@ -187,6 +187,9 @@ int ftf_label_dev(ftf_runner* r, const void* images, int32_t in_dtype, int64_t n
 /* Stream the runner launches on (cudaStream_t), for event timing by the caller. */
 void* ftf_runner_stream(ftf_runner* r);
 
+/* Number of this library's kernels launched by this process so far (all runners and device-level calls). */
+uint64_t ftf_launch_count(void);
+
 const char* ftf_version(void);
 
 #ifdef __cplusplus
