@@ -65,6 +65,10 @@ SYMBOLS = {
                                       C.c_float, C.c_void_p, C.c_int32, C.c_void_p]),
     "ftf_softmax_topk_dev": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                        C.c_void_p, C.c_void_p, C.c_void_p]),
+    "ftf_conv2d_bf16_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p,
+                                      C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
+                                      C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
+    "ftf_debug_activation": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int32)]),
     "ftf_label_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p]),
     "ftf_runner_stream": (C.c_void_p, [C.c_void_p]),

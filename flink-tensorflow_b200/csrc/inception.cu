@@ -1,26 +1,220 @@
-// inception.cu -- label model (placeholder until the convolution kernels land).
+// inception.cu -- the label model: Inception-v3 (inference, BN folded, bf16 activations) as a list of device
+// operations over a static activation arena; convolutions run on tcgen05 (conv_tc.cu).
+//
+// Stands where the reference loads and runs its frozen Inception graph:
+// flink-tensorflow-examples/src/main/scala/org/apache/flink/contrib/tensorflow/examples/inception/
+// InceptionModel.scala:51-67 (DefaultGraphLoader + ModelFunction[LabelMethod]).  The reference ships no graph
+// (models/README.md:5); architecture and seeded weight recipe are those of oracle/inception_oracle.c
+// (cross-checked there against torchvision).
+//
+// Data layout in HBM: every activation is a dense bf16 NHWC tensor; an Inception block's branches write
+// directly into channel slices of the block's output tensor (no concat pass).  The 1x1 convolutions of a block
+// that read the block input are one GEMM whose column ranges ("segments") go to different tensors; the pool
+// branch is conv1x1 -> fp32 scratch -> (avgpool3x3 + bias + ReLU) since pool and 1x1 conv commute.
 #include "inception.h"
+#include "conv_tc.h"
 #include <cuda_bf16.h>
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include <functional>
+#include <map>
+#include <thread>
+#include <vector>
 
 namespace ftf {
 
-struct InceptionV3::Impl {};
-InceptionV3::~InceptionV3() { delete impl_; }
-
-int InceptionV3::create(int, int, uint64_t, int, int, std::unique_ptr<InceptionV3>*, std::string* err) {
-    if (err) *err = "builtin:inception_v3 is not built yet";
-    return FTF_UNIMPLEMENTED;
-}
-int InceptionV3::forward(const void*, int64_t, float*, cudaStream_t, std::string* err) {
-    if (err) *err = "builtin:inception_v3 is not built yet";
-    return FTF_UNIMPLEMENTED;
-}
-
+// ------------------------------------------------------------------------------------------------
+// seeded weights (same recipe as the oracle: see oracle/inception_oracle.c header)
+// ------------------------------------------------------------------------------------------------
 namespace {
+
+inline uint64_t splitmix(uint64_t z) {
+    z += 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+inline uint64_t name_hash(const std::string& s) {
+    uint64_t h = 0xcbf29ce484222325ull;
+    for (unsigned char c : s) { h ^= c; h *= 0x100000001b3ull; }
+    return h;
+}
+struct Stream {
+    uint64_t key;
+    Stream(uint64_t seed, const std::string& name, int kind) : key(splitmix(seed ^ splitmix(name_hash(name) + (uint64_t)kind))) {}
+    double u_open(uint64_t i) const { return (double)((splitmix(key ^ i) >> 11) + 1) * (1.0 / 9007199254740992.0); }
+    double u_half(uint64_t i) const { return (double)(splitmix(key ^ i) >> 11) * (1.0 / 9007199254740992.0); }
+    double normal(uint64_t i) const { return sqrt(-2.0 * log(u_open(2 * i))) * cos(6.283185307179586476925286766559 * u_half(2 * i + 1)); }
+};
+
+void fill_parallel(int64_t n, const std::function<void(int64_t, int64_t)>& fn) {
+    unsigned hw = std::thread::hardware_concurrency();
+    int t = (int)(hw ? (hw > 16 ? 16 : hw) : 4);
+    if (n < 65536) { fn(0, n); return; }
+    std::vector<std::thread> th;
+    const int64_t per = (n + t - 1) / t;
+    for (int i = 0; i < t; ++i) {
+        const int64_t lo = i * per, hi = std::min<int64_t>(n, lo + per);
+        if (lo < hi) th.emplace_back(fn, lo, hi);
+    }
+    for (auto& x : th) x.join();
+}
+
+// folded conv weights [Cout][KH][KW][Cin] (fp32) and bias
+void conv_weights(uint64_t seed, const std::string& name, int cout, int kh, int kw, int cin, std::vector<float>* w,
+                  std::vector<float>* b) {
+    const Stream sw(seed, name, 0), sb(seed, name, 1);
+    const double sd = sqrt(2.0 / ((double)kh * kw * cin)), fold = 1.0 / sqrt(1.0 + 1e-3);
+    w->resize((size_t)cout * kh * kw * cin);
+    float* wp = w->data();
+    fill_parallel((int64_t)w->size(), [&](int64_t lo, int64_t hi) {
+        for (int64_t i = lo; i < hi; ++i) wp[i] = (float)(sw.normal((uint64_t)i) * sd * fold);
+    });
+    b->resize(cout);
+    for (int o = 0; o < cout; ++o) (*b)[o] = (float)(-0.1 + 0.2 * sb.u_half((uint64_t)o));
+}
+
+inline uint16_t bf16_bits(float f) {
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (uint16_t)(u >> 16);
+}
+inline float bf16_value(float f) {
+    uint32_t u = (uint32_t)bf16_bits(f) << 16;
+    float r;
+    memcpy(&r, &u, 4);
+    return r;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernels other than the tensor-core convolution
+// ------------------------------------------------------------------------------------------------
+// Conv2d_1a_3x3: 3 -> 32 channels, 3x3, stride 2, no padding.  K = 27 is far below a tensor-core tile and the
+// layer is bound by its 64-byte-per-pixel output: direct convolution, one thread per output pixel, weights as
+// kernel parameters (constant-bank operands of the FMAs).
+struct StemWeights {
+    float w[27][32];   // [kh][kw][cin] x cout, bf16-rounded values
+    float b[32];
+};
+__global__ void __launch_bounds__(128)
+stem_conv3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int OH, int OW,
+               const __grid_constant__ StemWeights sw) {
+    const long long total = (long long)n * OH * OW;
+    const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= total) return;
+    const int img = (int)(pix / (OH * OW));
+    const int rem = (int)(pix - (long long)img * OH * OW);
+    const int oy = rem / OW, ox = rem - oy * OW;
+    float acc[32];
+#pragma unroll
+    for (int o = 0; o < 32; ++o) acc[o] = 0.0f;
+    const __nv_bfloat16* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
+#pragma unroll
+    for (int ky = 0; ky < 3; ++ky) {
+        float x[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) x[i] = __bfloat162float(base[(size_t)ky * W * 3 + i]);   // 3 pixels x 3 channels, contiguous
+#pragma unroll
+        for (int i = 0; i < 9; ++i)
+#pragma unroll
+            for (int o = 0; o < 32; ++o) acc[o] = fmaf(x[i], sw.w[ky * 9 + i][o], acc[o]);
+    }
+    uint4* op = reinterpret_cast<uint4*>(out + (size_t)pix * 32);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        uint32_t r[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int o = q * 8 + j * 2;
+            __nv_bfloat162 h = __floats2bfloat162_rn(fmaxf(acc[o] + sw.b[o], 0.0f), fmaxf(acc[o + 1] + sw.b[o + 1], 0.0f));
+            r[j] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        op[q] = make_uint4(r[0], r[1], r[2], r[3]);
+    }
+}
+
+// 3x3 max pool, stride 2, no padding; 8 channels (16 bytes) per thread; writes a channel slice.
+__global__ void __launch_bounds__(256)
+maxpool3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int C, int OH, int OW,
+             int out_ld, int out_off) {
+    const int cg = C / 8;
+    const long long total = (long long)n * OH * OW * cg;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int g = (int)(t % cg);
+        const long long pix = t / cg;
+        const int ox = (int)(pix % OW);
+        const int oy = (int)((pix / OW) % OH);
+        const int img = (int)(pix / ((long long)OW * OH));
+        __nv_bfloat162 m[4];
+        bool first = true;
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + (((size_t)img * H + 2 * oy + ky) * W + 2 * ox + kx) * C + g * 8));
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) m[j] = first ? h[j] : __hmax2(m[j], h[j]);
+                first = false;
+            }
+        *reinterpret_cast<uint4*>(out + (size_t)pix * out_ld + out_off + g * 8) = *reinterpret_cast<uint4*>(m);
+    }
+}
+
+// out = bf16(relu(avgpool3x3_s1_p1(pre) * (1/9) + bias)); pre is the fp32 1x1-conv output [n,H,W,C]; taps summed
+// row-major in fp32; divisor 9 at the borders too (count_include_pad).  4 channels per thread.
+__global__ void __launch_bounds__(256)
+avgpool3x3_bias_relu(const float* __restrict__ pre, const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int n, int H,
+                     int W, int C, int out_ld, int out_off) {
+    const int cg = C / 4;
+    const long long total = (long long)n * H * W * cg;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
+        const int g = (int)(t % cg);
+        const long long pix = t / cg;
+        const int x = (int)(pix % W);
+        const int y = (int)((pix / W) % H);
+        const int img = (int)(pix / ((long long)W * H));
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int ky = -1; ky <= 1; ++ky)
+#pragma unroll
+            for (int kx = -1; kx <= 1; ++kx) {
+                const int iy = y + ky, ix = x + kx;
+                if (iy < 0 || iy >= H || ix < 0 || ix >= W) continue;
+                const float4 v = __ldg(reinterpret_cast<const float4*>(pre + (((size_t)img * H + iy) * W + ix) * C + g * 4));
+                s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+            }
+        const float4 b = __ldg(reinterpret_cast<const float4*>(bias + g * 4));
+        const float ninth = 1.0f / 9.0f;
+        const float r0 = fmaxf(__fadd_rn(__fmul_rn(s.x, ninth), b.x), 0.f), r1 = fmaxf(__fadd_rn(__fmul_rn(s.y, ninth), b.y), 0.f);
+        const float r2 = fmaxf(__fadd_rn(__fmul_rn(s.z, ninth), b.z), 0.f), r3 = fmaxf(__fadd_rn(__fmul_rn(s.w, ninth), b.w), 0.f);
+        __nv_bfloat162 h0 = __floats2bfloat162_rn(r0, r1), h1 = __floats2bfloat162_rn(r2, r3);
+        uint2 o = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
+        *reinterpret_cast<uint2*>(out + (size_t)pix * out_ld + out_off + g * 4) = o;
+    }
+}
+
+// global average pool over HW pixels: fp32 sum in pixel order, times 1/HW, rounded to bf16. One thread per (n, c).
+__global__ void __launch_bounds__(256)
+global_avgpool(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int HW, int C) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n * C) return;
+    const int img = idx / C, c = idx - img * C;
+    float s = 0.0f;
+    for (int p = 0; p < HW; ++p) s += __bfloat162float(in[((size_t)img * HW + p) * C + c]);
+    out[idx] = __float2bfloat16_rn(__fmul_rn(s, 1.0f / (float)HW));
+}
+
 __global__ void __launch_bounds__(256) cast_f32_bf16(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int64_t n) {
     const int64_t stride = (int64_t)gridDim.x * 256;
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) out[i] = __float2bfloat16_rn(__ldg(in + i));
 }
+
 }  // namespace
 
 int launch_cast_f32_bf16(const float* in, void* out, int64_t n, cudaStream_t s, std::string* err) {
@@ -32,6 +226,350 @@ int launch_cast_f32_bf16(const float* in, void* out, int64_t n, cudaStream_t s, 
     cast_f32_bf16<<<(unsigned)(want < cap ? want : cap), 256, 0, s>>>(in, (__nv_bfloat16*)out, n);
     count_launch();
     FTF_CUDA(cudaGetLastError(), err);
+    return FTF_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// network
+// ------------------------------------------------------------------------------------------------
+struct Act {
+    __nv_bfloat16* p = nullptr;
+    int h = 0, w = 0, c = 0;
+};
+
+struct Op {
+    enum Type { kStem, kConv, kMaxPool, kAvgPoolBiasRelu, kGap } type;
+    int plan = -1;                       // kConv
+    const void* in = nullptr;            // other kernels
+    void* out = nullptr;
+    const float* bias = nullptr;
+    int H = 0, W = 0, C = 0, OH = 0, OW = 0, out_ld = 0, out_off = 0;
+};
+
+struct InceptionV3::Impl {
+    int device = 0, sms = 148, max_batch = 0, classes = 0;
+    uint64_t seed = 0;
+    std::vector<void*> allocs;
+    std::vector<ConvPlan> plans;
+    std::vector<Op> ops;
+    std::map<std::string, Act> named;     // activations by layer / block name (test hook)
+    StemWeights stem;
+    Act image;                            // [max_batch,299,299,3] staging of the caller's images
+    float* logits = nullptr;              // [max_batch, classes] fp32
+    std::string* err = nullptr;
+    int rc = FTF_OK;
+
+    ~Impl() {
+        cudaSetDevice(device);
+        for (void* p : allocs) cudaFree(p);
+    }
+    void* dev_alloc(size_t bytes, bool zero) {
+        if (rc) return nullptr;
+        void* p = nullptr;
+        cudaError_t e = cudaMalloc(&p, bytes ? bytes : 16);
+        if (e != cudaSuccess) { rc = FTF_RESOURCE_EXHAUSTED; *err = std::string("activation/weight arena: ") + cudaGetErrorString(e); cudaGetLastError(); return nullptr; }
+        if (zero) cudaMemset(p, 0, bytes);
+        allocs.push_back(p);
+        return p;
+    }
+    Act act(int h, int w, int c) {
+        Act a; a.h = h; a.w = w; a.c = c;
+        a.p = (__nv_bfloat16*)dev_alloc((size_t)max_batch * h * w * c * 2, true);
+        return a;
+    }
+    struct Branch { std::string name; int cout; Act* dst; int coff; bool pool; };
+
+    // conv(s) reading `in`: all entries share kernel shape; their outputs are column ranges of one GEMM
+    void conv_multi(const Act& in, const std::vector<Branch>& br, int kh, int kw, int s, int ph, int pw) {
+        if (rc) return;
+        int total = 0;
+        for (auto& b : br) total += b.cout;
+        std::vector<uint16_t> w16((size_t)total * kh * kw * in.c);
+        std::vector<float> bias(total);
+        std::vector<ConvSegment> segs;
+        const int OH = (in.h + 2 * ph - kh) / s + 1, OW = (in.w + 2 * pw - kw) / s + 1;
+        int col = 0;
+        for (auto& b : br) {
+            std::vector<float> w, bb;
+            conv_weights(seed, b.name, b.cout, kh, kw, in.c, &w, &bb);
+            const size_t per = (size_t)kh * kw * in.c;
+            for (size_t i = 0; i < w.size(); ++i) w16[(size_t)col * per + i] = bf16_bits(w[i]);
+            for (int o = 0; o < b.cout; ++o) bias[col + o] = bb[o];
+            ConvSegment sg{};
+            sg.col_begin = col;
+            if (b.pool) {   // raw fp32 pre-activation for the pool branch; pooled, biased and activated by the next op
+                float* scratch = (float*)dev_alloc((size_t)max_batch * OH * OW * b.cout * 4, true);
+                float* dbias = (float*)dev_alloc((size_t)b.cout * 4, false);
+                if (rc) return;
+                cudaMemcpy(dbias, bb.data(), (size_t)b.cout * 4, cudaMemcpyHostToDevice);
+                sg.out = scratch; sg.ld = b.cout; sg.coff = 0; sg.flags = kSegF32;
+                pending_pool.push_back({scratch, dbias, b.dst, b.coff, b.cout, OH, OW});
+            } else {
+                sg.out = b.dst->p; sg.ld = b.dst->c; sg.coff = b.coff; sg.flags = kSegBias | kSegRelu;
+            }
+            segs.push_back(sg);
+            col += b.cout;
+        }
+        void* dw = dev_alloc(w16.size() * 2, false);
+        float* db = (float*)dev_alloc((size_t)total * 4, false);
+        if (rc) return;
+        cudaMemcpy(dw, w16.data(), w16.size() * 2, cudaMemcpyHostToDevice);
+        cudaMemcpy(db, bias.data(), (size_t)total * 4, cudaMemcpyHostToDevice);
+        ConvGeometry g{in.p, max_batch, in.h, in.w, in.c, in.c, dw, db, total, kh, kw, s, ph, pw};
+        ConvPlan plan;
+        rc = conv_tc_plan(g, segs.data(), (int)segs.size(), sms, &plan, err);
+        if (rc) return;
+        plans.push_back(plan);
+        Op op{}; op.type = Op::kConv; op.plan = (int)plans.size() - 1;
+        ops.push_back(op);
+        for (auto& pp : pending_pool) {
+            Op o{}; o.type = Op::kAvgPoolBiasRelu; o.in = pp.scratch; o.bias = pp.bias; o.out = pp.dst->p;
+            o.H = pp.h; o.W = pp.w; o.C = pp.c; o.out_ld = pp.dst->c; o.out_off = pp.coff;
+            ops.push_back(o);
+        }
+        pending_pool.clear();
+    }
+    struct PendingPool { float* scratch; float* bias; Act* dst; int coff, c, h, w; };
+    std::vector<PendingPool> pending_pool;
+
+    Act conv(const std::string& name, const Act& in, int cout, int kh, int kw, int s, int ph, int pw) {
+        Act out = act((in.h + 2 * ph - kh) / s + 1, (in.w + 2 * pw - kw) / s + 1, cout);
+        conv_multi(in, {{name, cout, &out, 0, false}}, kh, kw, s, ph, pw);
+        named[name] = out;
+        return out;
+    }
+    void conv_to(const std::string& name, const Act& in, int cout, int kh, int kw, int s, int ph, int pw, Act* dst, int coff) {
+        conv_multi(in, {{name, cout, dst, coff, false}}, kh, kw, s, ph, pw);
+    }
+    void maxpool_to(const Act& in, Act* dst, int coff) {
+        Op o{}; o.type = Op::kMaxPool; o.in = in.p; o.out = dst->p; o.H = in.h; o.W = in.w; o.C = in.c;
+        o.OH = (in.h - 3) / 2 + 1; o.OW = (in.w - 3) / 2 + 1; o.out_ld = dst->c; o.out_off = coff;
+        ops.push_back(o);
+    }
+
+    Act block_a(const std::string& blk, const Act& x, int pf) {
+        Act out = act(x.h, x.w, 224 + pf);
+        Act t5 = act(x.h, x.w, 48), t3 = act(x.h, x.w, 64);
+        conv_multi(x, {{blk + ".branch1x1", 64, &out, 0, false}, {blk + ".branch5x5_1", 48, &t5, 0, false},
+                       {blk + ".branch3x3dbl_1", 64, &t3, 0, false}, {blk + ".branch_pool", pf, &out, 224, true}}, 1, 1, 1, 0, 0);
+        conv_to(blk + ".branch5x5_2", t5, 64, 5, 5, 1, 2, 2, &out, 64);
+        Act u = conv(blk + ".branch3x3dbl_2", t3, 96, 3, 3, 1, 1, 1);
+        conv_to(blk + ".branch3x3dbl_3", u, 96, 3, 3, 1, 1, 1, &out, 128);
+        named[blk] = out;
+        return out;
+    }
+    Act block_b(const std::string& blk, const Act& x) {
+        const int oh = (x.h - 3) / 2 + 1, ow = (x.w - 3) / 2 + 1;
+        Act out = act(oh, ow, 384 + 96 + x.c);
+        conv_to(blk + ".branch3x3", x, 384, 3, 3, 2, 0, 0, &out, 0);
+        Act t = conv(blk + ".branch3x3dbl_1", x, 64, 1, 1, 1, 0, 0);
+        Act u = conv(blk + ".branch3x3dbl_2", t, 96, 3, 3, 1, 1, 1);
+        conv_to(blk + ".branch3x3dbl_3", u, 96, 3, 3, 2, 0, 0, &out, 384);
+        maxpool_to(x, &out, 480);
+        named[blk] = out;
+        return out;
+    }
+    Act block_c(const std::string& blk, const Act& x, int c7) {
+        Act out = act(x.h, x.w, 768);
+        Act t = act(x.h, x.w, c7), d = act(x.h, x.w, c7);
+        conv_multi(x, {{blk + ".branch1x1", 192, &out, 0, false}, {blk + ".branch7x7_1", c7, &t, 0, false},
+                       {blk + ".branch7x7dbl_1", c7, &d, 0, false}, {blk + ".branch_pool", 192, &out, 576, true}}, 1, 1, 1, 0, 0);
+        Act u = conv(blk + ".branch7x7_2", t, c7, 1, 7, 1, 0, 3);
+        conv_to(blk + ".branch7x7_3", u, 192, 7, 1, 1, 3, 0, &out, 192);
+        Act d2 = conv(blk + ".branch7x7dbl_2", d, c7, 7, 1, 1, 3, 0);
+        Act d3 = conv(blk + ".branch7x7dbl_3", d2, c7, 1, 7, 1, 0, 3);
+        Act d4 = conv(blk + ".branch7x7dbl_4", d3, c7, 7, 1, 1, 3, 0);
+        conv_to(blk + ".branch7x7dbl_5", d4, 192, 1, 7, 1, 0, 3, &out, 384);
+        named[blk] = out;
+        return out;
+    }
+    Act block_d(const std::string& blk, const Act& x) {
+        const int oh = (x.h - 3) / 2 + 1, ow = (x.w - 3) / 2 + 1;
+        Act out = act(oh, ow, 320 + 192 + x.c);
+        Act t = act(x.h, x.w, 192), s = act(x.h, x.w, 192);
+        conv_multi(x, {{blk + ".branch3x3_1", 192, &t, 0, false}, {blk + ".branch7x7x3_1", 192, &s, 0, false}}, 1, 1, 1, 0, 0);
+        conv_to(blk + ".branch3x3_2", t, 320, 3, 3, 2, 0, 0, &out, 0);
+        Act s2 = conv(blk + ".branch7x7x3_2", s, 192, 1, 7, 1, 0, 3);
+        Act s3 = conv(blk + ".branch7x7x3_3", s2, 192, 7, 1, 1, 3, 0);
+        conv_to(blk + ".branch7x7x3_4", s3, 192, 3, 3, 2, 0, 0, &out, 320);
+        maxpool_to(x, &out, 512);
+        named[blk] = out;
+        return out;
+    }
+    Act block_e(const std::string& blk, const Act& x) {
+        Act out = act(x.h, x.w, 2048);
+        Act t = act(x.h, x.w, 384), d = act(x.h, x.w, 448);
+        conv_multi(x, {{blk + ".branch1x1", 320, &out, 0, false}, {blk + ".branch3x3_1", 384, &t, 0, false},
+                       {blk + ".branch3x3dbl_1", 448, &d, 0, false}, {blk + ".branch_pool", 192, &out, 1856, true}}, 1, 1, 1, 0, 0);
+        conv_to(blk + ".branch3x3_2a", t, 384, 1, 3, 1, 0, 1, &out, 320);
+        conv_to(blk + ".branch3x3_2b", t, 384, 3, 1, 1, 1, 0, &out, 704);
+        Act u = conv(blk + ".branch3x3dbl_2", d, 384, 3, 3, 1, 1, 1);
+        conv_to(blk + ".branch3x3dbl_3a", u, 384, 1, 3, 1, 0, 1, &out, 1088);
+        conv_to(blk + ".branch3x3dbl_3b", u, 384, 3, 1, 1, 1, 0, &out, 1472);
+        named[blk] = out;
+        return out;
+    }
+
+    void build() {
+        image = act(299, 299, 3);
+        // stem layer 1: direct kernel
+        {
+            std::vector<float> w, b;
+            conv_weights(seed, "Conv2d_1a_3x3", 32, 3, 3, 3, &w, &b);
+            for (int o = 0; o < 32; ++o) {
+                for (int k = 0; k < 27; ++k) stem.w[k][o] = bf16_value(w[(size_t)o * 27 + k]);
+                stem.b[o] = b[o];
+            }
+        }
+        Act a1 = act(149, 149, 32);
+        { Op o{}; o.type = Op::kStem; o.in = image.p; o.out = a1.p; o.H = 299; o.W = 299; o.OH = 149; o.OW = 149; ops.push_back(o); }
+        named["Conv2d_1a_3x3"] = a1;
+        Act a2 = conv("Conv2d_2a_3x3", a1, 32, 3, 3, 1, 0, 0);
+        Act a3 = conv("Conv2d_2b_3x3", a2, 64, 3, 3, 1, 1, 1);
+        Act p1 = act(73, 73, 64);
+        maxpool_to(a3, &p1, 0);
+        named["pool1"] = p1;
+        Act a4 = conv("Conv2d_3b_1x1", p1, 80, 1, 1, 1, 0, 0);
+        Act a5 = conv("Conv2d_4a_3x3", a4, 192, 3, 3, 1, 0, 0);
+        Act p2 = act(35, 35, 192);
+        maxpool_to(a5, &p2, 0);
+        named["pool2"] = p2;
+        Act x = block_a("Mixed_5b", p2, 32);
+        x = block_a("Mixed_5c", x, 64);
+        x = block_a("Mixed_5d", x, 64);
+        x = block_b("Mixed_6a", x);
+        x = block_c("Mixed_6b", x, 128);
+        x = block_c("Mixed_6c", x, 160);
+        x = block_c("Mixed_6d", x, 160);
+        x = block_c("Mixed_6e", x, 192);
+        x = block_d("Mixed_7a", x);
+        x = block_e("Mixed_7b", x);
+        x = block_e("Mixed_7c", x);
+        Act gap = act(1, 1, x.c);
+        { Op o{}; o.type = Op::kGap; o.in = x.p; o.out = gap.p; o.H = x.h; o.W = x.w; o.C = x.c; ops.push_back(o); }
+        named["gap"] = gap;
+        // fc as a 1x1 convolution over a 1x1 image: N rounded up to 16 columns, fp32 logits, bias, no ReLU
+        if (rc) return;
+        const int cols = (classes + 15) / 16 * 16;
+        logits = (float*)dev_alloc((size_t)max_batch * cols * 4, true);
+        std::vector<uint16_t> w16((size_t)cols * x.c, 0);
+        std::vector<float> bias(cols, 0.0f);
+        {
+            const Stream sw(seed, "fc", 0);
+            uint16_t* wp = w16.data();
+            const int64_t n = (int64_t)classes * x.c;
+            fill_parallel(n, [&](int64_t lo, int64_t hi) { for (int64_t i = lo; i < hi; ++i) wp[i] = bf16_bits((float)(sw.normal((uint64_t)i) * 0.05)); });
+        }
+        void* dw = dev_alloc(w16.size() * 2, false);
+        float* db = (float*)dev_alloc((size_t)cols * 4, false);
+        if (rc) return;
+        cudaMemcpy(dw, w16.data(), w16.size() * 2, cudaMemcpyHostToDevice);
+        cudaMemcpy(db, bias.data(), (size_t)cols * 4, cudaMemcpyHostToDevice);
+        ConvSegment sg{}; sg.out = logits; sg.ld = cols; sg.coff = 0; sg.col_begin = 0; sg.flags = kSegBias | kSegF32;
+        ConvGeometry g{gap.p, max_batch, 1, 1, x.c, x.c, dw, db, cols, 1, 1, 1, 0, 0};
+        ConvPlan plan;
+        rc = conv_tc_plan(g, &sg, 1, sms, &plan, err);
+        if (rc) return;
+        plans.push_back(plan);
+        Op op{}; op.type = Op::kConv; op.plan = (int)plans.size() - 1;
+        ops.push_back(op);
+        logits_ld = cols;
+    }
+    int logits_ld = 0;
+};
+
+InceptionV3::~InceptionV3() { delete impl_; }
+
+int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batch, int compute_dtype,
+                        std::unique_ptr<InceptionV3>* out, std::string* err) {
+    if (compute_dtype != FTF_BFLOAT16) {
+        if (err) *err = "builtin:inception_v3 computes in bf16 (fp32 accumulate); compute_dtype FLOAT is not built";
+        return FTF_UNIMPLEMENTED;
+    }
+    if (max_batch <= 0 || max_batch > 1024 || num_classes <= 0 || num_classes > 65536) {
+        if (err) *err = "inception_v3: max_batch must be in [1,1024] and num_classes in [1,65536]";
+        return FTF_INVALID_ARGUMENT;
+    }
+    FTF_CUDA(cudaSetDevice(device), err);
+    std::unique_ptr<InceptionV3> net(new InceptionV3());
+    net->impl_ = new Impl();
+    Impl& m = *net->impl_;
+    m.device = device; m.sms = device_sm_count(device); m.max_batch = max_batch; m.classes = num_classes; m.seed = seed; m.err = err;
+    m.build();
+    if (m.rc) return m.rc;
+    FTF_CUDA(cudaDeviceSynchronize(), err);
+    m.err = nullptr;
+    net->classes_ = num_classes; net->max_batch_ = max_batch;
+    *out = std::move(net);
+    return FTF_OK;
+}
+
+int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cudaStream_t s, std::string* err) {
+    Impl& m = *impl_;
+    if (n < 0 || n > m.max_batch) { if (err) *err = "inception_v3: batch exceeds max_batch"; return FTF_INVALID_ARGUMENT; }
+    if (n == 0) return FTF_OK;
+    const int nb = (int)n;
+    if (images_bf16 != m.image.p)
+        FTF_CUDA(cudaMemcpyAsync(m.image.p, images_bf16, (size_t)n * 299 * 299 * 3 * 2, cudaMemcpyDeviceToDevice, s), err);
+    for (const Op& op : m.ops) {
+        switch (op.type) {
+        case Op::kStem: {
+            const long long pix = (long long)nb * op.OH * op.OW;
+            stem_conv3x3s2<<<(unsigned)((pix + 127) / 128), 128, 0, s>>>((const __nv_bfloat16*)op.in, (__nv_bfloat16*)op.out, nb, op.H,
+                                                                         op.W, op.OH, op.OW, m.stem);
+            count_launch();
+            break;
+        }
+        case Op::kConv: {
+            const int rc = conv_tc_launch(m.plans[op.plan], nb, s, err);
+            if (rc) return rc;
+            break;
+        }
+        case Op::kMaxPool: {
+            const long long total = (long long)nb * op.OH * op.OW * (op.C / 8);
+            const long long want = (total + 255) / 256, cap = (long long)m.sms * 16;
+            maxpool3x3s2<<<(unsigned)(want < cap ? want : cap), 256, 0, s>>>((const __nv_bfloat16*)op.in, (__nv_bfloat16*)op.out, nb, op.H,
+                                                                            op.W, op.C, op.OH, op.OW, op.out_ld, op.out_off);
+            count_launch();
+            break;
+        }
+        case Op::kAvgPoolBiasRelu: {
+            const long long total = (long long)nb * op.H * op.W * (op.C / 4);
+            const long long want = (total + 255) / 256, cap = (long long)m.sms * 16;
+            avgpool3x3_bias_relu<<<(unsigned)(want < cap ? want : cap), 256, 0, s>>>((const float*)op.in, op.bias, (__nv_bfloat16*)op.out, nb,
+                                                                                    op.H, op.W, op.C, op.out_ld, op.out_off);
+            count_launch();
+            break;
+        }
+        case Op::kGap: {
+            global_avgpool<<<(nb * op.C + 255) / 256, 256, 0, s>>>((const __nv_bfloat16*)op.in, (__nv_bfloat16*)op.out, nb, op.H * op.W, op.C);
+            count_launch();
+            break;
+        }
+        }
+    }
+    FTF_CUDA(cudaGetLastError(), err);
+    // logits: [n, classes] out of the padded [n, logits_ld] result
+    FTF_CUDA(cudaMemcpy2DAsync(logits, (size_t)m.classes * 4, m.logits, (size_t)m.logits_ld * 4, (size_t)m.classes * 4, (size_t)n,
+                               cudaMemcpyDeviceToDevice, s), err);
+    return FTF_OK;
+}
+
+int InceptionV3::activation(const std::string& name, int64_t n, float* host_out, int64_t cap, int dims[4], std::string* err) {
+    Impl& m = *impl_;
+    auto it = m.named.find(name);
+    if (it == m.named.end()) { if (err) *err = "no activation named " + name; return FTF_NOT_FOUND; }
+    const Act& a = it->second;
+    const int64_t elems = n * a.h * a.w * a.c;
+    dims[0] = (int)n; dims[1] = a.h; dims[2] = a.w; dims[3] = a.c;
+    if (!host_out) return FTF_OK;
+    if (elems > cap) { if (err) *err = "activation buffer too small"; return FTF_OUT_OF_RANGE; }
+    std::vector<uint16_t> tmp((size_t)elems);
+    FTF_CUDA(cudaMemcpy(tmp.data(), a.p, (size_t)elems * 2, cudaMemcpyDeviceToHost), err);
+    for (int64_t i = 0; i < elems; ++i) {
+        const uint32_t u = (uint32_t)tmp[(size_t)i] << 16;
+        memcpy(host_out + i, &u, 4);
+    }
     return FTF_OK;
 }
 

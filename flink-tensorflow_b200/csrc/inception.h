@@ -23,6 +23,9 @@ public:
     int forward(const void* images_bf16, int64_t n, float* logits, cudaStream_t s, std::string* err);
     int num_classes() const { return classes_; }
     int max_batch() const { return max_batch_; }
+    // Diagnostic: copies the named activation (layer or block name of oracle/inception_oracle.c) of the last
+    // forward to host fp32 [n,h,w,c]; host_out == NULL only reports dims.
+    int activation(const std::string& name, int64_t n, float* host_out, int64_t cap, int dims[4], std::string* err);
     // test hooks: copy of a named layer's weights/bias (host fp32, layout [Cout][KH][KW][Cin]) and a
     // device pointer to a named activation of the last forward.
     struct Impl;

@@ -8,6 +8,7 @@
 // CUDA stream each, so the upload of chunk c+1 overlaps the kernels of chunk c and the download of c-1.
 #include "runner.h"
 #include "inception.h"
+#include "conv_tc.h"
 #include <string.h>
 #include <algorithm>
 #include <atomic>
@@ -712,5 +713,39 @@ extern "C" int ftf_label_dev(ftf_runner* r, const void* images, int32_t in_dtype
         rc = launch_softmax_topk(lg, n, r->cfg.num_classes, r->cfg.num_classes, (idx && score) ? r->cfg.top_k : 0, 1, probs, idx, score,
                                  r->net_stream, &r->err);
     r->stats.kernel_launches += launches_so_far() - before;
+    return rc;
+}
+
+extern "C" int ftf_conv2d_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t cin, int32_t in_ld, const void* weights,
+                                   const float* bias, int32_t cout, int32_t kh, int32_t kw, int32_t stride, int32_t pad_h,
+                                   int32_t pad_w, int32_t relu, void* out, int32_t out_dtype, int32_t out_ld, int32_t out_off,
+                                   void* stream) {
+    std::string err;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_thread_error("cudaGetDevice failed"); return FTF_INTERNAL; }
+    if (n <= 0 || stride <= 0 || (out_dtype != FTF_BFLOAT16 && out_dtype != FTF_FLOAT)) {
+        set_thread_error("conv2d_bf16: bad batch, stride or output dtype");
+        return FTF_INVALID_ARGUMENT;
+    }
+    ConvSegment sg{};
+    sg.out = out; sg.ld = out_ld; sg.coff = out_off; sg.col_begin = 0;
+    sg.flags = (bias ? kSegBias : 0) | (relu ? kSegRelu : 0) | (out_dtype == FTF_FLOAT ? kSegF32 : 0);
+    ConvGeometry g{in, n, h, w, cin, in_ld, weights, bias, cout, kh, kw, stride, pad_h, pad_w};
+    ConvPlan plan;
+    int rc = conv_tc_plan(g, &sg, 1, device_sm_count(dev), &plan, &err);
+    if (!rc) rc = conv_tc_launch(plan, n, (cudaStream_t)stream, &err);
+    if (rc) set_thread_error(err);
+    return rc;
+}
+
+extern "C" int ftf_debug_activation(ftf_runner* r, const char* name, int64_t n, float* host_out, int64_t cap, int32_t* dims4) {
+    if (!r || !is_label_kind(r->kind) || !name || !dims4) return fail(r, FTF_INVALID_ARGUMENT, "debug_activation needs a label runner, a name and dims");
+    int rc = set_device(r);
+    if (rc) return rc;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { r->dead = true; return cuda_fail(e, "debug_activation", &r->err); }
+    int d[4];
+    rc = r->net->activation(name, n, host_out, cap, d, &r->err);
+    for (int i = 0; i < 4; ++i) dims4[i] = d[i];
     return rc;
 }

@@ -58,3 +58,19 @@ def top_labels(scores_np, n_labels, k):
     _, idx, score = softmax_topk(x, k, n_labels=n_labels, apply_softmax=False)
     torch.cuda.synchronize()
     return idx.cpu().numpy(), score.cpu().numpy()
+
+
+def conv2d_bf16(x, w, bias, stride=1, pad=(0, 0), relu=True, out_dtype=torch.bfloat16, out=None, out_off=0):
+    """K3: x bf16 [N,H,W,Cin], w bf16 [Cout,KH,KW,Cin], bias f32 [Cout] or None -> [N,OH,OW,Cout] (or a slice of out)."""
+    _need_cuda(x, w, bias, out)
+    n, h, wd, cin = x.shape
+    cout, kh, kw, cin2 = w.shape
+    if cin != cin2 or x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16:
+        raise ValueError("conv2d_bf16: bf16 NHWC input and [Cout,KH,KW,Cin] weights")
+    oh, ow = (h + 2 * pad[0] - kh) // stride + 1, (wd + 2 * pad[1] - kw) // stride + 1
+    y = out if out is not None else torch.empty((n, oh, ow, cout), dtype=out_dtype, device=x.device)
+    code = _abi.FLOAT if y.dtype == torch.float32 else _abi.BFLOAT16
+    _check(_abi.load_library().ftf_conv2d_bf16_dev(
+        x.data_ptr(), n, h, wd, cin, cin, w.data_ptr(), bias.data_ptr() if bias is not None else None, cout, kh, kw,
+        stride, pad[0], pad[1], 1 if relu else 0, y.data_ptr(), code, y.shape[-1], out_off, _stream()))
+    return y

@@ -179,11 +179,25 @@ int ftf_softmax_topk_dev(const float* x, int64_t m, int32_t n, int32_t n_labels,
                          int32_t apply_softmax, float* probs, int32_t* idx, float* score,
                          void* stream);
 
+/* K3: one convolution (+ bias, + ReLU) as an implicit GEMM on the tcgen05 tensor cores -- the Conv2D/BatchNorm/
+ * Relu nodes of the frozen graph EX/inception/InceptionModel.scala:58-67 runs, with BN folded into weights and
+ * bias.  in bf16 NHWC [n,h,w,in_ld] (channels [0,cin) are read), weights bf16 [cout][kh][kw][cin], bias fp32 [cout]
+ * or NULL; out bf16 or fp32 [n,oh,ow,out_ld] written at channel offset out_off.  cin, in_ld, out_ld, out_off
+ * multiples of 8; cout a multiple of 16; bf16 accumulate in fp32. */
+int ftf_conv2d_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t cin, int32_t in_ld,
+                        const void* weights, const float* bias, int32_t cout, int32_t kh, int32_t kw,
+                        int32_t stride, int32_t pad_h, int32_t pad_w, int32_t relu, void* out,
+                        int32_t out_dtype, int32_t out_ld, int32_t out_off, void* stream);
+
 /* Label path on device buffers: images [n,299,299,3] (f32 or bf16 per in_dtype) -> logits [n,classes]
  * f32, probs, top-k.  Runs on the runner's stream; the weights are the runner's. Any of
  * logits/probs/idx/score may be NULL. */
 int ftf_label_dev(ftf_runner* r, const void* images, int32_t in_dtype, int64_t n, float* logits,
                   float* probs, int32_t* idx, float* score);
+/* Diagnostic (no reference counterpart; TF-Java would fetch an intermediate tensor by name): copies a named
+ * activation of a label runner's last forward to host fp32 [n,h,w,c].  Names are torchvision's layer/block names
+ * ("Conv2d_2a_3x3", "Mixed_5b", "pool1", "gap", ...).  host_out NULL: dims only. */
+int ftf_debug_activation(ftf_runner* r, const char* name, int64_t n, float* host_out, int64_t cap, int32_t* dims4);
 /* Stream the runner launches on (cudaStream_t), for event timing by the caller. */
 void* ftf_runner_stream(ftf_runner* r);
 
