@@ -43,40 +43,58 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock and throttle reasons sampled DURING the timed region through NVML (the same counters as the
+    nvidia-smi clocks line of B200_PROFILING.md, at a 2 ms period so that short timed regions are covered)."""
 
     def __init__(self, index):
         self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+        self.sm_max = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(visible.split(",")[index]) if visible and visible.split(",")[index].isdigit() else index
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
 
     def _loop(self):
+        nv = self.nv
         while not self._stop.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
-                                      str(self.index)], capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                self.rows.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM),
+                                  nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)))
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.002)
 
     def __enter__(self):
-        self._t = threading.Thread(target=self._loop, daemon=True)
-        self._t.start()
+        if self.nv is not None:
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
         return self
 
     def __exit__(self, *a):
         self._stop.set()
-        self._t.join(timeout=6)
+        if self._t is not None:
+            self._t.join(timeout=2)
 
     def summary(self):
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+        if self.nv is None or not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": [], "samples": 0}
+        nv = self.nv
+        sm = sorted(r[0] for r in self.rows)
+        bits = 0
+        for _, r in self.rows:
+            bits |= r
+        names = {"hw_slowdown": getattr(nv, "nvmlClocksEventReasonHwSlowdown", 0x8),
+                 "hw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40),
+                 "sw_thermal_slowdown": getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20),
+                 "sw_power_cap": getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4)}
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": self.sm_max, "reasons": sorted(k for k, v in names.items() if bits & v),
+                "samples": len(sm)}
 
 
 def dist_env():
@@ -190,7 +208,9 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    from flink_tensorflow_b200.host import _check as _chk
     launches0 = lib.ftf_launch_count()
+    ext = None
     extra = {}
     if wl == "half_plus_two":
         n = HPT_N
@@ -217,19 +237,46 @@ def run_ours(args):
                   "parallelism": f"dp{world} (records sharded, no collective)", **NORM}
         bound, peak, peak_unit = "hbm", pk["hbm"], "GB/s"
     else:
-        raise SystemExit(f"workload {wl} not available in this build")
+        bsz = INC["batch"]
+        cfg = ftf.default_config(device=local_rank, max_batch=bsz, top_k=INC["top_k"], num_classes=INC["classes"], seed=INC["seed"])
+        lab = ftf.Runner("builtin:inception_v3", None, None, cfg)
+        ext = torch.cuda.ExternalStream(lib.ftf_runner_stream(lab.handle))
+        g = torch.Generator(device="cuda").manual_seed(7 + rank)
+        img = torch.randn((bsz, 299, 299, 3), device="cuda", generator=g).to(torch.bfloat16)
+        logits = torch.empty((bsz, INC["classes"]), dtype=torch.float32, device="cuda")
+        probs = torch.empty_like(logits)
+        idx = torch.empty((bsz, INC["top_k"]), dtype=torch.int32, device="cuda")
+        score = torch.empty((bsz, INC["top_k"]), dtype=torch.float32, device="cuda")
+        torch.cuda.synchronize()
+
+        def step():
+            _chk(lib.ftf_label_dev(lab.handle, img.data_ptr(), ftf._abi.BFLOAT16, bsz, logits.data_ptr(), probs.data_ptr(),
+                                     idx.data_ptr(), score.data_ptr()), lab.handle)
+        units_per_step, unit, metric, dtype = float(bsz), "images/s", "Inception-v3 images/sec", "bf16"
+        algo_bytes = None
+        config = {"workload": "Inception-v3 random-init labeling, bf16 (fp32 accumulate), batch 64 per GPU, top-5 "
+                              "(BASELINE config 4)", "l2": "activations of one step (about 1 GB written) exceed L2; no flush",
+                  "parallelism": f"dp{world} (records sharded, no collective)", **INC}
+        bound, peak, peak_unit = "tensor", pk["tf_sustained"], "TFLOP/s"
 
     # ---- device-resident timing ------------------------------------------------------------------
     for _ in range(Wm):
         step()
     barrier()
     with ClockSampler(local_rank) as clk:
-        ms_total = cuda_time(step, K, torch)
+        if ext is not None:
+            with torch.cuda.stream(ext):
+                ms_total = cuda_time(step, K, torch)
+        else:
+            ms_total = cuda_time(step, K, torch)
         barrier()
     ms_total = max_over_ranks(ms_total)
     ms_step = ms_total / K
     value = units_per_step * world / (ms_step / 1e3)
-    achieved = algo_bytes / (ms_step / 1e3) / 1e9
+    if wl == "inception":
+        achieved = INC_FLOP_PER_IMAGE * INC["batch"] / (ms_step / 1e3) / 1e12     # algorithmic TFLOP/s of the whole step
+    else:
+        achieved = algo_bytes / (ms_step / 1e3) / 1e9
     gpu_launches = int(lib.ftf_launch_count() - launches0)
 
     # ---- end to end through ftf_run with host buffers ----------------------------------------------
@@ -243,6 +290,15 @@ def run_ours(args):
         tv.data_type, tv.shape, tv.buffer = ftf.DataType.FLOAT, (HPT_N, 1), hx.view(np.uint8)
         in_key, out_key = "x", "y"
         h2d = d2h = 4 * HPT_N
+    elif wl == "inception":
+        r = lab
+        nb = INC["batch"] * 299 * 299 * 3 * 4
+        p, hx = pinned_array(lib, np, nb, np.float32)
+        hx[:] = np.random.default_rng(5 + rank).standard_normal(nb // 4, dtype=np.float32)
+        tv = ftf.TensorValue.__new__(ftf.TensorValue)
+        tv.data_type, tv.shape, tv.buffer = ftf.DataType.FLOAT, (INC["batch"], 299, 299, 3), hx.view(np.uint8)
+        in_key, out_key = "inputs", "top_k_indices"
+        h2d, d2h = nb, INC["batch"] * (2 * INC["classes"] * 4 + 2 * INC["top_k"] * 4)
     else:
         r = ftf.Runner("builtin:image_normalization", None, None,
                        ftf.default_config(device=local_rank, out_h=NORM["out_h"], out_w=NORM["out_w"], mean=NORM["mean"],
@@ -263,7 +319,8 @@ def run_ours(args):
     def e2e_step():
         _check(lib.ftf_run(r.handle, 1, ikeys, tin, 1, okeys, tout), r.handle)
         # the result (runner-owned pinned memory) is read by the host: first and last element
-        res = np.ctypeslib.as_array(C.cast(tout[0].data, C.POINTER(C.c_float)), shape=(tout[0].nbytes // 4,))
+        res = np.ctypeslib.as_array(C.cast(tout[0].data, C.POINTER(C.c_int32 if wl == "inception" else C.c_float)),
+                                    shape=(tout[0].nbytes // 4,))
         return float(res[0]) + float(res[-1])
     for _ in range(2):
         e2e_step()
@@ -274,7 +331,8 @@ def run_ours(args):
     barrier()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / e2e_steps
     e2e_value = units_per_step * world / (e2e_ms / 1e3)
-    e2e_launches = r.stats()["kernel_launches"]
+    st = r.stats()
+    e2e_launches = st["kernel_launches"]
     r.close()
     lib.ftf_host_free(p)
 
@@ -295,6 +353,32 @@ def run_ours(args):
                 reps += 1
             cpu = {"value": 8.0 * n * reps / 1e9 / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
                    "sample": f"{reps} passes over 2^26 floats (1/4 of the workload), all host threads"}
+        elif wl == "inception":
+            import oracle.inception as oinc
+            net = oinc.Net(INC["classes"], INC["seed"], 0)
+            b = 4
+            cimg = rng.standard_normal((b, 299, 299, 3)).astype(np.float32)
+            t0, reps = time.perf_counter(), 0
+            while time.perf_counter() - t0 < 10.0:
+                net.forward(cimg, threads=threads)
+                reps += 1
+            cpu = {"value": b * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
+                   "sample": f"{reps} passes over 4 images (1/16 of the batch), fp32 C oracle, all host threads"}
+            try:   # strongest CPU stand-in: torchvision on oneDNN, same architecture
+                import torchvision
+                tvm = torchvision.models.inception_v3(weights=None, aux_logits=False, transform_input=False, init_weights=False).eval()
+                torch.set_num_threads(threads)
+                tx = torch.randn(16, 3, 299, 299)
+                with torch.no_grad():
+                    tvm(tx)
+                    t0, reps = time.perf_counter(), 0
+                    while time.perf_counter() - t0 < 10.0:
+                        tvm(tx)
+                        reps += 1
+                extra["cpu_torchvision_onednn"] = {"value": 16 * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads,
+                                                   "sample": f"{reps} passes over 16 images, fp32"}
+            except Exception as ex:  # noqa: BLE001
+                extra["cpu_torchvision_onednn"] = {"unavailable": str(ex)[:200]}
         else:
             b = 32
             cimg = rng.integers(0, 256, (b, NORM["in_h"], NORM["in_w"], 3), dtype=np.uint8)
@@ -310,7 +394,9 @@ def run_ours(args):
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
             "data": "synthetic", "config": config,
             "roofline": {"bound": bound, "achieved": achieved, "peak": peak, "unit": peak_unit, "frac": achieved / peak,
-                         "traffic": None, "peak_source": pk["src"], "frac_of_nominal_8TBps": achieved / 8000.0,
+                         "traffic": None, "peak_source": pk["src"] + (" (sustained)" if wl == "inception" else ""),
+                         **({"frac_of_nominal_8TBps": achieved / 8000.0} if wl != "inception" else
+                            {"frac_of_burst": achieved / pk["tf_burst"], "scope": "whole step (all kernels), algorithmic FLOPs"}),
                          "kernel_ms": ms_step},
             "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": e2e_ms, "steps": e2e_steps, "gpu_launches": int(e2e_launches),
@@ -328,7 +414,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="half_plus_two", choices=["half_plus_two", "normalize", "inception"])
+    ap.add_argument("--workload", default="inception", choices=["half_plus_two", "normalize", "inception"])
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -9,6 +9,7 @@
 #include "runner.h"
 #include "inception.h"
 #include "conv_tc.h"
+#include "pools.h"
 #include <string.h>
 #include <algorithm>
 #include <atomic>
@@ -468,7 +469,7 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
 
     // ---- chunked pipeline -----------------------------------------------------------------------
     int64_t chunk = std::max<int64_t>(1, (int64_t)(kChunkBytes / std::max<size_t>(1, r->in_rec_bytes)));
-    if (is_label_kind(r->kind)) chunk = std::min<int64_t>(chunk, r->net->max_batch());
+    if (is_label_kind(r->kind)) chunk = r->net->max_batch();   // whole micro-batches: tile counts of the convolutions scale with n
     const bool parse = r->kind == Kind::kAffine && r->affine.input_is_examples;
     const bool direct = !parse && n > 0 && pinned(x->data);
     cudaError_t e;
@@ -747,5 +748,45 @@ extern "C" int ftf_debug_activation(ftf_runner* r, const char* name, int64_t n, 
     int d[4];
     rc = r->net->activation(name, n, host_out, cap, d, &r->err);
     for (int i = 0; i < 4; ++i) dims4[i] = d[i];
+    return rc;
+}
+
+extern "C" int ftf_maxpool3x3s2_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t c, void* out, int32_t out_ld,
+                                         int32_t out_off, void* stream) {
+    std::string err;
+    const int rc = launch_maxpool3x3s2(in, out, n, h, w, c, out_ld, out_off, (cudaStream_t)stream, &err);
+    if (rc) set_thread_error(err);
+    return rc;
+}
+
+extern "C" int ftf_global_avgpool_bf16_dev(const void* in, int32_t n, int32_t hw, int32_t c, void* out, void* stream) {
+    std::string err;
+    const int rc = launch_global_avgpool(in, out, n, hw, c, (cudaStream_t)stream, &err);
+    if (rc) set_thread_error(err);
+    return rc;
+}
+
+extern "C" int ftf_pool_branch_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t cin, int32_t in_ld,
+                                        const void* weights, const float* bias, int32_t cout, void* out, int32_t out_ld,
+                                        int32_t out_off, void* stream) {
+    std::string err;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { set_thread_error("cudaGetDevice failed"); return FTF_INTERNAL; }
+    if (n <= 0 || h <= 0 || w <= 0 || cout <= 0 || !bias) { set_thread_error("pool_branch: bad shape or null bias"); return FTF_INVALID_ARGUMENT; }
+    cudaStream_t s = (cudaStream_t)stream;
+    // scratch: the 1x1 convolution's fp32 pre-activation [n*h*w, cout], allocated in stream order
+    float* pre = nullptr;
+    const size_t bytes = (size_t)n * h * w * cout * sizeof(float);
+    cudaError_t e = cudaMallocAsync((void**)&pre, bytes, s);
+    if (e != cudaSuccess) { cudaGetLastError(); set_thread_error(std::string("pool_branch scratch: ") + cudaGetErrorString(e)); return FTF_RESOURCE_EXHAUSTED; }
+    ConvSegment sg{};
+    sg.out = pre; sg.ld = cout; sg.coff = 0; sg.col_begin = 0; sg.flags = kSegF32;
+    ConvGeometry g{in, n, h, w, cin, in_ld, weights, nullptr, cout, 1, 1, 1, 0, 0};
+    ConvPlan plan;
+    int rc = conv_tc_plan(g, &sg, 1, device_sm_count(dev), &plan, &err);
+    if (!rc) rc = conv_tc_launch(plan, n, s, &err);
+    if (!rc) rc = launch_avgpool3x3_bias_relu(pre, bias, out, n, h, w, cout, out_ld, out_off, s, &err);
+    cudaFreeAsync(pre, s);
+    if (rc) set_thread_error(err);
     return rc;
 }

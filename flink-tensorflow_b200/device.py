@@ -74,3 +74,32 @@ def conv2d_bf16(x, w, bias, stride=1, pad=(0, 0), relu=True, out_dtype=torch.bfl
         x.data_ptr(), n, h, wd, cin, cin, w.data_ptr(), bias.data_ptr() if bias is not None else None, cout, kh, kw,
         stride, pad[0], pad[1], 1 if relu else 0, y.data_ptr(), code, y.shape[-1], out_off, _stream()))
     return y
+
+
+def maxpool3x3s2(x, out=None, out_off=0):
+    """K4 on bf16 NHWC."""
+    _need_cuda(x, out)
+    n, h, w, c = x.shape
+    y = out if out is not None else torch.empty((n, (h - 3) // 2 + 1, (w - 3) // 2 + 1, c), dtype=torch.bfloat16, device=x.device)
+    _check(_abi.load_library().ftf_maxpool3x3s2_bf16_dev(x.data_ptr(), n, h, w, c, y.data_ptr(), y.shape[-1], out_off, _stream()))
+    return y
+
+
+def pool_branch(x, w, bias, out=None, out_off=0):
+    """K5: relu(avgpool3x3(conv1x1(x)) + bias); x bf16 [N,H,W,Cin], w bf16 [Cout,Cin], bias f32 [Cout]."""
+    _need_cuda(x, w, bias, out)
+    n, h, wd, cin = x.shape
+    cout = w.shape[0]
+    y = out if out is not None else torch.empty((n, h, wd, cout), dtype=torch.bfloat16, device=x.device)
+    _check(_abi.load_library().ftf_pool_branch_bf16_dev(x.data_ptr(), n, h, wd, cin, cin, w.data_ptr(), bias.data_ptr(), cout,
+                                                        y.data_ptr(), y.shape[-1], out_off, _stream()))
+    return y
+
+
+def global_avgpool(x):
+    """K6: bf16 [N,H,W,C] -> bf16 [N,C]."""
+    _need_cuda(x)
+    n, h, w, c = x.shape
+    y = torch.empty((n, c), dtype=torch.bfloat16, device=x.device)
+    _check(_abi.load_library().ftf_global_avgpool_bf16_dev(x.data_ptr(), n, h * w, c, y.data_ptr(), _stream()))
+    return y

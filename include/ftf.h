@@ -189,6 +189,19 @@ int ftf_conv2d_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t
                         int32_t stride, int32_t pad_h, int32_t pad_w, int32_t relu, void* out,
                         int32_t out_dtype, int32_t out_ld, int32_t out_off, void* stream);
 
+/* K4: 3x3 max pool, stride 2, no padding (the MaxPool nodes of the same graph).  bf16 NHWC [n,h,w,c] ->
+ * [n,(h-3)/2+1,(w-3)/2+1,out_ld] at channel offset out_off; c, out_ld, out_off multiples of 8. */
+int ftf_maxpool3x3s2_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t c, void* out,
+                              int32_t out_ld, int32_t out_off, void* stream);
+/* K5: an Inception block's pool branch, AvgPool(3x3, stride 1, SAME, divisor 9) -> Conv2D 1x1 -> BN -> Relu, computed
+ * as relu(avgpool(conv1x1(x)) + bias) (pool and 1x1 convolution commute).  weights bf16 [cout][cin], bias fp32.
+ * Uses fp32 scratch of n*h*w*cout elements, allocated and freed in stream order on `stream`. */
+int ftf_pool_branch_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t cin, int32_t in_ld,
+                             const void* weights, const float* bias, int32_t cout, void* out, int32_t out_ld,
+                             int32_t out_off, void* stream);
+/* K6: global average pool, bf16 [n,hw,c] -> bf16 [n,c] (fp32 mean over the pixels). */
+int ftf_global_avgpool_bf16_dev(const void* in, int32_t n, int32_t hw, int32_t c, void* out, void* stream);
+
 /* Label path on device buffers: images [n,299,299,3] (f32 or bf16 per in_dtype) -> logits [n,classes]
  * f32, probs, top-k.  Runs on the runner's stream; the weights are the runner's. Any of
  * logits/probs/idx/score may be NULL. */

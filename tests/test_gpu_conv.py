@@ -99,6 +99,34 @@ def test_conv_tc_is_batch_independent(dev, oracle):
         assert torch.equal(one[0], full[i])
 
 
+def test_pool_kernels_match_oracle(dev, oracle):
+    """K4 max pool, K5 pool branch, K6 global average pool on bf16 tensors."""
+    import torch
+    import oracle.inception as oi
+    rng = np.random.default_rng(12)
+    x = _bf16(oracle, rng.standard_normal((3, 17, 17, 96)))
+    xd = _to_bf16_cuda(x)
+    # K4: exact (max of bf16 values), into a concat slice
+    out = torch.zeros((3, 8, 8, 128), dtype=torch.bfloat16, device="cuda")
+    dev.maxpool3x3s2(xd, out=out, out_off=32)
+    win = np.lib.stride_tricks.sliding_window_view(x, (3, 3), axis=(1, 2))[:, ::2, ::2]      # [n,8,8,c,3,3]
+    assert np.array_equal(out.float().cpu().numpy()[..., 32:], win.max(axis=(-1, -2)))
+    assert torch.all(out[..., :32] == 0)
+    # K5: relu(avgpool3x3(conv1x1(x)) / 9 + b), fp32 until the final bf16 rounding
+    w = _bf16(oracle, rng.standard_normal((64, 96)) * 0.1)
+    b = rng.uniform(-0.1, 0.1, 64).astype(np.float32)
+    got = dev.pool_branch(xd, _to_bf16_cuda(w), torch.from_numpy(b).cuda()).float().cpu().numpy()
+    pre = oi.conv2d_nhwc(x, w.reshape(64, 1, 1, 96), b, relu=False, add_bias=False)
+    padded = np.pad(pre, ((0, 0), (1, 1), (1, 1), (0, 0)))
+    pooled = np.lib.stride_tricks.sliding_window_view(padded, (3, 3), axis=(1, 2)).sum(axis=(-1, -2), dtype=np.float32)
+    want = np.maximum(pooled * np.float32(1.0 / 9.0) + b, 0.0)
+    assert np.all(np.abs(got - want) <= np.abs(want) * 2.0 ** -8 + 1e-4 * np.abs(want).max())
+    # K6: fp32 mean of the pixels, rounded to bf16
+    g = dev.global_avgpool(xd).float().cpu().numpy()
+    want = x.reshape(3, -1, 96).mean(axis=1, dtype=np.float32)
+    assert np.all(np.abs(g - want) <= np.abs(want) * 2.0 ** -8 + 1e-6)
+
+
 @pytest.fixture(scope="module")
 def label_runner(ftf):
     r = ftf.Runner("builtin:inception_v3", None, None, ftf.default_config(max_batch=4, top_k=5, num_classes=1000, seed=2024))
