@@ -199,6 +199,19 @@ int ftf_maxpool3x3s2_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, i
 int ftf_pool_branch_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t cin, int32_t in_ld,
                              const void* weights, const float* bias, int32_t cout, void* out, int32_t out_ld,
                              int32_t out_off, void* stream);
+/* K5 without any device allocation.  No counterpart in the reference: it exists for callers of this library that
+ * cannot allocate GPU memory when they call -- a Flink task thread on the per-record path that shares its GPU with other
+ * subtasks (an allocation or free can synchronise the device and stall their streams), or a deployment that assigns all
+ * HBM at open() and treats later allocations as faults.  Same arguments and result as ftf_pool_branch_bf16_dev; the fp32
+ * scratch is a fixed FTF_POOL_BRANCH_STATIC_MAX_BYTES array inside the library (resident on every GPU that loads it
+ * until the process exits).  n*h*w*cout*4 beyond that size is refused with FTF_RESOURCE_EXHAUSTED.  The first call on a
+ * device also looks up the array's device address; make that call before starting any stream capture.  All calls on a
+ * device share the array: calls whose GPU work may overlap (other streams, other threads) race and must be ordered by
+ * the caller.  Nothing in it needs clearing between calls. */
+#define FTF_POOL_BRANCH_STATIC_MAX_BYTES (8ll << 20)
+int ftf_pool_branch_bf16_static_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t cin, int32_t in_ld,
+                                    const void* weights, const float* bias, int32_t cout, void* out,
+                                    int32_t out_ld, int32_t out_off, void* stream);
 /* K6: global average pool, bf16 [n,hw,c] -> bf16 [n,c] (fp32 mean over the pixels). */
 int ftf_global_avgpool_bf16_dev(const void* in, int32_t n, int32_t hw, int32_t c, void* out, void* stream);
 
