@@ -41,7 +41,7 @@ int launch_softmax_topk(const float* x, int64_t m, int n, int n_labels, int k, i
                         float* probs, int32_t* idx, float* score, cudaStream_t s, std::string* err);
 
 // Count of this library's kernel launches (process-wide, relaxed).
-void count_launch(int n = 1);
+void count_launch(int n = 1);   // n may be negative (a graph recording counted launches that did not run)
 uint64_t launches_so_far();
 
 }  // namespace ftf

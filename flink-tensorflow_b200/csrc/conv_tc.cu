@@ -253,8 +253,22 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     p.OH = OH; p.OW = OW; p.stride = g.stride; p.pad_h = g.pad_h; p.pad_w = g.pad_w; p.KH = g.KH; p.KW = g.KW;
     p.Cin = g.Cin; p.cin_chunks = (g.Cin + kBlockK - 1) / kBlockK;
     p.N_total = g.Cout;
-    p.n_tiles = (g.Cout + 255) / 256;
-    p.block_n = ((g.Cout + p.n_tiles - 1) / p.n_tiles + 15) / 16 * 16;
+    p.M = g.n_max * OH * OW;
+    p.m_tiles = (p.M + kBlockM - 1) / kBlockM;
+    {   // N tile: the split of Cout that minimises  waves x (per-CTA work ~ block_n + fixed cost); smaller N tiles
+        // buy more CTAs when there are few M tiles (8x8 and 17x17 maps) at the price of re-reading A from L2
+        int best_tiles = (g.Cout + 255) / 256;
+        long long best_cost = -1;
+        for (int nt = best_tiles; nt <= (g.Cout + 31) / 32; ++nt) {
+            const int bn = ((g.Cout + nt - 1) / nt + 15) / 16 * 16;
+            if (bn > 256) continue;
+            const int tiles_n = (g.Cout + bn - 1) / bn;
+            const long long waves = ((long long)p.m_tiles * tiles_n + sm_count - 1) / sm_count;
+            const long long cost = waves * (bn + 64);
+            if (best_cost < 0 || cost < best_cost) { best_cost = cost; best_tiles = tiles_n; p.block_n = bn; }
+        }
+        p.n_tiles = best_tiles;
+    }
     p.b_stage_bytes = p.block_n * kBlockK * 2;
     const int stage_bytes = kAStageBytes + p.b_stage_bytes;
     p.stages = (200 * 1024) / stage_bytes;
@@ -262,8 +276,6 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     p.bias = g.bias;
     p.n_seg = n_seg;
     for (int i = 0; i < n_seg; ++i) p.seg[i] = segs[i];
-    p.M = g.n_max * OH * OW;
-    p.m_tiles = (p.M + kBlockM - 1) / kBlockM;
     plan->smem = (size_t)p.stages * stage_bytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
     plan->grid = sm_count;
 

@@ -16,6 +16,7 @@
 #include "pools.h"
 #include <cuda_bf16.h>
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <functional>
@@ -164,8 +165,12 @@ struct Act {
     int h = 0, w = 0, c = 0;
 };
 
+constexpr int kLanes = 4;                // streams an Inception block's independent branches are spread over
+
 struct Op {
-    enum Type { kStem, kConv, kMaxPool, kAvgPoolBiasRelu, kGap } type;
+    enum Type { kStem, kConv, kMaxPool, kAvgPoolBiasRelu, kGap, kFork, kJoin } type;
+    int lane = 0;                        // stream the op runs on (0 = the caller's stream)
+    int lanes = 0;                       // kFork/kJoin: bit mask of the lanes 1..3 that branch off / come back
     int plan = -1;                       // kConv
     const void* in = nullptr;            // other kernels
     void* out = nullptr;
@@ -185,10 +190,31 @@ struct InceptionV3::Impl {
     float* logits = nullptr;              // [max_batch, classes] fp32
     std::string* err = nullptr;
     int rc = FTF_OK;
+    int cur_lane = 0;
+    cudaStream_t lane_stream[kLanes] = {nullptr, nullptr, nullptr, nullptr};   // [0] unused: lane 0 is the caller's stream
+    cudaEvent_t fork_ev = nullptr, join_ev[kLanes] = {nullptr, nullptr, nullptr, nullptr};
+    std::map<int, cudaGraphExec_t> graphs;   // one instantiated graph of the whole forward per batch size
+    std::map<int, int> graph_kernels;        // kernels per replay of that graph
 
     ~Impl() {
         cudaSetDevice(device);
+        for (auto& g : graphs) cudaGraphExecDestroy(g.second);
+        for (int i = 1; i < kLanes; ++i) {
+            if (lane_stream[i]) cudaStreamDestroy(lane_stream[i]);
+            if (join_ev[i]) cudaEventDestroy(join_ev[i]);
+        }
+        if (fork_ev) cudaEventDestroy(fork_ev);
         for (void* p : allocs) cudaFree(p);
+    }
+    void fork(int lanes) { Op o{}; o.type = Op::kFork; o.lanes = lanes; ops.push_back(o); }
+    void join(int lanes) { Op o{}; o.type = Op::kJoin; o.lanes = lanes; ops.push_back(o); cur_lane = 0; }
+    void emit_pools() {      // the (avgpool + bias + ReLU) halves of the pool branches recorded by conv_multi
+        for (auto& pp : pending_pool) {
+            Op o{}; o.type = Op::kAvgPoolBiasRelu; o.lane = cur_lane; o.in = pp.scratch; o.bias = pp.bias; o.out = pp.dst->p;
+            o.H = pp.h; o.W = pp.w; o.C = pp.c; o.out_ld = pp.dst->c; o.out_off = pp.coff;
+            ops.push_back(o);
+        }
+        pending_pool.clear();
     }
     void* dev_alloc(size_t bytes, bool zero) {
         if (rc) return nullptr;
@@ -247,14 +273,8 @@ struct InceptionV3::Impl {
         rc = conv_tc_plan(g, segs.data(), (int)segs.size(), sms, &plan, err);
         if (rc) return;
         plans.push_back(plan);
-        Op op{}; op.type = Op::kConv; op.plan = (int)plans.size() - 1;
+        Op op{}; op.type = Op::kConv; op.lane = cur_lane; op.plan = (int)plans.size() - 1;
         ops.push_back(op);
-        for (auto& pp : pending_pool) {
-            Op o{}; o.type = Op::kAvgPoolBiasRelu; o.in = pp.scratch; o.bias = pp.bias; o.out = pp.dst->p;
-            o.H = pp.h; o.W = pp.w; o.C = pp.c; o.out_ld = pp.dst->c; o.out_off = pp.coff;
-            ops.push_back(o);
-        }
-        pending_pool.clear();
     }
     struct PendingPool { float* scratch; float* bias; Act* dst; int coff, c, h, w; };
     std::vector<PendingPool> pending_pool;
@@ -269,30 +289,37 @@ struct InceptionV3::Impl {
         conv_multi(in, {{name, cout, dst, coff, false}}, kh, kw, s, ph, pw);
     }
     void maxpool_to(const Act& in, Act* dst, int coff) {
-        Op o{}; o.type = Op::kMaxPool; o.in = in.p; o.out = dst->p; o.H = in.h; o.W = in.w; o.C = in.c;
+        Op o{}; o.type = Op::kMaxPool; o.lane = cur_lane; o.in = in.p; o.out = dst->p; o.H = in.h; o.W = in.w; o.C = in.c;
         o.OH = (in.h - 3) / 2 + 1; o.OW = (in.w - 3) / 2 + 1; o.out_ld = dst->c; o.out_off = coff;
         ops.push_back(o);
     }
 
+    // Each block: the 1x1 convolutions that read the block input run first as one GEMM on lane 0; then the branches
+    // (independent of each other, writing disjoint channel slices) run on separate streams and join at the block end.
     Act block_a(const std::string& blk, const Act& x, int pf) {
         Act out = act(x.h, x.w, 224 + pf);
         Act t5 = act(x.h, x.w, 48), t3 = act(x.h, x.w, 64);
         conv_multi(x, {{blk + ".branch1x1", 64, &out, 0, false}, {blk + ".branch5x5_1", 48, &t5, 0, false},
                        {blk + ".branch3x3dbl_1", 64, &t3, 0, false}, {blk + ".branch_pool", pf, &out, 224, true}}, 1, 1, 1, 0, 0);
-        conv_to(blk + ".branch5x5_2", t5, 64, 5, 5, 1, 2, 2, &out, 64);
-        Act u = conv(blk + ".branch3x3dbl_2", t3, 96, 3, 3, 1, 1, 1);
+        fork(0b0110);
+        cur_lane = 0; conv_to(blk + ".branch5x5_2", t5, 64, 5, 5, 1, 2, 2, &out, 64);
+        cur_lane = 1; Act u = conv(blk + ".branch3x3dbl_2", t3, 96, 3, 3, 1, 1, 1);
         conv_to(blk + ".branch3x3dbl_3", u, 96, 3, 3, 1, 1, 1, &out, 128);
+        cur_lane = 2; emit_pools();
+        join(0b0110);
         named[blk] = out;
         return out;
     }
     Act block_b(const std::string& blk, const Act& x) {
         const int oh = (x.h - 3) / 2 + 1, ow = (x.w - 3) / 2 + 1;
         Act out = act(oh, ow, 384 + 96 + x.c);
-        conv_to(blk + ".branch3x3", x, 384, 3, 3, 2, 0, 0, &out, 0);
-        Act t = conv(blk + ".branch3x3dbl_1", x, 64, 1, 1, 1, 0, 0);
+        fork(0b0110);
+        cur_lane = 0; conv_to(blk + ".branch3x3", x, 384, 3, 3, 2, 0, 0, &out, 0);
+        cur_lane = 1; Act t = conv(blk + ".branch3x3dbl_1", x, 64, 1, 1, 1, 0, 0);
         Act u = conv(blk + ".branch3x3dbl_2", t, 96, 3, 3, 1, 1, 1);
         conv_to(blk + ".branch3x3dbl_3", u, 96, 3, 3, 2, 0, 0, &out, 384);
-        maxpool_to(x, &out, 480);
+        cur_lane = 2; maxpool_to(x, &out, 480);
+        join(0b0110);
         named[blk] = out;
         return out;
     }
@@ -301,12 +328,15 @@ struct InceptionV3::Impl {
         Act t = act(x.h, x.w, c7), d = act(x.h, x.w, c7);
         conv_multi(x, {{blk + ".branch1x1", 192, &out, 0, false}, {blk + ".branch7x7_1", c7, &t, 0, false},
                        {blk + ".branch7x7dbl_1", c7, &d, 0, false}, {blk + ".branch_pool", 192, &out, 576, true}}, 1, 1, 1, 0, 0);
-        Act u = conv(blk + ".branch7x7_2", t, c7, 1, 7, 1, 0, 3);
+        fork(0b0110);
+        cur_lane = 0; Act u = conv(blk + ".branch7x7_2", t, c7, 1, 7, 1, 0, 3);
         conv_to(blk + ".branch7x7_3", u, 192, 7, 1, 1, 3, 0, &out, 192);
-        Act d2 = conv(blk + ".branch7x7dbl_2", d, c7, 7, 1, 1, 3, 0);
+        cur_lane = 1; Act d2 = conv(blk + ".branch7x7dbl_2", d, c7, 7, 1, 1, 3, 0);
         Act d3 = conv(blk + ".branch7x7dbl_3", d2, c7, 1, 7, 1, 0, 3);
         Act d4 = conv(blk + ".branch7x7dbl_4", d3, c7, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7dbl_5", d4, 192, 1, 7, 1, 0, 3, &out, 384);
+        cur_lane = 2; emit_pools();
+        join(0b0110);
         named[blk] = out;
         return out;
     }
@@ -315,11 +345,13 @@ struct InceptionV3::Impl {
         Act out = act(oh, ow, 320 + 192 + x.c);
         Act t = act(x.h, x.w, 192), s = act(x.h, x.w, 192);
         conv_multi(x, {{blk + ".branch3x3_1", 192, &t, 0, false}, {blk + ".branch7x7x3_1", 192, &s, 0, false}}, 1, 1, 1, 0, 0);
-        conv_to(blk + ".branch3x3_2", t, 320, 3, 3, 2, 0, 0, &out, 0);
-        Act s2 = conv(blk + ".branch7x7x3_2", s, 192, 1, 7, 1, 0, 3);
+        fork(0b0110);
+        cur_lane = 0; conv_to(blk + ".branch3x3_2", t, 320, 3, 3, 2, 0, 0, &out, 0);
+        cur_lane = 1; Act s2 = conv(blk + ".branch7x7x3_2", s, 192, 1, 7, 1, 0, 3);
         Act s3 = conv(blk + ".branch7x7x3_3", s2, 192, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7x3_4", s3, 192, 3, 3, 2, 0, 0, &out, 320);
-        maxpool_to(x, &out, 512);
+        cur_lane = 2; maxpool_to(x, &out, 512);
+        join(0b0110);
         named[blk] = out;
         return out;
     }
@@ -328,16 +360,24 @@ struct InceptionV3::Impl {
         Act t = act(x.h, x.w, 384), d = act(x.h, x.w, 448);
         conv_multi(x, {{blk + ".branch1x1", 320, &out, 0, false}, {blk + ".branch3x3_1", 384, &t, 0, false},
                        {blk + ".branch3x3dbl_1", 448, &d, 0, false}, {blk + ".branch_pool", 192, &out, 1856, true}}, 1, 1, 1, 0, 0);
-        conv_to(blk + ".branch3x3_2a", t, 384, 1, 3, 1, 0, 1, &out, 320);
-        conv_to(blk + ".branch3x3_2b", t, 384, 3, 1, 1, 1, 0, &out, 704);
-        Act u = conv(blk + ".branch3x3dbl_2", d, 384, 3, 3, 1, 1, 1);
+        fork(0b1110);
+        cur_lane = 0; conv_to(blk + ".branch3x3_2a", t, 384, 1, 3, 1, 0, 1, &out, 320);
+        cur_lane = 1; conv_to(blk + ".branch3x3_2b", t, 384, 3, 1, 1, 1, 0, &out, 704);
+        cur_lane = 2; Act u = conv(blk + ".branch3x3dbl_2", d, 384, 3, 3, 1, 1, 1);
         conv_to(blk + ".branch3x3dbl_3a", u, 384, 1, 3, 1, 0, 1, &out, 1088);
         conv_to(blk + ".branch3x3dbl_3b", u, 384, 3, 1, 1, 1, 0, &out, 1472);
+        cur_lane = 3; emit_pools();
+        join(0b1110);
         named[blk] = out;
         return out;
     }
 
     void build() {
+        for (int i = 1; i < kLanes && !rc; ++i)
+            if (cudaStreamCreateWithFlags(&lane_stream[i], cudaStreamNonBlocking) != cudaSuccess ||
+                cudaEventCreateWithFlags(&join_ev[i], cudaEventDisableTiming) != cudaSuccess) { rc = FTF_INTERNAL; *err = "stream/event creation failed"; }
+        if (!rc && cudaEventCreateWithFlags(&fork_ev, cudaEventDisableTiming) != cudaSuccess) { rc = FTF_INTERNAL; *err = "event creation failed"; }
+        if (rc) return;
         image = act(299, 299, 3);
         // stem layer 1: direct kernel
         {
@@ -431,6 +471,58 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
     return FTF_OK;
 }
 
+// Enqueues every op of the network for nb images: lane 0 on `s`, the other lanes on the net's own streams,
+// fenced by events at each block's fork and join (the same calls record a graph when `s` is being captured).
+static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* err) {
+    auto stream_of = [&](int lane) { return lane == 0 ? s : m.lane_stream[lane]; };
+    for (const Op& op : m.ops) {
+        cudaStream_t st = stream_of(op.lane);
+        switch (op.type) {
+        case Op::kFork:
+            FTF_CUDA(cudaEventRecord(m.fork_ev, s), err);
+            for (int l = 1; l < kLanes; ++l)
+                if (op.lanes & (1 << l)) FTF_CUDA(cudaStreamWaitEvent(m.lane_stream[l], m.fork_ev, 0), err);
+            break;
+        case Op::kJoin:
+            for (int l = 1; l < kLanes; ++l)
+                if (op.lanes & (1 << l)) {
+                    FTF_CUDA(cudaEventRecord(m.join_ev[l], m.lane_stream[l]), err);
+                    FTF_CUDA(cudaStreamWaitEvent(s, m.join_ev[l], 0), err);
+                }
+            break;
+        case Op::kStem: {
+            const long long pix = (long long)nb * op.OH * op.OW;
+            stem_conv3x3s2<<<(unsigned)((pix + 127) / 128), 128, 0, st>>>((const __nv_bfloat16*)op.in, (__nv_bfloat16*)op.out, nb, op.H,
+                                                                          op.W, op.OH, op.OW, m.stem);
+            count_launch();
+            break;
+        }
+        case Op::kConv: {
+            const int rc = conv_tc_launch(m.plans[op.plan], nb, st, err);
+            if (rc) return rc;
+            break;
+        }
+        case Op::kMaxPool: {
+            const int rc = launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err);
+            if (rc) return rc;
+            break;
+        }
+        case Op::kAvgPoolBiasRelu: {
+            const int rc = launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err);
+            if (rc) return rc;
+            break;
+        }
+        case Op::kGap: {
+            const int rc = launch_global_avgpool(op.in, op.out, nb, op.H * op.W, op.C, st, err);
+            if (rc) return rc;
+            break;
+        }
+        }
+    }
+    FTF_CUDA(cudaGetLastError(), err);
+    return FTF_OK;
+}
+
 int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cudaStream_t s, std::string* err) {
     Impl& m = *impl_;
     if (n < 0 || n > m.max_batch) { if (err) *err = "inception_v3: batch exceeds max_batch"; return FTF_INVALID_ARGUMENT; }
@@ -438,38 +530,35 @@ int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cuda
     const int nb = (int)n;
     if (images_bf16 != m.image.p)
         FTF_CUDA(cudaMemcpyAsync(m.image.p, images_bf16, (size_t)n * 299 * 299 * 3 * 2, cudaMemcpyDeviceToDevice, s), err);
-    for (const Op& op : m.ops) {
-        switch (op.type) {
-        case Op::kStem: {
-            const long long pix = (long long)nb * op.OH * op.OW;
-            stem_conv3x3s2<<<(unsigned)((pix + 127) / 128), 128, 0, s>>>((const __nv_bfloat16*)op.in, (__nv_bfloat16*)op.out, nb, op.H,
-                                                                         op.W, op.OH, op.OW, m.stem);
-            count_launch();
-            break;
+    // The whole forward (about 80 kernels over 4 streams) is one CUDA graph per batch size: recorded on first use,
+    // replayed afterwards.  FTF_NO_GRAPH=1 keeps the plain stream launches (debugging, profilers that want them).
+    static const bool use_graph = !(getenv("FTF_NO_GRAPH") && getenv("FTF_NO_GRAPH")[0] == '1');
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    FTF_CUDA(cudaStreamIsCapturing(s, &cap), err);
+    if (!use_graph || cap != cudaStreamCaptureStatusNone) {
+        const int rc = run_ops(m, nb, s, err);
+        if (rc) return rc;
+    } else {
+        auto it = m.graphs.find(nb);
+        if (it == m.graphs.end()) {
+            const uint64_t before = launches_so_far();
+            FTF_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal), err);
+            const int rc = run_ops(m, nb, s, err);
+            cudaGraph_t graph = nullptr;
+            const cudaError_t e = cudaStreamEndCapture(s, &graph);
+            if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+            if (e != cudaSuccess) return cuda_fail(e, "cudaStreamEndCapture", err);
+            cudaGraphExec_t exec = nullptr;
+            const cudaError_t e2 = cudaGraphInstantiate(&exec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (e2 != cudaSuccess) return cuda_fail(e2, "cudaGraphInstantiate", err);
+            m.graph_kernels[nb] = (int)(launches_so_far() - before);
+            count_launch(-m.graph_kernels[nb]);          // recording launched nothing
+            it = m.graphs.emplace(nb, exec).first;
         }
-        case Op::kConv: {
-            const int rc = conv_tc_launch(m.plans[op.plan], nb, s, err);
-            if (rc) return rc;
-            break;
-        }
-        case Op::kMaxPool: {
-            const int rc = launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, s, err);
-            if (rc) return rc;
-            break;
-        }
-        case Op::kAvgPoolBiasRelu: {
-            const int rc = launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, s, err);
-            if (rc) return rc;
-            break;
-        }
-        case Op::kGap: {
-            const int rc = launch_global_avgpool(op.in, op.out, nb, op.H * op.W, op.C, s, err);
-            if (rc) return rc;
-            break;
-        }
-        }
+        FTF_CUDA(cudaGraphLaunch(it->second, s), err);
+        count_launch(m.graph_kernels[nb]);
     }
-    FTF_CUDA(cudaGetLastError(), err);
     // logits: [n, classes] out of the padded [n, logits_ld] result
     FTF_CUDA(cudaMemcpy2DAsync(logits, (size_t)m.classes * 4, m.logits, (size_t)m.logits_ld * 4, (size_t)m.classes * 4, (size_t)n,
                                cudaMemcpyDeviceToDevice, s), err);
