@@ -30,7 +30,19 @@ struct ConvParams {
     const float* bias;          // [N_total]
     int n_seg;
     ConvSegment seg[kConvMaxSegments];
+    // ---- halo mode (stride-1 KxK): one shared-memory window of the padded input serves every filter tap ----
+    int halo_mode;              // 0: one im2col load per tap (any stride); 1: halo window
+    int Hp, Wp;                 // padded input extent: H + 2*pad_h, W + 2*pad_w
+    long long Q;                // virtual outputs = n * Hp * Wp (valid where hp < OH and wp < OW)
+    int S;                      // 128-row sub-tiles per CTA tile
+    int a_loads;                // im2col loads of kHaloLoadRows rows that fill one window
+    int a_stage_bytes;          // a_loads * kHaloLoadRows * 128
+    int b_stages;               // weight-tile ring depth
+    int acc_stages;             // 1 or 2 TMEM accumulator sets of S * block_n columns
+    unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
 };
+
+constexpr int kHaloLoadRows = 64;
 
 struct ConvPlan {
     CUtensorMap tm_a;           // im2col view of the NHWC input
@@ -53,5 +65,10 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
                  std::string* err);
 // Enqueues the convolution for the first n images.
 int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err);
+// Diagnostic: copies (and optionally clears) the 16 pipeline cycle counters the kernels accumulate when the
+// environment has FTF_CONV_PROFILE=1: [0] CTAs, [1] producer cycles, [2] producer waiting for free stages,
+// [3] MMA-issuer cycles, [4] waiting for operands, [5] waiting for a drained accumulator, [6] epilogue cycles,
+// [7] epilogue waiting for an accumulator, [8] tiles.
+int conv_tc_profile_read(unsigned long long* out16, int reset);
 
 }  // namespace ftf

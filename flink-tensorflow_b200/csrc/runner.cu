@@ -790,3 +790,10 @@ extern "C" int ftf_pool_branch_bf16_dev(const void* in, int32_t n, int32_t h, in
     if (rc) set_thread_error(err);
     return rc;
 }
+
+extern "C" int ftf_debug_conv_profile(uint64_t* out16, int32_t reset) {
+    if (!out16) return FTF_INVALID_ARGUMENT;
+    cudaError_t e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) { set_thread_error(std::string("conv_profile: ") + cudaGetErrorString(e)); return FTF_INTERNAL; }
+    return conv_tc_profile_read((unsigned long long*)out16, reset);
+}

@@ -224,6 +224,10 @@ int ftf_label_dev(ftf_runner* r, const void* images, int32_t in_dtype, int64_t n
  * activation of a label runner's last forward to host fp32 [n,h,w,c].  Names are torchvision's layer/block names
  * ("Conv2d_2a_3x3", "Mixed_5b", "pool1", "gap", ...).  host_out NULL: dims only. */
 int ftf_debug_activation(ftf_runner* r, const char* name, int64_t n, float* host_out, int64_t cap, int32_t* dims4);
+/* Diagnostic (no reference counterpart): with FTF_CONV_PROFILE=1 in the environment the convolution kernels add up, per
+ * role, the cycles they run and the cycles they wait on each other; this copies the 16 counters (see csrc/conv_tc.h) and
+ * optionally clears them.  Synchronises the device. */
+int ftf_debug_conv_profile(uint64_t* out16, int32_t reset);
 /* Stream the runner launches on (cudaStream_t), for event timing by the caller. */
 void* ftf_runner_stream(ftf_runner* r);
 

@@ -87,6 +87,15 @@ def main():
         flop = 2.0 * args.batch * oh * ow * cout * kh * kw * cin
         byts = x.numel() * 2 + wt.numel() * 2 + out.numel() * 2
         tf = flop / us / 1e6
+        if os.environ.get("FTF_CONV_PROFILE") == "1":
+            import ctypes as C
+            from flink_tensorflow_b200 import _abi
+            buf = (C.c_uint64 * 16)()
+            _abi.load_library().ftf_debug_conv_profile(buf, 1)
+            ctas, launches = max(1, buf[0]), args.iters + 3
+            f = lambda i: buf[i] / ctas
+            print(f"   per CTA-launch cycles: producer {f(1):9.0f} (wait free stage {f(2):9.0f}) | mma {f(3):9.0f} (wait operands {f(4):9.0f}, "
+                  f"wait acc {f(5):8.0f}) | epilogue {f(6):9.0f} (wait acc {f(7):9.0f}) | tiles/CTA {buf[8] / ctas:.1f}")
         rows.append(dict(layer=name, us=round(us, 2), gflop=round(flop / 1e9, 2), tflops=round(tf, 1), frac_peak=round(tf / peak, 3),
                          hbm_gbs=round(byts / us / 1e3, 1), m_tiles=(args.batch * oh * ow + 127) // 128))
         print(f"{name:24s} {us:9.2f} us  {flop / 1e9:8.2f} GFLOP  {tf:8.1f} TFLOP/s  {tf / peak:6.3f} of peak  "
