@@ -1,0 +1,603 @@
+// K3  convolution + folded-BN bias + ReLU as an implicit GEMM on tcgen05 tensor cores.
+//
+// Stands where the reference's Session.run executes the Conv2D/BatchNorm/Relu nodes of its frozen
+// Inception graph (flink-tensorflow-examples/.../inception/InceptionModel.scala:58-67 feeds "input", fetches
+// "output"; flink-tensorflow/.../models/ModelFunction.scala:65 runs it).
+//
+//   D[M = n*OH*OW pixels, N = Cout] = A[M, K = KH*KW*Cin] * B[N, K]^T      (bf16 in, fp32 accumulate)
+//
+// * A is never materialised: for every filter tap (kh, kw) and 64-channel chunk, one TMA *im2col* load
+//   (cp.async.bulk.tensor.4d...im2col) brings the 128 output pixels' input vectors -- zero-filled outside the
+//   image, wrapping across rows and images -- into a 128x64 bf16, 128B-swizzled shared-memory tile.
+// * B (weights, [Cout][KH*KW*Cin], K-major) arrives by a 2-D tiled TMA load into the same swizzle.
+// * One elected thread issues tcgen05.mma (M=128, N=block_n, K=16) with the fp32 accumulator in TMEM; two
+//   accumulator stages let the epilogue of tile i overlap the MMAs of tile i+1.
+// * Epilogue warps read TMEM (tcgen05.ld), add the folded BN bias, apply ReLU, round to bf16 and write
+//   straight into the channel slice of the concat buffer the layer feeds ("segments"); sibling 1x1 branches
+//   that read the same input are one GEMM with several segments.
+// Persistent kernel: grid = min(tiles, SMs); warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM
+// allocator, warps 4-7 = epilogue.
+#include "conv_pm.h"
+#include "ptx.cuh"
+#include <cuda_bf16.h>
+#include <stdlib.h>
+#include <mutex>
+
+namespace ftf {
+namespace pm {
+
+namespace {
+
+constexpr int kBlockM = 128;
+constexpr int kThreads = 256;
+constexpr int kAccStages = 2;
+constexpr int kTmemCols = 512;              // 2 x 256 fp32 columns
+constexpr int kMaxStages = 8;
+
+typedef CUresult (*encode_im2col_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                     const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                     const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                     CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+encode_im2col_fn get_encode_im2col() {
+    static std::once_flag once;
+    static encode_im2col_fn fn = nullptr;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (encode_im2col_fn)p;
+    });
+    return fn;
+}
+
+__device__ unsigned long long g_conv_prof[16];
+
+// mbarrier wait that adds the cycles spent waiting to *acc when profiling
+__device__ __forceinline__ void timed_wait(uint64_t* bar, uint32_t parity, bool prof, long long* acc) {
+    if (!prof) { ptx::mbar_wait(bar, parity); return; }
+    const long long t0 = clock64();
+    ptx::mbar_wait(bar, parity);
+    *acc += clock64() - t0;
+}
+
+__device__ __forceinline__ void tma_load_im2col(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
+                                                int off_w, int off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(
+            ptx::smem_u32(dst)),
+        "l"(m), "r"(ptx::smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+        : "memory");
+}
+
+// K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t smem_desc(uint32_t smem_addr, int row_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);      // start address, 16-byte units
+    d |= (uint64_t)1 << 16;                            // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)((8 * row_bytes) >> 4) << 32;       // stride byte offset: one 8-row group
+    d |= (uint64_t)1 << 46;                            // descriptor version (Blackwell)
+    d |= (uint64_t)(row_bytes == 128 ? 2 : 4) << 61;   // SWIZZLE_128B / SWIZZLE_64B
+    return d;
+}
+// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M x N tile.
+__device__ __forceinline__ uint32_t instr_desc_bf16(int m, int n) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// One 16-column chunk of one accumulator row: bias, ReLU, rounding and the store into the segment that owns
+// GEMM column gc (m = output pixel index, row_ok = the row is a real output).
+__device__ __forceinline__ void epilogue_chunk(const ConvParams& p, int gc, long long m, bool row_ok, const uint32_t (&v)[16]) {
+    int s = 0;
+#pragma unroll
+    for (int q = 1; q < kConvMaxSegments; ++q)
+        if (q < p.n_seg && p.seg[q].col_begin <= gc) s = q;
+    const ConvSegment& sg = p.seg[s];
+    float f[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
+    if (sg.flags & kSegBias) {
+        const float4* bp = reinterpret_cast<const float4*>(p.bias + gc);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float4 b = __ldg(bp + i);
+            f[4 * i] += b.x; f[4 * i + 1] += b.y; f[4 * i + 2] += b.z; f[4 * i + 3] += b.w;
+        }
+    }
+    if (sg.flags & kSegRelu) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.0f);
+    }
+    if (row_ok) {
+        const size_t off = (size_t)m * sg.ld + sg.coff + (gc - sg.col_begin);
+        if (sg.flags & kSegF32) {
+            float4* o = reinterpret_cast<float4*>((float*)sg.out + off);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) o[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+        } else {
+            uint4* o = reinterpret_cast<uint4*>((__nv_bfloat16*)sg.out + off);
+            o[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+            o[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+               const __grid_constant__ ConvParams p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // carve: [stages x (A | B)] [barriers] [tmem slot]
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const int rb = 2 * p.kc;                                   // bytes per operand row
+    const int stage_bytes = p.a_tile_bytes + p.b_stage_bytes;
+    uint64_t* full_bar = (uint64_t*)(smem + (size_t)p.stages * stage_bytes);
+    uint64_t* empty_bar = full_bar + kMaxStages;
+    uint64_t* tmem_full = empty_bar + kMaxStages;
+    uint64_t* tmem_empty = tmem_full + kAccStages;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_empty + kAccStages);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int k_blocks = p.KH * p.KW * p.cin_chunks;
+    const int total_tiles = p.m_tiles * p.n_tiles;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tm_a);
+        ptx::prefetch_tensormap(&tm_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < p.stages; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
+        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], 4); }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ===== TMA producer =====
+        int stage = 0, phase = 0;
+        const bool prof = p.prof != nullptr;
+        long long t_wait = 0;
+        const long long t_begin = prof ? clock64() : 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int m_tile = tile / p.n_tiles, n_tile = tile - m_tile * p.n_tiles;
+            const int m0 = m_tile * kBlockM;
+            const int img = m0 / (p.OH * p.OW);
+            const int rem = m0 - img * (p.OH * p.OW);
+            const int oh = rem / p.OW, ow = rem - oh * p.OW;
+            const int base_w = ow * p.stride - p.pad_w, base_h = oh * p.stride - p.pad_h;
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                const int taps_ = p.KH * p.KW;                     // K order: channel chunk outer, filter tap inner (as in halo mode)
+                const int chunk = kb / taps_, tap = kb - chunk * taps_;
+                const int kh = tap / p.KW, kw = tap - kh * p.KW;
+                timed_wait(&empty_bar[stage], phase ^ 1, prof, &t_wait);
+                uint8_t* a_dst = smem + (size_t)stage * stage_bytes;
+                uint8_t* b_dst = a_dst + p.a_tile_bytes;
+                ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+                tma_load_im2col(a_dst, &tm_a, &full_bar[stage], chunk * p.kc, base_w, base_h, img, kw, kh);
+                ptx::tma_load_2d(b_dst, &tm_b, &full_bar[stage], tap * p.Cin + chunk * p.kc, n_tile * p.block_n);
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+        if (prof) { atomicAdd(&p.prof[0], 1ull); atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[2], (unsigned long long)t_wait); }
+    } else if (warp == 1 && lane == 0) {
+        // ===== MMA issuer =====
+        const uint32_t idesc = instr_desc_bf16(kBlockM, p.block_n);
+        int stage = 0, phase = 0, acc = 0, acc_phase = 0;
+        const bool prof = p.prof != nullptr;
+        long long w_full = 0, w_acc = 0;
+        const long long t_begin = prof ? clock64() : 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            timed_wait(&tmem_empty[acc], acc_phase ^ 1, prof, &w_acc);       // epilogue has drained this accumulator
+            ptx::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
+            for (int kb = 0; kb < k_blocks; ++kb) {
+                timed_wait(&full_bar[stage], phase, prof, &w_full);           // TMA bytes have landed
+                ptx::tc_fence_after();
+                const uint32_t a_addr = ptx::smem_u32(smem + (size_t)stage * stage_bytes);
+                const uint64_t a_desc = smem_desc(a_addr, rb);
+                const uint64_t b_desc = smem_desc(a_addr + p.a_tile_bytes, rb);
+                for (int k = 0; k < p.kc / 16; ++k)             // 32 bytes (two 16-byte units) per K=16 step
+                    ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
+                                   (kb | k) != 0 ? 1u : 0u);
+                ptx::umma_commit(&empty_bar[stage]);               // frees the smem stage when the MMAs retire
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+            ptx::umma_commit(&tmem_full[acc]);                     // accumulator complete -> epilogue
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (prof) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
+    } else if (warp >= 4) {
+        // ===== epilogue: TMEM -> registers -> bias/ReLU -> global =====
+        const int e = warp - 4;                                    // TMEM lane quarter of this warp
+        const int row = e * 32 + lane;
+        int acc = 0, acc_phase = 0;
+        const bool prof = p.prof != nullptr && threadIdx.x == 128;
+        long long w_epi = 0, n_tiles_done = 0;
+        const long long t_begin = prof ? clock64() : 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            ++n_tiles_done;
+            const int m_tile = tile / p.n_tiles, n_tile = tile - m_tile * p.n_tiles;
+            const long long m = (long long)m_tile * kBlockM + row;
+            const bool row_ok = m < p.M;
+            timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
+            ptx::tc_fence_after();
+            const uint32_t t_row = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(e * 32) << 16);
+            for (int col = 0; col < p.block_n; col += 16) {
+                const int gc = n_tile * p.block_n + col;
+                if (gc >= p.N_total) break;                        // warp-uniform
+                uint32_t v[16];
+                tmem_ld_x16(t_row + (uint32_t)col, v);
+                ptx::tmem_ld_wait();
+                epilogue_chunk(p, gc, m, row_ok, v);
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+            if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (prof) { atomicAdd(&p.prof[6], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[7], (unsigned long long)w_epi); atomicAdd(&p.prof[8], (unsigned long long)n_tiles_done); }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Halo mode: stride-1 KxK convolutions.
+//
+// Index outputs by the PADDED-linear position q = (img*Hp + hp)*Wp + wp (Hp = H + 2*pad_h, Wp = W + 2*pad_w); the
+// real outputs are those with hp < OH and wp < OW, the rest (KW-1 columns per row, KH-1 rows per image) are computed
+// and dropped.  In that index space filter tap (kh, kw) of output q reads padded-input pixel q + kh*Wp + kw: a pure
+// row shift.  So a CTA tile of T = 128*S consecutive q needs ONE window of T + (KH-1)*Wp + (KW-1) padded-input pixels
+// per 64-channel chunk -- fetched once by TMA im2col loads over the padded bounding box (zeros in the padding,
+// wrapping rows and images) -- and every tap's A operand is the same 128B-swizzled buffer entered at a different
+// row: the UMMA descriptor's start address moves by (kh*Wp + kw)*128 bytes (the swizzle is address based, see
+// tools/probe_umma_shift.cu).  L2->SM operand traffic drops from KH*KW reads of every input pixel to about one,
+// and the weight tiles are shared by S sub-tiles.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1)
+conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                 const __grid_constant__ ConvParams p) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    constexpr int kAStages = 2;
+    uint8_t* a_base = smem;
+    const int rb = 2 * p.kc;
+    uint8_t* b_base = smem + (size_t)kAStages * p.a_stage_bytes;
+    uint64_t* a_full = (uint64_t*)(b_base + (size_t)p.b_stages * p.b_stage_bytes);
+    uint64_t* a_empty = a_full + kAStages;
+    uint64_t* b_full = a_empty + kAStages;
+    uint64_t* b_empty = b_full + kMaxStages;
+    uint64_t* tmem_full = b_empty + kMaxStages;
+    uint64_t* tmem_empty = tmem_full + kAccStages;
+    uint32_t* tmem_slot = (uint32_t*)(tmem_empty + kAccStages);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int taps = p.KH * p.KW;
+    const int T = p.S * kBlockM;
+    const int q_tiles = (int)((p.Q + T - 1) / T);
+    const int total_tiles = q_tiles * p.n_tiles;
+    const int acc_cols = p.S * p.block_n;
+
+    if (warp == 0 && lane == 0) {
+        ptx::prefetch_tensormap(&tm_a);
+        ptx::prefetch_tensormap(&tm_b);
+    }
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kAStages; ++s) { ptx::mbar_init(&a_full[s], 1); ptx::mbar_init(&a_empty[s], 1); }
+        for (int s = 0; s < p.b_stages; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
+        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], 4); }
+        ptx::fence_mbar_init();
+    }
+    if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_slot);
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0 && lane == 0) {
+        // ===== TMA producer =====
+        int as = 0, aph = 0, bs = 0, bph = 0;
+        const bool prof = p.prof != nullptr;
+        long long t_wait = 0;
+        const long long t_begin = prof ? clock64() : 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int q_tile = tile / p.n_tiles, n_tile = tile - q_tile * p.n_tiles;
+            const long long q0 = (long long)q_tile * T;
+            for (int chunk = 0; chunk < p.cin_chunks; ++chunk) {
+                timed_wait(&a_empty[as], aph ^ 1, prof, &t_wait);
+                uint8_t* a_dst = a_base + (size_t)as * p.a_stage_bytes;
+                ptx::mbar_expect_tx(&a_full[as], (uint32_t)p.a_stage_bytes);
+                for (int i = 0; i < p.a_loads; ++i) {           // the window, kHaloLoadRows padded pixels per load
+                    const long long q = q0 + (long long)i * kHaloLoadRows;
+                    const int wp = (int)(q % p.Wp);
+                    const long long t = q / p.Wp;
+                    const int hp = (int)(t % p.Hp);
+                    const int img = (int)(t / p.Hp);
+                    tma_load_im2col(a_dst + (size_t)i * kHaloLoadRows * rb, &tm_a, &a_full[as], chunk * p.kc, wp - p.pad_w,
+                                    hp - p.pad_h, img, 0, 0);
+                }
+                for (int tap = 0; tap < taps; ++tap) {
+                    timed_wait(&b_empty[bs], bph ^ 1, prof, &t_wait);
+                    ptx::mbar_expect_tx(&b_full[bs], (uint32_t)p.b_stage_bytes);
+                    ptx::tma_load_2d(b_base + (size_t)bs * p.b_stage_bytes, &tm_b, &b_full[bs], tap * p.Cin + chunk * p.kc,
+                                     n_tile * p.block_n);
+                    if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
+                }
+                if (++as == kAStages) { as = 0; aph ^= 1; }
+            }
+        }
+        if (prof) { atomicAdd(&p.prof[0], 1ull); atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[2], (unsigned long long)t_wait); }
+    } else if (warp == 1 && lane == 0) {
+        // ===== MMA issuer =====
+        const uint32_t idesc = instr_desc_bf16(kBlockM, p.block_n);
+        int as = 0, aph = 0, bs = 0, bph = 0, acc = 0, acc_phase = 0;
+        const bool prof = p.prof != nullptr;
+        long long w_full = 0, w_acc = 0;
+        const long long t_begin = prof ? clock64() : 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            timed_wait(&tmem_empty[acc], acc_phase ^ 1, prof, &w_acc);
+            ptx::tc_fence_after();
+            const uint32_t d_tmem = tmem_base + (uint32_t)(acc * acc_cols);
+            for (int chunk = 0; chunk < p.cin_chunks; ++chunk) {
+                timed_wait(&a_full[as], aph, prof, &w_full);
+                ptx::tc_fence_after();
+                const uint32_t a_addr = ptx::smem_u32(a_base + (size_t)as * p.a_stage_bytes);
+                for (int tap = 0; tap < taps; ++tap) {
+                    const int kh = tap / p.KW, kw = tap - kh * p.KW;
+                    timed_wait(&b_full[bs], bph, prof, &w_full);
+                    ptx::tc_fence_after();
+                    const uint64_t b_desc = smem_desc(ptx::smem_u32(b_base + (size_t)bs * p.b_stage_bytes), rb);
+                    const uint32_t first = (chunk | tap) != 0 ? 1u : 0u;
+                    for (int s = 0; s < p.S; ++s) {
+                        // tap (kh, kw) of sub-tile s: the window entered (s*128 + kh*Wp + kw) rows further down
+                        const uint64_t a_desc = smem_desc(a_addr + (uint32_t)(s * kBlockM + kh * p.Wp + kw) * (uint32_t)rb, rb);
+                        for (int k = 0; k < p.kc / 16; ++k)
+                            ptx::umma_bf16(d_tmem + (uint32_t)(s * p.block_n), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k),
+                                           idesc, (first | (uint32_t)k) != 0 ? 1u : 0u);
+                    }
+                    ptx::umma_commit(&b_empty[bs]);
+                    if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
+                }
+                ptx::umma_commit(&a_empty[as]);
+                if (++as == kAStages) { as = 0; aph ^= 1; }
+            }
+            ptx::umma_commit(&tmem_full[acc]);
+            if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (prof) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
+    } else if (warp >= 4) {
+        // ===== epilogue =====
+        const int e = warp - 4;
+        const int row = e * 32 + lane;
+        int acc = 0, acc_phase = 0;
+        const bool prof = p.prof != nullptr && threadIdx.x == 128;
+        long long w_epi = 0, n_tiles_done = 0;
+        const long long t_begin = prof ? clock64() : 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            ++n_tiles_done;
+            const int q_tile = tile / p.n_tiles, n_tile = tile - q_tile * p.n_tiles;
+            timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
+            ptx::tc_fence_after();
+            for (int s = 0; s < p.S; ++s) {
+                const long long q = (long long)q_tile * T + s * kBlockM + row;
+                const int wp = (int)(q % p.Wp);
+                const long long t = q / p.Wp;
+                const int hp = (int)(t % p.Hp);
+                const long long img = t / p.Hp;
+                const bool row_ok = q < p.Q && wp < p.OW && hp < p.OH;
+                const long long m = (img * p.OH + hp) * p.OW + wp;
+                const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + s * p.block_n) + ((uint32_t)(e * 32) << 16);
+                for (int col = 0; col < p.block_n; col += 16) {
+                    const int gc = n_tile * p.block_n + col;
+                    if (gc >= p.N_total) break;
+                    uint32_t v[16];
+                    tmem_ld_x16(t_row + (uint32_t)col, v);
+                    ptx::tmem_ld_wait();
+                    epilogue_chunk(p, gc, m, row_ok, v);
+                }
+            }
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+            if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1; }
+        }
+        if (prof) { atomicAdd(&p.prof[6], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[7], (unsigned long long)w_epi); atomicAdd(&p.prof[8], (unsigned long long)n_tiles_done); }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+}
+
+}  // namespace
+
+int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan, std::string* err,
+         double* est_cycles, bool may_use_halo) {
+    auto bad = [&](const std::string& m) { if (err) *err = "conv_pm plan: " + m; return FTF_INVALID_ARGUMENT; };
+    if (n_seg < 1 || n_seg > kConvMaxSegments) return bad("segment count");
+    if (g.Cin % 8 || g.in_ld % 8 || g.Cout % 16) return bad("Cin and the input row stride must be multiples of 8, Cout of 16");
+    if (((uintptr_t)g.in | (uintptr_t)g.weights) & 15) return bad("unaligned tensor base");
+    const int OH = (g.H + 2 * g.pad_h - g.KH) / g.stride + 1, OW = (g.W + 2 * g.pad_w - g.KW) / g.stride + 1;
+    if (OH <= 0 || OW <= 0) return bad("empty output");
+    for (int i = 0; i < n_seg; ++i)
+        if (segs[i].col_begin % 16 || segs[i].coff % 8 || segs[i].ld % 8 || (i && segs[i].col_begin <= segs[i - 1].col_begin))
+            return bad("segment alignment / order");
+    auto enc_tiled = get_tensor_map_encode_tiled();
+    auto enc_im2col = get_encode_im2col();
+    if (!enc_tiled || !enc_im2col) { if (err) *err = "cuTensorMapEncode* entry points not found"; return FTF_INTERNAL; }
+
+    ConvParams& p = plan->p;
+    p = ConvParams{};
+    p.OH = OH; p.OW = OW; p.stride = g.stride; p.pad_h = g.pad_h; p.pad_w = g.pad_w; p.KH = g.KH; p.KW = g.KW;
+    p.Cin = g.Cin;
+    p.N_total = g.Cout;
+    p.M = g.n_max * OH * OW;
+    p.m_tiles = (p.M + kBlockM - 1) / kBlockM;
+    p.bias = g.bias;
+    p.n_seg = n_seg;
+    for (int i = 0; i < n_seg; ++i) p.seg[i] = segs[i];
+    plan->grid = sm_count;
+    static const bool want_prof = getenv("FTF_CONV_PROFILE") && getenv("FTF_CONV_PROFILE")[0] == '1';
+    if (want_prof) {
+        void* sym = nullptr;
+        if (cudaGetSymbolAddress(&sym, g_conv_prof) == cudaSuccess) p.prof = (unsigned long long*)sym; else cudaGetLastError();
+    }
+    // ---- tile shape: (N tile, im2col or halo window with S sub-tiles) that minimises
+    //      waves x (max(MMA cycles, operand bytes / per-SM fill bandwidth) + fixed cost).  Every tcgen05.mma with
+    //      M = 128 costs about 128 cycles whatever N is (measured), so fewer, wider N tiles are cheaper. ----
+    const bool env_halo = !(getenv("FTF_NO_HALO") && getenv("FTF_NO_HALO")[0] == '1');
+    const bool allow_halo = env_halo && may_use_halo;
+    const int taps = g.KH * g.KW;
+    const int Hp = g.H + 2 * g.pad_h, Wp = g.W + 2 * g.pad_w;
+    const int halo = (g.KH - 1) * Wp + (g.KW - 1);
+    const long long Q = (long long)g.n_max * Hp * Wp;
+    static const bool allow_kc32 = !(getenv("FTF_NO_KC32") && getenv("FTF_NO_KC32")[0] == '1');
+    const double kFill = 36.0, kFixed = 2500.0;
+    const long long kSmem = 208 * 1024;
+    double best = -1.0;
+    for (int kc = 64; kc >= 32; kc -= 32) {
+        const int chunks = (g.Cin + kc - 1) / kc, rb = 2 * kc, ksteps = kc / 16;
+        // 32-channel K blocks exactly when they save MMAs (Cin % 64 in 1..32): a fixed rule, so that every candidate
+        // kernel of a layer walks K in the same order and produces the same bits
+        const bool kc32_saves = allow_kc32 && ((g.Cin + 31) / 32) * 2 < ((g.Cin + 63) / 64) * 4;
+        if ((kc == 32) != kc32_saves) continue;
+        const double real_frac = (double)g.Cin / (chunks * kc);
+        const long long a_tile = (long long)kBlockM * rb;
+        for (int nt = (g.Cout + 255) / 256; nt <= (g.Cout + 31) / 32; ++nt) {
+            const int bn = ((g.Cout + nt - 1) / nt + 15) / 16 * 16;
+            if (bn > 256) continue;
+            const int tiles_n = (g.Cout + bn - 1) / bn;
+            const long long b_bytes = (long long)bn * rb;
+            {   // one im2col load per tap
+                const long long tiles = (long long)p.m_tiles * tiles_n, waves = (tiles + sm_count - 1) / sm_count;
+                const double cyc = (double)taps * chunks * ksteps * 128.0, bytes = (double)taps * chunks * (a_tile + b_bytes) * real_frac;
+                const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
+                if (best < 0 || t < best) {
+                    best = t; p.halo_mode = 0; p.block_n = bn; p.n_tiles = tiles_n; p.kc = kc; p.cin_chunks = chunks;
+                    p.a_tile_bytes = (int)a_tile; p.b_stage_bytes = (int)b_bytes;
+                }
+            }
+            if (!(allow_halo && g.stride == 1 && taps > 1)) continue;
+            for (int S = 1; S <= 4; S *= 2) {
+                if (2 * S * bn > kTmemCols) continue;                  // keep two accumulator sets: epilogue overlaps the next tile
+                const int T = S * kBlockM;
+                const int loads = (T + halo + kHaloLoadRows - 1) / kHaloLoadRows;
+                const long long a_bytes = (long long)loads * kHaloLoadRows * rb;
+                const long long room = kSmem - 2 * a_bytes;
+                if (room < 2 * b_bytes) continue;
+                const long long tiles = (Q + T - 1) / T * tiles_n, waves = (tiles + sm_count - 1) / sm_count;
+                const double cyc = (double)chunks * taps * S * ksteps * 128.0;
+                const double bytes = chunks * (a_bytes + (double)taps * b_bytes) * real_frac;
+                const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
+                if (t < best) {
+                    best = t;
+                    p.halo_mode = 1; p.Hp = Hp; p.Wp = Wp; p.Q = Q; p.S = S; p.block_n = bn; p.n_tiles = tiles_n; p.kc = kc; p.cin_chunks = chunks;
+                    p.a_loads = loads; p.a_stage_bytes = (int)a_bytes; p.b_stage_bytes = (int)b_bytes;
+                    p.b_stages = (int)(room / b_bytes > kMaxStages ? kMaxStages : room / b_bytes);
+                    p.acc_stages = 2;
+                }
+            }
+        }
+    }
+    if (est_cycles) *est_cycles = best;
+    if (p.halo_mode) {
+        plan->smem = 2 * (size_t)p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + 1024 + 512;
+    } else {
+        const int stage_bytes = p.a_tile_bytes + p.b_stage_bytes;
+        p.stages = (200 * 1024) / stage_bytes;
+        if (p.stages > kMaxStages) p.stages = kMaxStages;
+        plan->smem = (size_t)p.stages * stage_bytes + 1024 /*alignment slack*/ + 256 /*barriers*/;
+    }
+
+    const CUtensorMapSwizzle swz = p.kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    // A: NHWC input seen through an im2col window. dims fastest-first {C, W, H, N}.
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)g.Cin, (cuuint64_t)g.W, (cuuint64_t)g.H, (cuuint64_t)g.n_max};
+        cuuint64_t strides[3] = {(cuuint64_t)g.in_ld * 2, (cuuint64_t)g.W * g.in_ld * 2, (cuuint64_t)g.H * g.W * g.in_ld * 2};
+        int lower[2] = {-g.pad_w, -g.pad_h};
+        int upper[2] = {g.pad_w - (g.KW - 1), g.pad_h - (g.KH - 1)};
+        if (p.halo_mode) { upper[0] = g.pad_w; upper[1] = g.pad_h; }      // the whole padded image, one pixel per "filter"
+        cuuint32_t estr[4] = {1, (cuuint32_t)g.stride, (cuuint32_t)g.stride, 1};
+        CUresult rc = enc_im2col(&plan->tm_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, (void*)g.in, dims, strides, lower, upper,
+                                 (cuuint32_t)p.kc, p.halo_mode ? kHaloLoadRows : kBlockM, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (rc != CUDA_SUCCESS) { if (err) *err = "cuTensorMapEncodeIm2col failed, code " + std::to_string((int)rc); return FTF_INTERNAL; }
+    }
+    // B: weights [Cout][K] with K = KH*KW*Cin contiguous.
+    {
+        const cuuint64_t K = (cuuint64_t)g.KH * g.KW * g.Cin;
+        cuuint64_t dims[2] = {K, (cuuint64_t)g.Cout};
+        cuuint64_t strides[1] = {K * 2};
+        cuuint32_t box[2] = {(cuuint32_t)p.kc, (cuuint32_t)p.block_n};
+        cuuint32_t estr[2] = {1, 1};
+        CUresult rc = enc_tiled(&plan->tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)g.weights, dims, strides, box, estr,
+                                CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (rc != CUDA_SUCCESS) { if (err) *err = "cuTensorMapEncodeTiled (weights) failed, code " + std::to_string((int)rc); return FTF_INTERNAL; }
+    }
+    static std::once_flag attr_once;
+    static cudaError_t attr_rc = cudaSuccess;
+    std::call_once(attr_once, [] {
+        attr_rc = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    });
+    // the attribute is per device: set it again when planning on another device
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc_kernel)", err);
+    e = cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_halo_kernel)", err);
+    return FTF_OK;
+}
+
+int profile_read(unsigned long long* out16, int reset) {
+    if (cudaMemcpyFromSymbol(out16, g_conv_prof, sizeof(unsigned long long) * 16) != cudaSuccess) { cudaGetLastError(); return FTF_INTERNAL; }
+    if (reset) {
+        unsigned long long zero[16] = {0};
+        if (cudaMemcpyToSymbol(g_conv_prof, zero, sizeof(zero)) != cudaSuccess) { cudaGetLastError(); return FTF_INTERNAL; }
+    }
+    return FTF_OK;
+}
+
+int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err) {
+    ConvParams p = plan.p;
+    p.M = n * p.OH * p.OW;
+    if (p.M <= 0) return FTF_OK;
+    p.m_tiles = (p.M + kBlockM - 1) / kBlockM;
+    if (p.halo_mode) {
+        p.Q = (long long)n * p.Hp * p.Wp;
+        const int T = p.S * kBlockM;
+        const long long tiles = (p.Q + T - 1) / T * p.n_tiles;
+        const int grid = (int)(tiles < plan.grid ? tiles : plan.grid);
+        conv_halo_kernel<<<grid, kThreads, plan.smem, s>>>(plan.tm_a, plan.tm_b, p);
+        count_launch();
+        FTF_CUDA(cudaGetLastError(), err);
+        return FTF_OK;
+    }
+    const int tiles = p.m_tiles * p.n_tiles;
+    const int grid = tiles < plan.grid ? tiles : plan.grid;
+    conv_tc_kernel<<<grid, kThreads, plan.smem, s>>>(plan.tm_a, plan.tm_b, p);
+    count_launch();
+    FTF_CUDA(cudaGetLastError(), err);
+    return FTF_OK;
+}
+
+}  // namespace pm
+}  // namespace ftf

@@ -1,74 +1,36 @@
-// conv_tc.h -- implicit-GEMM convolution on the 5th-generation tensor cores (tcgen05 + TMEM + TMA im2col).
+// conv_tc.h -- the tensor-core convolution (K3): plan once per layer, launch per batch.
+//
+// Two kernels share the work (conv_pm.cu, conv_wm.cu):
+//  * pixel-major  (pm): 128 pixels on the UMMA M side, output channels on the N side.  Cheap epilogue (a thread owns a
+//    pixel and stores 16-byte channel runs), but every MMA costs ~128 cycles whatever N is, so the tensor pipe runs at
+//    Cout_tile/256 of its rate.
+//  * weight-major (wm): 128 output channels on the M side, up to 256 pixels on the N side: full MMA rate for Cout >= 128
+//    and twice the pm rate for Cout <= 128; the epilogue (a thread owns a channel, 2-byte stores) costs ~11 issue slots
+//    per pixel, so it only pays when K is large.
+// Each has an im2col mode and a halo-window mode.  The plan keeps the fastest candidate: timed on the layer's own buffers
+// when `tune` is set (network build), else by a cycle model.
 #pragma once
-#include "common.h"
-#include <string>
+#include "conv_pm.h"
+#include "conv_wm.h"
 
 namespace ftf {
 
-constexpr int kConvMaxSegments = 6;
-
-// Where a range of output channels (GEMM columns) goes.  Column ranges start at multiples of 16.
-struct ConvSegment {
-    void* out;        // base of the destination tensor [M, ld]
-    int ld;           // destination row stride in elements (channels of the concat buffer)
-    int coff;         // channel offset inside the destination row
-    int col_begin;    // first GEMM column of this segment
-    int flags;        // kSegBiasRelu | kSegF32
-};
-enum { kSegBias = 1, kSegRelu = 2, kSegF32 = 4 };
-
-struct ConvParams {
-    int M;                      // output pixels = n * OH * OW
-    int OH, OW;
-    int stride, pad_h, pad_w, KH, KW;
-    int Cin, cin_chunks;        // cin_chunks = ceil(Cin / 64)
-    int N_total;                // output channels (GEMM N)
-    int block_n;                // N tile: multiple of 16, <= 256
-    int m_tiles, n_tiles;
-    int stages;                 // smem pipeline depth
-    int b_stage_bytes;          // block_n * 128
-    const float* bias;          // [N_total]
-    int n_seg;
-    ConvSegment seg[kConvMaxSegments];
-    // ---- halo mode (stride-1 KxK): one shared-memory window of the padded input serves every filter tap ----
-    int halo_mode;              // 0: one im2col load per tap (any stride); 1: halo window
-    int Hp, Wp;                 // padded input extent: H + 2*pad_h, W + 2*pad_w
-    long long Q;                // virtual outputs = n * Hp * Wp (valid where hp < OH and wp < OW)
-    int S;                      // 128-row sub-tiles per CTA tile
-    int a_loads;                // im2col loads of kHaloLoadRows rows that fill one window
-    int a_stage_bytes;          // a_loads * kHaloLoadRows * 128
-    int b_stages;               // weight-tile ring depth
-    int acc_stages;             // 1 or 2 TMEM accumulator sets of S * block_n columns
-    unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
-};
-
-constexpr int kHaloLoadRows = 64;
-
 struct ConvPlan {
-    CUtensorMap tm_a;           // im2col view of the NHWC input
-    CUtensorMap tm_b;           // weights [Cout, KH*KW*Cin] K-major
-    ConvParams p;
-    int grid;
-    size_t smem;
-};
-
-struct ConvGeometry {
-    const void* in;             // bf16 NHWC [n_max, H, W, in_ld]; channels [0, Cin) are convolved
-    int n_max, H, W, Cin, in_ld;
-    const void* weights;        // bf16 [Cout][KH][KW][Cin]
-    const float* bias;          // fp32 [Cout]
-    int Cout, KH, KW, stride, pad_h, pad_w;
+    int kind;                   // 0 = pixel-major, 1 = weight-major
+    double est_cycles;          // modelled cycles of the chosen kernel
+    pm::ConvPlan pm;
+    wm::ConvPlan wm;
 };
 
 // Encodes the tensor maps and tile shapes for one convolution (called once, at network build).
+// tune: time the candidate kernels (pixel-/weight-major, with and without the halo window) on the layer's own buffers
+// for n_max images and keep the fastest; otherwise the cycle model decides.  Every candidate accumulates K in the same
+// order (channel chunk, filter tap, 16-element step).
 int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
-                 std::string* err);
+                 std::string* err, bool tune = false);
 // Enqueues the convolution for the first n images.
 int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err);
-// Diagnostic: copies (and optionally clears) the 16 pipeline cycle counters the kernels accumulate when the
-// environment has FTF_CONV_PROFILE=1: [0] CTAs, [1] producer cycles, [2] producer waiting for free stages,
-// [3] MMA-issuer cycles, [4] waiting for operands, [5] waiting for a drained accumulator, [6] epilogue cycles,
-// [7] epilogue waiting for an accumulator, [8] tiles.
+// Diagnostic cycle counters of both kernels, summed (see conv_pm.h).
 int conv_tc_profile_read(unsigned long long* out16, int reset);
 
 }  // namespace ftf

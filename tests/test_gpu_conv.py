@@ -99,6 +99,33 @@ def test_conv_tc_is_batch_independent(dev, oracle):
         assert torch.equal(one[0], full[i])
 
 
+def test_conv_variants_agree(dev, monkeypatch):
+    """The plan may pick either kernel (pixel-major / weight-major), with or without the halo window.  All of them
+    accumulate K in the same order (channel chunk, filter tap, 16-element step): the halo window changes nothing in a
+    kernel's result, and the two kernels agree to fp32 accumulation rounding."""
+    import torch
+    rng = np.random.default_rng(21)
+    for (n, h, w, cin, cout, kh, kw, ph, pw) in [(2, 35, 35, 96, 96, 3, 3, 1, 1), (2, 17, 17, 160, 192, 7, 1, 3, 0),
+                                                   (2, 19, 19, 32, 64, 3, 3, 1, 1), (3, 8, 8, 448, 384, 3, 3, 1, 1)]:
+        x = _to_bf16_cuda(rng.standard_normal((n, h, w, cin)))
+        wt = _to_bf16_cuda(rng.standard_normal((cout, kh, kw, cin)) * np.sqrt(2.0 / (kh * kw * cin)))
+        b = torch.from_numpy(rng.uniform(-0.1, 0.1, cout).astype(np.float32)).cuda()
+        outs = {}
+        for kind in ("pm", "wm"):
+            for no_halo in ("1", "0"):
+                monkeypatch.setenv("FTF_CONV_KIND", kind)
+                monkeypatch.setenv("FTF_NO_HALO", no_halo)
+                monkeypatch.setenv("FTF_CONV_TUNE", "0")
+                outs[(kind, no_halo)] = dev.conv2d_bf16(x, wt, b, 1, (ph, pw), out_dtype=torch.float32).clone()
+        for k in ("FTF_CONV_KIND", "FTF_NO_HALO", "FTF_CONV_TUNE"):
+            monkeypatch.delenv(k)
+        scale = float(outs[("pm", "1")].abs().max())
+        diffs = {k: float((v - outs[("pm", "1")]).abs().max()) / scale for k, v in outs.items()}
+        assert torch.equal(outs[("pm", "0")], outs[("pm", "1")]), diffs
+        assert torch.equal(outs[("wm", "0")], outs[("wm", "1")]), diffs
+        assert diffs[("wm", "1")] <= 1e-5, diffs
+
+
 def test_pool_kernels_match_oracle(dev, oracle):
     """K4 max pool, K5 pool branch, K6 global average pool on bf16 tensors."""
     import torch
