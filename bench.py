@@ -177,6 +177,59 @@ def pinned_array(lib, np, nbytes, dtype):
     return p, np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,)).view(dtype)
 
 
+def streaming_bench(ftf, lib, np, device, n_records=64 * 40):
+    """BASELINE config 5 on one GPU: raw 640x480 RGB records through ftf_submit/ftf_poll (normalise -> Inception-v3 ->
+    top-5 on the device, micro-batches of 64, 2 ms deadline), at saturation; latency = submit -> result polled."""
+    from flink_tensorflow_b200.host import _as_ftf, FtfTensor, _check
+    cfg = ftf.default_config(device=device, max_batch=INC["batch"], max_delay_us=2000, top_k=INC["top_k"], out_h=299, out_w=299,
+                             mean=128.0, scale=128.0, num_classes=INC["classes"], seed=INC["seed"])
+    r = ftf.Runner("builtin:normalize_label", None, None, cfg)
+    rec_bytes = 480 * 640 * 3
+    n_buf = 4 * INC["batch"]                                   # records stay untouched until polled: a ring of pinned payloads
+    p, ring = pinned_array(lib, np, n_buf * rec_bytes, np.uint8)
+    ring[:] = np.random.default_rng(3).integers(0, 256, ring.size, dtype=np.uint8)
+    dims = (C.c_int64 * 3)(480, 640, 3)
+    recs = [FtfTensor(ftf.DataType.UINT8, 3, dims, ring.ctypes.data + i * rec_bytes, rec_bytes) for i in range(n_buf)]
+    keys = (C.c_char_p * 2)(b"top_k_indices", b"top_k_scores")
+    tags = (C.c_uint64 * 256)()
+    outs = (FtfTensor * 512)()
+    n_ready = C.c_int32()
+    done = 0
+
+    def drain(block):
+        nonlocal done
+        _check(lib.ftf_poll(r.handle, 1 if block else 0, tags, outs, 256, C.byref(n_ready)), r.handle)
+        done += n_ready.value
+    # warm-up (graph capture, allocations)
+    for i in range(2 * INC["batch"]):
+        _check(lib.ftf_submit(r.handle, i, C.byref(recs[i % n_buf])), r.handle)
+        if i == 0:
+            _check(lib.ftf_poll_select(r.handle, 2, keys), r.handle)
+    _check(lib.ftf_flush(r.handle), r.handle)
+    while done < 2 * INC["batch"]:
+        drain(True)
+    done = 0
+    r2 = r.stats()
+    t0 = time.perf_counter()
+    for i in range(n_records):
+        while i - done >= n_buf - INC["batch"]:                # back-pressure: never overwrite an unpolled record
+            drain(True)
+        _check(lib.ftf_submit(r.handle, i, C.byref(recs[i % n_buf])), r.handle)
+        if i % 16 == 15:
+            drain(False)
+    _check(lib.ftf_flush(r.handle), r.handle)
+    while done < n_records:
+        drain(True)
+    dt = time.perf_counter() - t0
+    st = r.stats()
+    r.close()
+    lib.ftf_host_free(p)
+    return {"records_per_s": n_records / dt, "records": n_records, "latency_us_p50": st["queue_latency_us_p50"],
+            "latency_us_p99": st["queue_latency_us_p99"], "max_batch": INC["batch"], "max_delay_us": 2000,
+            "h2d_bytes_per_record": rec_bytes, "pipeline": "u8 640x480 RGB -> resize+normalise (bf16) -> Inception-v3 -> softmax/top-5",
+            "api": "ftf_submit/ftf_poll, pinned record payloads", "launches": int(st["kernel_launches"] - r2["kernel_launches"])}
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -201,12 +254,10 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    from flink_tensorflow_b200 import sharding
+
     def max_over_ranks(ms):
-        if world == 1:
-            return ms
-        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        return sharding.max_over_ranks(ms, device="cuda")
 
     from flink_tensorflow_b200.host import _check as _chk
     launches0 = lib.ftf_launch_count()
@@ -336,6 +387,8 @@ def run_ours(args):
     r.close()
     lib.ftf_host_free(p)
 
+    if wl == "inception":
+        extra["streaming"] = streaming_bench(ftf, lib, np, local_rank)
     if rank != 0:
         return
     # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -----------------------------------------
@@ -390,11 +443,17 @@ def run_ours(args):
             cpu = {"value": b * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
                    "sample": f"{reps} passes over 32 images (1/8 of the batch), all host threads"}
 
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(wl, {}).get("dram_bytes_per_launch")
+    except Exception:
+        pass
     line = {"metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype,
             "data": "synthetic", "config": config,
             "roofline": {"bound": bound, "achieved": achieved, "peak": peak, "unit": peak_unit, "frac": achieved / peak,
-                         "traffic": None, "peak_source": pk["src"] + (" (sustained)" if wl == "inception" else ""),
+                         "traffic": traffic, "peak_source": pk["src"] + (" (sustained)" if wl == "inception" else ""),
                          **({"frac_of_nominal_8TBps": achieved / 8000.0} if wl != "inception" else
                             {"frac_of_burst": achieved / pk["tf_burst"], "scope": "whole step (all kernels), algorithmic FLOPs"}),
                          "kernel_ms": ms_step},

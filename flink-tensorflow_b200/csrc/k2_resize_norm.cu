@@ -26,6 +26,10 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kMaxBandRows = 64;   // output rows per band upper bound (row tables in smem)
+constexpr int kCols = 4;           // output columns a thread carries through a band
+
+// exact u8 -> f32 without the quarter-rate I2F: 2^23 + b has b in its low mantissa bits
+__device__ __forceinline__ float u8_to_f32(uint8_t b) { return __fsub_rn(__uint_as_float(0x4B000000u | (uint32_t)b), 8388608.0f); }
 
 struct ResizeParams {
     int in_h, in_w, out_h, out_w;
@@ -52,67 +56,94 @@ __device__ __forceinline__ float finish(float top, float bot, float yl, const Re
 }
 
 // ---- TMA-staged band kernel -------------------------------------------------------------------
+// Persistent: a CTA walks bands blockIdx.x, blockIdx.x + gridDim.x, ... with two shared-memory stages, so the TMA
+// fetch of the next band is in flight while the current band is interpolated and stored.
 template <bool kMulRecip, typename OutT>
-__global__ void __launch_bounds__(kThreads)
-resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p) {
+__global__ void __launch_bounds__(kThreads, 4)
+resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p, long long total_bands,
+                     int stage_bytes) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bar;
+    __shared__ __align__(8) uint64_t bar[2];
     __shared__ int row_lo[kMaxBandRows], row_hi[kMaxBandRows];
     __shared__ float row_l[kMaxBandRows];
 
-    const long long blk = blockIdx.x;
-    const long long img = blk / p.bands;
-    const int band = (int)(blk - img * p.bands);
-    const int oy0 = band * p.th;
-    const int rows = min(p.th, p.out_h - oy0);
-    const int iy0 = (int)__fmul_rn((float)oy0, p.hs);  // first input row of the band
+    auto issue = [&](long long blk, int stage) {       // one thread: fetch the input rows of band `blk`
+        const long long img = blk / p.bands;
+        const int band = (int)(blk - img * p.bands);
+        const int iy0 = (int)__fmul_rn((float)(band * p.th), p.hs);
+        ptx::mbar_expect_tx(&bar[stage], (uint32_t)(p.n_chunks * p.cw * p.br));
+        for (int k = 0; k < p.n_chunks; ++k)
+            ptx::tma_load_3d(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, &tmap, &bar[stage], k * p.cw, iy0, (int)img);
+    };
 
     if (threadIdx.x == 0) {
-        ptx::mbar_init(&bar, 1);
+        ptx::mbar_init(&bar[0], 1);
+        ptx::mbar_init(&bar[1], 1);
         ptx::fence_mbar_init();
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        ptx::mbar_expect_tx(&bar, (uint32_t)(p.n_chunks * p.cw * p.br));
-        for (int k = 0; k < p.n_chunks; ++k)
-            ptx::tma_load_3d(smem + (size_t)k * p.chunk_stride, &tmap, &bar, k * p.cw, iy0, (int)img);
-    }
-    // per-row interpolation table while the copy is in flight
-    if (threadIdx.x < rows) {
-        const float py = __fmul_rn((float)(oy0 + threadIdx.x), p.hs);
-        const int lo = (int)py;
-        const int hi = min(lo + 1, p.in_h - 1);
-        row_lo[threadIdx.x] = (lo - iy0) * p.cw;
-        row_hi[threadIdx.x] = (hi - iy0) * p.cw;
-        row_l[threadIdx.x] = __fsub_rn(py, (float)lo);
-    }
-    __syncthreads();
+    if (threadIdx.x == 0 && (long long)blockIdx.x < total_bands) issue(blockIdx.x, 0);
 
     const int ow3 = p.out_w * 3;
-    OutT* obase = out + ((size_t)img * p.out_h + oy0) * ow3;
-    bool waited = false;
-    for (int col = threadIdx.x; col < ow3; col += kThreads) {
-        const int px = col / 3, c = col - px * 3;
-        const float fx = __fmul_rn((float)px, p.ws);
-        const int lo = (int)fx;
-        const int hi = min(lo + 1, p.in_w - 1);
-        const float xl = __fsub_rn(fx, (float)lo);
-        const int blo = lo * 3 + c, bhi = hi * 3 + c;
-        const int klo = blo / p.cw, khi = bhi / p.cw;
-        const uint8_t* s_lo = smem + (size_t)klo * p.chunk_stride + (blo - klo * p.cw);
-        const uint8_t* s_hi = smem + (size_t)khi * p.chunk_stride + (bhi - khi * p.cw);
-        if (!waited) { ptx::mbar_wait(&bar, 0); waited = true; }
-#pragma unroll 4
-        for (int r = 0; r < rows; ++r) {
-            const int o0 = row_lo[r], o1 = row_hi[r];
-            const float tl = (float)s_lo[o0], tr = (float)s_hi[o0];
-            const float bl = (float)s_lo[o1], br = (float)s_hi[o1];
-            const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(tr, tl), xl));
-            const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(br, bl), xl));
-            obase[(size_t)r * ow3 + col] = to_out<OutT>(finish<kMulRecip>(top, bot, row_l[r], p));
+    int it = 0;
+    for (long long blk = blockIdx.x; blk < total_bands; blk += gridDim.x, ++it) {
+        const int stage = it & 1;
+        const long long img = blk / p.bands;
+        const int band = (int)(blk - img * p.bands);
+        const int oy0 = band * p.th;
+        const int rows = min(p.th, p.out_h - oy0);
+        const int iy0 = (int)__fmul_rn((float)oy0, p.hs);  // first input row of the band
+        // stage^1 was last read in iteration it-1, which every thread has left (barrier at the loop end)
+        if (threadIdx.x == 0 && blk + gridDim.x < total_bands) issue(blk + gridDim.x, stage ^ 1);
+        if (threadIdx.x < rows) {                           // per-row interpolation table
+            const float py = __fmul_rn((float)(oy0 + threadIdx.x), p.hs);
+            const int lo = (int)py;
+            const int hi = min(lo + 1, p.in_h - 1);
+            row_lo[threadIdx.x] = (lo - iy0) * p.cw;
+            row_hi[threadIdx.x] = (hi - iy0) * p.cw;
+            row_l[threadIdx.x] = __fsub_rn(py, (float)lo);
         }
+        __syncthreads();
+        ptx::mbar_wait(&bar[stage], (uint32_t)((it >> 1) & 1));
+        const uint8_t* sbase = smem + (size_t)stage * stage_bytes;
+        OutT* obase = out + ((size_t)img * p.out_h + oy0) * ow3;
+        // A thread owns up to kCols output columns (col = c0 + j*kThreads): their x terms live in registers for the whole
+        // band; the row loop is uniform, so row bases sit in uniform registers and the inner body is 4 byte loads, the
+        // lerps and one store, with no per-element address arithmetic.
+        for (int c0 = threadIdx.x; c0 < ow3; c0 += kThreads * kCols) {
+            int off_lo[kCols], off_hi[kCols];
+            float xl[kCols];
+#pragma unroll
+            for (int j = 0; j < kCols; ++j) {
+                const int col = min(c0 + j * kThreads, ow3 - 1);       // clamped: a surplus column recomputes the last one
+                const int px = col / 3, c = col - px * 3;
+                const float fx = __fmul_rn((float)px, p.ws);
+                const int lo = (int)fx;
+                const int hi = min(lo + 1, p.in_w - 1);
+                xl[j] = __fsub_rn(fx, (float)lo);
+                const int blo = lo * 3 + c, bhi = hi * 3 + c;
+                const int klo = blo / p.cw, khi = bhi / p.cw;
+                off_lo[j] = klo * p.chunk_stride + (blo - klo * p.cw);
+                off_hi[j] = khi * p.chunk_stride + (bhi - khi * p.cw);
+            }
+            for (int r = 0; r < rows; ++r) {
+                const uint8_t* r0 = sbase + row_lo[r];
+                const uint8_t* r1 = sbase + row_hi[r];
+                const float yl = row_l[r];
+                OutT* orow = obase + (size_t)r * ow3;
+#pragma unroll
+                for (int j = 0; j < kCols; ++j) {
+                    const float tl = u8_to_f32(r0[off_lo[j]]), tr = u8_to_f32(r0[off_hi[j]]);
+                    const float bl = u8_to_f32(r1[off_lo[j]]), br = u8_to_f32(r1[off_hi[j]]);
+                    const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(tr, tl), xl[j]));
+                    const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(br, bl), xl[j]));
+                    const int col = c0 + j * kThreads;
+                    if (col < ow3) orow[col] = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
+                }
+            }
+        }
+        __syncthreads();                                    // everyone is done with this stage and the row table
     }
-    if (!waited) ptx::mbar_wait(&bar, 0);  // never leave a copy in flight behind an exiting CTA
 }
 
 // ---- direct kernel: any alignment, any size; one thread per output element ---------------------
@@ -173,9 +204,10 @@ int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool 
                  const CUtensorMap* tmap, int sms, cudaStream_t s, std::string* err) {
     if (use_tma) {
         auto kern = recip ? resize_norm_band_tma<true, OutT> : resize_norm_band_tma<false, OutT>;
-        FTF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), err);
-        const long long blocks = p.n * p.bands;
-        kern<<<(unsigned)blocks, kThreads, smem, s>>>(*tmap, out, p);
+        FTF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem)), err);
+        const long long bands = p.n * p.bands;
+        const long long resident = (long long)sms * 4;      // persistent: 4 CTAs per SM, two stages each
+        kern<<<(unsigned)(bands < resident ? bands : resident), kThreads, 2 * smem, s>>>(*tmap, out, p, bands, (int)smem);
     } else {
         auto kern = recip ? resize_norm_direct<true, OutT> : resize_norm_direct<false, OutT>;
         const long long total = p.n * p.out_h * p.out_w * 3;
@@ -227,7 +259,7 @@ int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out
             p.br = band_input_rows(p.th, in_h, out_h, p.hs);
             p.chunk_stride = (p.cw * p.br + 127) / 128 * 128;
             smem = (size_t)p.chunk_stride * p.n_chunks;
-            if (p.br <= 256 && smem <= 96 * 1024) { fits = true; break; }
+            if (p.br <= 256 && smem <= 27 * 1024) { fits = true; break; }      // two stages x four CTAs per SM
         }
         p.bands = (out_h + p.th - 1) / p.th;
         if (!fits || n * (long long)p.bands > 0x7fffffffLL) use_tma = false;

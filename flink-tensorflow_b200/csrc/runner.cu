@@ -163,14 +163,16 @@ int wait_slot(ftf_runner* r, Slot& s) {
 
 // Enqueues one batch on a slot: upload n records from h_src, run the model, download into h_dst[j].
 // h_src must be pinned (the slot's own staging or caller memory from ftf_host_alloc).
-int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h_dst) {
+int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h_dst, bool uploaded = false) {
     std::string* err = &r->err;
     int rc;
     if ((rc = s.d_in.ensure((size_t)n * r->in_rec_bytes, err))) return rc;
     for (size_t j = 0; j < r->outs.size(); ++j)
         if ((rc = s.d_out[j].ensure((size_t)n * r->outs[j].rec_bytes, err))) return rc;
-    FTF_CUDA(cudaMemcpyAsync(s.d_in.p, h_src, (size_t)n * r->in_rec_bytes, cudaMemcpyHostToDevice, s.stream), err);
-    r->stats.h2d_bytes += (uint64_t)n * r->in_rec_bytes;
+    if (!uploaded) {     // micro-batched records were uploaded one by one as they were submitted
+        FTF_CUDA(cudaMemcpyAsync(s.d_in.p, h_src, (size_t)n * r->in_rec_bytes, cudaMemcpyHostToDevice, s.stream), err);
+        r->stats.h2d_bytes += (uint64_t)n * r->in_rec_bytes;
+    }
     const uint64_t before = launches_so_far();
     switch (r->kind) {
     case Kind::kAffine:
@@ -261,7 +263,7 @@ int launch_open(ftf_runner* r) {
         if ((rc = s.h_out[j].ensure((size_t)s.n * r->outs[j].rec_bytes, &r->err))) return rc;
     std::vector<void*> dst(r->outs.size());
     for (size_t j = 0; j < dst.size(); ++j) dst[j] = s.h_out[j].p;
-    rc = enqueue(r, s, s.n, s.h_in.p, dst.data());
+    rc = enqueue(r, s, s.n, s.h_in.p, dst.data(), /*uploaded=*/true);
     if (rc) { if (rc == FTF_INTERNAL) r->dead = true; return rc; }
     r->in_flight.push_back(r->open_slot);
     r->open_slot = -1;
@@ -566,10 +568,22 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
         r->next_slot = (r->next_slot + 1) % kSlots;
         cand.n = 0; cand.emitted = 0; cand.tags.clear(); cand.t_submit.clear();
         const int cap = is_label_kind(r->kind) ? std::min(r->cfg.max_batch, r->net->max_batch()) : r->cfg.max_batch;
-        if ((rc = cand.h_in.ensure((size_t)cap * bytes, &r->err))) { r->open_slot = -1; return rc; }
+        if ((rc = cand.h_in.ensure((size_t)cap * bytes, &r->err)) || (rc = cand.d_in.ensure((size_t)cap * bytes, &r->err))) { r->open_slot = -1; return rc; }
     }
     Slot& s = r->slots[r->open_slot];
-    memcpy((uint8_t*)s.h_in.p + (size_t)s.n * bytes, payload, bytes);
+    // The record starts its way to HBM now, on the slot's stream, so that the upload overlaps the batches in flight.
+    // A payload in pinned memory (ftf_host_alloc) is read in place by the copy engine -- the caller keeps it untouched
+    // until the record's result has been polled; any other payload is first copied into the pinned slot.
+    const void* src = payload;
+    if (!(payload == rec->data && pinned(payload))) {
+        memcpy((uint8_t*)s.h_in.p + (size_t)s.n * bytes, payload, bytes);
+        src = (uint8_t*)s.h_in.p + (size_t)s.n * bytes;
+    }
+    {
+        cudaError_t e = cudaMemcpyAsync((uint8_t*)s.d_in.p + (size_t)s.n * bytes, src, bytes, cudaMemcpyHostToDevice, s.stream);
+        if (e != cudaSuccess) { r->dead = true; return cuda_fail(e, "record upload", &r->err); }
+        r->stats.h2d_bytes += bytes;
+    }
     s.tags.push_back(tag);
     s.t_submit.push_back(std::chrono::steady_clock::now());
     s.n += 1;

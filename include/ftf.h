@@ -108,7 +108,8 @@ void ftf_release(ftf_runner* r, ftf_tensor* outs, int32_t n);
  * FT/common/functions/AbstractFlatMapFunction.scala:12-14).  ftf_submit copies one record into
  * the pinned ring; a batch is launched at max_batch records or max_delay_us; results come back
  * from ftf_poll in submission order.  ftf_flush drains everything in flight (checkpoint/close).
- * outs[i] stays valid until the next ftf_poll or ftf_submit on this runner. */
+ * outs[i] stays valid until the next ftf_poll or ftf_submit on this runner.  A record whose payload lies in
+ * ftf_host_alloc memory is uploaded in place (no staging copy): keep it unchanged until its result has been polled. */
 int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* record);
 int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor* outs, int32_t cap,
              int32_t* n_ready);
