@@ -105,6 +105,26 @@ def dist_env():
 # ================================================================================================
 # reference arm: the reference's CPU implementation of the path (oracle stand-in for TF-Java Session.run)
 # ================================================================================================
+def torchvision_cpu(threads, unit, seconds=10.0):
+    """Strongest CPU stand-in available offline: torchvision's Inception-v3 (same architecture, random init) on oneDNN,
+    fp32, all host threads.  An extra beside the oracle number, never the thing the parity tests compare against."""
+    try:
+        import torch
+        import torchvision
+        tvm = torchvision.models.inception_v3(weights=None, aux_logits=False, transform_input=False, init_weights=False).eval()
+        torch.set_num_threads(threads)
+        tx = torch.randn(16, 3, 299, 299)
+        with torch.no_grad():
+            tvm(tx)
+            t0, reps = time.perf_counter(), 0
+            while time.perf_counter() - t0 < seconds:
+                tvm(tx)
+                reps += 1
+        return {"value": 16 * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads, "sample": f"{reps} passes over 16 images, fp32"}
+    except Exception as ex:  # noqa: BLE001
+        return {"unavailable": str(ex)[:200]}
+
+
 def run_reference(args):
     import numpy as np
     import oracle
@@ -152,6 +172,8 @@ def run_reference(args):
             "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "CPU oracle (C restatement of the TF-1.1 op sequence) stands in for TF-Java Session.run, which "
                     "cannot run without a JVM; it omits the reference's per-record JNI/dispatch overhead"}
+    if wl == "inception":
+        line["cpu_torchvision_onednn"] = torchvision_cpu(threads, unit)
     print(json.dumps(line), flush=True)
 
 
@@ -417,21 +439,7 @@ def run_ours(args):
                 reps += 1
             cpu = {"value": b * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
                    "sample": f"{reps} passes over 4 images (1/16 of the batch), fp32 C oracle, all host threads"}
-            try:   # strongest CPU stand-in: torchvision on oneDNN, same architecture
-                import torchvision
-                tvm = torchvision.models.inception_v3(weights=None, aux_logits=False, transform_input=False, init_weights=False).eval()
-                torch.set_num_threads(threads)
-                tx = torch.randn(16, 3, 299, 299)
-                with torch.no_grad():
-                    tvm(tx)
-                    t0, reps = time.perf_counter(), 0
-                    while time.perf_counter() - t0 < 10.0:
-                        tvm(tx)
-                        reps += 1
-                extra["cpu_torchvision_onednn"] = {"value": 16 * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads,
-                                                   "sample": f"{reps} passes over 16 images, fp32"}
-            except Exception as ex:  # noqa: BLE001
-                extra["cpu_torchvision_onednn"] = {"unavailable": str(ex)[:200]}
+            extra["cpu_torchvision_onednn"] = torchvision_cpu(threads, unit)
         else:
             b = 32
             cimg = rng.integers(0, 256, (b, NORM["in_h"], NORM["in_w"], 3), dtype=np.uint8)

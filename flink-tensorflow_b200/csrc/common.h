@@ -1,5 +1,6 @@
 // common.h -- shared declarations of the runner library (host + device).
 #pragma once
+#include <stdlib.h>
 #include <cuda_runtime.h>
 #include <cuda.h>
 #include <stdint.h>
@@ -39,6 +40,20 @@ int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out
                        std::string* err);
 int launch_softmax_topk(const float* x, int64_t m, int n, int n_labels, int k, int apply_softmax,
                         float* probs, int32_t* idx, float* score, cudaStream_t s, std::string* err);
+
+// Launch with programmatic dependent launch allowed (see ptx::pdl_wait): inside a stream or a captured graph the next
+// kernel's prologue overlaps this kernel's tail.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    static const bool off = getenv("FTF_NO_PDL") != nullptr;      // A/B switch for measurements
+    cfg.attrs = at; cfg.numAttrs = off ? 0 : 1;
+    return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
 
 // Count of this library's kernel launches (process-wide, relaxed).
 void count_launch(int n = 1);   // n may be negative (a graph recording counted launches that did not run)

@@ -138,6 +138,35 @@ __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, int gc, long
     }
 }
 
+// All column chunks of one accumulator row block: TMEM loads of 32 columns, double-buffered so that the load of group
+// g+1 is in flight while group g is biased, rounded and stored.
+__device__ __forceinline__ void tmem_ld_group(uint32_t taddr, int cols, uint32_t (&v)[32]) {
+    if (cols > 16) ptx::tmem_ld_32x32(taddr, v);
+    else tmem_ld_x16(taddr, reinterpret_cast<uint32_t(&)[16]>(v));
+}
+__device__ __forceinline__ void epilogue_group(const ConvParams& p, int gc, int cols, long long m, bool row_ok, const uint32_t (&v)[32]) {
+    epilogue_chunk(p, gc, m, row_ok, reinterpret_cast<const uint32_t(&)[16]>(v));
+    if (cols > 16) epilogue_chunk(p, gc + 16, m, row_ok, *reinterpret_cast<const uint32_t(*)[16]>(&v[16]));
+}
+__device__ __forceinline__ void epilogue_row(const ConvParams& p, uint32_t t_row, int n_tile, long long m, bool row_ok) {
+    const int gc0 = n_tile * p.block_n;
+    const int n_cols = min(p.block_n, p.N_total - gc0);           // multiple of 16, warp-uniform
+    uint32_t va[32], vb[32];
+    tmem_ld_group(t_row, n_cols, va);
+    ptx::tmem_ld_wait();
+    for (int col = 0; col < n_cols; col += 64) {
+        const int c1 = col + 32, c2 = col + 64;
+        if (c1 < n_cols) tmem_ld_group(t_row + (uint32_t)c1, n_cols - c1, vb);
+        epilogue_group(p, gc0 + col, n_cols - col, m, row_ok, va);
+        ptx::tmem_ld_wait();
+        if (c1 < n_cols) {
+            if (c2 < n_cols) tmem_ld_group(t_row + (uint32_t)c2, n_cols - c2, va);
+            epilogue_group(p, gc0 + c1, n_cols - c1, m, row_ok, vb);
+            ptx::tmem_ld_wait();
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                const __grid_constant__ ConvParams p) {
@@ -170,6 +199,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_launch_dependents();      // the next kernel may start its prologue
+    ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
@@ -241,14 +272,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
             const uint32_t t_row = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(e * 32) << 16);
-            for (int col = 0; col < p.block_n; col += 16) {
-                const int gc = n_tile * p.block_n + col;
-                if (gc >= p.N_total) break;                        // warp-uniform
-                uint32_t v[16];
-                tmem_ld_x16(t_row + (uint32_t)col, v);
-                ptx::tmem_ld_wait();
-                epilogue_chunk(p, gc, m, row_ok, v);
-            }
+            epilogue_row(p, t_row, n_tile, m, row_ok);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
@@ -313,6 +337,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    ptx::pdl_launch_dependents();      // the next kernel may start its prologue
+    ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
@@ -407,14 +433,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const bool row_ok = q < p.Q && wp < p.OW && hp < p.OH;
                 const long long m = (img * p.OH + hp) * p.OW + wp;
                 const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + s * p.block_n) + ((uint32_t)(e * 32) << 16);
-                for (int col = 0; col < p.block_n; col += 16) {
-                    const int gc = n_tile * p.block_n + col;
-                    if (gc >= p.N_total) break;
-                    uint32_t v[16];
-                    tmem_ld_x16(t_row + (uint32_t)col, v);
-                    ptx::tmem_ld_wait();
-                    epilogue_chunk(p, gc, m, row_ok, v);
-                }
+                epilogue_row(p, t_row, n_tile, m, row_ok);
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -586,16 +605,14 @@ int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err) {
         const int T = p.S * kBlockM;
         const long long tiles = (p.Q + T - 1) / T * p.n_tiles;
         const int grid = (int)(tiles < plan.grid ? tiles : plan.grid);
-        conv_halo_kernel<<<grid, kThreads, plan.smem, s>>>(plan.tm_a, plan.tm_b, p);
+        FTF_CUDA(launch_pdl(conv_halo_kernel, dim3(grid), dim3(kThreads), plan.smem, s, plan.tm_a, plan.tm_b, p), err);
         count_launch();
-        FTF_CUDA(cudaGetLastError(), err);
         return FTF_OK;
     }
     const int tiles = p.m_tiles * p.n_tiles;
     const int grid = tiles < plan.grid ? tiles : plan.grid;
-    conv_tc_kernel<<<grid, kThreads, plan.smem, s>>>(plan.tm_a, plan.tm_b, p);
+    FTF_CUDA(launch_pdl(conv_tc_kernel, dim3(grid), dim3(kThreads), plan.smem, s, plan.tm_a, plan.tm_b, p), err);
     count_launch();
-    FTF_CUDA(cudaGetLastError(), err);
     return FTF_OK;
 }
 

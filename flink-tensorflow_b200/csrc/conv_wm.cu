@@ -155,6 +155,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = bars->tmem_slot;
+    ptx::pdl_launch_dependents();      // the next kernel may start its prologue
+    ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
 
     if (warp == 0 && lane == 0) {
         // ===================================== TMA producer =====================================
@@ -517,10 +519,9 @@ int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err) {
     const long long span = p.halo_mode ? p.Q : p.M;
     const long long tiles = (span + T - 1) / T * p.m_tiles;
     const int grid = (int)(tiles < plan.grid ? tiles : plan.grid);
-    if (p.halo_mode) conv_tc_kernel<true><<<grid, kThreads, plan.smem, s>>>(plan.tm_p, plan.tm_w, p);
-    else conv_tc_kernel<false><<<grid, kThreads, plan.smem, s>>>(plan.tm_p, plan.tm_w, p);
+    if (p.halo_mode) FTF_CUDA(launch_pdl(conv_tc_kernel<true>, dim3(grid), dim3(kThreads), plan.smem, s, plan.tm_p, plan.tm_w, p), err);
+    else FTF_CUDA(launch_pdl(conv_tc_kernel<false>, dim3(grid), dim3(kThreads), plan.smem, s, plan.tm_p, plan.tm_w, p), err);
     count_launch();
-    FTF_CUDA(cudaGetLastError(), err);
     return FTF_OK;
 }
 

@@ -14,6 +14,7 @@
 #include "inception.h"
 #include "conv_tc.h"
 #include "pools.h"
+#include "ptx.cuh"
 #include <cuda_bf16.h>
 #include <math.h>
 #include <stdlib.h>
@@ -104,6 +105,8 @@ struct StemWeights {
 __global__ void __launch_bounds__(128)
 stem_conv3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int OH, int OW,
                const __grid_constant__ StemWeights sw) {
+    ptx::pdl_launch_dependents();
+    ptx::pdl_wait();
     const long long total = (long long)n * OH * OW;
     const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= total) return;
@@ -492,8 +495,8 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
             break;
         case Op::kStem: {
             const long long pix = (long long)nb * op.OH * op.OW;
-            stem_conv3x3s2<<<(unsigned)((pix + 127) / 128), 128, 0, st>>>((const __nv_bfloat16*)op.in, (__nv_bfloat16*)op.out, nb, op.H,
-                                                                          op.W, op.OH, op.OW, m.stem);
+            FTF_CUDA(launch_pdl(stem_conv3x3s2, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const __nv_bfloat16*)op.in,
+                                (__nv_bfloat16*)op.out, nb, op.H, op.W, op.OH, op.OW, m.stem), err);
             count_launch();
             break;
         }
