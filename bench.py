@@ -409,13 +409,13 @@ def run_ours(args):
     r.close()
     lib.ftf_host_free(p)
 
-    if wl == "inception":
+    if wl == "inception" and not args.quick:
         extra["streaming"] = streaming_bench(ftf, lib, np, local_rank)
     if rank != 0:
         return
     # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -----------------------------------------
     cpu = None
-    if world == 1:
+    if world == 1 and not args.quick:
         threads = oracle.num_threads()
         rng = np.random.default_rng(1234)
         if wl == "half_plus_two":
@@ -481,6 +481,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--quick", action="store_true", help="development A/B runs: skip the CPU baseline and the streaming leg")
     ap.add_argument("--workload", default="inception", choices=["half_plus_two", "normalize", "inception"])
     args = ap.parse_args()
     if args.impl == "reference":

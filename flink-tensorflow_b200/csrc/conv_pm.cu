@@ -103,7 +103,7 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 
 // One 16-column chunk of one accumulator row: bias, ReLU, rounding and the store into the segment that owns
 // GEMM column gc (m = output pixel index, row_ok = the row is a real output).
-__device__ __forceinline__ void epilogue_chunk(const ConvParams& p, int gc, long long m, bool row_ok, const uint32_t (&v)[16]) {
+__device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const float* bias, int gc, long long m, bool row_ok, const uint32_t (&v)[16]) {
     int s = 0;
 #pragma unroll
     for (int q = 1; q < kConvMaxSegments; ++q)
@@ -113,10 +113,10 @@ __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, int gc, long
 #pragma unroll
     for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
     if (sg.flags & kSegBias) {
-        const float4* bp = reinterpret_cast<const float4*>(p.bias + gc);
+        const float4* bp = reinterpret_cast<const float4*>(bias + gc);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const float4 b = __ldg(bp + i);
+            const float4 b = bp[i];
             f[4 * i] += b.x; f[4 * i + 1] += b.y; f[4 * i + 2] += b.z; f[4 * i + 3] += b.w;
         }
     }
@@ -138,17 +138,28 @@ __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, int gc, long
     }
 }
 
+// The epilogue warps (threads 128..255) copy the layer's bias vector into shared memory while the first accumulator is
+// still being computed; every later read is a broadcast from smem instead of an L2 round trip per 16-column chunk.
+constexpr int kBiasCap = 2048;
+constexpr int kMaxDynSmem = 227 * 1024 - kBiasCap * 4;       // the bias copy is static shared memory
+__device__ __forceinline__ const float* stage_bias(const ConvParams& p, float* bias_s) {
+    if (p.N_total > kBiasCap || p.bias == nullptr) return p.bias;
+    for (int i = (int)threadIdx.x - 128; i < p.N_total; i += 128) bias_s[i] = __ldg(p.bias + i);
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    return bias_s;
+}
+
 // All column chunks of one accumulator row block: TMEM loads of 32 columns, double-buffered so that the load of group
 // g+1 is in flight while group g is biased, rounded and stored.
 __device__ __forceinline__ void tmem_ld_group(uint32_t taddr, int cols, uint32_t (&v)[32]) {
     if (cols > 16) ptx::tmem_ld_32x32(taddr, v);
     else tmem_ld_x16(taddr, reinterpret_cast<uint32_t(&)[16]>(v));
 }
-__device__ __forceinline__ void epilogue_group(const ConvParams& p, int gc, int cols, long long m, bool row_ok, const uint32_t (&v)[32]) {
-    epilogue_chunk(p, gc, m, row_ok, reinterpret_cast<const uint32_t(&)[16]>(v));
-    if (cols > 16) epilogue_chunk(p, gc + 16, m, row_ok, *reinterpret_cast<const uint32_t(*)[16]>(&v[16]));
+__device__ __forceinline__ void epilogue_group(const ConvParams& p, const float* bias, int gc, int cols, long long m, bool row_ok, const uint32_t (&v)[32]) {
+    epilogue_chunk(p, bias, gc, m, row_ok, reinterpret_cast<const uint32_t(&)[16]>(v));
+    if (cols > 16) epilogue_chunk(p, bias, gc + 16, m, row_ok, *reinterpret_cast<const uint32_t(*)[16]>(&v[16]));
 }
-__device__ __forceinline__ void epilogue_row(const ConvParams& p, uint32_t t_row, int n_tile, long long m, bool row_ok) {
+__device__ __forceinline__ void epilogue_row(const ConvParams& p, const float* bias, uint32_t t_row, int n_tile, long long m, bool row_ok) {
     const int gc0 = n_tile * p.block_n;
     const int n_cols = min(p.block_n, p.N_total - gc0);           // multiple of 16, warp-uniform
     uint32_t va[32], vb[32];
@@ -157,11 +168,11 @@ __device__ __forceinline__ void epilogue_row(const ConvParams& p, uint32_t t_row
     for (int col = 0; col < n_cols; col += 64) {
         const int c1 = col + 32, c2 = col + 64;
         if (c1 < n_cols) tmem_ld_group(t_row + (uint32_t)c1, n_cols - c1, vb);
-        epilogue_group(p, gc0 + col, n_cols - col, m, row_ok, va);
+        epilogue_group(p, bias, gc0 + col, n_cols - col, m, row_ok, va);
         ptx::tmem_ld_wait();
         if (c1 < n_cols) {
             if (c2 < n_cols) tmem_ld_group(t_row + (uint32_t)c2, n_cols - c2, va);
-            epilogue_group(p, gc0 + c1, n_cols - c1, m, row_ok, vb);
+            epilogue_group(p, bias, gc0 + c1, n_cols - c1, m, row_ok, vb);
             ptx::tmem_ld_wait();
         }
     }
@@ -171,6 +182,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ __align__(16) float bias_s[kBiasCap];
+    ptx::tl_stamp_min(p.tl);
     // carve: [stages x (A | B)] [barriers] [tmem slot]
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const int rb = 2 * p.kc;                                   // bytes per operand row
@@ -199,8 +212,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    ptx::pdl_launch_dependents();      // the next kernel may start its prologue
     ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
+    ptx::tl_stamp_min(p.tl ? p.tl + 2 : nullptr);
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
@@ -255,9 +268,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             ptx::umma_commit(&tmem_full[acc]);                     // accumulator complete -> epilogue
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
+        // all MMAs of this CTA are issued: the next kernel in the stream may now be scheduled onto SMs as they drain.
+        // (Triggering at kernel start parks its CTAs -- with their shared memory -- on SMs a sibling branch could use.)
+        ptx::pdl_launch_dependents();
         if (prof) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
     } else if (warp >= 4) {
         // ===== epilogue: TMEM -> registers -> bias/ReLU -> global =====
+        const float* bias = stage_bias(p, bias_s);
         const int e = warp - 4;                                    // TMEM lane quarter of this warp
         const int row = e * 32 + lane;
         int acc = 0, acc_phase = 0;
@@ -272,7 +289,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
             const uint32_t t_row = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(e * 32) << 16);
-            epilogue_row(p, t_row, n_tile, m, row_ok);
+            epilogue_row(p, bias, t_row, n_tile, m, row_ok);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
@@ -283,6 +300,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+    ptx::tl_stamp_max(p.tl ? p.tl + 1 : nullptr);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -302,6 +320,8 @@ __global__ void __launch_bounds__(kThreads, 1)
 conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                  const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ __align__(16) float bias_s[kBiasCap];
+    ptx::tl_stamp_min(p.tl);
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     constexpr int kAStages = 2;
     uint8_t* a_base = smem;
@@ -337,8 +357,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    ptx::pdl_launch_dependents();      // the next kernel may start its prologue
     ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
+    ptx::tl_stamp_min(p.tl ? p.tl + 2 : nullptr);
 
     if (warp == 0 && lane == 0) {
         // ===== TMA producer =====
@@ -410,9 +430,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             ptx::umma_commit(&tmem_full[acc]);
             if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1; }
         }
+        // all MMAs of this CTA are issued: the next kernel in the stream may now be scheduled onto SMs as they drain.
+        // (Triggering at kernel start parks its CTAs -- with their shared memory -- on SMs a sibling branch could use.)
+        ptx::pdl_launch_dependents();
         if (prof) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
     } else if (warp >= 4) {
         // ===== epilogue =====
+        const float* bias = stage_bias(p, bias_s);
         const int e = warp - 4;
         const int row = e * 32 + lane;
         int acc = 0, acc_phase = 0;
@@ -433,7 +457,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const bool row_ok = q < p.Q && wp < p.OW && hp < p.OH;
                 const long long m = (img * p.OH + hp) * p.OW + wp;
                 const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + s * p.block_n) + ((uint32_t)(e * 32) << 16);
-                epilogue_row(p, t_row, n_tile, m, row_ok);
+                epilogue_row(p, bias, t_row, n_tile, m, row_ok);
             }
             ptx::tc_fence_before();
             __syncwarp();
@@ -445,6 +469,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+    ptx::tl_stamp_max(p.tl ? p.tl + 1 : nullptr);
 }
 
 }  // namespace
@@ -495,9 +520,11 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     double best = -1.0;
     for (int kc = 64; kc >= 32; kc -= 32) {
         const int chunks = (g.Cin + kc - 1) / kc, rb = 2 * kc, ksteps = kc / 16;
-        // 32-channel K blocks exactly when they save MMAs (Cin % 64 in 1..32): a fixed rule, so that every candidate
-        // kernel of a layer walks K in the same order and produces the same bits
-        const bool kc32_saves = allow_kc32 && ((g.Cin + 31) / 32) * 2 < ((g.Cin + 63) / 64) * 4;
+        // 32-channel K blocks (SWIZZLE_64B rows) only for Cin <= 32: measured, an MMA on 64-byte rows costs about twice
+        // one on 128-byte rows, so halving the MMA count gains nothing; what remains is the halved operand window of
+        // the 32-channel stem layers.  A fixed rule, so that every candidate kernel of a layer walks K in the same order
+        // and produces the same bits.
+        const bool kc32_saves = allow_kc32 && g.Cin <= 32;
         if ((kc == 32) != kc32_saves) continue;
         const double real_frac = (double)g.Cin / (chunks * kc);
         const long long a_tile = (long long)kBlockM * rb;
@@ -576,12 +603,12 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     static std::once_flag attr_once;
     static cudaError_t attr_rc = cudaSuccess;
     std::call_once(attr_once, [] {
-        attr_rc = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        attr_rc = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     });
     // the attribute is per device: set it again when planning on another device
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc_kernel)", err);
-    e = cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    e = cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_halo_kernel)", err);
     return FTF_OK;
 }
@@ -595,8 +622,9 @@ int profile_read(unsigned long long* out16, int reset) {
     return FTF_OK;
 }
 
-int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err) {
+int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl) {
     ConvParams p = plan.p;
+    p.tl = tl;
     p.M = n * p.OH * p.OW;
     if (p.M <= 0) return FTF_OK;
     p.m_tiles = (p.M + kBlockM - 1) / kBlockM;

@@ -25,6 +25,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     // FTF_CONV_KIND=pm|wm forces one kernel (tests and profiling); FTF_CONV_TUNE=0/1 overrides the caller's choice
     const char* force = getenv("FTF_CONV_KIND");
     const char* tenv = getenv("FTF_CONV_TUNE");
+    const bool halo_only = getenv("FTF_CONV_HALO_ONLY") != nullptr;     // profiling: drop the im2col candidate where a halo one exists
     if (tenv) tune = tenv[0] == '1';
     ConvPlan cands[4];
     int n_cand = 0;
@@ -37,6 +38,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
             std::string e;
             const int rc = kind ? wm::plan(g, segs, n_seg, sm_count, &c.wm, &e, &c.est_cycles, halo != 0)
                                 : pm::plan(g, segs, n_seg, sm_count, &c.pm, &e, &c.est_cycles, halo != 0);
+            if (rc == FTF_INTERNAL) { if (err) *err = e; return rc; }   // a CUDA/driver failure, not "this variant does not apply"
             if (rc) { if (first_err.empty()) first_err = e; continue; }
             const bool is_halo = kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
             if (halo && !is_halo) continue;                    // same plan as the no-halo candidate
@@ -44,6 +46,14 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         }
     }
     if (n_cand == 0) { if (err) *err = first_err; return FTF_INVALID_ARGUMENT; }
+    if (halo_only) {
+        int w = 0;
+        for (int i = 0; i < n_cand; ++i) {
+            const bool hm = cands[i].kind ? cands[i].wm.p.halo_mode != 0 : cands[i].pm.p.halo_mode != 0;
+            if (hm) cands[w++] = cands[i];
+        }
+        if (w > 0) n_cand = w;
+    }
     int best = 0;
     for (int i = 1; i < n_cand; ++i)
         if (cands[i].est_cycles < cands[best].est_cycles) best = i;
@@ -76,8 +86,8 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     return FTF_OK;
 }
 
-int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err) {
-    return plan.kind ? wm::launch(plan.wm, n, s, err) : pm::launch(plan.pm, n, s, err);
+int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl) {
+    return plan.kind ? wm::launch(plan.wm, n, s, err, tl) : pm::launch(plan.pm, n, s, err, tl);
 }
 
 int conv_tc_profile_read(unsigned long long* out16, int reset) {

@@ -29,7 +29,7 @@ struct ConvPlan {
 int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
                  std::string* err, bool tune = false);
 // Enqueues the convolution for the first n images.
-int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err);
+int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
 // Diagnostic cycle counters of both kernels, summed (see conv_pm.h).
 int conv_tc_profile_read(unsigned long long* out16, int reset);
 

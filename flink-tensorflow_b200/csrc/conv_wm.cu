@@ -121,6 +121,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__ CUtensorMap tm_w,
                const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
+    ptx::tl_stamp_min(p.tl);
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const int rb = 2 * p.kc;                                   // bytes per operand row
     // im2col: [stages x (W | P)]            halo: [2 x window][w_stages x W]
@@ -155,8 +156,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
     __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = bars->tmem_slot;
-    ptx::pdl_launch_dependents();      // the next kernel may start its prologue
     ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
+    ptx::tl_stamp_min(p.tl ? p.tl + 2 : nullptr);
 
     if (warp == 0 && lane == 0) {
         // ===================================== TMA producer =====================================
@@ -263,6 +264,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
             ptx::umma_commit(&bars->tmem_full[acc]);                           // accumulator complete -> epilogue
             if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1; }
         }
+        // all MMAs of this CTA are issued: the next kernel in the stream may now be scheduled onto SMs as they drain.
+        // (Triggering at kernel start parks its CTAs -- with their shared memory -- on SMs a sibling branch could use.)
+        ptx::pdl_launch_dependents();
         if (profiling) {
             atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin));
             atomicAdd(&p.prof[4], (unsigned long long)w_full);
@@ -367,6 +371,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+    ptx::tl_stamp_max(p.tl ? p.tl + 1 : nullptr);
 }
 
 }  // namespace
@@ -419,7 +424,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
         const int chunks = (g.Cin + kc - 1) / kc, rb = 2 * kc, ksteps = kc / 16;
         // 32-channel K blocks exactly when they save MMAs (Cin % 64 in 1..32): a fixed rule, so that every candidate
         // kernel of a layer walks K in the same order and produces the same bits
-        const bool kc32_saves = allow_kc32 && ((g.Cin + 31) / 32) * 2 < ((g.Cin + 63) / 64) * 4;
+        const bool kc32_saves = allow_kc32 && g.Cin <= 32;       // same rule as the pixel-major kernel (see conv_pm.cu)
         if ((kc == 32) != kc32_saves) continue;
         const double real = (double)g.Cin / (chunks * kc);
         const long long w_bytes = (long long)kWRows * rb;
@@ -510,8 +515,9 @@ int profile_read(unsigned long long* out16, int reset) {
     return FTF_OK;
 }
 
-int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err) {
+int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl) {
     ConvParams p = plan.p;
+    p.tl = tl;
     p.M = (long long)n * p.OH * p.OW;
     p.Q = (long long)n * p.Hp * p.Wp;
     if (p.M <= 0) return FTF_OK;

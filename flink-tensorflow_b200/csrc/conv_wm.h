@@ -30,6 +30,7 @@ struct ConvParams {
     int w_stages;               // halo mode: weight-tile ring depth
     int acc_stages;             // 1 or 2 TMEM accumulator sets of S * np columns
     unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
+    unsigned long long* tl;     // timeline stamps of this launch (FTF_TIMELINE), else NULL
 };
 
 constexpr int kHaloLoadRows = 128;
@@ -47,7 +48,7 @@ struct ConvPlan {
 int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
          std::string* err, double* est_cycles, bool may_use_halo = true);
 // Enqueues the convolution for the first n images.
-int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err);
+int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
 // Diagnostic: copies (and optionally clears) the 16 pipeline cycle counters the kernels accumulate when the
 // environment has FTF_CONV_PROFILE=1: [0] CTAs, [1] producer cycles, [2] producer waiting for free stages,
 // [3] MMA-issuer cycles, [4] waiting for operands, [5] waiting for a drained accumulator, [6] epilogue cycles,

@@ -104,9 +104,11 @@ struct StemWeights {
 };
 __global__ void __launch_bounds__(128)
 stem_conv3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int OH, int OW,
-               const __grid_constant__ StemWeights sw) {
+               const __grid_constant__ StemWeights sw, unsigned long long* tl) {
+    ptx::tl_stamp_min(tl);
     ptx::pdl_launch_dependents();
     ptx::pdl_wait();
+    ptx::tl_stamp_min(tl ? tl + 2 : nullptr);
     const long long total = (long long)n * OH * OW;
     const long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (pix >= total) return;
@@ -139,6 +141,7 @@ stem_conv3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__
         }
         op[q] = make_uint4(r[0], r[1], r[2], r[3]);
     }
+    ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
 }
 
 __global__ void __launch_bounds__(256) cast_f32_bf16(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int64_t n) {
@@ -179,6 +182,7 @@ struct Op {
     void* out = nullptr;
     const float* bias = nullptr;
     int H = 0, W = 0, C = 0, OH = 0, OW = 0, out_ld = 0, out_off = 0;
+    std::string tag;                     // layer name(s) for the FTF_TIMELINE dump
 };
 
 struct InceptionV3::Impl {
@@ -198,6 +202,8 @@ struct InceptionV3::Impl {
     cudaEvent_t fork_ev = nullptr, join_ev[kLanes] = {nullptr, nullptr, nullptr, nullptr};
     std::map<int, cudaGraphExec_t> graphs;   // one instantiated graph of the whole forward per batch size
     std::map<int, int> graph_kernels;        // kernels per replay of that graph
+    unsigned long long* tl_dev = nullptr;    // FTF_TIMELINE=<k>: 4 stamps per op, dumped after the k-th forward
+    int tl_after = 0, tl_calls = 0;
 
     ~Impl() {
         cudaSetDevice(device);
@@ -273,11 +279,23 @@ struct InceptionV3::Impl {
         cudaMemcpy(db, bias.data(), (size_t)total * 4, cudaMemcpyHostToDevice);
         ConvGeometry g{in.p, max_batch, in.h, in.w, in.c, in.c, dw, db, total, kh, kw, s, ph, pw};
         ConvPlan plan;
-        rc = conv_tc_plan(g, segs.data(), (int)segs.size(), sms, &plan, err, /*tune=*/true);
+        rc = conv_tc_plan(g, segs.data(), (int)segs.size(), share(), &plan, err, /*tune=*/true);
         if (rc) return;
         plans.push_back(plan);
         Op op{}; op.type = Op::kConv; op.lane = cur_lane; op.plan = (int)plans.size() - 1;
+        op.tag = br[0].name + (br.size() > 1 ? "+" + std::to_string(br.size() - 1) : std::string()) + " " + std::to_string(kh) + "x" + std::to_string(kw) +
+                 " " + std::to_string(in.c) + "->" + std::to_string(total) + " @" + std::to_string(OH);
         ops.push_back(op);
+    }
+    // SMs a convolution may plan for.  The layers of the 17x17 and 8x8 blocks are single-wave kernels whose time is the
+    // serial fill -> MMA -> epilogue chain of one tile, and a kernel that spreads over all SMs leaves no room for the
+    // sibling branch on another stream.  Inside a fork each branch therefore gets a fixed share of the SMs (its
+    // persistent CTAs loop over more tiles, overlapping their epilogues with the next tile) and the branches really
+    // run side by side.  FTF_NO_SM_SPLIT=1 plans every layer for the whole GPU (measurement switch).
+    int sm_share_den = 1;
+    int share() const {
+        static const bool off = getenv("FTF_NO_SM_SPLIT") != nullptr;
+        return off || sm_share_den <= 1 ? sms : (sms / sm_share_den > 0 ? sms / sm_share_den : 1);
     }
     struct PendingPool { float* scratch; float* bias; Act* dst; int coff, c, h, w; };
     std::vector<PendingPool> pending_pool;
@@ -332,12 +350,14 @@ struct InceptionV3::Impl {
         conv_multi(x, {{blk + ".branch1x1", 192, &out, 0, false}, {blk + ".branch7x7_1", c7, &t, 0, false},
                        {blk + ".branch7x7dbl_1", c7, &d, 0, false}, {blk + ".branch_pool", 192, &out, 576, true}}, 1, 1, 1, 0, 0);
         fork(0b0110);
+        sm_share_den = 2;
         cur_lane = 0; Act u = conv(blk + ".branch7x7_2", t, c7, 1, 7, 1, 0, 3);
         conv_to(blk + ".branch7x7_3", u, 192, 7, 1, 1, 3, 0, &out, 192);
         cur_lane = 1; Act d2 = conv(blk + ".branch7x7dbl_2", d, c7, 7, 1, 1, 3, 0);
         Act d3 = conv(blk + ".branch7x7dbl_3", d2, c7, 1, 7, 1, 0, 3);
         Act d4 = conv(blk + ".branch7x7dbl_4", d3, c7, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7dbl_5", d4, 192, 1, 7, 1, 0, 3, &out, 384);
+        sm_share_den = 1;
         cur_lane = 2; emit_pools();
         join(0b0110);
         named[blk] = out;
@@ -349,10 +369,12 @@ struct InceptionV3::Impl {
         Act t = act(x.h, x.w, 192), s = act(x.h, x.w, 192);
         conv_multi(x, {{blk + ".branch3x3_1", 192, &t, 0, false}, {blk + ".branch7x7x3_1", 192, &s, 0, false}}, 1, 1, 1, 0, 0);
         fork(0b0110);
+        sm_share_den = 2;
         cur_lane = 0; conv_to(blk + ".branch3x3_2", t, 320, 3, 3, 2, 0, 0, &out, 0);
         cur_lane = 1; Act s2 = conv(blk + ".branch7x7x3_2", s, 192, 1, 7, 1, 0, 3);
         Act s3 = conv(blk + ".branch7x7x3_3", s2, 192, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7x3_4", s3, 192, 3, 3, 2, 0, 0, &out, 320);
+        sm_share_den = 1;
         cur_lane = 2; maxpool_to(x, &out, 512);
         join(0b0110);
         named[blk] = out;
@@ -364,11 +386,14 @@ struct InceptionV3::Impl {
         conv_multi(x, {{blk + ".branch1x1", 320, &out, 0, false}, {blk + ".branch3x3_1", 384, &t, 0, false},
                        {blk + ".branch3x3dbl_1", 448, &d, 0, false}, {blk + ".branch_pool", 192, &out, 1856, true}}, 1, 1, 1, 0, 0);
         fork(0b1110);
+        sm_share_den = 4;
         cur_lane = 0; conv_to(blk + ".branch3x3_2a", t, 384, 1, 3, 1, 0, 1, &out, 320);
         cur_lane = 1; conv_to(blk + ".branch3x3_2b", t, 384, 3, 1, 1, 1, 0, &out, 704);
+        sm_share_den = 2;
         cur_lane = 2; Act u = conv(blk + ".branch3x3dbl_2", d, 384, 3, 3, 1, 1, 1);
         conv_to(blk + ".branch3x3dbl_3a", u, 384, 1, 3, 1, 0, 1, &out, 1088);
         conv_to(blk + ".branch3x3dbl_3b", u, 384, 3, 1, 1, 1, 0, &out, 1472);
+        sm_share_den = 1;
         cur_lane = 3; emit_pools();
         join(0b1110);
         named[blk] = out;
@@ -441,7 +466,7 @@ struct InceptionV3::Impl {
         rc = conv_tc_plan(g, &sg, 1, sms, &plan, err, /*tune=*/true);
         if (rc) return;
         plans.push_back(plan);
-        Op op{}; op.type = Op::kConv; op.plan = (int)plans.size() - 1;
+        Op op{}; op.type = Op::kConv; op.plan = (int)plans.size() - 1; op.tag = "fc";
         ops.push_back(op);
         logits_ld = cols;
     }
@@ -467,6 +492,11 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
     m.device = device; m.sms = device_sm_count(device); m.max_batch = max_batch; m.classes = num_classes; m.seed = seed; m.err = err;
     m.build();
     if (m.rc) return m.rc;
+    if (const char* tl = getenv("FTF_TIMELINE")) {         // diagnostics only: kernels stamp their start/end times
+        m.tl_after = atoi(tl);
+        if (m.tl_after > 0) m.tl_dev = (unsigned long long*)m.dev_alloc(m.ops.size() * 4 * 8, true);
+        if (m.rc) return m.rc;
+    }
     FTF_CUDA(cudaDeviceSynchronize(), err);
     m.err = nullptr;
     net->classes_ = num_classes; net->max_batch_ = max_batch;
@@ -478,8 +508,10 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
 // fenced by events at each block's fork and join (the same calls record a graph when `s` is being captured).
 static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* err) {
     auto stream_of = [&](int lane) { return lane == 0 ? s : m.lane_stream[lane]; };
-    for (const Op& op : m.ops) {
+    for (size_t oi = 0; oi < m.ops.size(); ++oi) {
+        const Op& op = m.ops[oi];
         cudaStream_t st = stream_of(op.lane);
+        unsigned long long* tl = m.tl_dev ? m.tl_dev + 4 * oi : nullptr;
         switch (op.type) {
         case Op::kFork:
             FTF_CUDA(cudaEventRecord(m.fork_ev, s), err);
@@ -496,27 +528,27 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
         case Op::kStem: {
             const long long pix = (long long)nb * op.OH * op.OW;
             FTF_CUDA(launch_pdl(stem_conv3x3s2, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const __nv_bfloat16*)op.in,
-                                (__nv_bfloat16*)op.out, nb, op.H, op.W, op.OH, op.OW, m.stem), err);
+                                (__nv_bfloat16*)op.out, nb, op.H, op.W, op.OH, op.OW, m.stem, tl), err);
             count_launch();
             break;
         }
         case Op::kConv: {
-            const int rc = conv_tc_launch(m.plans[op.plan], nb, st, err);
+            const int rc = conv_tc_launch(m.plans[op.plan], nb, st, err, tl);
             if (rc) return rc;
             break;
         }
         case Op::kMaxPool: {
-            const int rc = launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err);
+            const int rc = launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
             if (rc) return rc;
             break;
         }
         case Op::kAvgPoolBiasRelu: {
-            const int rc = launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err);
+            const int rc = launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
             if (rc) return rc;
             break;
         }
         case Op::kGap: {
-            const int rc = launch_global_avgpool(op.in, op.out, nb, op.H * op.W, op.C, st, err);
+            const int rc = launch_global_avgpool(op.in, op.out, nb, op.H * op.W, op.C, st, err, tl);
             if (rc) return rc;
             break;
         }
@@ -524,6 +556,37 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
     }
     FTF_CUDA(cudaGetLastError(), err);
     return FTF_OK;
+}
+
+// FTF_TIMELINE=<k>: after the k-th forward, print when each kernel of that forward started, got past its dependency
+// wait and ended (microseconds from the first start), taken from %globaltimer stamps written by the kernels.
+static void dump_timeline(InceptionV3::Impl& m, int nb) {
+    std::vector<unsigned long long> t(m.ops.size() * 4);
+    if (cudaMemcpy(t.data(), m.tl_dev, t.size() * 8, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); return; }
+    unsigned long long t0 = ~0ull, t1 = 0;
+    for (size_t k = 0; k < m.ops.size(); ++k) {
+        if (t[4 * k] < t0) t0 = t[4 * k];
+        if (t[4 * k + 1] > t1) t1 = t[4 * k + 1];
+    }
+    static const char* kNames[] = {"stem", "conv", "maxpool", "avgpool", "gap", "fork", "join"};
+    fprintf(stderr, "timeline batch %d: %zu ops, %.1f us first start -> last end\n", nb, m.ops.size(), (t1 - t0) * 1e-3);
+    fprintf(stderr, "%4s %4s %-8s %9s %9s %9s %8s  %s\n", "op", "lane", "kind", "start", "go", "end", "busy", "layer");
+    double busy_sum = 0;
+    for (size_t k = 0; k < m.ops.size(); ++k) {
+        const Op& op = m.ops[k];
+        if (op.type == Op::kFork || op.type == Op::kJoin) { fprintf(stderr, "%4zu %4s %-8s\n", k, "-", kNames[op.type]); continue; }
+        const double a = (t[4 * k] - t0) * 1e-3, g = (t[4 * k + 2] - t0) * 1e-3, b = (t[4 * k + 1] - t0) * 1e-3;
+        busy_sum += b - g;
+        std::string tag = op.tag;
+        if (op.type == Op::kConv) {
+            const ConvPlan& pl = m.plans[op.plan];
+            const bool hm = pl.kind ? pl.wm.p.halo_mode : pl.pm.p.halo_mode;
+            tag += pl.kind ? " [wm" : " [pm";
+            tag += hm ? " halo]" : "]";
+        }
+        fprintf(stderr, "%4zu %4d %-8s %9.1f %9.1f %9.1f %8.1f  %s\n", k, op.lane, kNames[op.type], a, g, b, b - g, tag.c_str());
+    }
+    fprintf(stderr, "sum of (end - go) over kernels: %.1f us\n", busy_sum);
 }
 
 int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cudaStream_t s, std::string* err) {
@@ -536,6 +599,13 @@ int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cuda
     // The whole forward (about 80 kernels over 4 streams) is one CUDA graph per batch size: recorded on first use,
     // replayed afterwards.  FTF_NO_GRAPH=1 keeps the plain stream launches (debugging, profilers that want them).
     static const bool use_graph = !(getenv("FTF_NO_GRAPH") && getenv("FTF_NO_GRAPH")[0] == '1');
+    const bool tl_now = m.tl_dev && ++m.tl_calls == m.tl_after;
+    if (tl_now) {
+        std::vector<unsigned long long> init(m.ops.size() * 4);
+        for (size_t k = 0; k < m.ops.size(); ++k) { init[4 * k] = ~0ull; init[4 * k + 1] = 0; init[4 * k + 2] = ~0ull; init[4 * k + 3] = 0; }
+        FTF_CUDA(cudaStreamSynchronize(s), err);
+        FTF_CUDA(cudaMemcpy(m.tl_dev, init.data(), init.size() * 8, cudaMemcpyHostToDevice), err);
+    }
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     FTF_CUDA(cudaStreamIsCapturing(s, &cap), err);
     if (!use_graph || cap != cudaStreamCaptureStatusNone) {
@@ -561,6 +631,10 @@ int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cuda
         }
         FTF_CUDA(cudaGraphLaunch(it->second, s), err);
         count_launch(m.graph_kernels[nb]);
+    }
+    if (tl_now) {
+        FTF_CUDA(cudaStreamSynchronize(s), err);
+        dump_timeline(m, nb);
     }
     // logits: [n, classes] out of the padded [n, logits_ld] result
     FTF_CUDA(cudaMemcpy2DAsync(logits, (size_t)m.classes * 4, m.logits, (size_t)m.logits_ld * 4, (size_t)m.classes * 4, (size_t)n,

@@ -14,9 +14,11 @@ namespace {
 // arithmetic (the launcher rejects tensors of 2^31 items), the nine loads issued together.
 __global__ void __launch_bounds__(256)
 maxpool3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int C, int OH, int OW,
-             int out_ld, int out_off) {
+             int out_ld, int out_off, unsigned long long* tl) {
+    ptx::tl_stamp_min(tl);
     ptx::pdl_launch_dependents();
     ptx::pdl_wait();
+    ptx::tl_stamp_min(tl ? tl + 2 : nullptr);
     const unsigned cg = (unsigned)C / 8u;
     const unsigned total = (unsigned)n * OH * OW * cg;
     const unsigned stride = gridDim.x * blockDim.x;
@@ -39,6 +41,7 @@ maxpool3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ o
             for (int j = 0; j < 4; ++j) m[j] = __hmax2(m[j], reinterpret_cast<const __nv_bfloat162*>(&v[k])[j]);
         *reinterpret_cast<uint4*>(out + (size_t)pix * out_ld + out_off + g * 8) = *reinterpret_cast<uint4*>(m);
     }
+    ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
 }
 
 // out = bf16(relu(avgpool3x3_s1_p1(pre) * (1/9) + bias)); pre is the fp32 1x1-conv output [n,H,W,C]; taps summed
@@ -46,9 +49,11 @@ maxpool3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ o
 // issued together, out-of-image taps read the centre pixel and contribute +0.
 __global__ void __launch_bounds__(256)
 avgpool3x3_bias_relu(const float* __restrict__ pre, const float* __restrict__ bias, __nv_bfloat16* __restrict__ out, int n, int H,
-                     int W, int C, int out_ld, int out_off) {
+                     int W, int C, int out_ld, int out_off, unsigned long long* tl) {
+    ptx::tl_stamp_min(tl);
     ptx::pdl_launch_dependents();
     ptx::pdl_wait();
+    ptx::tl_stamp_min(tl ? tl + 2 : nullptr);
     const unsigned cg = (unsigned)C / 4u;
     const unsigned total = (unsigned)n * H * W * cg;
     const unsigned stride = gridDim.x * blockDim.x;
@@ -78,16 +83,19 @@ avgpool3x3_bias_relu(const float* __restrict__ pre, const float* __restrict__ bi
         uint2 o = make_uint2(*reinterpret_cast<uint32_t*>(&h0), *reinterpret_cast<uint32_t*>(&h1));
         *reinterpret_cast<uint2*>(out + (size_t)pix * out_ld + out_off + g * 4) = o;
     }
+    ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
 }
 
 // global average pool over HW pixels: fp32 sum in pixel order, times 1/HW, rounded to bf16. One thread per (n, 2 channels).
 __global__ void __launch_bounds__(256)
-global_avgpool(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int HW, int C) {
+global_avgpool(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int HW, int C, unsigned long long* tl) {
+    ptx::tl_stamp_min(tl);
     ptx::pdl_launch_dependents();
     ptx::pdl_wait();
+    ptx::tl_stamp_min(tl ? tl + 2 : nullptr);
     const int c2 = C / 2;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= n * c2) return;
+    if (idx >= n * c2) { ptx::tl_stamp_max(tl ? tl + 1 : nullptr); return; }
     const int img = idx / c2, c = (idx - img * c2) * 2;
     const __nv_bfloat16* src = in + (size_t)img * HW * C + c;
     float s0 = 0.0f, s1 = 0.0f;
@@ -99,6 +107,7 @@ global_avgpool(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__
     }
     const float inv = 1.0f / (float)HW;
     *reinterpret_cast<__nv_bfloat162*>(out + (size_t)img * C + c) = __floats2bfloat162_rn(__fmul_rn(s0, inv), __fmul_rn(s1, inv));
+    ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
 }
 
 }  // namespace
@@ -110,7 +119,7 @@ static long long grid_cap(cudaStream_t) {
 }
 
 int launch_maxpool3x3s2(const void* in, void* out, int n, int H, int W, int C, int out_ld, int out_off, cudaStream_t s,
-                        std::string* err) {
+                        std::string* err, unsigned long long* tl) {
     if (n <= 0) return FTF_OK;
     if (H < 3 || W < 3 || C % 8 || out_ld % 8 || out_off % 8) { if (err) *err = "maxpool3x3s2: H,W >= 3 and C, out_ld, out_off multiples of 8"; return FTF_INVALID_ARGUMENT; }
     const int OH = (H - 3) / 2 + 1, OW = (W - 3) / 2 + 1;
@@ -118,28 +127,28 @@ int launch_maxpool3x3s2(const void* in, void* out, int n, int H, int W, int C, i
     if (total >= (1ll << 31)) { if (err) *err = "maxpool3x3s2: tensor too large"; return FTF_INVALID_ARGUMENT; }
     const long long want = (total + 255) / 256, cap = grid_cap(s);
     FTF_CUDA(launch_pdl(maxpool3x3s2, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, H, W, C,
-                        OH, OW, out_ld, out_off), err);
+                        OH, OW, out_ld, out_off, tl), err);
     count_launch();
     return FTF_OK;
 }
 
 int launch_avgpool3x3_bias_relu(const float* pre, const float* bias, void* out, int n, int H, int W, int C, int out_ld,
-                                int out_off, cudaStream_t s, std::string* err) {
+                                int out_off, cudaStream_t s, std::string* err, unsigned long long* tl) {
     if (n <= 0) return FTF_OK;
     if (C % 4 || out_ld % 4 || out_off % 4) { if (err) *err = "avgpool3x3: C, out_ld, out_off multiples of 4"; return FTF_INVALID_ARGUMENT; }
     const long long total = (long long)n * H * W * (C / 4);
     if (total >= (1ll << 31)) { if (err) *err = "avgpool3x3: tensor too large"; return FTF_INVALID_ARGUMENT; }
     const long long want = (total + 255) / 256, cap = grid_cap(s);
     FTF_CUDA(launch_pdl(avgpool3x3_bias_relu, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, pre, bias, (__nv_bfloat16*)out, n, H, W, C,
-                        out_ld, out_off), err);
+                        out_ld, out_off, tl), err);
     count_launch();
     return FTF_OK;
 }
 
-int launch_global_avgpool(const void* in, void* out, int n, int HW, int C, cudaStream_t s, std::string* err) {
+int launch_global_avgpool(const void* in, void* out, int n, int HW, int C, cudaStream_t s, std::string* err, unsigned long long* tl) {
     if (n <= 0) return FTF_OK;
     if (C % 2) { if (err) *err = "global_avgpool: C must be even"; return FTF_INVALID_ARGUMENT; }
-    FTF_CUDA(launch_pdl(global_avgpool, dim3((n * (C / 2) + 255) / 256), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, HW, C), err);
+    FTF_CUDA(launch_pdl(global_avgpool, dim3((n * (C / 2) + 255) / 256), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, HW, C, tl), err);
     count_launch();
     return FTF_OK;
 }

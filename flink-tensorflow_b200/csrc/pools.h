@@ -7,11 +7,13 @@ namespace ftf {
 
 // bf16 NHWC [n,H,W,C] -> bf16 [n,OH,OW,out_ld] at channel offset out_off; OH = (H-3)/2+1.
 int launch_maxpool3x3s2(const void* in, void* out, int n, int H, int W, int C, int out_ld, int out_off, cudaStream_t s,
-                        std::string* err);
+                        std::string* err, unsigned long long* tl = nullptr);
 // out = bf16(relu(avgpool3x3_s1_p1(pre)/9 + bias)); pre fp32 [n,H,W,C] (a 1x1 convolution's raw output).
 int launch_avgpool3x3_bias_relu(const float* pre, const float* bias, void* out, int n, int H, int W, int C, int out_ld,
-                                int out_off, cudaStream_t s, std::string* err);
+                                int out_off, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
 // bf16 [n,HW,C] -> bf16 [n,C]: fp32 mean over the pixels.
-int launch_global_avgpool(const void* in, void* out, int n, int HW, int C, cudaStream_t s, std::string* err);
+int launch_global_avgpool(const void* in, void* out, int n, int HW, int C, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
+
+// tl (all launchers): timeline stamps of this launch for the FTF_TIMELINE diagnostics, else NULL.
 
 }  // namespace ftf

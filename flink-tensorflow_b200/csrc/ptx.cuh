@@ -17,6 +17,16 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ---- timeline stamps (FTF_TIMELINE diagnostics): tl[0] = earliest CTA start, tl[1] = latest CTA end,
+// tl[2] = earliest return from pdl_wait; all in %globaltimer nanoseconds.  tl == NULL outside diagnostics.
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+__device__ __forceinline__ void tl_stamp_min(unsigned long long* slot) { if (slot && threadIdx.x == 0) atomicMin(slot, globaltimer_ns()); }
+__device__ __forceinline__ void tl_stamp_max(unsigned long long* slot) { if (slot && threadIdx.x == 0) atomicMax(slot, globaltimer_ns()); }
+
 // ---- mbarrier --------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

@@ -471,7 +471,10 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
 
     // ---- chunked pipeline -----------------------------------------------------------------------
     int64_t chunk = std::max<int64_t>(1, (int64_t)(kChunkBytes / std::max<size_t>(1, r->in_rec_bytes)));
-    if (is_label_kind(r->kind)) chunk = r->net->max_batch();   // whole micro-batches: tile counts of the convolutions scale with n
+    if (is_label_kind(r->kind)) {
+        chunk = r->net->max_batch();   // whole micro-batches: tile counts of the convolutions scale with n
+        if (const char* e = getenv("FTF_RUN_CHUNK")) chunk = std::max<int64_t>(1, std::min<int64_t>(chunk, atoll(e)));   // measurement switch
+    }
     const bool parse = r->kind == Kind::kAffine && r->affine.input_is_examples;
     const bool direct = !parse && n > 0 && pinned(x->data);
     cudaError_t e;
