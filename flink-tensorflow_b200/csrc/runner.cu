@@ -571,7 +571,17 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
         r->next_slot = (r->next_slot + 1) % kSlots;
         cand.n = 0; cand.emitted = 0; cand.tags.clear(); cand.t_submit.clear();
         const int cap = is_label_kind(r->kind) ? std::min(r->cfg.max_batch, r->net->max_batch()) : r->cfg.max_batch;
-        if ((rc = cand.h_in.ensure((size_t)cap * bytes, &r->err)) || (rc = cand.d_in.ensure((size_t)cap * bytes, &r->err))) { r->open_slot = -1; return rc; }
+        // device staging of every slot on the first batch (an allocation later would stall the batches in flight); the
+        // pinned host staging only if a payload ever arrives in pageable memory (see below)
+        for (auto& sl : r->slots) {
+            rc = sl.d_in.ensure((size_t)cap * bytes, &r->err);
+            for (size_t j = 0; !rc && j < r->outs.size(); ++j) {
+                rc = sl.d_out[j].ensure((size_t)cap * r->outs[j].rec_bytes, &r->err);
+                if (!rc) rc = sl.h_out[j].ensure((size_t)cap * r->outs[j].rec_bytes, &r->err);
+            }
+            if (!rc && is_label_kind(r->kind)) rc = sl.d_img.ensure((size_t)cap * kInceptionSide * kInceptionSide * 3 * 2, &r->err);
+            if (rc) { r->open_slot = -1; return rc; }
+        }
     }
     Slot& s = r->slots[r->open_slot];
     // The record starts its way to HBM now, on the slot's stream, so that the upload overlaps the batches in flight.
@@ -579,6 +589,8 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
     // until the record's result has been polled; any other payload is first copied into the pinned slot.
     const void* src = payload;
     if (!(payload == rec->data && pinned(payload))) {
+        const int cap0 = is_label_kind(r->kind) ? std::min(r->cfg.max_batch, r->net->max_batch()) : r->cfg.max_batch;
+        if ((rc = s.h_in.ensure((size_t)cap0 * bytes, &r->err))) return rc;
         memcpy((uint8_t*)s.h_in.p + (size_t)s.n * bytes, payload, bytes);
         src = (uint8_t*)s.h_in.p + (size_t)s.n * bytes;
     }
