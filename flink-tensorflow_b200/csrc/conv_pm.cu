@@ -245,6 +245,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     } else if (warp == 1 && lane == 0) {
         // ===== MMA issuer =====
         const uint32_t idesc = instr_desc_bf16(kBlockM, p.block_n);
+        const int last_chunk_kb = (p.cin_chunks - 1) * p.KH * p.KW;            // K blocks run chunk-major
         int stage = 0, phase = 0, acc = 0, acc_phase = 0;
         const bool prof = p.prof != nullptr;
         long long w_full = 0, w_acc = 0;
@@ -259,7 +260,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 const uint32_t a_addr = ptx::smem_u32(smem + (size_t)stage * stage_bytes);
                 const uint64_t a_desc = smem_desc(a_addr, rb);
                 const uint64_t b_desc = smem_desc(a_addr + p.a_tile_bytes, rb);
-                for (int k = 0; k < p.kc / 16; ++k)             // 32 bytes (two 16-byte units) per K=16 step
+                // K=16 steps of this block (32 bytes, two 16-byte units each); the last channel chunk stops where the
+                // real channels end -- the rest of its rows is TMA zero fill and would add exact zeros
+                const int nk = kb >= last_chunk_kb ? p.ksteps_last : p.kc / 16;
+                for (int k = 0; k < nk; ++k)
                     ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
                                    (kb | k) != 0 ? 1u : 0u);
                 ptx::umma_commit(&empty_bar[stage]);               // frees the smem stage when the MMAs retire
@@ -408,6 +412,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 timed_wait(&a_full[as], aph, prof, &w_full);
                 ptx::tc_fence_after();
                 const uint32_t a_addr = ptx::smem_u32(a_base + (size_t)as * p.a_stage_bytes);
+                const int nk = chunk == p.cin_chunks - 1 ? p.ksteps_last : p.kc / 16;     // skip the all-zero K steps
                 for (int tap = 0; tap < taps; ++tap) {
                     const int kh = tap / p.KW, kw = tap - kh * p.KW;
                     timed_wait(&b_full[bs], bph, prof, &w_full);
@@ -417,7 +422,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     for (int s = 0; s < p.S; ++s) {
                         // tap (kh, kw) of sub-tile s: the window entered (s*128 + kh*Wp + kw) rows further down
                         const uint64_t a_desc = smem_desc(a_addr + (uint32_t)(s * kBlockM + kh * p.Wp + kw) * (uint32_t)rb, rb);
-                        for (int k = 0; k < p.kc / 16; ++k)
+                        for (int k = 0; k < nk; ++k)
                             ptx::umma_bf16(d_tmem + (uint32_t)(s * p.block_n), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k),
                                            idesc, (first | (uint32_t)k) != 0 ? 1u : 0u);
                     }
@@ -520,6 +525,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     double best = -1.0;
     for (int kc = 64; kc >= 32; kc -= 32) {
         const int chunks = (g.Cin + kc - 1) / kc, rb = 2 * kc, ksteps = kc / 16;
+        const int total_ksteps = (chunks - 1) * ksteps + (g.Cin - kc * (chunks - 1) + 15) / 16;   // all-zero K steps are skipped
         // 32-channel K blocks (SWIZZLE_64B rows) only for Cin <= 32: measured, an MMA on 64-byte rows costs about twice
         // one on 128-byte rows, so halving the MMA count gains nothing; what remains is the halved operand window of
         // the 32-channel stem layers.  A fixed rule, so that every candidate kernel of a layer walks K in the same order
@@ -535,7 +541,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             const long long b_bytes = (long long)bn * rb;
             {   // one im2col load per tap
                 const long long tiles = (long long)p.m_tiles * tiles_n, waves = (tiles + sm_count - 1) / sm_count;
-                const double cyc = (double)taps * chunks * ksteps * 128.0, bytes = (double)taps * chunks * (a_tile + b_bytes) * real_frac;
+                const double cyc = (double)taps * total_ksteps * 128.0, bytes = (double)taps * chunks * (a_tile + b_bytes) * real_frac;
                 const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
                 if (best < 0 || t < best) {
                     best = t; p.halo_mode = 0; p.block_n = bn; p.n_tiles = tiles_n; p.kc = kc; p.cin_chunks = chunks;
@@ -551,7 +557,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                 const long long room = kSmem - 2 * a_bytes;
                 if (room < 2 * b_bytes) continue;
                 const long long tiles = (Q + T - 1) / T * tiles_n, waves = (tiles + sm_count - 1) / sm_count;
-                const double cyc = (double)chunks * taps * S * ksteps * 128.0;
+                const double cyc = (double)total_ksteps * taps * S * 128.0;
                 const double bytes = chunks * (a_bytes + (double)taps * b_bytes) * real_frac;
                 const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
                 if (t < best) {
@@ -564,6 +570,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             }
         }
     }
+    p.ksteps_last = (g.Cin - p.kc * (p.cin_chunks - 1) + 15) / 16;
     if (est_cycles) *est_cycles = best;
     if (p.halo_mode) {
         plan->smem = 2 * (size_t)p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + 1024 + 512;

@@ -29,6 +29,7 @@ struct ConvParams {
     int a_stage_bytes;          // a_loads * kHaloLoadRows * 128
     int b_stages;               // weight-tile ring depth
     int acc_stages;             // 1 or 2 TMEM accumulator sets of S * block_n columns
+    int ksteps_last;            // K=16 steps holding real channels in the LAST channel chunk (the all-zero rest is skipped)
     unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
     unsigned long long* tl;     // timeline stamps of this launch (FTF_TIMELINE), else NULL
 };

@@ -65,10 +65,19 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
             // the model's choice stands unless another candidate is measurably (8 %) faster: near-ties then resolve the
             // same way on every runner
             const int model = best;
+            const bool verbose = getenv("FTF_CONV_VERBOSE") != nullptr;
+            auto describe = [&](int i, float t) {
+                const ConvPlan& c = cands[i];
+                const bool hm = c.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
+                fprintf(stderr, "   candidate %s%s kc %d: %.1f us (model %.0f cycles)%s\n", c.kind ? "wm" : "pm", hm ? " halo" : "",
+                        c.kind ? c.wm.p.kc : c.pm.p.kc, t * 1e3f, c.est_cycles, i == model ? "  <- model" : "");
+            };
             float best_t = time_candidate(cands[model], g.n_max, s, e0, e1);
+            if (verbose) describe(model, best_t);
             for (int i = 0; i < n_cand; ++i) {
                 if (i == model) continue;
                 const float t = time_candidate(cands[i], g.n_max, s, e0, e1);
+                if (verbose) describe(i, t);
                 if (t >= 0 && (best_t < 0 || t < 0.92f * best_t)) { best_t = t; best = i; }
             }
         }

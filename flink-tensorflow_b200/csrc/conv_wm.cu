@@ -231,7 +231,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                     ptx::tc_fence_after();
                     const uint32_t w_addr = ptx::smem_u32(smem + (size_t)as * stage_bytes);
                     const uint64_t w_desc = smem_desc(w_addr, rb), x_desc = smem_desc(w_addr + p.w_stage_bytes, rb);
-                    for (int k = 0; k < ksteps; ++k)                           // 32 bytes (two 16-byte units) per K = 16 step
+                    const int nk = kb >= (p.cin_chunks - 1) * taps ? p.ksteps_last : ksteps;      // skip the all-zero K steps of the last chunk
+                    for (int k = 0; k < nk; ++k)                               // 32 bytes (two 16-byte units) per K = 16 step
                         ptx::umma_bf16(d_tmem, w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
                     ptx::umma_commit(&bars->a_empty[as]);                      // frees the stage when these MMAs retire
                     if (++as == p.stages) { as = 0; aph ^= 1; }
@@ -241,6 +242,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                     timed_wait(&bars->a_full[as], aph, profiling, &w_full);
                     ptx::tc_fence_after();
                     const uint32_t win_addr = ptx::smem_u32(win_base + (size_t)as * p.p_stage_bytes);
+                    const int nk = chunk == p.cin_chunks - 1 ? p.ksteps_last : ksteps;
                     for (int tap = 0; tap < taps; ++tap) {
                         const int kh = tap / p.KW, kw = tap - kh * p.KW;
                         timed_wait(&bars->b_full[bs], bph, profiling, &w_full);
@@ -250,7 +252,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                         for (int s = 0; s < p.S; ++s) {
                             // tap (kh, kw) of sub-tile s: the window entered (s*np + kh*Wp + kw) rows further down
                             const uint64_t x_desc = smem_desc(win_addr + (uint32_t)(s * p.np + kh * p.Wp + kw) * (uint32_t)rb, rb);
-                            for (int k = 0; k < ksteps; ++k)
+                            for (int k = 0; k < nk; ++k)
                                 ptx::umma_bf16(d_tmem + (uint32_t)(s * p.np), w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc,
                                                (first | (uint32_t)k) != 0 ? 1u : 0u);
                         }
@@ -422,6 +424,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     double best = -1.0;
     for (int kc = 64; kc >= 32; kc -= 32) {
         const int chunks = (g.Cin + kc - 1) / kc, rb = 2 * kc, ksteps = kc / 16;
+        const int total_ksteps = (chunks - 1) * ksteps + (g.Cin - kc * (chunks - 1) + 15) / 16;   // all-zero K steps are skipped
         // 32-channel K blocks exactly when they save MMAs (Cin % 64 in 1..32): a fixed rule, so that every candidate
         // kernel of a layer walks K in the same order and produces the same bits
         const bool kc32_saves = allow_kc32 && g.Cin <= 32;       // same rule as the pixel-major kernel (see conv_pm.cu)
@@ -434,7 +437,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                 int stages = (int)(kSmem / stage);
                 if (stages > kMaxStages) stages = kMaxStages;
                 const long long tiles = (p.M + np - 1) / np * p.m_tiles, waves = (tiles + sm_count - 1) / sm_count;
-                const double cyc = (double)taps * chunks * ksteps * 128.0, bytes = (double)taps * chunks * stage * real;
+                const double cyc = (double)taps * total_ksteps * 128.0, bytes = (double)taps * chunks * stage * real;
                 double work = cyc > bytes / kFill ? cyc : bytes / kFill;
                 if (work < np * kEpi) work = np * kEpi;
                 const double t = waves * (work + kFixed);
@@ -453,7 +456,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                 const long long room = kSmem - 2 * p_bytes;
                 if (room < 2 * w_bytes) continue;
                 const long long tiles = (Q + T - 1) / T * p.m_tiles, waves = (tiles + sm_count - 1) / sm_count;
-                const double cyc = (double)chunks * taps * S * ksteps * 128.0;
+                const double cyc = (double)total_ksteps * taps * S * 128.0;
                 const double bytes = (double)chunks * (p_bytes + (double)taps * w_bytes) * real;
                 double work = cyc > bytes / kFill ? cyc : bytes / kFill;
                 if (work < T * kEpi) work = T * kEpi;
@@ -470,6 +473,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     }
     if (best < 0) return bad("no tile shape fits shared memory");
     if (est_cycles) *est_cycles = best;
+    p.ksteps_last = (g.Cin - p.kc * (p.cin_chunks - 1) + 15) / 16;
     p.Hp = Hp; p.Wp = Wp; p.Q = Q;
     plan->smem = (p.halo_mode ? 2 * (size_t)p.p_stage_bytes + (size_t)p.w_stages * p.w_stage_bytes
                               : (size_t)p.stages * (p.w_stage_bytes + p.p_stage_bytes)) + 1024 /*alignment slack*/ + sizeof(Bars);
