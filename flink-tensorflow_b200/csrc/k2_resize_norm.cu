@@ -25,11 +25,16 @@ namespace ftf {
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxBandRows = 64;   // output rows per band upper bound (row tables in smem)
 constexpr int kCols = 4;           // output columns a thread carries through a band
 
 // exact u8 -> f32 without the quarter-rate I2F: 2^23 + b has b in its low mantissa bits
-__device__ __forceinline__ float u8_to_f32(uint8_t b) { return __fsub_rn(__uint_as_float(0x4B000000u | (uint32_t)b), 8388608.0f); }
+__device__ __forceinline__ float u8_to_f32(uint32_t b) { return __fsub_rn(__uint_as_float(0x4B000000u | b), 8388608.0f); }
+// one byte of shared memory by its 32-bit shared-window address, zero-extended
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+    return v;
+}
 
 struct ResizeParams {
     int in_h, in_w, out_h, out_w;
@@ -39,6 +44,7 @@ struct ResizeParams {
     int bands;               // bands per image
     int br;                  // input rows fetched per band (TMA box height)
     int cw;                  // chunk width in bytes (TMA box width)
+    float inv_cw;            // 1/cw
     int n_chunks;
     int chunk_stride;        // bytes between chunk regions in smem (128-byte multiple)
     long long n;             // images
@@ -55,94 +61,118 @@ __device__ __forceinline__ float finish(float top, float bot, float yl, const Re
     return kMulRecip ? __fmul_rn(d, p.inv_scale) : __fdiv_rn(d, p.scale);
 }
 
+// The interpolation of kN output columns (c0 + j*kThreads) over the rows of one band; see the kernel below.
+// u8 -> f32 uses the 2^23 trick: m(b) = bits 0x4B000000|b = 2^23 + b exactly.  A tap that only enters a difference needs
+// no conversion at all, since m(tr) - m(tl) = tr - tl exactly; the left taps are converted with one FADD each.
+template <int kN, bool kMulRecip, typename OutT>
+__device__ __forceinline__ void band_columns(const ResizeParams& p, uint32_t sbase, int c0, int ow3, int rows, int oy0, int iy0,
+                                             OutT* __restrict__ orow) {
+    uint32_t off_lo[kN], off_hi[kN];
+    float xl[kN];
+    bool live[kN];
+#pragma unroll
+    for (int j = 0; j < kN; ++j) {
+        live[j] = c0 + j * kThreads < ow3;
+        const int col = min(c0 + j * kThreads, ow3 - 1);                   // a dead lane recomputes the last column, unstored
+        const int px = col / 3, c = col - px * 3;
+        const float fx = __fmul_rn((float)px, p.ws);
+        const int lo = (int)fx;
+        const int hi = min(lo + 1, p.in_w - 1);
+        xl[j] = __fsub_rn(fx, (float)lo);
+        const int blo = lo * 3 + c, bhi = hi * 3 + c;
+        // chunk index = byte / cw without an integer division: (b + 0.5)/cw is at least 0.5/cw away from an integer
+        const int klo = (int)(((float)blo + 0.5f) * p.inv_cw), khi = (int)(((float)bhi + 0.5f) * p.inv_cw);
+        off_lo[j] = sbase + (uint32_t)(klo * p.chunk_stride + (blo - klo * p.cw));
+        off_hi[j] = sbase + (uint32_t)(khi * p.chunk_stride + (bhi - khi * p.cw));
+    }
+    for (int r = 0; r < rows; ++r, orow += ow3) {
+        const float py = __fmul_rn((float)(oy0 + r), p.hs);                // the row terms: a few uniform operations
+        const int ylo = (int)py;
+        const int yhi = min(ylo + 1, p.in_h - 1);
+        const uint32_t r0 = (uint32_t)((ylo - iy0) * p.cw), r1 = (uint32_t)((yhi - iy0) * p.cw);
+        const float yl = __fsub_rn(py, (float)ylo);
+#pragma unroll
+        for (int j = 0; j < kN; ++j) {
+            const float mtl = __uint_as_float(0x4B000000u | lds_u8(r0 + off_lo[j])), mtr = __uint_as_float(0x4B000000u | lds_u8(r0 + off_hi[j]));
+            const float mbl = __uint_as_float(0x4B000000u | lds_u8(r1 + off_lo[j])), mbr = __uint_as_float(0x4B000000u | lds_u8(r1 + off_hi[j]));
+            const float tl = __fsub_rn(mtl, 8388608.0f), bl = __fsub_rn(mbl, 8388608.0f);
+            const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(mtr, mtl), xl[j]));
+            const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(mbr, mbl), xl[j]));
+            const OutT v = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
+            if (live[j]) orow[j * kThreads] = v;
+        }
+    }
+}
+
 // ---- TMA-staged band kernel -------------------------------------------------------------------
-// Persistent: a CTA walks bands blockIdx.x, blockIdx.x + gridDim.x, ... with two shared-memory stages, so the TMA
-// fetch of the next band is in flight while the current band is interpolated and stored.
+// Persistent: a CTA walks bands blockIdx.x, blockIdx.x + gridDim.x, ... through two shared-memory stages guarded by
+// full/empty mbarriers: thread 0 refills a stage as soon as all eight warps have released it, and no warp ever waits for
+// another one (no __syncthreads in the loop), so the warps drift apart and hide each other's shared-memory latency.
 template <bool kMulRecip, typename OutT>
 __global__ void __launch_bounds__(kThreads, 4)
 resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p, long long total_bands,
                      int stage_bytes) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t bar[2];
-    __shared__ int row_lo[kMaxBandRows], row_hi[kMaxBandRows];
-    __shared__ float row_l[kMaxBandRows];
+    __shared__ __align__(8) uint64_t full[2], empty[2];
 
     auto issue = [&](long long blk, int stage) {       // one thread: fetch the input rows of band `blk`
         const long long img = blk / p.bands;
         const int band = (int)(blk - img * p.bands);
         const int iy0 = (int)__fmul_rn((float)(band * p.th), p.hs);
-        ptx::mbar_expect_tx(&bar[stage], (uint32_t)(p.n_chunks * p.cw * p.br));
+        ptx::mbar_expect_tx(&full[stage], (uint32_t)(p.n_chunks * p.cw * p.br));
         for (int k = 0; k < p.n_chunks; ++k)
-            ptx::tma_load_3d(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, &tmap, &bar[stage], k * p.cw, iy0, (int)img);
+            ptx::tma_load_3d(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, &tmap, &full[stage], k * p.cw, iy0, (int)img);
     };
 
     if (threadIdx.x == 0) {
-        ptx::mbar_init(&bar[0], 1);
-        ptx::mbar_init(&bar[1], 1);
+        ptx::mbar_init(&full[0], 1);
+        ptx::mbar_init(&full[1], 1);
+        ptx::mbar_init(&empty[0], kThreads / 32);
+        ptx::mbar_init(&empty[1], kThreads / 32);
         ptx::fence_mbar_init();
     }
     __syncthreads();
-    if (threadIdx.x == 0 && (long long)blockIdx.x < total_bands) issue(blockIdx.x, 0);
+    if (threadIdx.x == 0) {
+        if ((long long)blockIdx.x < total_bands) issue(blockIdx.x, 0);
+        if ((long long)blockIdx.x + gridDim.x < total_bands) issue((long long)blockIdx.x + gridDim.x, 1);
+    }
 
     const int ow3 = p.out_w * 3;
+    const uint32_t smem_a = ptx::smem_u32(smem);             // 32-bit shared-window addresses: no generic-pointer arithmetic
     int it = 0;
     for (long long blk = blockIdx.x; blk < total_bands; blk += gridDim.x, ++it) {
         const int stage = it & 1;
+        const uint32_t phase = (uint32_t)((it >> 1) & 1);
         const long long img = blk / p.bands;
         const int band = (int)(blk - img * p.bands);
         const int oy0 = band * p.th;
         const int rows = min(p.th, p.out_h - oy0);
         const int iy0 = (int)__fmul_rn((float)oy0, p.hs);  // first input row of the band
-        // stage^1 was last read in iteration it-1, which every thread has left (barrier at the loop end)
-        if (threadIdx.x == 0 && blk + gridDim.x < total_bands) issue(blk + gridDim.x, stage ^ 1);
-        if (threadIdx.x < rows) {                           // per-row interpolation table
-            const float py = __fmul_rn((float)(oy0 + threadIdx.x), p.hs);
-            const int lo = (int)py;
-            const int hi = min(lo + 1, p.in_h - 1);
-            row_lo[threadIdx.x] = (lo - iy0) * p.cw;
-            row_hi[threadIdx.x] = (hi - iy0) * p.cw;
-            row_l[threadIdx.x] = __fsub_rn(py, (float)lo);
-        }
-        __syncthreads();
-        ptx::mbar_wait(&bar[stage], (uint32_t)((it >> 1) & 1));
-        const uint8_t* sbase = smem + (size_t)stage * stage_bytes;
+        ptx::mbar_wait(&full[stage], phase);
+        const uint32_t sbase = smem_a + (uint32_t)(stage * stage_bytes);
         OutT* obase = out + ((size_t)img * p.out_h + oy0) * ow3;
-        // A thread owns up to kCols output columns (col = c0 + j*kThreads): their x terms live in registers for the whole
-        // band; the row loop is uniform, so row bases sit in uniform registers and the inner body is 4 byte loads, the
-        // lerps and one store, with no per-element address arithmetic.
-        for (int c0 = threadIdx.x; c0 < ow3; c0 += kThreads * kCols) {
-            int off_lo[kCols], off_hi[kCols];
-            float xl[kCols];
-#pragma unroll
-            for (int j = 0; j < kCols; ++j) {
-                const int col = min(c0 + j * kThreads, ow3 - 1);       // clamped: a surplus column recomputes the last one
-                const int px = col / 3, c = col - px * 3;
-                const float fx = __fmul_rn((float)px, p.ws);
-                const int lo = (int)fx;
-                const int hi = min(lo + 1, p.in_w - 1);
-                xl[j] = __fsub_rn(fx, (float)lo);
-                const int blo = lo * 3 + c, bhi = hi * 3 + c;
-                const int klo = blo / p.cw, khi = bhi / p.cw;
-                off_lo[j] = klo * p.chunk_stride + (blo - klo * p.cw);
-                off_hi[j] = khi * p.chunk_stride + (bhi - khi * p.cw);
-            }
-            for (int r = 0; r < rows; ++r) {
-                const uint8_t* r0 = sbase + row_lo[r];
-                const uint8_t* r1 = sbase + row_hi[r];
-                const float yl = row_l[r];
-                OutT* orow = obase + (size_t)r * ow3;
-#pragma unroll
-                for (int j = 0; j < kCols; ++j) {
-                    const float tl = u8_to_f32(r0[off_lo[j]]), tr = u8_to_f32(r0[off_hi[j]]);
-                    const float bl = u8_to_f32(r1[off_lo[j]]), br = u8_to_f32(r1[off_hi[j]]);
-                    const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(tr, tl), xl[j]));
-                    const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(br, bl), xl[j]));
-                    const int col = c0 + j * kThreads;
-                    if (col < ow3) orow[col] = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
-                }
+        // A thread owns up to kCols output columns (col = c0 + j*kThreads): their x terms and shared-memory offsets live in
+        // registers for the whole band, and the row loop is specialised on how many of them the WARP has (the last group of
+        // a row is usually partial), so its body is branch-free straight-line code: per output value 4 address adds,
+        // 4 byte loads, the conversions, the 11 rounded fp32 operations of the reference's formula and one store.
+        for (int c0 = threadIdx.x; c0 - (int)(threadIdx.x & 31) < ow3; c0 += kThreads * kCols) {
+            const int warp_c0 = c0 - (int)(threadIdx.x & 31);                 // first column of this warp's group
+            const int nj = min(kCols, (ow3 - warp_c0 + kThreads - 1) / kThreads);   // columns with at least one live lane
+            OutT* orow = obase + c0;
+            switch (nj) {
+            case 4: band_columns<4, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
+            case 3: band_columns<3, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
+            case 2: band_columns<2, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
+            default: band_columns<1, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
             }
         }
-        __syncthreads();                                    // everyone is done with this stage and the row table
+        // this warp is done with the stage; thread 0 refills it (band it+2) once every warp has said so
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&empty[stage]);
+        if (threadIdx.x == 0 && blk + 2ll * gridDim.x < total_bands) {
+            ptx::mbar_wait(&empty[stage], phase);
+            issue(blk + 2ll * gridDim.x, stage);
+        }
     }
 }
 
@@ -262,6 +292,7 @@ int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out
             if (p.br <= 256 && smem <= 27 * 1024) { fits = true; break; }      // two stages x four CTAs per SM
         }
         p.bands = (out_h + p.th - 1) / p.th;
+        p.inv_cw = 1.0f / (float)p.cw;
         if (!fits || n * (long long)p.bands > 0x7fffffffLL) use_tma = false;
     }
     if (use_tma) {
