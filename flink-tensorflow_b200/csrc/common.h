@@ -1,5 +1,6 @@
 // common.h -- shared declarations of the runner library (host + device).
 #pragma once
+#include <utility>
 #include <stdlib.h>
 #include <cuda_runtime.h>
 #include <cuda.h>
@@ -44,15 +45,20 @@ int launch_softmax_topk(const float* x, int64_t m, int n, int n_labels, int k, i
 // Launch with programmatic dependent launch allowed (see ptx::pdl_wait): inside a stream or a captured graph the next
 // kernel's prologue overlaps this kernel's tail.
 template <typename... KArgs, typename... Args>
-inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+inline cudaError_t launch_pdl_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, int cluster, Args&&... args) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute at[2];
     static const bool off = getenv("FTF_NO_PDL") != nullptr;      // A/B switch for measurements
-    cfg.attrs = at; cfg.numAttrs = off ? 0 : 1;
+    int n = 0;
+    if (!off) { at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[n].val.programmaticStreamSerializationAllowed = 1; ++n; }
+    if (cluster > 1) { at[n].id = cudaLaunchAttributeClusterDimension; at[n].val.clusterDim.x = (unsigned)cluster; at[n].val.clusterDim.y = 1; at[n].val.clusterDim.z = 1; ++n; }
+    cfg.attrs = at; cfg.numAttrs = (unsigned)n;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args&&... args) {
+    return launch_pdl_cluster(kernel, grid, block, smem, s, 1, std::forward<Args>(args)...);
 }
 
 // Count of this library's kernel launches (process-wide, relaxed).

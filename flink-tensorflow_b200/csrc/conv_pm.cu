@@ -178,13 +178,29 @@ __device__ __forceinline__ void epilogue_row(const ConvParams& p, const float* b
     }
 }
 
+__device__ __forceinline__ void tma_load_im2col_pair(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
+                                                     int off_w, int off_h) {
+    asm volatile(
+        "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(
+            ptx::smem_u32(dst)),
+        "l"(m), "r"(ptx::smem_u32(bar) & ptx::kPeerMask), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+        : "memory");
+}
+
+// kPair = false: one CTA per 128-pixel tile.  kPair = true: a cluster of two CTAs on one TPC works on 256 pixels with
+// cta_group::2 MMAs -- CTA r loads the im2col rows of ITS 128 pixels and rows [r*block_n/2, (r+1)*block_n/2) of the weight
+// tile, CTA 0 issues the M = 256 MMA, each CTA's TMEM holds its own 128 accumulator rows and its epilogue warps store
+// them.  Per CTA and MMA that is half the weight bytes written to and read from shared memory, which is what bounds the
+// one-CTA kernel (every operand byte is written once by TMA and read once by the tensor core: ~64 + N/2 cycles per MMA
+// instead of N/2; with the pair ~64 + N/4).
+template <bool kPair>
 __global__ void __launch_bounds__(kThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
                const __grid_constant__ ConvParams p) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(16) float bias_s[kBiasCap];
     ptx::tl_stamp_min(p.tl);
-    // carve: [stages x (A | B)] [barriers] [tmem slot]
+    // carve: [stages x (A | B)] [barriers] [tmem slot]; identical offsets in both CTAs of a pair
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const int rb = 2 * p.kc;                                   // bytes per operand row
     const int stage_bytes = p.a_tile_bytes + p.b_stage_bytes;
@@ -196,7 +212,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int k_blocks = p.KH * p.KW * p.cin_chunks;
-    const int total_tiles = p.m_tiles * p.n_tiles;
+    const int rank = kPair ? (int)ptx::cluster_ctarank() : 0;
+    // work items: (tile of 128 pixels, or pair of tiles) x n_tile, walked by CTA (or cluster) index
+    const int worker = kPair ? (int)(blockIdx.x >> 1) : (int)blockIdx.x, n_workers = kPair ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+    const int total_items = (kPair ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tm_a);
@@ -204,30 +223,33 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
-        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], 4); }
+        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], kPair ? 8 : 4); }
         ptx::fence_mbar_init();
     }
-    if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_slot);
+    if (warp == 2) { if (kPair) ptx::tmem_alloc_pair<kTmemCols>(tmem_slot); else ptx::tmem_alloc<kTmemCols>(tmem_slot); }
     ptx::tc_fence_before();
-    __syncthreads();
+    if (kPair) ptx::cluster_sync(); else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
     ptx::tl_stamp_min(p.tl ? p.tl + 2 : nullptr);
 
     if (warp == 0 && lane == 0) {
-        // ===== TMA producer =====
+        // ===== TMA producer (one per CTA) =====
         int stage = 0, phase = 0;
         const bool prof = p.prof != nullptr;
         long long t_wait = 0;
         const long long t_begin = prof ? clock64() : 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const int m_tile = tile / p.n_tiles, n_tile = tile - m_tile * p.n_tiles;
+        for (int item = worker; item < total_items; item += n_workers) {
+            const int m_grp = item / p.n_tiles, n_tile = item - m_grp * p.n_tiles;
+            // an odd tile count leaves the last pair's second CTA without pixels: it reloads the last tile, stores nothing
+            const int m_tile = kPair ? min(2 * m_grp + rank, p.m_tiles - 1) : m_grp;
             const int m0 = m_tile * kBlockM;
             const int img = m0 / (p.OH * p.OW);
             const int rem = m0 - img * (p.OH * p.OW);
             const int oh = rem / p.OW, ow = rem - oh * p.OW;
             const int base_w = ow * p.stride - p.pad_w, base_h = oh * p.stride - p.pad_h;
+            const int b_row = n_tile * p.block_n + (kPair ? rank * (p.block_n / 2) : 0);
             for (int kb = 0; kb < k_blocks; ++kb) {
                 const int taps_ = p.KH * p.KW;                     // K order: channel chunk outer, filter tap inner (as in halo mode)
                 const int chunk = kb / taps_, tap = kb - chunk * taps_;
@@ -235,27 +257,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 timed_wait(&empty_bar[stage], phase ^ 1, prof, &t_wait);
                 uint8_t* a_dst = smem + (size_t)stage * stage_bytes;
                 uint8_t* b_dst = a_dst + p.a_tile_bytes;
-                ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
-                tma_load_im2col(a_dst, &tm_a, &full_bar[stage], chunk * p.kc, base_w, base_h, img, kw, kh);
-                ptx::tma_load_2d(b_dst, &tm_b, &full_bar[stage], tap * p.Cin + chunk * p.kc, n_tile * p.block_n);
+                if (kPair) {
+                    // both CTAs' bytes complete on CTA 0's barrier, which alone carries the expectation
+                    if (rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2u * (uint32_t)stage_bytes);
+                    tma_load_im2col_pair(a_dst, &tm_a, &full_bar[stage], chunk * p.kc, base_w, base_h, img, kw, kh);
+                    ptx::tma_load_2d_pair(b_dst, &tm_b, &full_bar[stage], tap * p.Cin + chunk * p.kc, b_row);
+                } else {
+                    ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
+                    tma_load_im2col(a_dst, &tm_a, &full_bar[stage], chunk * p.kc, base_w, base_h, img, kw, kh);
+                    ptx::tma_load_2d(b_dst, &tm_b, &full_bar[stage], tap * p.Cin + chunk * p.kc, b_row);
+                }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
         if (prof) { atomicAdd(&p.prof[0], 1ull); atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[2], (unsigned long long)t_wait); }
-    } else if (warp == 1 && lane == 0) {
-        // ===== MMA issuer =====
-        const uint32_t idesc = instr_desc_bf16(kBlockM, p.block_n);
+    } else if (warp == 1 && lane == 0 && rank == 0) {
+        // ===== MMA issuer (CTA 0 of a pair issues for both) =====
+        const uint32_t idesc = instr_desc_bf16(kPair ? 2 * kBlockM : kBlockM, p.block_n);
         const int last_chunk_kb = (p.cin_chunks - 1) * p.KH * p.KW;            // K blocks run chunk-major
         int stage = 0, phase = 0, acc = 0, acc_phase = 0;
         const bool prof = p.prof != nullptr;
         long long w_full = 0, w_acc = 0;
         const long long t_begin = prof ? clock64() : 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            timed_wait(&tmem_empty[acc], acc_phase ^ 1, prof, &w_acc);       // epilogue has drained this accumulator
+        for (int item = worker; item < total_items; item += n_workers) {
+            timed_wait(&tmem_empty[acc], acc_phase ^ 1, prof, &w_acc);       // the epilogue warps (of both CTAs) have drained this accumulator
             ptx::tc_fence_after();
             const uint32_t d_tmem = tmem_base + (uint32_t)(acc * 256);
             for (int kb = 0; kb < k_blocks; ++kb) {
-                timed_wait(&full_bar[stage], phase, prof, &w_full);           // TMA bytes have landed
+                timed_wait(&full_bar[stage], phase, prof, &w_full);           // TMA bytes have landed (in both CTAs)
                 ptx::tc_fence_after();
                 const uint32_t a_addr = ptx::smem_u32(smem + (size_t)stage * stage_bytes);
                 const uint64_t a_desc = smem_desc(a_addr, rb);
@@ -263,13 +292,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 // K=16 steps of this block (32 bytes, two 16-byte units each); the last channel chunk stops where the
                 // real channels end -- the rest of its rows is TMA zero fill and would add exact zeros
                 const int nk = kb >= last_chunk_kb ? p.ksteps_last : p.kc / 16;
-                for (int k = 0; k < nk; ++k)
-                    ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc,
-                                   (kb | k) != 0 ? 1u : 0u);
-                ptx::umma_commit(&empty_bar[stage]);               // frees the smem stage when the MMAs retire
+                for (int k = 0; k < nk; ++k) {
+                    if (kPair) ptx::umma_bf16_pair(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    else ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                }
+                // frees the smem stage (in both CTAs) when the MMAs retire
+                if (kPair) ptx::umma_commit_pair(&empty_bar[stage]); else ptx::umma_commit(&empty_bar[stage]);
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
-            ptx::umma_commit(&tmem_full[acc]);                     // accumulator complete -> epilogue
+            // accumulator complete -> epilogue warps (of both CTAs)
+            if (kPair) ptx::umma_commit_pair(&tmem_full[acc]); else ptx::umma_commit(&tmem_full[acc]);
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
         // all MMAs of this CTA are issued: the next kernel in the stream may now be scheduled onto SMs as they drain.
@@ -285,25 +317,26 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         const bool prof = p.prof != nullptr && threadIdx.x == 128;
         long long w_epi = 0, n_tiles_done = 0;
         const long long t_begin = prof ? clock64() : 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        for (int item = worker; item < total_items; item += n_workers) {
             ++n_tiles_done;
-            const int m_tile = tile / p.n_tiles, n_tile = tile - m_tile * p.n_tiles;
+            const int m_grp = item / p.n_tiles, n_tile = item - m_grp * p.n_tiles;
+            const int m_tile = kPair ? 2 * m_grp + rank : m_grp;
             const long long m = (long long)m_tile * kBlockM + row;
-            const bool row_ok = m < p.M;
+            const bool row_ok = m < p.M;                               // also false for the surplus CTA of an odd last pair
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
             const uint32_t t_row = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(e * 32) << 16);
             epilogue_row(p, bias, t_row, n_tile, m, row_ok);
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+            if (lane == 0) { if (kPair) ptx::mbar_arrive_leader(&tmem_empty[acc]); else ptx::mbar_arrive(&tmem_empty[acc]); }
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
         if (prof) { atomicAdd(&p.prof[6], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[7], (unsigned long long)w_epi); atomicAdd(&p.prof[8], (unsigned long long)n_tiles_done); }
     }
     ptx::tc_fence_before();
-    __syncthreads();
-    if (warp == 2) ptx::tmem_dealloc<kTmemCols>(tmem_base);
+    if (kPair) ptx::cluster_sync(); else __syncthreads();
+    if (warp == 2) { if (kPair) ptx::tmem_dealloc_pair<kTmemCols>(tmem_base); else ptx::tmem_dealloc<kTmemCols>(tmem_base); }
     ptx::tl_stamp_max(p.tl ? p.tl + 1 : nullptr);
 }
 
@@ -480,7 +513,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 }  // namespace
 
 int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan, std::string* err,
-         double* est_cycles, bool may_use_halo) {
+         double* est_cycles, bool may_use_halo, bool pair) {
     auto bad = [&](const std::string& m) { if (err) *err = "conv_pm plan: " + m; return FTF_INVALID_ARGUMENT; };
     if (n_seg < 1 || n_seg > kConvMaxSegments) return bad("segment count");
     if (g.Cin % 8 || g.in_ld % 8 || g.Cout % 16) return bad("Cin and the input row stride must be multiples of 8, Cout of 16");
@@ -539,14 +572,28 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             if (bn > 256) continue;
             const int tiles_n = (g.Cout + bn - 1) / bn;
             const long long b_bytes = (long long)bn * rb;
-            {   // one im2col load per tap
+            if (!pair) {   // one im2col load per tap.  Every operand byte is written to shared memory once and read once: 64 + N/2 cycles per MMA
                 const long long tiles = (long long)p.m_tiles * tiles_n, waves = (tiles + sm_count - 1) / sm_count;
-                const double cyc = (double)taps * total_ksteps * 128.0, bytes = (double)taps * chunks * (a_tile + b_bytes) * real_frac;
+                const double cyc = (double)taps * total_ksteps * (64.0 + bn / 2.0), bytes = (double)taps * chunks * (a_tile + b_bytes) * real_frac;
                 const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
                 if (best < 0 || t < best) {
                     best = t; p.halo_mode = 0; p.block_n = bn; p.n_tiles = tiles_n; p.kc = kc; p.cin_chunks = chunks;
                     p.a_tile_bytes = (int)a_tile; p.b_stage_bytes = (int)b_bytes;
                 }
+            } else {       // CTA pair: 256 pixels per work item, each CTA holds half of the weight rows
+                if (sm_count < 2) continue;
+                const long long items = (long long)((p.m_tiles + 1) / 2) * tiles_n, workers = sm_count / 2, waves = (items + workers - 1) / workers;
+                // Measured (tools/probe_mainloop.cu): a K block costs the issuing thread ~600 cycles whatever the MMA shape, so a
+                // pair -- same K blocks per worker, half the workers -- is modelled slightly SLOWER than one CTA per tile and
+                // is only chosen where the plan-time measurement says it wins (less weight traffic from L2).
+                const double per_mma = 64.0 + bn / 2.0;
+                const double cyc = (double)taps * total_ksteps * per_mma * 1.02, bytes = (double)taps * chunks * (a_tile + b_bytes / 2) * real_frac;
+                const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
+                if (best < 0 || t < best) {
+                    best = t; p.halo_mode = 0; p.pair = 1; p.block_n = bn; p.n_tiles = tiles_n; p.kc = kc; p.cin_chunks = chunks;
+                    p.a_tile_bytes = (int)a_tile; p.b_stage_bytes = (int)(b_bytes / 2);
+                }
+                continue;
             }
             if (!(allow_halo && g.stride == 1 && taps > 1)) continue;
             for (int S = 1; S <= 4; S *= 2) {
@@ -600,7 +647,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
         const cuuint64_t K = (cuuint64_t)g.KH * g.KW * g.Cin;
         cuuint64_t dims[2] = {K, (cuuint64_t)g.Cout};
         cuuint64_t strides[1] = {K * 2};
-        cuuint32_t box[2] = {(cuuint32_t)p.kc, (cuuint32_t)p.block_n};
+        cuuint32_t box[2] = {(cuuint32_t)p.kc, (cuuint32_t)(p.pair ? p.block_n / 2 : p.block_n)};
         cuuint32_t estr[2] = {1, 1};
         CUresult rc = enc_tiled(&plan->tm_b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)g.weights, dims, strides, box, estr,
                                 CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -610,11 +657,13 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     static std::once_flag attr_once;
     static cudaError_t attr_rc = cudaSuccess;
     std::call_once(attr_once, [] {
-        attr_rc = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+        attr_rc = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     });
     // the attribute is per device: set it again when planning on another device
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc_kernel)", err);
+    e = cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc_kernel<pair>)", err);
     e = cudaFuncSetAttribute(conv_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxDynSmem);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_halo_kernel)", err);
     return FTF_OK;
@@ -644,9 +693,16 @@ int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsign
         count_launch();
         return FTF_OK;
     }
+    if (p.pair) {
+        const int items = (p.m_tiles + 1) / 2 * p.n_tiles, workers = plan.grid / 2;
+        const int grid = 2 * (items < workers ? items : workers);
+        FTF_CUDA(launch_pdl_cluster(conv_tc_kernel<true>, dim3(grid), dim3(kThreads), plan.smem, s, /*cluster=*/2, plan.tm_a, plan.tm_b, p), err);
+        count_launch();
+        return FTF_OK;
+    }
     const int tiles = p.m_tiles * p.n_tiles;
     const int grid = tiles < plan.grid ? tiles : plan.grid;
-    FTF_CUDA(launch_pdl(conv_tc_kernel, dim3(grid), dim3(kThreads), plan.smem, s, plan.tm_a, plan.tm_b, p), err);
+    FTF_CUDA(launch_pdl(conv_tc_kernel<false>, dim3(grid), dim3(kThreads), plan.smem, s, plan.tm_a, plan.tm_b, p), err);
     count_launch();
     return FTF_OK;
 }

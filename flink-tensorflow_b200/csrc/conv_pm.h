@@ -29,6 +29,7 @@ struct ConvParams {
     int a_stage_bytes;          // a_loads * kHaloLoadRows * 128
     int b_stages;               // weight-tile ring depth
     int acc_stages;             // 1 or 2 TMEM accumulator sets of S * block_n columns
+    int pair;                   // 1: CTA-pair kernel (cta_group::2): tiles of 256 pixels, each CTA holds block_n/2 weight rows
     int ksteps_last;            // K=16 steps holding real channels in the LAST channel chunk (the all-zero rest is skipped)
     unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
     unsigned long long* tl;     // timeline stamps of this launch (FTF_TIMELINE), else NULL
@@ -47,7 +48,7 @@ struct ConvPlan {
 // Encodes the tensor maps and tile shapes for one convolution (called once, at network build).
 // *est_cycles: modelled cycles of the whole layer on sm_count SMs (for choosing between the two kernels).
 int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
-         std::string* err, double* est_cycles, bool may_use_halo = true);
+         std::string* err, double* est_cycles, bool may_use_halo = true, bool pair = false);
 // Enqueues the convolution for the first n images.
 int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
 // Diagnostic: copies (and optionally clears) the 16 pipeline cycle counters the kernels accumulate when the

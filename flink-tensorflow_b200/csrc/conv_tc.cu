@@ -27,23 +27,29 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     const char* tenv = getenv("FTF_CONV_TUNE");
     const bool halo_only = getenv("FTF_CONV_HALO_ONLY") != nullptr;     // profiling: drop the im2col candidate where a halo one exists
     if (tenv) tune = tenv[0] == '1';
-    ConvPlan cands[4];
+    ConvPlan cands[5];
     int n_cand = 0;
     std::string first_err;
-    for (int kind = 0; kind < 2; ++kind) {
-        if (force && ((force[0] == 'p' && kind == 1) || (force[0] == 'w' && kind == 0))) continue;
-        for (int halo = 0; halo < 2; ++halo) {
-            ConvPlan& c = cands[n_cand];
-            c.kind = kind;
-            std::string e;
-            const int rc = kind ? wm::plan(g, segs, n_seg, sm_count, &c.wm, &e, &c.est_cycles, halo != 0)
-                                : pm::plan(g, segs, n_seg, sm_count, &c.pm, &e, &c.est_cycles, halo != 0);
-            if (rc == FTF_INTERNAL) { if (err) *err = e; return rc; }   // a CUDA/driver failure, not "this variant does not apply"
-            if (rc) { if (first_err.empty()) first_err = e; continue; }
-            const bool is_halo = kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
-            if (halo && !is_halo) continue;                    // same plan as the no-halo candidate
-            ++n_cand;
-        }
+    // candidates: pixel-major (im2col / halo window / CTA pair), weight-major (im2col / halo window)
+    struct Variant { int kind; bool halo, pair; };
+    static const Variant kVariants[] = {{0, false, false}, {0, true, false}, {0, false, true}, {1, false, false}, {1, true, false}};
+    static const bool no_pair = getenv("FTF_NO_PAIR") != nullptr;
+    for (const Variant& v : kVariants) {
+        if (force) {   // FTF_CONV_KIND: "pm" = one-CTA pixel-major, "pm2" = CTA-pair pixel-major, "wm" = weight-major
+            const bool want_pair = force[0] == 'p' && force[2] == '2';
+            if ((force[0] == 'p') != (v.kind == 0) || (v.kind == 0 && want_pair != v.pair)) continue;
+        } else if (v.pair && no_pair) continue;
+        ConvPlan& c = cands[n_cand];
+        c.kind = v.kind;
+        std::string e;
+        const int rc = v.kind ? wm::plan(g, segs, n_seg, sm_count, &c.wm, &e, &c.est_cycles, v.halo)
+                              : pm::plan(g, segs, n_seg, sm_count, &c.pm, &e, &c.est_cycles, v.halo, v.pair);
+        if (rc == FTF_INTERNAL) { if (err) *err = e; return rc; }   // a CUDA/driver failure, not "this variant does not apply"
+        if (rc) { if (first_err.empty()) first_err = e; continue; }
+        const bool is_halo = v.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
+        if (v.halo && !is_halo) continue;                      // same plan as the no-halo candidate
+        if (v.pair && !c.pm.p.pair) continue;
+        ++n_cand;
     }
     if (n_cand == 0) { if (err) *err = first_err; return FTF_INVALID_ARGUMENT; }
     if (halo_only) {
@@ -69,7 +75,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
             auto describe = [&](int i, float t) {
                 const ConvPlan& c = cands[i];
                 const bool hm = c.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
-                fprintf(stderr, "   candidate %s%s kc %d: %.1f us (model %.0f cycles)%s\n", c.kind ? "wm" : "pm", hm ? " halo" : "",
+                fprintf(stderr, "   candidate %s%s kc %d: %.1f us (model %.0f cycles)%s\n", c.kind ? "wm" : (c.pm.p.pair ? "pm pair" : "pm"), hm ? " halo" : "",
                         c.kind ? c.wm.p.kc : c.pm.p.kc, t * 1e3f, c.est_cycles, i == model ? "  <- model" : "");
             };
             float best_t = time_candidate(cands[model], g.n_max, s, e0, e1);
@@ -90,7 +96,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     if (getenv("FTF_CONV_VERBOSE")) {
         const bool hm = plan->kind ? plan->wm.p.halo_mode : plan->pm.p.halo_mode;
         fprintf(stderr, "conv %dx%d s%d Cin %d Cout %d HxW %dx%d -> %s%s kc %d (%d candidates, %s)\n", g.KH, g.KW, g.stride, g.Cin, g.Cout, g.H, g.W,
-                plan->kind ? "weight-major" : "pixel-major", hm ? " halo" : "", plan->kind ? plan->wm.p.kc : plan->pm.p.kc, n_cand, tune ? "timed" : "model");
+                plan->kind ? "weight-major" : (plan->pm.p.pair ? "pixel-major pair" : "pixel-major"), hm ? " halo" : "", plan->kind ? plan->wm.p.kc : plan->pm.p.kc, n_cand, tune ? "timed" : "model");
     }
     return FTF_OK;
 }

@@ -581,7 +581,7 @@ static void dump_timeline(InceptionV3::Impl& m, int nb) {
         if (op.type == Op::kConv) {
             const ConvPlan& pl = m.plans[op.plan];
             const bool hm = pl.kind ? pl.wm.p.halo_mode : pl.pm.p.halo_mode;
-            tag += pl.kind ? " [wm" : " [pm";
+            tag += pl.kind ? " [wm" : (pl.pm.p.pair ? " [pm pair" : " [pm");
             tag += hm ? " halo]" : "]";
         }
         fprintf(stderr, "%4zu %4d %-8s %9.1f %9.1f %9.1f %8.1f  %s\n", k, op.lane, kNames[op.type], a, g, b, b - g, tag.c_str());

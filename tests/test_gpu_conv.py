@@ -100,7 +100,7 @@ def test_conv_tc_is_batch_independent(dev, oracle):
 
 
 def test_conv_variants_agree(dev, monkeypatch):
-    """The plan may pick either kernel (pixel-major / weight-major), with or without the halo window.  All of them
+    """The plan may pick either kernel (pixel-major, also as a CTA pair / weight-major), with or without the halo window.  All of them
     accumulate K in the same order (channel chunk, filter tap, 16-element step): the halo window changes nothing in a
     kernel's result, and the two kernels agree to fp32 accumulation rounding."""
     import torch
@@ -111,8 +111,10 @@ def test_conv_variants_agree(dev, monkeypatch):
         wt = _to_bf16_cuda(rng.standard_normal((cout, kh, kw, cin)) * np.sqrt(2.0 / (kh * kw * cin)))
         b = torch.from_numpy(rng.uniform(-0.1, 0.1, cout).astype(np.float32)).cuda()
         outs = {}
-        for kind in ("pm", "wm"):
+        for kind in ("pm", "wm", "pm2"):
             for no_halo in ("1", "0"):
+                if kind == "pm2" and no_halo == "0":
+                    continue                                   # the CTA-pair kernel has no halo variant
                 monkeypatch.setenv("FTF_CONV_KIND", kind)
                 monkeypatch.setenv("FTF_NO_HALO", no_halo)
                 monkeypatch.setenv("FTF_CONV_TUNE", "0")
@@ -123,6 +125,7 @@ def test_conv_variants_agree(dev, monkeypatch):
         diffs = {k: float((v - outs[("pm", "1")]).abs().max()) / scale for k, v in outs.items()}
         assert torch.equal(outs[("pm", "0")], outs[("pm", "1")]), diffs
         assert torch.equal(outs[("wm", "0")], outs[("wm", "1")]), diffs
+        assert torch.equal(outs[("pm2", "1")], outs[("pm", "1")]), diffs      # cta_group::2: same K order, same bits
         assert diffs[("wm", "1")] <= 1e-5, diffs
 
 
