@@ -185,17 +185,31 @@ static void tap(net_t* N, const char* name, const tens* t) {
     if (N->tap_out && len <= N->tap_cap) memcpy(N->tap_out, t->d, sizeof(float) * (size_t)len);
 }
 
+/* Generated layer parameters are kept between forward passes (the product builds its weights once, at create; a CPU
+ * arm that regenerated 24 M normal draws per pass would time the generator, not the convolutions).  Keyed by everything
+ * that determines the values; single-threaded use (the parallelism is inside a convolution). */
+typedef struct wcache { uint64_t seed; char name[96]; int cout, kh, kw, cin, mode; float* w; float* b; struct wcache* next; } wcache;
+static wcache* g_wcache = NULL;
+static const wcache* layer_params(net_t* N, const char* name, int cout, int kh, int kw, int cin) {
+    for (wcache* e = g_wcache; e; e = e->next)
+        if (e->seed == N->seed && e->cout == cout && e->kh == kh && e->kw == kw && e->cin == cin && e->mode == N->mode && !strcmp(e->name, name)) return e;
+    wcache* e = (wcache*)calloc(1, sizeof(wcache));
+    const size_t nw = (size_t)cout * kh * kw * cin;
+    e->seed = N->seed; snprintf(e->name, sizeof e->name, "%s", name); e->cout = cout; e->kh = kh; e->kw = kw; e->cin = cin; e->mode = N->mode;
+    e->w = (float*)malloc(sizeof(float) * nw);
+    e->b = (float*)malloc(sizeof(float) * (size_t)cout);
+    orc_inc_conv_params(N->seed, name, cout, kh, kw, cin, e->w, e->b);
+    if (N->mode == 1) for (size_t i = 0; i < nw; ++i) e->w[i] = orc_bf16_round(e->w[i]);
+    e->next = g_wcache; g_wcache = e;
+    return e;
+}
+
 /* conv + folded BN + ReLU into a slice of `out`; pre_only: raw conv output (no bias/relu/rounding) */
 static void conv_into(net_t* N, const char* name, const tens* in, int cout, int kh, int kw, int s, int ph, int pw,
                       tens* out, int off, int pre_only) {
-    const size_t nw = (size_t)cout * kh * kw * in->c;
-    float* w = (float*)malloc(sizeof(float) * nw);
-    float* b = (float*)malloc(sizeof(float) * (size_t)cout);
-    orc_inc_conv_params(N->seed, name, cout, kh, kw, in->c, w, b);
-    if (N->mode == 1) for (size_t i = 0; i < nw; ++i) w[i] = orc_bf16_round(w[i]);
-    orc_conv2d_nhwc(in->d, in->n, in->h, in->w, in->c, w, b, cout, kh, kw, s, s, ph, pw, !pre_only, !pre_only,
+    const wcache* L = layer_params(N, name, cout, kh, kw, in->c);
+    orc_conv2d_nhwc(in->d, in->n, in->h, in->w, in->c, L->w, L->b, cout, kh, kw, s, s, ph, pw, !pre_only, !pre_only,
                     !pre_only && N->mode == 1, out->d, out->c, off, N->threads);
-    free(w); free(b);
 }
 static tens conv(net_t* N, const char* name, const tens* in, int cout, int kh, int kw, int s, int ph, int pw) {
     tens out = t_new(in->n, (in->h + 2 * ph - kh) / s + 1, (in->w + 2 * pw - kw) / s + 1, cout);
@@ -206,11 +220,8 @@ static tens conv(net_t* N, const char* name, const tens* in, int cout, int kh, i
 static void pool_branch(net_t* N, const char* name, const tens* in, int cout, tens* out, int off) {
     tens pre = t_new(in->n, in->h, in->w, cout);
     conv_into(N, name, in, cout, 1, 1, 1, 0, 0, &pre, 0, 1);
-    float* w = (float*)malloc(sizeof(float) * (size_t)cout * in->c);
-    float* b = (float*)malloc(sizeof(float) * (size_t)cout);
-    orc_inc_conv_params(N->seed, name, cout, 1, 1, in->c, w, b);
-    avgpool_bias_relu(&pre, b, N->mode == 1, out->d, out->c, off);
-    free(w); free(b); t_free(&pre);
+    avgpool_bias_relu(&pre, layer_params(N, name, cout, 1, 1, in->c)->b, N->mode == 1, out->d, out->c, off);
+    t_free(&pre);
 }
 #define NAME(buf, blk, leaf) (snprintf(buf, sizeof buf, "%s.%s", blk, leaf), buf)
 
