@@ -234,8 +234,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
     ptx::tl_stamp_min(p.tl ? p.tl + 2 : nullptr);
 
-    if (warp == 0 && lane == 0) {
-        // ===== TMA producer (one per CTA) =====
+    if (warp == 0) {
+        // ===== TMA producer (one warp per CTA; whole-warp issue, one elected lane per instruction) =====
         int stage = 0, phase = 0;
         const bool prof = p.prof != nullptr;
         long long t_wait = 0;
@@ -257,22 +257,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 timed_wait(&empty_bar[stage], phase ^ 1, prof, &t_wait);
                 uint8_t* a_dst = smem + (size_t)stage * stage_bytes;
                 uint8_t* b_dst = a_dst + p.a_tile_bytes;
-                if (kPair) {
-                    // both CTAs' bytes complete on CTA 0's barrier, which alone carries the expectation
-                    if (rank == 0) ptx::mbar_expect_tx(&full_bar[stage], 2u * (uint32_t)stage_bytes);
-                    tma_load_im2col_pair(a_dst, &tm_a, &full_bar[stage], chunk * p.kc, base_w, base_h, img, kw, kh);
-                    ptx::tma_load_2d_pair(b_dst, &tm_b, &full_bar[stage], tap * p.Cin + chunk * p.kc, b_row);
-                } else {
-                    ptx::mbar_expect_tx(&full_bar[stage], (uint32_t)stage_bytes);
-                    tma_load_im2col(a_dst, &tm_a, &full_bar[stage], chunk * p.kc, base_w, base_h, img, kw, kh);
-                    ptx::tma_load_2d(b_dst, &tm_b, &full_bar[stage], tap * p.Cin + chunk * p.kc, b_row);
-                }
+                // pair: both CTAs' bytes complete on CTA 0's barrier, which alone carries the expectation
+                if (!kPair || rank == 0) ptx::mbar_expect_tx_elect(&full_bar[stage], (kPair ? 2u : 1u) * (uint32_t)stage_bytes);
+                ptx::tma_load_im2col_elect(a_dst, &tm_a, &full_bar[stage], chunk * p.kc, base_w, base_h, img, kw, kh, kPair);
+                ptx::tma_load_2d_elect(b_dst, &tm_b, &full_bar[stage], tap * p.Cin + chunk * p.kc, b_row, kPair);
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
-        if (prof) { atomicAdd(&p.prof[0], 1ull); atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[2], (unsigned long long)t_wait); }
-    } else if (warp == 1 && lane == 0 && rank == 0) {
-        // ===== MMA issuer (CTA 0 of a pair issues for both) =====
+        if (prof && lane == 0) { atomicAdd(&p.prof[0], 1ull); atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[2], (unsigned long long)t_wait); }
+    } else if (warp == 1 && rank == 0) {
+        // ===== MMA issuer: the whole warp walks the loop, one elected lane issues (CTA 0 of a pair issues for both) =====
         const uint32_t idesc = instr_desc_bf16(kPair ? 2 * kBlockM : kBlockM, p.block_n);
         const int last_chunk_kb = (p.cin_chunks - 1) * p.KH * p.KW;            // K blocks run chunk-major
         int stage = 0, phase = 0, acc = 0, acc_phase = 0;
@@ -293,21 +287,21 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 // real channels end -- the rest of its rows is TMA zero fill and would add exact zeros
                 const int nk = kb >= last_chunk_kb ? p.ksteps_last : p.kc / 16;
                 for (int k = 0; k < nk; ++k) {
-                    if (kPair) ptx::umma_bf16_pair(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
-                    else ptx::umma_bf16(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    if (kPair) ptx::umma_bf16_pair_elect(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    else ptx::umma_bf16_elect(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
                 }
                 // frees the smem stage (in both CTAs) when the MMAs retire
-                if (kPair) ptx::umma_commit_pair(&empty_bar[stage]); else ptx::umma_commit(&empty_bar[stage]);
+                if (kPair) ptx::umma_commit_pair_elect(&empty_bar[stage]); else ptx::umma_commit_elect(&empty_bar[stage]);
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
             // accumulator complete -> epilogue warps (of both CTAs)
-            if (kPair) ptx::umma_commit_pair(&tmem_full[acc]); else ptx::umma_commit(&tmem_full[acc]);
+            if (kPair) ptx::umma_commit_pair_elect(&tmem_full[acc]); else ptx::umma_commit_elect(&tmem_full[acc]);
             if (++acc == kAccStages) { acc = 0; acc_phase ^= 1; }
         }
         // all MMAs of this CTA are issued: the next kernel in the stream may now be scheduled onto SMs as they drain.
         // (Triggering at kernel start parks its CTAs -- with their shared memory -- on SMs a sibling branch could use.)
         ptx::pdl_launch_dependents();
-        if (prof) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
+        if (prof && lane == 0) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
     } else if (warp >= 4) {
         // ===== epilogue: TMEM -> registers -> bias/ReLU -> global =====
         const float* bias = stage_bias(p, bias_s);
@@ -397,7 +391,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
     ptx::tl_stamp_min(p.tl ? p.tl + 2 : nullptr);
 
-    if (warp == 0 && lane == 0) {
+    if (warp == 0) {
         // ===== TMA producer =====
         int as = 0, aph = 0, bs = 0, bph = 0;
         const bool prof = p.prof != nullptr;
@@ -409,29 +403,29 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             for (int chunk = 0; chunk < p.cin_chunks; ++chunk) {
                 timed_wait(&a_empty[as], aph ^ 1, prof, &t_wait);
                 uint8_t* a_dst = a_base + (size_t)as * p.a_stage_bytes;
-                ptx::mbar_expect_tx(&a_full[as], (uint32_t)p.a_stage_bytes);
+                ptx::mbar_expect_tx_elect(&a_full[as], (uint32_t)p.a_stage_bytes);
                 for (int i = 0; i < p.a_loads; ++i) {           // the window, kHaloLoadRows padded pixels per load
                     const long long q = q0 + (long long)i * kHaloLoadRows;
                     const int wp = (int)(q % p.Wp);
                     const long long t = q / p.Wp;
                     const int hp = (int)(t % p.Hp);
                     const int img = (int)(t / p.Hp);
-                    tma_load_im2col(a_dst + (size_t)i * kHaloLoadRows * rb, &tm_a, &a_full[as], chunk * p.kc, wp - p.pad_w,
-                                    hp - p.pad_h, img, 0, 0);
+                    ptx::tma_load_im2col_elect(a_dst + (size_t)i * kHaloLoadRows * rb, &tm_a, &a_full[as], chunk * p.kc, wp - p.pad_w,
+                                    hp - p.pad_h, img, 0, 0, false);
                 }
                 for (int tap = 0; tap < taps; ++tap) {
                     timed_wait(&b_empty[bs], bph ^ 1, prof, &t_wait);
-                    ptx::mbar_expect_tx(&b_full[bs], (uint32_t)p.b_stage_bytes);
-                    ptx::tma_load_2d(b_base + (size_t)bs * p.b_stage_bytes, &tm_b, &b_full[bs], tap * p.Cin + chunk * p.kc,
-                                     n_tile * p.block_n);
+                    ptx::mbar_expect_tx_elect(&b_full[bs], (uint32_t)p.b_stage_bytes);
+                    ptx::tma_load_2d_elect(b_base + (size_t)bs * p.b_stage_bytes, &tm_b, &b_full[bs], tap * p.Cin + chunk * p.kc,
+                                     n_tile * p.block_n, false);
                     if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
                 }
                 if (++as == kAStages) { as = 0; aph ^= 1; }
             }
         }
-        if (prof) { atomicAdd(&p.prof[0], 1ull); atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[2], (unsigned long long)t_wait); }
-    } else if (warp == 1 && lane == 0) {
-        // ===== MMA issuer =====
+        if (prof && lane == 0) { atomicAdd(&p.prof[0], 1ull); atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[2], (unsigned long long)t_wait); }
+    } else if (warp == 1) {
+        // ===== MMA issuer: whole warp, one elected lane issues =====
         const uint32_t idesc = instr_desc_bf16(kBlockM, p.block_n);
         int as = 0, aph = 0, bs = 0, bph = 0, acc = 0, acc_phase = 0;
         const bool prof = p.prof != nullptr;
@@ -456,22 +450,22 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                         // tap (kh, kw) of sub-tile s: the window entered (s*128 + kh*Wp + kw) rows further down
                         const uint64_t a_desc = smem_desc(a_addr + (uint32_t)(s * kBlockM + kh * p.Wp + kw) * (uint32_t)rb, rb);
                         for (int k = 0; k < nk; ++k)
-                            ptx::umma_bf16(d_tmem + (uint32_t)(s * p.block_n), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k),
+                            ptx::umma_bf16_elect(d_tmem + (uint32_t)(s * p.block_n), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k),
                                            idesc, (first | (uint32_t)k) != 0 ? 1u : 0u);
                     }
-                    ptx::umma_commit(&b_empty[bs]);
+                    ptx::umma_commit_elect(&b_empty[bs]);
                     if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
                 }
-                ptx::umma_commit(&a_empty[as]);
+                ptx::umma_commit_elect(&a_empty[as]);
                 if (++as == kAStages) { as = 0; aph ^= 1; }
             }
-            ptx::umma_commit(&tmem_full[acc]);
+            ptx::umma_commit_elect(&tmem_full[acc]);
             if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1; }
         }
         // all MMAs of this CTA are issued: the next kernel in the stream may now be scheduled onto SMs as they drain.
         // (Triggering at kernel start parks its CTAs -- with their shared memory -- on SMs a sibling branch could use.)
         ptx::pdl_launch_dependents();
-        if (prof) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
+        if (prof && lane == 0) { atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin)); atomicAdd(&p.prof[4], (unsigned long long)w_full); atomicAdd(&p.prof[5], (unsigned long long)w_acc); }
     } else if (warp >= 4) {
         // ===== epilogue =====
         const float* bias = stage_bias(p, bias_s);

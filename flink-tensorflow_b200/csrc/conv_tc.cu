@@ -33,7 +33,9 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     // candidates: pixel-major (im2col / halo window / CTA pair), weight-major (im2col / halo window)
     struct Variant { int kind; bool halo, pair; };
     static const Variant kVariants[] = {{0, false, false}, {0, true, false}, {0, false, true}, {1, false, false}, {1, true, false}};
-    static const bool no_pair = getenv("FTF_NO_PAIR") != nullptr;
+    // the CTA-pair kernel ties with the one-CTA kernel in isolation and loses a little inside the network (half as many,
+    // twice as large work items per layer): a candidate only on request (FTF_CONV_PAIR=1) or when forced (FTF_CONV_KIND=pm2)
+    static const bool no_pair = !(getenv("FTF_CONV_PAIR") && getenv("FTF_CONV_PAIR")[0] == '1');
     for (const Variant& v : kVariants) {
         if (force) {   // FTF_CONV_KIND: "pm" = one-CTA pixel-major, "pm2" = CTA-pair pixel-major, "wm" = weight-major
             const bool want_pair = force[0] == 'p' && force[2] == '2';

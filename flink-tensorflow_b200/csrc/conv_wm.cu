@@ -159,7 +159,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
     ptx::pdl_wait();                   // the previous kernel's outputs (this layer's input) are complete
     ptx::tl_stamp_min(p.tl ? p.tl + 2 : nullptr);
 
-    if (warp == 0 && lane == 0) {
+    if (warp == 0) {
         // ===================================== TMA producer =====================================
         long long t_wait = 0;
         const long long t_begin = profiling ? clock64() : 0;
@@ -177,9 +177,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                         const int kh = tap / p.KW, kw = tap - kh * p.KW;
                         timed_wait(&bars->a_empty[as], aph ^ 1, profiling, &t_wait);
                         uint8_t* w_dst = smem + (size_t)as * stage_bytes;
-                        ptx::mbar_expect_tx(&bars->a_full[as], (uint32_t)stage_bytes);
-                        ptx::tma_load_2d(w_dst, &tm_w, &bars->a_full[as], tap * p.Cin + chunk * p.kc, m_tile * kWRows);
-                        tma_load_im2col(w_dst + p.w_stage_bytes, &tm_p, &bars->a_full[as], chunk * p.kc, base_w, base_h, img, kw, kh);
+                        ptx::mbar_expect_tx_elect(&bars->a_full[as], (uint32_t)stage_bytes);
+                        ptx::tma_load_2d_elect(w_dst, &tm_w, &bars->a_full[as], tap * p.Cin + chunk * p.kc, m_tile * kWRows, false);
+                        ptx::tma_load_im2col_elect(w_dst + p.w_stage_bytes, &tm_p, &bars->a_full[as], chunk * p.kc, base_w, base_h, img, kw, kh, false);
                         if (++as == p.stages) { as = 0; aph ^= 1; }
                     }
                 }
@@ -187,34 +187,34 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                 for (int chunk = 0; chunk < p.cin_chunks; ++chunk) {
                     timed_wait(&bars->a_empty[as], aph ^ 1, profiling, &t_wait);
                     uint8_t* dst = win_base + (size_t)as * p.p_stage_bytes;
-                    ptx::mbar_expect_tx(&bars->a_full[as], (uint32_t)p.p_stage_bytes);
+                    ptx::mbar_expect_tx_elect(&bars->a_full[as], (uint32_t)p.p_stage_bytes);
                     for (int i = 0; i < p.p_loads; ++i) {                  // the window, kHaloLoadRows padded pixels per load
                         const long long q = x0 + (long long)i * kHaloLoadRows;
                         const int wp = (int)(q % p.Wp);
                         const long long t = q / p.Wp;
                         const int hp = (int)(t % p.Hp);
                         const int img = (int)(t / p.Hp);
-                        tma_load_im2col(dst + (size_t)i * kHaloLoadRows * rb, &tm_p, &bars->a_full[as], chunk * p.kc, wp - p.pad_w,
-                                        hp - p.pad_h, img, 0, 0);
+                        ptx::tma_load_im2col_elect(dst + (size_t)i * kHaloLoadRows * rb, &tm_p, &bars->a_full[as], chunk * p.kc, wp - p.pad_w,
+                                        hp - p.pad_h, img, 0, 0, false);
                     }
                     for (int tap = 0; tap < taps; ++tap) {
                         timed_wait(&bars->b_empty[bs], bph ^ 1, profiling, &t_wait);
-                        ptx::mbar_expect_tx(&bars->b_full[bs], (uint32_t)p.w_stage_bytes);
-                        ptx::tma_load_2d(wt_base + (size_t)bs * p.w_stage_bytes, &tm_w, &bars->b_full[bs], tap * p.Cin + chunk * p.kc,
-                                         m_tile * kWRows);
+                        ptx::mbar_expect_tx_elect(&bars->b_full[bs], (uint32_t)p.w_stage_bytes);
+                        ptx::tma_load_2d_elect(wt_base + (size_t)bs * p.w_stage_bytes, &tm_w, &bars->b_full[bs], tap * p.Cin + chunk * p.kc,
+                                         m_tile * kWRows, false);
                         if (++bs == p.w_stages) { bs = 0; bph ^= 1; }
                     }
                     if (++as == 2) { as = 0; aph ^= 1; }
                 }
             }
         }
-        if (profiling) {
+        if (profiling && lane == 0) {
             atomicAdd(&p.prof[0], 1ull);
             atomicAdd(&p.prof[1], (unsigned long long)(clock64() - t_begin));
             atomicAdd(&p.prof[2], (unsigned long long)t_wait);
         }
-    } else if (warp == 1 && lane == 0) {
-        // ===================================== MMA issuer =====================================
+    } else if (warp == 1) {
+        // ============== MMA issuer: the whole warp walks the loop, one elected lane issues (see ptx.cuh) ==============
         const uint32_t idesc = instr_desc_bf16(kWRows, p.np);
         const int ksteps = p.kc / 16;
         long long w_full = 0, w_acc = 0;
@@ -233,8 +233,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                     const uint64_t w_desc = smem_desc(w_addr, rb), x_desc = smem_desc(w_addr + p.w_stage_bytes, rb);
                     const int nk = kb >= (p.cin_chunks - 1) * taps ? p.ksteps_last : ksteps;      // skip the all-zero K steps of the last chunk
                     for (int k = 0; k < nk; ++k)                               // 32 bytes (two 16-byte units) per K = 16 step
-                        ptx::umma_bf16(d_tmem, w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
-                    ptx::umma_commit(&bars->a_empty[as]);                      // frees the stage when these MMAs retire
+                        ptx::umma_bf16_elect(d_tmem, w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    ptx::umma_commit_elect(&bars->a_empty[as]);                      // frees the stage when these MMAs retire
                     if (++as == p.stages) { as = 0; aph ^= 1; }
                 }
             } else {
@@ -253,23 +253,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                             // tap (kh, kw) of sub-tile s: the window entered (s*np + kh*Wp + kw) rows further down
                             const uint64_t x_desc = smem_desc(win_addr + (uint32_t)(s * p.np + kh * p.Wp + kw) * (uint32_t)rb, rb);
                             for (int k = 0; k < nk; ++k)
-                                ptx::umma_bf16(d_tmem + (uint32_t)(s * p.np), w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc,
+                                ptx::umma_bf16_elect(d_tmem + (uint32_t)(s * p.np), w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc,
                                                (first | (uint32_t)k) != 0 ? 1u : 0u);
                         }
-                        ptx::umma_commit(&bars->b_empty[bs]);
+                        ptx::umma_commit_elect(&bars->b_empty[bs]);
                         if (++bs == p.w_stages) { bs = 0; bph ^= 1; }
                     }
-                    ptx::umma_commit(&bars->a_empty[as]);
+                    ptx::umma_commit_elect(&bars->a_empty[as]);
                     if (++as == 2) { as = 0; aph ^= 1; }
                 }
             }
-            ptx::umma_commit(&bars->tmem_full[acc]);                           // accumulator complete -> epilogue
+            ptx::umma_commit_elect(&bars->tmem_full[acc]);                           // accumulator complete -> epilogue
             if (++acc == p.acc_stages) { acc = 0; acc_phase ^= 1; }
         }
         // all MMAs of this CTA are issued: the next kernel in the stream may now be scheduled onto SMs as they drain.
         // (Triggering at kernel start parks its CTAs -- with their shared memory -- on SMs a sibling branch could use.)
         ptx::pdl_launch_dependents();
-        if (profiling) {
+        if (profiling && lane == 0) {
             atomicAdd(&p.prof[3], (unsigned long long)(clock64() - t_begin));
             atomicAdd(&p.prof[4], (unsigned long long)w_full);
             atomicAdd(&p.prof[5], (unsigned long long)w_acc);

@@ -106,7 +106,7 @@ __device__ __forceinline__ void band_columns(const ResizeParams& p, uint32_t sba
 
 // ---- TMA-staged band kernel -------------------------------------------------------------------
 // Persistent: a CTA walks bands blockIdx.x, blockIdx.x + gridDim.x, ... through two shared-memory stages guarded by
-// full/empty mbarriers: thread 0 refills a stage as soon as all eight warps have released it, and no warp ever waits for
+// full/empty mbarriers: warp 0 refills a stage as soon as all eight warps have released it, and no warp ever waits for
 // another one (no __syncthreads in the loop), so the warps drift apart and hide each other's shared-memory latency.
 template <bool kMulRecip, typename OutT>
 __global__ void __launch_bounds__(kThreads, 4)
@@ -115,13 +115,14 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full[2], empty[2];
 
-    auto issue = [&](long long blk, int stage) {       // one thread: fetch the input rows of band `blk`
+    // run by all lanes of warp 0 on warp-uniform values; one elected lane issues each instruction (see ptx.cuh)
+    auto issue = [&](long long blk, int stage) {       // fetch the input rows of band `blk`
         const long long img = blk / p.bands;
         const int band = (int)(blk - img * p.bands);
         const int iy0 = (int)__fmul_rn((float)(band * p.th), p.hs);
-        ptx::mbar_expect_tx(&full[stage], (uint32_t)(p.n_chunks * p.cw * p.br));
+        ptx::mbar_expect_tx_elect(&full[stage], (uint32_t)(p.n_chunks * p.cw * p.br));
         for (int k = 0; k < p.n_chunks; ++k)
-            ptx::tma_load_3d(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, &tmap, &full[stage], k * p.cw, iy0, (int)img);
+            ptx::tma_load_3d_elect(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, &tmap, &full[stage], k * p.cw, iy0, (int)img);
     };
 
     if (threadIdx.x == 0) {
@@ -132,7 +133,7 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
         ptx::fence_mbar_init();
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
+    if (threadIdx.x < 32) {
         if ((long long)blockIdx.x < total_bands) issue(blockIdx.x, 0);
         if ((long long)blockIdx.x + gridDim.x < total_bands) issue((long long)blockIdx.x + gridDim.x, 1);
     }
@@ -169,7 +170,7 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
         // this warp is done with the stage; thread 0 refills it (band it+2) once every warp has said so
         __syncwarp();
         if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&empty[stage]);
-        if (threadIdx.x == 0 && blk + 2ll * gridDim.x < total_bands) {
+        if (threadIdx.x < 32 && blk + 2ll * gridDim.x < total_bands) {     // warp 0 refills
             ptx::mbar_wait(&empty[stage], phase);
             issue(blk + 2ll * gridDim.x, stage);
         }

@@ -187,6 +187,102 @@ __device__ __forceinline__ void umma_commit_pair(uint64_t* bar) {
                  : "memory");
 }
 
+// ---- whole-warp issue ----------------------------------------------------------------------------------------
+// The MMA warp runs its loop with all 32 lanes on warp-uniform values and one elected lane issues each instruction.  With a
+// single-lane branch (`if (lane == 0)`) the compiler cannot keep the descriptors in uniform registers and wraps every
+// tcgen05.mma in an ELECT / R2UR.BROADCAST / BRA.U.ANY waterfall: measured 69 cycles per MMA issue against 45 this way
+// (tools/probe_mainloop.cu: 612 -> 460 cycles per K = 64 block).
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_bf16_pair_elect(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+        "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair_elect(uint64_t* bar) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+        "h"((uint16_t)3)
+        : "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx_elect(uint64_t* bar, uint32_t bytes) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(smem_u32(bar)), "r"(bytes)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_elect(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "elect.sync _|q, 0xffffffff;\n\t"
+        "@q cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];\n\t}" ::"r"(
+            smem_u32(dst)),
+        "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2)
+        : "memory");
+}
+// pair != 0: the cta_group::2 form, completing on CTA 0's barrier
+__device__ __forceinline__ void tma_load_2d_elect(void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, bool pair) {
+    if (pair)
+        asm volatile(
+            "{\n\t.reg .pred q;\n\t"
+            "elect.sync _|q, 0xffffffff;\n\t"
+            "@q cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}" ::"r"(
+                smem_u32(dst)),
+            "l"(m), "r"(smem_u32(bar) & kPeerMask), "r"(c0), "r"(c1)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred q;\n\t"
+            "elect.sync _|q, 0xffffffff;\n\t"
+            "@q cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}" ::"r"(
+                smem_u32(dst)),
+            "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+            : "memory");
+}
+
+// whole-warp issue of an im2col load (see above): pair != 0 is the cta_group::2 form completing on CTA 0's barrier
+__device__ __forceinline__ void tma_load_im2col_elect(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
+                                                      int off_w, int off_h, bool pair) {
+    if (pair)
+        asm volatile(
+            "{\n\t.reg .pred q;\n\t"
+            "elect.sync _|q, 0xffffffff;\n\t"
+            "@q cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};\n\t}" ::"r"(
+                smem_u32(dst)),
+            "l"(m), "r"(smem_u32(bar) & kPeerMask), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+            : "memory");
+    else
+        asm volatile(
+            "{\n\t.reg .pred q;\n\t"
+            "elect.sync _|q, 0xffffffff;\n\t"
+            "@q cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};\n\t}" ::"r"(
+                smem_u32(dst)),
+            "l"(m), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
+            : "memory");
+}
+
 // 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread t <-> TMEM lane base+t).
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(

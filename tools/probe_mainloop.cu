@@ -25,7 +25,20 @@ __device__ __forceinline__ uint64_t sw128_desc(uint32_t addr) {
     return d;
 }
 
-struct Params { int N, stages, k_blocks, tiles, sub, spin; };   // spin: warps 4-7 poll the final barrier like epilogue warps do   // sub = 64-element sub-blocks per stage (1 or 2)
+
+// Whole-warp variants: every lane executes the instruction stream with warp-uniform operands and one elected lane issues, so
+// the compiler can keep descriptors in uniform registers (no per-MMA ELECT / R2UR.BROADCAST waterfall).
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint64_t da, uint64_t db, uint32_t idesc, uint32_t acc) {
+    asm volatile("{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|q, 0xffffffff;\n\t@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+                 "l"(da), "l"(db), "r"(idesc), "r"(acc)
+                 : "memory");
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+    asm volatile("{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(ptx::smem_u32(bar))
+                 : "memory");
+}
+
+struct Params { int N, stages, k_blocks, tiles, sub, spin, whole_warp; };   // spin: warps 4-7 poll the final barrier like epilogue warps do   // sub = 64-element sub-blocks per stage (1 or 2)
 
 __global__ void __launch_bounds__(256, 1) mainloop(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, Params p,
                                                    unsigned long long* out) {
@@ -59,7 +72,7 @@ __global__ void __launch_bounds__(256, 1) mainloop(const __grid_constant__ CUten
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp == 1 && lane == 0) {
+    } else if (warp == 1 && lane == 0 && !p.whole_warp) {
         const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         int stage = 0, phase = 0;
         long long t_wait = 0, t_mma = 0, t_commit = 0;
@@ -87,6 +100,39 @@ __global__ void __launch_bounds__(256, 1) mainloop(const __grid_constant__ CUten
         out[blockIdx.x * 4 + 1] = (unsigned long long)t_wait;
         out[blockIdx.x * 4 + 2] = (unsigned long long)t_mma;
         out[blockIdx.x * 4 + 3] = (unsigned long long)t_commit;
+    }
+    else if (warp == 1 && p.whole_warp) {
+        // the same loop run by all 32 lanes of the MMA warp
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+        int stage = 0, phase = 0;
+        long long t_wait = 0, t_mma = 0, t_commit = 0;
+        const long long t0 = clock64();
+        for (int i = 0; i < total; ++i) {
+            const long long w0 = clock64();
+            ptx::mbar_wait(&full[stage], phase);
+            const long long w1 = clock64();
+            ptx::tc_fence_after();
+            const uint32_t a_addr = ptx::smem_u32(smem + (size_t)stage * stage_bytes);
+            for (int u = 0; u < p.sub; ++u) {
+                const uint64_t da = sw128_desc(a_addr + u * 128 * 128), db = sw128_desc(a_addr + a_bytes + u * p.N * 128);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16_elect(tmem, da + 2 * k, db + 2 * k, idesc, (i | u | k) ? 1u : 0u);
+            }
+            const long long w2 = clock64();
+            umma_commit_elect(&empty[stage]);
+            const long long w3 = clock64();
+            t_wait += w1 - w0; t_mma += w2 - w1; t_commit += w3 - w2;
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_elect(&done);
+        ptx::mbar_wait(&done, 0);
+        const long long t1 = clock64();
+        if (lane == 0) {
+            out[blockIdx.x * 4] = (unsigned long long)(t1 - t0);
+            out[blockIdx.x * 4 + 1] = (unsigned long long)t_wait;
+            out[blockIdx.x * 4 + 2] = (unsigned long long)t_mma;
+            out[blockIdx.x * 4 + 3] = (unsigned long long)t_commit;
+        }
     }
     else if (warp >= 4 && p.spin) {
         if (p.spin == 1) ptx::mbar_wait(&done, 0);                      // plain try_wait loop
@@ -117,9 +163,9 @@ int main() {
                   enc(&tma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, da, d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
                 { cuuint64_t d[2] = {(cuuint64_t)K, (cuuint64_t)NMAX}, s[1] = {(cuuint64_t)K * 2}; cuuint32_t b[2] = {64, (cuuint32_t)N}, e[2] = {1, 1};
                   enc(&tmb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, db, d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
-                for (int spin : {0, 1, 2})
+                for (int spin : {0, 1})
                 for (int ctas : {1, CTAS}) {
-                    Params p{N, stages, 32 / sub, TILES, sub, spin};
+                    Params p{N, stages, 32 / sub, TILES, sub, 0, spin};
                     for (int rep = 0; rep < 2; ++rep) mainloop<<<ctas, 256, smem>>>(tma, tmb, p, dout);
                     cudaError_t e = cudaDeviceSynchronize();
                     if (e != cudaSuccess) { printf("N %d sub %d stages %d: %s\n", N, sub, stages, cudaGetErrorString(e)); return 2; }
@@ -127,7 +173,7 @@ int main() {
                     double tot = 0, wait = 0, mma = 0, com = 0;
                     for (int c = 0; c < ctas; ++c) { tot += (double)ho[4 * c]; wait += (double)ho[4 * c + 1]; mma += (double)ho[4 * c + 2]; com += (double)ho[4 * c + 3]; }
                     const double blocks = (double)ctas * TILES * 32;
-                    printf("%4d %4d %6d %6d spin %d | total %7.1f | wait full %7.1f | fence+desc+issue MMAs %7.1f | commit %7.1f   (cycles per K=64 block)\n", N, sub, stages, ctas, spin,
+                    printf("%4d %4d %6d %6d whole-warp %d | total %7.1f | wait full %7.1f | fence+desc+issue MMAs %7.1f | commit %7.1f   (cycles per K=64 block)\n", N, sub, stages, ctas, spin,
                            tot / blocks, wait / blocks, mma / blocks, com / blocks);
                 }
             }
