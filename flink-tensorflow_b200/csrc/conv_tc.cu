@@ -33,9 +33,13 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     // candidates: pixel-major (im2col / halo window / CTA pair), weight-major (im2col / halo window)
     struct Variant { int kind; bool halo, pair; };
     static const Variant kVariants[] = {{0, false, false}, {0, true, false}, {0, false, true}, {1, false, false}, {1, true, false}};
-    // the CTA-pair kernel ties with the one-CTA kernel in isolation and loses a little inside the network (half as many,
-    // twice as large work items per layer): a candidate only on request (FTF_CONV_PAIR=1) or when forced (FTF_CONV_KIND=pm2)
-    static const bool no_pair = !(getenv("FTF_CONV_PAIR") && getenv("FTF_CONV_PAIR")[0] == '1');
+    // The CTA-pair kernel halves the weight bytes each SM pulls from L2.  That pays on layers of many waves, which are bound by
+    // L2 -> SM operand fill (Conv2d_4a: 155 -> 137 us); single-wave layers are bound by the K-block cadence of the issuing
+    // warp and a pair only halves the number of workers.  So it is a candidate from four tiles per SM on (FTF_CONV_PAIR=0/1
+    // forces it off/on for every layer, FTF_CONV_KIND=pm2 selects it alone).
+    const long long m_tiles = ((long long)g.n_max * ((g.H + 2 * g.pad_h - g.KH) / g.stride + 1) * ((g.W + 2 * g.pad_w - g.KW) / g.stride + 1) + 127) / 128;
+    const char* pair_env = getenv("FTF_CONV_PAIR");
+    const bool no_pair = pair_env ? pair_env[0] != '1' : m_tiles < 4ll * sm_count;
     for (const Variant& v : kVariants) {
         if (force) {   // FTF_CONV_KIND: "pm" = one-CTA pixel-major, "pm2" = CTA-pair pixel-major, "wm" = weight-major
             const bool want_pair = force[0] == 'p' && force[2] == '2';
