@@ -297,6 +297,12 @@ struct InceptionV3::Impl {
         static const bool off = getenv("FTF_NO_SM_SPLIT") != nullptr;
         return off || sm_share_den <= 1 ? sms : (sms / sm_share_den > 0 ? sms / sm_share_den : 1);
     }
+    // the sibling branches of a fork are shorter than this one: from here on it plans for the whole GPU again
+    // (FTF_SPLIT_WHOLE_BRANCH=1 keeps the share to the end of the branch: measurement switch)
+    void rest_alone() {
+        static const bool keep = getenv("FTF_SPLIT_WHOLE_BRANCH") != nullptr;
+        if (!keep) sm_share_den = 1;
+    }
     struct PendingPool { float* scratch; float* bias; Act* dst; int coff, c, h, w; };
     std::vector<PendingPool> pending_pool;
 
@@ -355,6 +361,7 @@ struct InceptionV3::Impl {
         conv_to(blk + ".branch7x7_3", u, 192, 7, 1, 1, 3, 0, &out, 192);
         cur_lane = 1; Act d2 = conv(blk + ".branch7x7dbl_2", d, c7, 7, 1, 1, 3, 0);
         Act d3 = conv(blk + ".branch7x7dbl_3", d2, c7, 1, 7, 1, 0, 3);
+        rest_alone();            // the other branch (two convolutions) has finished by now: the rest of this one gets every SM
         Act d4 = conv(blk + ".branch7x7dbl_4", d3, c7, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7dbl_5", d4, 192, 1, 7, 1, 0, 3, &out, 384);
         sm_share_den = 1;
@@ -372,6 +379,7 @@ struct InceptionV3::Impl {
         sm_share_den = 2;
         cur_lane = 0; conv_to(blk + ".branch3x3_2", t, 320, 3, 3, 2, 0, 0, &out, 0);
         cur_lane = 1; Act s2 = conv(blk + ".branch7x7x3_2", s, 192, 1, 7, 1, 0, 3);
+        rest_alone();            // the 3x3 branch is a single convolution: after it this branch is alone
         Act s3 = conv(blk + ".branch7x7x3_3", s2, 192, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7x3_4", s3, 192, 3, 3, 2, 0, 0, &out, 320);
         sm_share_den = 1;
@@ -391,6 +399,7 @@ struct InceptionV3::Impl {
         cur_lane = 1; conv_to(blk + ".branch3x3_2b", t, 384, 3, 1, 1, 1, 0, &out, 704);
         sm_share_den = 2;
         cur_lane = 2; Act u = conv(blk + ".branch3x3dbl_2", d, 384, 3, 3, 1, 1, 1);
+        rest_alone();            // the 3x3 branches are done before the 448-channel 3x3 is: its two followers get every SM
         conv_to(blk + ".branch3x3dbl_3a", u, 384, 1, 3, 1, 0, 1, &out, 1088);
         conv_to(blk + ".branch3x3dbl_3b", u, 384, 3, 1, 1, 1, 0, &out, 1472);
         sm_share_den = 1;
