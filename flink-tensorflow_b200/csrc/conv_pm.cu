@@ -81,6 +81,27 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t smem_addr, int row_bytes)
     d |= (uint64_t)(row_bytes == 128 ? 2 : 4) << 61;   // SWIZZLE_128B / SWIZZLE_64B
     return d;
 }
+// The same descriptor in two 32-bit halves (see the halo kernel's MMA loop).
+__device__ __forceinline__ uint32_t desc_hi(int row_bytes) {
+    return (uint32_t)((8 * row_bytes) >> 4) | (1u << 14) | ((uint32_t)(row_bytes == 128 ? 2 : 4) << 29);
+}
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr) { return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16); }
+__device__ __forceinline__ uint64_t make_desc(uint32_t lo, uint32_t hi) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
+}
+// kNK K steps for each of S sub-tiles of one filter tap (halo kernel), no branches inside.
+template <int kNK>
+__device__ __forceinline__ void issue_subtiles(int S, uint32_t d, uint32_t d_step, uint32_t a_lo, uint32_t a_step, uint32_t b_lo, uint32_t hi,
+                                               uint32_t idesc, uint32_t accumulate_first) {
+    for (int s = 0; s < S; ++s, a_lo += a_step, d += d_step) {
+#pragma unroll
+        for (int k = 0; k < kNK; ++k)
+            ptx::umma_bf16_elect(d, make_desc(a_lo + 2u * k, hi), make_desc(b_lo + 2u * k, hi), idesc, k ? 1u : accumulate_first);
+    }
+}
+
 // kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M x N tile.
 __device__ __forceinline__ uint32_t instr_desc_bf16(int m, int n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
@@ -399,19 +420,22 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         const long long t_begin = prof ? clock64() : 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int q_tile = tile / p.n_tiles, n_tile = tile - q_tile * p.n_tiles;
-            const long long q0 = (long long)q_tile * T;
+            // first padded pixel of the window, decoded once per tile (32-bit: the plan keeps Q below 2^31); the loads then
+            // step through the padded image incrementally instead of dividing per load
+            const uint32_t q0 = (uint32_t)q_tile * (uint32_t)T;
+            const int wp0 = (int)(q0 % (uint32_t)p.Wp);
+            const uint32_t t0 = q0 / (uint32_t)p.Wp;
+            const int hp0 = (int)(t0 % (uint32_t)p.Hp), img0 = (int)(t0 / (uint32_t)p.Hp);
             for (int chunk = 0; chunk < p.cin_chunks; ++chunk) {
                 timed_wait(&a_empty[as], aph ^ 1, prof, &t_wait);
                 uint8_t* a_dst = a_base + (size_t)as * p.a_stage_bytes;
                 ptx::mbar_expect_tx_elect(&a_full[as], (uint32_t)p.a_stage_bytes);
+                int wp = wp0, hp = hp0, img = img0;
                 for (int i = 0; i < p.a_loads; ++i) {           // the window, kHaloLoadRows padded pixels per load
-                    const long long q = q0 + (long long)i * kHaloLoadRows;
-                    const int wp = (int)(q % p.Wp);
-                    const long long t = q / p.Wp;
-                    const int hp = (int)(t % p.Hp);
-                    const int img = (int)(t / p.Hp);
                     ptx::tma_load_im2col_elect(a_dst + (size_t)i * kHaloLoadRows * rb, &tm_a, &a_full[as], chunk * p.kc, wp - p.pad_w,
                                     hp - p.pad_h, img, 0, 0, false);
+                    wp += kHaloLoadRows;
+                    while (wp >= p.Wp) { wp -= p.Wp; if (++hp == p.Hp) { hp = 0; ++img; } }
                 }
                 for (int tap = 0; tap < taps; ++tap) {
                     timed_wait(&b_empty[bs], bph ^ 1, prof, &t_wait);
@@ -427,6 +451,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     } else if (warp == 1) {
         // ===== MMA issuer: whole warp, one elected lane issues =====
         const uint32_t idesc = instr_desc_bf16(kBlockM, p.block_n);
+        const uint32_t hi = desc_hi(rb), rows16 = (uint32_t)rb >> 4, sub16 = (uint32_t)(kBlockM * rb) >> 4;   // descriptor address units (16 B)
         int as = 0, aph = 0, bs = 0, bph = 0, acc = 0, acc_phase = 0;
         const bool prof = p.prof != nullptr;
         long long w_full = 0, w_acc = 0;
@@ -438,24 +463,32 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             for (int chunk = 0; chunk < p.cin_chunks; ++chunk) {
                 timed_wait(&a_full[as], aph, prof, &w_full);
                 ptx::tc_fence_after();
-                const uint32_t a_addr = ptx::smem_u32(a_base + (size_t)as * p.a_stage_bytes);
+                // Descriptors as two 32-bit words: the high word (stride, version, swizzle) never changes, the low word is
+                // 0x10000 | (address >> 4), so stepping to another tap, sub-tile or K step is one 32-bit add.  (The loop used
+                // to rebuild 64-bit descriptors per MMA: ~50 dependent instructions per MMA made this warp the bottleneck of
+                // the 32-channel stem layers -- profiles/r01_conv_roles.md.)
+                const uint32_t a_lo0 = desc_lo(ptx::smem_u32(a_base + (size_t)as * p.a_stage_bytes));
                 const int nk = chunk == p.cin_chunks - 1 ? p.ksteps_last : p.kc / 16;     // skip the all-zero K steps
-                for (int tap = 0; tap < taps; ++tap) {
-                    const int kh = tap / p.KW, kw = tap - kh * p.KW;
-                    timed_wait(&b_full[bs], bph, prof, &w_full);
-                    ptx::tc_fence_after();
-                    const uint64_t b_desc = smem_desc(ptx::smem_u32(b_base + (size_t)bs * p.b_stage_bytes), rb);
-                    const uint32_t first = (chunk | tap) != 0 ? 1u : 0u;
-                    for (int s = 0; s < p.S; ++s) {
+                int tap = 0;
+                for (int kh = 0; kh < p.KH; ++kh)
+                    for (int kw = 0; kw < p.KW; ++kw, ++tap) {
+                        timed_wait(&b_full[bs], bph, prof, &w_full);
+                        ptx::tc_fence_after();
+                        const uint32_t b_lo = desc_lo(ptx::smem_u32(b_base + (size_t)bs * p.b_stage_bytes));
+                        const uint32_t first = (chunk | tap) != 0 ? 1u : 0u;
                         // tap (kh, kw) of sub-tile s: the window entered (s*128 + kh*Wp + kw) rows further down
-                        const uint64_t a_desc = smem_desc(a_addr + (uint32_t)(s * kBlockM + kh * p.Wp + kw) * (uint32_t)rb, rb);
-                        for (int k = 0; k < nk; ++k)
-                            ptx::umma_bf16_elect(d_tmem + (uint32_t)(s * p.block_n), a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k),
-                                           idesc, (first | (uint32_t)k) != 0 ? 1u : 0u);
+                        const uint32_t a_lo = a_lo0 + (uint32_t)(kh * p.Wp + kw) * rows16;
+                        // straight-line issue: the number of K steps is resolved once per tap, not per MMA (a conditional
+                        // around an elected instruction costs a convergence check each time)
+                        switch (nk) {
+                        case 4: issue_subtiles<4>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                        case 3: issue_subtiles<3>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                        case 2: issue_subtiles<2>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                        default: issue_subtiles<1>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                        }
+                        ptx::umma_commit_elect(&b_empty[bs]);
+                        if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
                     }
-                    ptx::umma_commit_elect(&b_empty[bs]);
-                    if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
-                }
                 ptx::umma_commit_elect(&a_empty[as]);
                 if (++as == kAStages) { as = 0; aph ^= 1; }
             }
@@ -481,12 +514,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
             for (int s = 0; s < p.S; ++s) {
-                const long long q = (long long)q_tile * T + s * kBlockM + row;
-                const int wp = (int)(q % p.Wp);
-                const long long t = q / p.Wp;
-                const int hp = (int)(t % p.Hp);
-                const long long img = t / p.Hp;
-                const bool row_ok = q < p.Q && wp < p.OW && hp < p.OH;
+                const uint32_t q = (uint32_t)q_tile * (uint32_t)T + (uint32_t)(s * kBlockM + row);      // < 2^31 by plan
+                const int wp = (int)(q % (uint32_t)p.Wp);
+                const uint32_t t = q / (uint32_t)p.Wp;
+                const int hp = (int)(t % (uint32_t)p.Hp);
+                const long long img = (long long)(t / (uint32_t)p.Hp);
+                const bool row_ok = (long long)q < p.Q && wp < p.OW && hp < p.OH;
                 const long long m = (img * p.OH + hp) * p.OW + wp;
                 const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + s * p.block_n) + ((uint32_t)(e * 32) << 16);
                 epilogue_row(p, bias, t_row, n_tile, m, row_ok);
@@ -589,7 +622,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                 }
                 continue;
             }
-            if (!(allow_halo && g.stride == 1 && taps > 1)) continue;
+            if (!(allow_halo && g.stride == 1 && taps > 1) || Q >= (1ll << 31) - 4096) continue;
             for (int S = 1; S <= 4; S *= 2) {
                 if (2 * S * bn > kTmemCols) continue;                  // keep two accumulator sets: epilogue overlaps the next tile
                 const int T = S * kBlockM;

@@ -60,7 +60,7 @@ __device__ __forceinline__ uint64_t sw128_desc(uint32_t addr) {
 // CG = 1: one CTA, M = 128, all N rows of B.  CG = 2: a CTA pair, M = 256, N/2 rows of B per CTA.
 template <int CG>
 __global__ void __launch_bounds__(128) probe(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b, float* out,
-                                             int N, int reps, unsigned long long* cycles, int commit_every) {
+                                             int N, int reps, unsigned long long* cycles, int commit_every, int a_shift_rows, int sw64) {
     extern __shared__ __align__(1024) uint8_t raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)raw + 1023) & ~(uintptr_t)1023);
     uint8_t* a_buf = smem;                        // 128 x 128 B
@@ -91,12 +91,17 @@ __global__ void __launch_bounds__(128) probe(const __grid_constant__ CUtensorMap
             ptx::mbar_wait(&full, 0);
             ptx::tc_fence_after();
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)((128 * CG) >> 4) << 24);
-            const uint64_t da = sw128_desc(ptx::smem_u32(a_buf)), db = sw128_desc(ptx::smem_u32(b_buf));
+            uint64_t da = sw128_desc(ptx::smem_u32(a_buf) + (uint32_t)a_shift_rows * 128u), db = sw128_desc(ptx::smem_u32(b_buf));
+            if (sw64) {   // 64-byte rows: 8-row groups 512 bytes apart, layout type SWIZZLE_64B; two K = 16 steps per row
+                auto d64 = [](uint32_t addr) { uint64_t d = 0; d |= (uint64_t)((addr & 0x3FFFF) >> 4); d |= (uint64_t)1 << 16; d |= (uint64_t)(512 >> 4) << 32; d |= (uint64_t)1 << 46; d |= (uint64_t)4 << 61; return d; };
+                da = d64(ptx::smem_u32(a_buf) + (uint32_t)a_shift_rows * 64u); db = d64(ptx::smem_u32(b_buf));
+            }
             const long long t0 = clock64();
             for (int r = 0; r < reps; ++r) {
                 for (int k = 0; k < 4; ++k) {
-                    if (CG == 2) umma_bf16_2sm(tmem, da + 2 * k, db + 2 * k, idesc, (r | k) ? 1u : 0u);
-                    else ptx::umma_bf16(tmem, da + 2 * k, db + 2 * k, idesc, (r | k) ? 1u : 0u);
+                    const int kk = sw64 ? (k & 1) : k;            // a 64-byte row holds two K steps
+                    if (CG == 2) umma_bf16_2sm(tmem, da + 2 * kk, db + 2 * kk, idesc, (r | k) ? 1u : 0u);
+                    else ptx::umma_bf16(tmem, da + 2 * kk, db + 2 * kk, idesc, (r | k) ? 1u : 0u);
                 }
                 // as a pipelined main loop does: a commit per K block (here onto a barrier nobody waits for)
                 if (commit_every && (r + 1) % commit_every == 0) { if (CG == 2) umma_commit_2sm(&dummy_bar, 0b11); else ptx::umma_commit(&dummy_bar); }
@@ -121,14 +126,14 @@ __global__ void __launch_bounds__(128) probe(const __grid_constant__ CUtensorMap
 }
 
 template <int CG>
-static cudaError_t launch(const CUtensorMap& tma, const CUtensorMap& tmb, float* out, int N, int reps, unsigned long long* cyc, int commit_every = 0) {
+static cudaError_t launch(const CUtensorMap& tma, const CUtensorMap& tmb, float* out, int N, int reps, unsigned long long* cyc, int commit_every = 0, int a_shift_rows = 0, int sw64 = 0) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(CG); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = 128 * 128 + 256 * 128 + 2048;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension; at[0].val.clusterDim.x = CG; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     cudaFuncSetAttribute(probe<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cfg.dynamicSmemBytes);
-    cudaError_t e = cudaLaunchKernelEx(&cfg, probe<CG>, tma, tmb, out, N, reps, cyc, commit_every);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, probe<CG>, tma, tmb, out, N, reps, cyc, commit_every, a_shift_rows, sw64);
     if (e != cudaSuccess) return e;
     return cudaDeviceSynchronize();
 }
@@ -178,6 +183,36 @@ int main() {
             printf("N %3d cta_group::%d (M %3d): %s (%d mismatches%s)  cycles per MMA: %.1f with one commit at the end, %.1f with a commit per 4 MMAs, %.1f per 16 MMAs\n", N, cg, rows,
                    bad ? "MISMATCH" : "ok", bad, first >= 0 ? ", first shown below" : "", (double)cyc / 1024.0, (double)cyc1 / 1024.0, (double)cyc4 / 1024.0);
             if (first >= 0) printf("   first mismatch at row %d col %d: got %.1f\n", first / N, first % N, ho[first]);
+        }
+    }
+    // 64-byte operand rows (SWIZZLE_64B, 32-channel K blocks): the timing only (buffers filled by the 128B maps, values irrelevant)
+    for (int N : {32, 64, 160}) {
+        CUtensorMap tma, tmb;
+        { cuuint64_t d[2] = {(cuuint64_t)K, (cuuint64_t)M}, s[1] = {(cuuint64_t)K * 2}; cuuint32_t b[2] = {64, 128}, e[2] = {1, 1};
+          enc(&tma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, da, d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
+        { cuuint64_t d[2] = {(cuuint64_t)K, (cuuint64_t)NMAX}, s[1] = {(cuuint64_t)K * 2}; cuuint32_t b[2] = {64, (cuuint32_t)N}, e[2] = {1, 1};
+          enc(&tmb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, db, d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
+        for (int shift : {0, 3}) {
+            unsigned long long cyc = 0;
+            cudaError_t e = launch<1>(tma, tmb, dout, N, 256, dcyc, 0, shift, 1);
+            if (e != cudaSuccess) { printf("sw64 probe: %s\n", cudaGetErrorString(e)); return 2; }
+            cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+            printf("N %3d, SWIZZLE_64B operands, A starting %d rows in: %.1f cycles per MMA\n", N, shift, (double)cyc / 1024.0);
+        }
+    }
+    // an A descriptor that starts at a row which is not a multiple of 8 (the halo-window trick): does the MMA slow down?
+    for (int N : {32, 64, 160}) {
+        CUtensorMap tma, tmb;
+        { cuuint64_t d[2] = {(cuuint64_t)K, (cuuint64_t)M}, s[1] = {(cuuint64_t)K * 2}; cuuint32_t b[2] = {64, 128}, e[2] = {1, 1};
+          enc(&tma, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, da, d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
+        { cuuint64_t d[2] = {(cuuint64_t)K, (cuuint64_t)NMAX}, s[1] = {(cuuint64_t)K * 2}; cuuint32_t b[2] = {64, (cuuint32_t)N}, e[2] = {1, 1};
+          enc(&tmb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, db, d, s, b, e, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE); }
+        for (int shift : {0, 1, 3, 8, 37}) {
+            unsigned long long cyc = 0;
+            cudaError_t e = launch<1>(tma, tmb, dout, N, 256, dcyc, 0, shift);
+            if (e != cudaSuccess) { printf("shift probe: %s\n", cudaGetErrorString(e)); return 2; }
+            cudaMemcpy(&cyc, dcyc, 8, cudaMemcpyDeviceToHost);
+            printf("N %3d, A descriptor starting %2d rows into the swizzled buffer: %.1f cycles per MMA\n", N, shift, (double)cyc / 1024.0);
         }
     }
     return 0;
