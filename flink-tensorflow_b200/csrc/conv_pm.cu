@@ -29,7 +29,8 @@ namespace pm {
 namespace {
 
 constexpr int kBlockM = 128;
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;              // warps 0-3: TMA, MMA, TMEM allocator, idle; warps 4-11: epilogue
+constexpr int kEpiWarps = 8;                // two per TMEM lane quarter: each takes half of a tile's columns
 constexpr int kAccStages = 2;
 constexpr int kTmemCols = 512;              // 2 x 256 fp32 columns
 constexpr int kMaxStages = 8;
@@ -91,6 +92,16 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t lo, uint32_t hi) {
     asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
     return d;
 }
+// kNK K steps of one K block (im2col kernel), no branches inside.
+template <int kNK, bool kPair>
+__device__ __forceinline__ void issue_ksteps(uint32_t d, uint32_t a_lo, uint32_t b_lo, uint32_t hi, uint32_t idesc, uint32_t accumulate_first) {
+#pragma unroll
+    for (int k = 0; k < kNK; ++k) {
+        if (kPair) ptx::umma_bf16_pair_elect(d, make_desc(a_lo + 2u * k, hi), make_desc(b_lo + 2u * k, hi), idesc, k ? 1u : accumulate_first);
+        else ptx::umma_bf16_elect(d, make_desc(a_lo + 2u * k, hi), make_desc(b_lo + 2u * k, hi), idesc, k ? 1u : accumulate_first);
+    }
+}
+
 // kNK K steps for each of S sub-tiles of one filter tap (halo kernel), no branches inside.
 template <int kNK>
 __device__ __forceinline__ void issue_subtiles(int S, uint32_t d, uint32_t d_step, uint32_t a_lo, uint32_t a_step, uint32_t b_lo, uint32_t hi,
@@ -165,8 +176,8 @@ constexpr int kBiasCap = 2048;
 constexpr int kMaxDynSmem = 227 * 1024 - kBiasCap * 4;       // the bias copy is static shared memory
 __device__ __forceinline__ const float* stage_bias(const ConvParams& p, float* bias_s) {
     if (p.N_total > kBiasCap || p.bias == nullptr) return p.bias;
-    for (int i = (int)threadIdx.x - 128; i < p.N_total; i += 128) bias_s[i] = __ldg(p.bias + i);
-    asm volatile("bar.sync 1, 128;" ::: "memory");
+    for (int i = (int)threadIdx.x - 128; i < p.N_total; i += 32 * kEpiWarps) bias_s[i] = __ldg(p.bias + i);
+    asm volatile("bar.sync 1, 256;" ::: "memory");
     return bias_s;
 }
 
@@ -180,20 +191,26 @@ __device__ __forceinline__ void epilogue_group(const ConvParams& p, const float*
     epilogue_chunk(p, bias, gc, m, row_ok, reinterpret_cast<const uint32_t(&)[16]>(v));
     if (cols > 16) epilogue_chunk(p, bias, gc + 16, m, row_ok, *reinterpret_cast<const uint32_t(*)[16]>(&v[16]));
 }
-__device__ __forceinline__ void epilogue_row(const ConvParams& p, const float* bias, uint32_t t_row, int n_tile, long long m, bool row_ok) {
+__device__ __forceinline__ void epilogue_row(const ConvParams& p, const float* bias, uint32_t t_row, int n_tile, long long m, bool row_ok, int half) {
     const int gc0 = n_tile * p.block_n;
-    const int n_cols = min(p.block_n, p.N_total - gc0);           // multiple of 16, warp-uniform
+    const int n_all = min(p.block_n, p.N_total - gc0);            // multiple of 16, warp-uniform
+    // the two warps of a lane quarter split the columns at a multiple of 32
+    const int split = ((n_all / 2 + 31) / 32) * 32;
+    const int c_begin = half ? min(split, n_all) : 0, n_cols = (half ? n_all : min(split, n_all)) - c_begin;
+    if (n_cols <= 0) return;
+    t_row += (uint32_t)c_begin;
+    const int gcb = gc0 + c_begin;
     uint32_t va[32], vb[32];
     tmem_ld_group(t_row, n_cols, va);
     ptx::tmem_ld_wait();
     for (int col = 0; col < n_cols; col += 64) {
         const int c1 = col + 32, c2 = col + 64;
         if (c1 < n_cols) tmem_ld_group(t_row + (uint32_t)c1, n_cols - c1, vb);
-        epilogue_group(p, bias, gc0 + col, n_cols - col, m, row_ok, va);
+        epilogue_group(p, bias, gcb + col, n_cols - col, m, row_ok, va);
         ptx::tmem_ld_wait();
         if (c1 < n_cols) {
             if (c2 < n_cols) tmem_ld_group(t_row + (uint32_t)c2, n_cols - c2, va);
-            epilogue_group(p, bias, gc0 + c1, n_cols - c1, m, row_ok, vb);
+            epilogue_group(p, bias, gcb + c1, n_cols - c1, m, row_ok, vb);
             ptx::tmem_ld_wait();
         }
     }
@@ -244,7 +261,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     }
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { ptx::mbar_init(&full_bar[s], 1); ptx::mbar_init(&empty_bar[s], 1); }
-        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], kPair ? 8 : 4); }
+        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], kPair ? 2 * kEpiWarps : kEpiWarps); }
         ptx::fence_mbar_init();
     }
     if (warp == 2) { if (kPair) ptx::tmem_alloc_pair<kTmemCols>(tmem_slot); else ptx::tmem_alloc<kTmemCols>(tmem_slot); }
@@ -289,6 +306,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     } else if (warp == 1 && rank == 0) {
         // ===== MMA issuer: the whole warp walks the loop, one elected lane issues (CTA 0 of a pair issues for both) =====
         const uint32_t idesc = instr_desc_bf16(kPair ? 2 * kBlockM : kBlockM, p.block_n);
+        const uint32_t hi = desc_hi(rb);
         const int last_chunk_kb = (p.cin_chunks - 1) * p.KH * p.KW;            // K blocks run chunk-major
         int stage = 0, phase = 0, acc = 0, acc_phase = 0;
         const bool prof = p.prof != nullptr;
@@ -302,14 +320,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
                 timed_wait(&full_bar[stage], phase, prof, &w_full);           // TMA bytes have landed (in both CTAs)
                 ptx::tc_fence_after();
                 const uint32_t a_addr = ptx::smem_u32(smem + (size_t)stage * stage_bytes);
-                const uint64_t a_desc = smem_desc(a_addr, rb);
-                const uint64_t b_desc = smem_desc(a_addr + p.a_tile_bytes, rb);
+                const uint32_t a_lo = desc_lo(a_addr), b_lo = desc_lo(a_addr + (uint32_t)p.a_tile_bytes);
                 // K=16 steps of this block (32 bytes, two 16-byte units each); the last channel chunk stops where the
-                // real channels end -- the rest of its rows is TMA zero fill and would add exact zeros
+                // real channels end -- the rest of its rows is TMA zero fill and would add exact zeros.  Straight-line issue.
                 const int nk = kb >= last_chunk_kb ? p.ksteps_last : p.kc / 16;
-                for (int k = 0; k < nk; ++k) {
-                    if (kPair) ptx::umma_bf16_pair_elect(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
-                    else ptx::umma_bf16_elect(d_tmem, a_desc + (uint64_t)(2 * k), b_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                const uint32_t first = kb != 0 ? 1u : 0u;
+                switch (nk) {
+                case 4: issue_ksteps<4, kPair>(d_tmem, a_lo, b_lo, hi, idesc, first); break;
+                case 3: issue_ksteps<3, kPair>(d_tmem, a_lo, b_lo, hi, idesc, first); break;
+                case 2: issue_ksteps<2, kPair>(d_tmem, a_lo, b_lo, hi, idesc, first); break;
+                default: issue_ksteps<1, kPair>(d_tmem, a_lo, b_lo, hi, idesc, first); break;
                 }
                 // frees the smem stage (in both CTAs) when the MMAs retire
                 if (kPair) ptx::umma_commit_pair_elect(&empty_bar[stage]); else ptx::umma_commit_elect(&empty_bar[stage]);
@@ -326,7 +346,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     } else if (warp >= 4) {
         // ===== epilogue: TMEM -> registers -> bias/ReLU -> global =====
         const float* bias = stage_bias(p, bias_s);
-        const int e = warp - 4;                                    // TMEM lane quarter of this warp
+        const int e = (warp - 4) & 3, half = (warp - 4) >> 2;      // TMEM lane quarter (a hardware rule: warp % 4) and column half of this warp
         const int row = e * 32 + lane;
         int acc = 0, acc_phase = 0;
         const bool prof = p.prof != nullptr && threadIdx.x == 128;
@@ -341,7 +361,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
             const uint32_t t_row = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(e * 32) << 16);
-            epilogue_row(p, bias, t_row, n_tile, m, row_ok);
+            epilogue_row(p, bias, t_row, n_tile, m, row_ok, half);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) { if (kPair) ptx::mbar_arrive_leader(&tmem_empty[acc]); else ptx::mbar_arrive(&tmem_empty[acc]); }
@@ -401,7 +421,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kAStages; ++s) { ptx::mbar_init(&a_full[s], 1); ptx::mbar_init(&a_empty[s], 1); }
         for (int s = 0; s < p.b_stages; ++s) { ptx::mbar_init(&b_full[s], 1); ptx::mbar_init(&b_empty[s], 1); }
-        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], 4); }
+        for (int a = 0; a < kAccStages; ++a) { ptx::mbar_init(&tmem_full[a], 1); ptx::mbar_init(&tmem_empty[a], kEpiWarps); }
         ptx::fence_mbar_init();
     }
     if (warp == 2) ptx::tmem_alloc<kTmemCols>(tmem_slot);
@@ -502,7 +522,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     } else if (warp >= 4) {
         // ===== epilogue =====
         const float* bias = stage_bias(p, bias_s);
-        const int e = warp - 4;
+        const int e = (warp - 4) & 3, half = (warp - 4) >> 2;
         const int row = e * 32 + lane;
         int acc = 0, acc_phase = 0;
         const bool prof = p.prof != nullptr && threadIdx.x == 128;
@@ -522,7 +542,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const bool row_ok = (long long)q < p.Q && wp < p.OW && hp < p.OH;
                 const long long m = (img * p.OH + hp) * p.OW + wp;
                 const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + s * p.block_n) + ((uint32_t)(e * 32) << 16);
-                epilogue_row(p, bias, t_row, n_tile, m, row_ok);
+                epilogue_row(p, bias, t_row, n_tile, m, row_ok, half);
             }
             ptx::tc_fence_before();
             __syncwarp();

@@ -94,6 +94,36 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t smem_addr, int row_bytes)
     d |= (uint64_t)(row_bytes == 128 ? 2 : 4) << 61;              // SWIZZLE_128B / SWIZZLE_64B
     return d;
 }
+// The same descriptor in two 32-bit halves: the high word (stride, version, swizzle) never changes inside a kernel, the low
+// word is 0x10000 | (address >> 4), so another tap, sub-tile or K step is one 32-bit add (see conv_pm.cu).
+__device__ __forceinline__ uint32_t desc_hi(int row_bytes) {
+    return (uint32_t)((8 * row_bytes) >> 4) | (1u << 14) | ((uint32_t)(row_bytes == 128 ? 2 : 4) << 29);
+}
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr) { return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16); }
+__device__ __forceinline__ uint64_t make_desc(uint32_t lo, uint32_t hi) {
+    uint64_t d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+    return d;
+}
+// kNK K steps for each of S sub-tiles (S = 1 outside halo mode), no branches inside.
+template <int kNK>
+__device__ __forceinline__ void issue_subtiles(int S, uint32_t d, uint32_t d_step, uint32_t w_lo, uint32_t x_lo, uint32_t x_step, uint32_t hi,
+                                               uint32_t idesc, uint32_t accumulate_first) {
+    for (int s = 0; s < S; ++s, x_lo += x_step, d += d_step) {
+#pragma unroll
+        for (int k = 0; k < kNK; ++k)
+            ptx::umma_bf16_elect(d, make_desc(w_lo + 2u * k, hi), make_desc(x_lo + 2u * k, hi), idesc, k ? 1u : accumulate_first);
+    }
+}
+__device__ __forceinline__ void issue_dispatch(int nk, int S, uint32_t d, uint32_t d_step, uint32_t w_lo, uint32_t x_lo, uint32_t x_step, uint32_t hi,
+                                               uint32_t idesc, uint32_t accumulate_first) {
+    switch (nk) {
+    case 4: issue_subtiles<4>(S, d, d_step, w_lo, x_lo, x_step, hi, idesc, accumulate_first); break;
+    case 3: issue_subtiles<3>(S, d, d_step, w_lo, x_lo, x_step, hi, idesc, accumulate_first); break;
+    case 2: issue_subtiles<2>(S, d, d_step, w_lo, x_lo, x_step, hi, idesc, accumulate_first); break;
+    default: issue_subtiles<1>(S, d, d_step, w_lo, x_lo, x_step, hi, idesc, accumulate_first); break;
+    }
+}
 // kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, M x N tile.
 __device__ __forceinline__ uint32_t instr_desc_bf16(int m, int n) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
@@ -217,6 +247,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
         // ============== MMA issuer: the whole warp walks the loop, one elected lane issues (see ptx.cuh) ==============
         const uint32_t idesc = instr_desc_bf16(kWRows, p.np);
         const int ksteps = p.kc / 16;
+        const uint32_t hi = desc_hi(rb);
         long long w_full = 0, w_acc = 0;
         const long long t_begin = profiling ? clock64() : 0;
         int as = 0, aph = 0, bs = 0, bph = 0, acc = 0, acc_phase = 0;
@@ -230,10 +261,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                     timed_wait(&bars->a_full[as], aph, profiling, &w_full);
                     ptx::tc_fence_after();
                     const uint32_t w_addr = ptx::smem_u32(smem + (size_t)as * stage_bytes);
-                    const uint64_t w_desc = smem_desc(w_addr, rb), x_desc = smem_desc(w_addr + p.w_stage_bytes, rb);
                     const int nk = kb >= (p.cin_chunks - 1) * taps ? p.ksteps_last : ksteps;      // skip the all-zero K steps of the last chunk
-                    for (int k = 0; k < nk; ++k)                               // 32 bytes (two 16-byte units) per K = 16 step
-                        ptx::umma_bf16_elect(d_tmem, w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc, (kb | k) != 0 ? 1u : 0u);
+                    issue_dispatch(nk, 1, d_tmem, 0u, desc_lo(w_addr), desc_lo(w_addr + (uint32_t)p.w_stage_bytes), 0u, hi, idesc, kb != 0 ? 1u : 0u);
                     ptx::umma_commit_elect(&bars->a_empty[as]);                      // frees the stage when these MMAs retire
                     if (++as == p.stages) { as = 0; aph ^= 1; }
                 }
@@ -243,22 +272,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                     ptx::tc_fence_after();
                     const uint32_t win_addr = ptx::smem_u32(win_base + (size_t)as * p.p_stage_bytes);
                     const int nk = chunk == p.cin_chunks - 1 ? p.ksteps_last : ksteps;
-                    for (int tap = 0; tap < taps; ++tap) {
-                        const int kh = tap / p.KW, kw = tap - kh * p.KW;
-                        timed_wait(&bars->b_full[bs], bph, profiling, &w_full);
-                        ptx::tc_fence_after();
-                        const uint64_t w_desc = smem_desc(ptx::smem_u32(wt_base + (size_t)bs * p.w_stage_bytes), rb);
-                        const uint32_t first = (chunk | tap) != 0 ? 1u : 0u;
-                        for (int s = 0; s < p.S; ++s) {
+                    int tap = 0;
+                    for (int kh = 0; kh < p.KH; ++kh)
+                        for (int kw = 0; kw < p.KW; ++kw, ++tap) {
+                            timed_wait(&bars->b_full[bs], bph, profiling, &w_full);
+                            ptx::tc_fence_after();
+                            const uint32_t w_lo = desc_lo(ptx::smem_u32(wt_base + (size_t)bs * p.w_stage_bytes));
                             // tap (kh, kw) of sub-tile s: the window entered (s*np + kh*Wp + kw) rows further down
-                            const uint64_t x_desc = smem_desc(win_addr + (uint32_t)(s * p.np + kh * p.Wp + kw) * (uint32_t)rb, rb);
-                            for (int k = 0; k < nk; ++k)
-                                ptx::umma_bf16_elect(d_tmem + (uint32_t)(s * p.np), w_desc + (uint64_t)(2 * k), x_desc + (uint64_t)(2 * k), idesc,
-                                               (first | (uint32_t)k) != 0 ? 1u : 0u);
+                            const uint32_t x_lo = desc_lo(win_addr) + (uint32_t)(kh * p.Wp + kw) * ((uint32_t)rb >> 4);
+                            issue_dispatch(nk, p.S, d_tmem, (uint32_t)p.np, w_lo, x_lo, (uint32_t)(p.np * rb) >> 4, hi, idesc, (chunk | tap) != 0 ? 1u : 0u);
+                            ptx::umma_commit_elect(&bars->b_empty[bs]);
+                            if (++bs == p.w_stages) { bs = 0; bph ^= 1; }
                         }
-                        ptx::umma_commit_elect(&bars->b_empty[bs]);
-                        if (++bs == p.w_stages) { bs = 0; bph ^= 1; }
-                    }
                     ptx::umma_commit_elect(&bars->a_empty[as]);
                     if (++as == 2) { as = 0; aph ^= 1; }
                 }
