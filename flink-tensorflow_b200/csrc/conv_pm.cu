@@ -128,6 +128,10 @@ __device__ __forceinline__ void tmem_ld_x16(uint32_t taddr, uint32_t (&v)[16]) {
         : "memory");
 }
 
+__device__ __forceinline__ void st_global_v8(void* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d, uint32_t e, uint32_t f, uint32_t g, uint32_t h) {
+    asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d), "r"(e), "r"(f), "r"(g), "r"(h) : "memory");
+}
+
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
@@ -157,15 +161,30 @@ __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const float*
         for (int i = 0; i < 16; ++i) f[i] = fmaxf(f[i], 0.0f);
     }
     if (row_ok) {
+        // A thread owns a row, so the 32 lanes of a store instruction hit 32 different cache lines and the LSU spends a tag
+        // lookup per lane whatever the width: 256-bit stores (one full 32-byte sector per lane) halve the instruction count
+        // of the 1x1 layers' epilogue, which is what bounds them.  p.wide_stores: every segment keeps 32-byte alignment.
         const size_t off = (size_t)m * sg.ld + sg.coff + (gc - sg.col_begin);
         if (sg.flags & kSegF32) {
-            float4* o = reinterpret_cast<float4*>((float*)sg.out + off);
+            float* o = (float*)sg.out + off;
+            if (p.wide_stores) {
+                st_global_v8(o, __float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]), __float_as_uint(f[4]),
+                             __float_as_uint(f[5]), __float_as_uint(f[6]), __float_as_uint(f[7]));
+                st_global_v8(o + 8, __float_as_uint(f[8]), __float_as_uint(f[9]), __float_as_uint(f[10]), __float_as_uint(f[11]), __float_as_uint(f[12]),
+                             __float_as_uint(f[13]), __float_as_uint(f[14]), __float_as_uint(f[15]));
+            } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) o[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+                for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(o)[i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+            }
         } else {
-            uint4* o = reinterpret_cast<uint4*>((__nv_bfloat16*)sg.out + off);
-            o[0] = make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
-            o[1] = make_uint4(pack_bf16(f[8], f[9]), pack_bf16(f[10], f[11]), pack_bf16(f[12], f[13]), pack_bf16(f[14], f[15]));
+            __nv_bfloat16* o = (__nv_bfloat16*)sg.out + off;
+            const uint32_t w0 = pack_bf16(f[0], f[1]), w1 = pack_bf16(f[2], f[3]), w2 = pack_bf16(f[4], f[5]), w3 = pack_bf16(f[6], f[7]);
+            const uint32_t w4 = pack_bf16(f[8], f[9]), w5 = pack_bf16(f[10], f[11]), w6 = pack_bf16(f[12], f[13]), w7 = pack_bf16(f[14], f[15]);
+            if (p.wide_stores) st_global_v8(o, w0, w1, w2, w3, w4, w5, w6, w7);
+            else {
+                reinterpret_cast<uint4*>(o)[0] = make_uint4(w0, w1, w2, w3);
+                reinterpret_cast<uint4*>(o)[1] = make_uint4(w4, w5, w6, w7);
+            }
         }
     }
 }
@@ -665,6 +684,11 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
         }
     }
     p.ksteps_last = (g.Cin - p.kc * (p.cin_chunks - 1) + 15) / 16;
+    p.wide_stores = 1;
+    for (int i = 0; i < n_seg; ++i) {
+        const int esz = (segs[i].flags & kSegF32) ? 4 : 2;
+        if (((uintptr_t)segs[i].out & 31) || (segs[i].ld * esz) % 32 || (segs[i].coff * esz) % 32) p.wide_stores = 0;
+    }
     if (est_cycles) *est_cycles = best;
     if (p.halo_mode) {
         plan->smem = 2 * (size_t)p.a_stage_bytes + (size_t)p.b_stages * p.b_stage_bytes + 1024 + 512;

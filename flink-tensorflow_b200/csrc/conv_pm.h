@@ -30,6 +30,7 @@ struct ConvParams {
     int b_stages;               // weight-tile ring depth
     int acc_stages;             // 1 or 2 TMEM accumulator sets of S * block_n columns
     int pair;                   // 1: CTA-pair kernel (cta_group::2): tiles of 256 pixels, each CTA holds block_n/2 weight rows
+    int wide_stores;            // 1: every segment's rows and channel offset are 32-byte aligned (256-bit epilogue stores)
     int ksteps_last;            // K=16 steps holding real channels in the LAST channel chunk (the all-zero rest is skipped)
     unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
     unsigned long long* tl;     // timeline stamps of this launch (FTF_TIMELINE), else NULL
