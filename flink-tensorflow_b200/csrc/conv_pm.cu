@@ -139,12 +139,20 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
 
 // One 16-column chunk of one accumulator row: bias, ReLU, rounding and the store into the segment that owns
 // GEMM column gc (m = output pixel index, row_ok = the row is a real output).
+__device__ __forceinline__ void epilogue_chunk_seg(const ConvParams& p, const ConvSegment& sg, const float* bias, int gc, long long m, bool row_ok,
+                                                   const uint32_t (&v)[16]);
 __device__ __forceinline__ void epilogue_chunk(const ConvParams& p, const float* bias, int gc, long long m, bool row_ok, const uint32_t (&v)[16]) {
+    // most layers have one segment: its fields then sit at fixed offsets of the parameter block instead of behind a
+    // register-indexed constant load per 16-column chunk
+    if (p.n_seg == 1) { epilogue_chunk_seg(p, p.seg[0], bias, gc, m, row_ok, v); return; }
     int s = 0;
 #pragma unroll
     for (int q = 1; q < kConvMaxSegments; ++q)
         if (q < p.n_seg && p.seg[q].col_begin <= gc) s = q;
-    const ConvSegment& sg = p.seg[s];
+    epilogue_chunk_seg(p, p.seg[s], bias, gc, m, row_ok, v);
+}
+__device__ __forceinline__ void epilogue_chunk_seg(const ConvParams& p, const ConvSegment& sg, const float* bias, int gc, long long m, bool row_ok,
+                                                   const uint32_t (&v)[16]) {
     float f[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) f[i] = __uint_as_float(v[i]);
