@@ -45,6 +45,7 @@ constexpr int kEpiWarps = 8;
 constexpr int kTmemCols = 512;
 constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 2;
+constexpr int kStageRow = 40;               // u16 per staged pixel row: 32 channels + 8 of padding (80 bytes: conflict-free 16-byte reads)
 constexpr int kMaxTilePixels = 1024;        // S * np upper bound (4 x 256)
 
 typedef CUresult (*encode_im2col_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -160,7 +161,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
     uint8_t* wt_base = smem + 2 * (size_t)p.p_stage_bytes;
     Bars* bars = (Bars*)(kHalo ? wt_base + (size_t)p.w_stages * p.w_stage_bytes : smem + (size_t)p.stages * stage_bytes);
 
-    __shared__ int pix_tab[2 * kMaxTilePixels];                // halo mode: tile column -> output pixel index or -1 (double buffered)
+    __shared__ int pix_tab[2 * kMaxTilePixels];
+    __shared__ __align__(16) uint16_t stage_t[kEpiWarps * 32 * kStageRow];   // per-warp 32 pixel x 32 channel transposition tiles                // halo mode: tile column -> output pixel index or -1 (double buffered)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int taps = p.KH * p.KW;
     const int T = p.S * p.np;                                  // (virtual) pixels per CTA tile
@@ -347,7 +349,50 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
             const float bias = (ch_ok && (flags & kSegBias)) ? __ldg(p.bias + ch) : 0.0f;
             timed_wait(&bars->tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
-            if (warp_has_work) {
+            // Fast path (bf16 output, all 32 channels of this warp real and in one segment): a 32 pixel x 32 channel block is
+            // transposed through shared memory, so that a lane then owns a PIXEL and stores its 32 channels as four 16-byte
+            // words -- ~5 instructions per value instead of ~11 for one 2-byte store per value (the weight-major kernel was
+            // epilogue-bound on the 35x35 layers: profiles/r01_conv_roles.md).
+            // (every shuffle outside the && chain: a short-circuited __shfl_sync would wait for lanes that skipped it)
+            const int si_lo = __shfl_sync(0xffffffffu, si, 0), si_hi = __shfl_sync(0xffffffffu, si, 31);
+            const bool ch_ok_hi = __shfl_sync(0xffffffffu, (int)ch_ok, 31) != 0;
+            const bool fast = si_lo == si_hi && ch_ok_hi && !f32 && p.seg[si].coff % 8 == 0 && p.seg[si].ld % 8 == 0;
+            if (fast) {
+                const unsigned long long ob = (unsigned long long)out_base;
+                char* const warp_base = (char*)(((unsigned long long)__shfl_sync(0xffffffffu, (unsigned)(ob >> 32), 0) << 32) |
+                                                (unsigned long long)__shfl_sync(0xffffffffu, (unsigned)ob, 0));
+                uint16_t* stg = stage_t + (warp - 4) * 32 * kStageRow;
+                for (int s = 0; s < p.S; ++s) {
+                    const int j0 = s * p.np + half * hcols;
+                    const long long x0 = tile_x0 + j0;
+                    const int* tab = pix_tab + tbuf * kMaxTilePixels + j0;
+                    const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + j0) + ((uint32_t)(e * 32) << 16);
+                    for (int col = 0; col < hcols; col += 32) {
+                        if (x0 + col >= span) break;                                   // warp-uniform
+                        uint32_t v[32];
+                        ptx::tmem_ld_32x32(t_row + (uint32_t)col, v);
+                        ptx::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) {
+                            float f = __uint_as_float(v[j]) + bias;
+                            f = relu ? fmaxf(f, 0.0f) : f;
+                            stg[j * kStageRow + lane] = __bfloat16_as_ushort(__float2bfloat16_rn(f));
+                        }
+                        __syncwarp();
+                        long long m;                                                   // the output pixel this lane now owns
+                        bool ok;
+                        if (kHalo) { const int t = tab[col + lane]; ok = t >= 0; m = t; }
+                        else { m = x0 + col + lane; ok = m < span; }
+                        if (ok) {
+                            const uint4* r = reinterpret_cast<const uint4*>(stg + lane * kStageRow);
+                            uint4* dst = reinterpret_cast<uint4*>(warp_base + m * step);
+                            const uint4 q0 = r[0], q1 = r[1], q2 = r[2], q3 = r[3];
+                            dst[0] = q0; dst[1] = q1; dst[2] = q2; dst[3] = q3;
+                        }
+                        __syncwarp();
+                    }
+                }
+            } else if (warp_has_work) {
                 for (int s = 0; s < p.S; ++s) {
                     const int j0 = s * p.np + half * hcols;                            // first column of this warp in the tile
                     const long long x0 = tile_x0 + j0;
@@ -445,7 +490,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     const long long Q = (long long)g.n_max * Hp * Wp;
     const double kFill = 36.0, kFixed = 3000.0;                     // bytes/cycle/SM with every SM pulling; cycles per tile
     const double kEpi = 11.0;                                       // epilogue issue slots per pixel (one SMSP serves 32 channels)
-    const long long kSmem = 208 * 1024;   // dynamic smem budget (8 KB static table + barriers + alignment slack on top)
+    const long long kSmem = 188 * 1024;   // dynamic smem budget (28 KB static table + transposition tiles, barriers and alignment slack on top)
     double best = -1.0;
     for (int kc = 64; kc >= 32; kc -= 32) {
         const int chunks = (g.Cin + kc - 1) / kc, rb = 2 * kc, ksteps = kc / 16;
@@ -529,8 +574,8 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
         if (rc != CUDA_SUCCESS) { if (err) *err = "cuTensorMapEncodeTiled (weights) failed, code " + std::to_string((int)rc); return FTF_INTERNAL; }
     }
     // the attribute is per device: set it whenever a plan is made
-    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 218 * 1024);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 218 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(conv_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 198 * 1024);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(conv_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 198 * 1024);
     if (e != cudaSuccess) return cuda_fail(e, "cudaFuncSetAttribute(conv_tc_kernel)", err);
     return FTF_OK;
 }
