@@ -628,6 +628,8 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     const long long Q = (long long)g.n_max * Hp * Wp;
     static const bool allow_kc32 = !(getenv("FTF_NO_KC32") && getenv("FTF_NO_KC32")[0] == '1');
     const double kFill = 36.0, kFixed = 2500.0;
+    // experiment switches: force the number of N tiles / halo sub-tiles the shape search may pick
+    const int force_nt = getenv("FTF_PM_NT") ? atoi(getenv("FTF_PM_NT")) : 0, force_S = getenv("FTF_PM_S") ? atoi(getenv("FTF_PM_S")) : 0;
     const long long kSmem = 208 * 1024;
     double best = -1.0;
     for (int kc = 64; kc >= 32; kc -= 32) {
@@ -644,6 +646,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
         for (int nt = (g.Cout + 255) / 256; nt <= (g.Cout + 31) / 32; ++nt) {
             const int bn = ((g.Cout + nt - 1) / nt + 15) / 16 * 16;
             if (bn > 256) continue;
+            if (force_nt && nt != force_nt) continue;
             const int tiles_n = (g.Cout + bn - 1) / bn;
             const long long b_bytes = (long long)bn * rb;
             if (!pair) {   // one im2col load per tap.  Every operand byte is written to shared memory once and read once: 64 + N/2 cycles per MMA
@@ -671,6 +674,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             }
             if (!(allow_halo && g.stride == 1 && taps > 1) || Q >= (1ll << 31) - 4096) continue;
             for (int S = 1; S <= 4; S *= 2) {
+                if (force_S && S != force_S) continue;
                 if (2 * S * bn > kTmemCols) continue;                  // keep two accumulator sets: epilogue overlaps the next tile
                 const int T = S * kBlockM;
                 const int loads = (T + halo + kHaloLoadRows - 1) / kHaloLoadRows;

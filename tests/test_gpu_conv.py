@@ -217,6 +217,27 @@ def test_inception_logits_and_top5(ftf, oracle, label_runner):
     assert np.array_equal(res["top_k_scores"].to_array(), np.take_along_axis(p, res["top_k_indices"].to_array(), 1))
 
 
+@pytest.mark.parametrize("kind", ["pm", "pm2", "wm"])
+def test_whole_network_on_one_kernel_family(ftf, oracle, monkeypatch, kind):
+    """The network built from ONE kernel family (one-CTA pixel-major, CTA-pair pixel-major, weight-major), so that every
+    layer shape -- the multi-segment fused 1x1 groups and the fp32 pool-branch segments included -- runs through that
+    family's epilogue and shape logic, not only the layers the plan-time timing happens to give it."""
+    import oracle.inception as oi
+    monkeypatch.setenv("FTF_CONV_KIND", kind)
+    monkeypatch.setenv("FTF_CONV_TUNE", "0")
+    r = ftf.Runner("builtin:inception_v3", None, None, ftf.default_config(max_batch=2, top_k=5, num_classes=1000, seed=2024))
+    try:
+        x = np.random.default_rng(7).standard_normal((2, 299, 299, 3)).astype(np.float32)
+        res = r.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits", "top_k_indices"])
+    finally:
+        r.close()
+    want = oi.Net(1000, 2024, mode=1).forward(x)
+    logits = res["logits"].to_array()
+    assert np.abs(logits - want).max() <= 1e-2 * np.abs(want).max()
+    wi, _ = oracle.top_labels(oracle.softmax_rows(want), 1000, 5)
+    assert np.array_equal(res["top_k_indices"].to_array(), wi)
+
+
 def test_label_results_do_not_depend_on_batch(ftf, label_runner):
     x = np.random.default_rng(8).standard_normal((4, 299, 299, 3)).astype(np.float32)
     full = label_runner.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits"])["logits"].to_array()
