@@ -440,6 +440,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     const int q_tiles = (int)((p.Q + T - 1) / T);
     const int total_tiles = q_tiles * p.n_tiles;
     const int acc_cols = p.S * p.block_n;
+    const int b_tap_bytes = p.block_n * rb;                      // one tap's weight tile; a B stage holds p.b_group of them
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&tm_a);
@@ -484,11 +485,13 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                     wp += kHaloLoadRows;
                     while (wp >= p.Wp) { wp -= p.Wp; if (++hp == p.Hp) { hp = 0; ++img; } }
                 }
-                for (int tap = 0; tap < taps; ++tap) {
+                for (int tap0 = 0; tap0 < taps; tap0 += p.b_group) {       // b_group taps' weight tiles per stage and barrier round trip
+                    const int g_taps = min(p.b_group, taps - tap0);
                     timed_wait(&b_empty[bs], bph ^ 1, prof, &t_wait);
-                    ptx::mbar_expect_tx_elect(&b_full[bs], (uint32_t)p.b_stage_bytes);
-                    ptx::tma_load_2d_elect(b_base + (size_t)bs * p.b_stage_bytes, &tm_b, &b_full[bs], tap * p.Cin + chunk * p.kc,
-                                     n_tile * p.block_n, false);
+                    ptx::mbar_expect_tx_elect(&b_full[bs], (uint32_t)(g_taps * b_tap_bytes));
+                    for (int t = 0; t < g_taps; ++t)
+                        ptx::tma_load_2d_elect(b_base + (size_t)bs * p.b_stage_bytes + (size_t)t * b_tap_bytes, &tm_b, &b_full[bs],
+                                               (tap0 + t) * p.Cin + chunk * p.kc, n_tile * p.block_n, false);
                     if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
                 }
                 if (++as == kAStages) { as = 0; aph ^= 1; }
@@ -516,26 +519,31 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 // the 32-channel stem layers -- profiles/r01_conv_roles.md.)
                 const uint32_t a_lo0 = desc_lo(ptx::smem_u32(a_base + (size_t)as * p.a_stage_bytes));
                 const int nk = chunk == p.cin_chunks - 1 ? p.ksteps_last : p.kc / 16;     // skip the all-zero K steps
-                int tap = 0;
-                for (int kh = 0; kh < p.KH; ++kh)
-                    for (int kw = 0; kw < p.KW; ++kw, ++tap) {
+                int tap = 0, in_group = 0, kh = 0, kw = 0;
+                for (; tap < taps; ++tap) {
+                    if (in_group == 0) {                                   // a new group of taps' weights
                         timed_wait(&b_full[bs], bph, prof, &w_full);
                         ptx::tc_fence_after();
-                        const uint32_t b_lo = desc_lo(ptx::smem_u32(b_base + (size_t)bs * p.b_stage_bytes));
-                        const uint32_t first = (chunk | tap) != 0 ? 1u : 0u;
-                        // tap (kh, kw) of sub-tile s: the window entered (s*128 + kh*Wp + kw) rows further down
-                        const uint32_t a_lo = a_lo0 + (uint32_t)(kh * p.Wp + kw) * rows16;
-                        // straight-line issue: the number of K steps is resolved once per tap, not per MMA (a conditional
-                        // around an elected instruction costs a convergence check each time)
-                        switch (nk) {
-                        case 4: issue_subtiles<4>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
-                        case 3: issue_subtiles<3>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
-                        case 2: issue_subtiles<2>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
-                        default: issue_subtiles<1>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
-                        }
+                    }
+                    const uint32_t b_lo = desc_lo(ptx::smem_u32(b_base + (size_t)bs * p.b_stage_bytes + (size_t)in_group * b_tap_bytes));
+                    const uint32_t first = (chunk | tap) != 0 ? 1u : 0u;
+                    // tap (kh, kw) of sub-tile s: the window entered (s*128 + kh*Wp + kw) rows further down
+                    const uint32_t a_lo = a_lo0 + (uint32_t)(kh * p.Wp + kw) * rows16;
+                    // straight-line issue: the number of K steps is resolved once per tap, not per MMA (a conditional
+                    // around an elected instruction costs a convergence check each time)
+                    switch (nk) {
+                    case 4: issue_subtiles<4>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                    case 3: issue_subtiles<3>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                    case 2: issue_subtiles<2>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                    default: issue_subtiles<1>(p.S, d_tmem, (uint32_t)p.block_n, a_lo, sub16, b_lo, hi, idesc, first); break;
+                    }
+                    if (++kw == p.KW) { kw = 0; ++kh; }
+                    if (++in_group == p.b_group || tap + 1 == taps) {      // group consumed: release the stage
+                        in_group = 0;
                         ptx::umma_commit_elect(&b_empty[bs]);
                         if (++bs == p.b_stages) { bs = 0; bph ^= 1; }
                     }
+                }
                 ptx::umma_commit_elect(&a_empty[as]);
                 if (++as == kAStages) { as = 0; aph ^= 1; }
             }
@@ -629,7 +637,8 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     static const bool allow_kc32 = !(getenv("FTF_NO_KC32") && getenv("FTF_NO_KC32")[0] == '1');
     const double kFill = 36.0, kFixed = 2500.0;
     // experiment switches: force the number of N tiles / halo sub-tiles the shape search may pick
-    const int force_nt = getenv("FTF_PM_NT") ? atoi(getenv("FTF_PM_NT")) : 0, force_S = getenv("FTF_PM_S") ? atoi(getenv("FTF_PM_S")) : 0;
+    const int force_nt = getenv("FTF_PM_NT") ? atoi(getenv("FTF_PM_NT")) : 0, force_S = getenv("FTF_PM_S") ? atoi(getenv("FTF_PM_S")) : 0,
+              force_grp = getenv("FTF_PM_BGROUP") ? atoi(getenv("FTF_PM_BGROUP")) : 0;
     const long long kSmem = 208 * 1024;
     double best = -1.0;
     for (int kc = 64; kc >= 32; kc -= 32) {
@@ -688,8 +697,16 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                 if (t < best) {
                     best = t;
                     p.halo_mode = 1; p.Hp = Hp; p.Wp = Wp; p.Q = Q; p.S = S; p.block_n = bn; p.n_tiles = tiles_n; p.kc = kc; p.cin_chunks = chunks;
-                    p.a_loads = loads; p.a_stage_bytes = (int)a_bytes; p.b_stage_bytes = (int)b_bytes;
-                    p.b_stages = (int)(room / b_bytes > kMaxStages ? kMaxStages : room / b_bytes);
+                    p.a_loads = loads; p.a_stage_bytes = (int)a_bytes;
+                    // weight tiles of several taps share a stage (one barrier round trip per group): as many as leave three
+                    // stages, at most one filter row... the whole filter when its tiles are tiny
+                    int grp = (int)(room / (3 * b_bytes));
+                    if (grp > taps) grp = taps;
+                    if (grp < 1) grp = 1;
+                    if (force_grp) grp = force_grp < taps ? force_grp : taps;
+                    p.b_group = grp; p.b_stage_bytes = (int)(grp * b_bytes);
+                    p.b_stages = (int)(room / p.b_stage_bytes > kMaxStages ? kMaxStages : room / p.b_stage_bytes);
+                    if (p.b_stages < 2) { p.b_group = 1; p.b_stage_bytes = (int)b_bytes; p.b_stages = (int)(room / b_bytes > kMaxStages ? kMaxStages : room / b_bytes); }
                     p.acc_stages = 2;
                 }
             }

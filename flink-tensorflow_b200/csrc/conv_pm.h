@@ -28,6 +28,7 @@ struct ConvParams {
     int a_loads;                // im2col loads of kHaloLoadRows rows that fill one window
     int a_stage_bytes;          // a_loads * kHaloLoadRows * 128
     int b_stages;               // weight-tile ring depth
+    int b_group;                // filter taps whose weight tiles share one stage (halo mode)
     int acc_stages;             // 1 or 2 TMEM accumulator sets of S * block_n columns
     int pair;                   // 1: CTA-pair kernel (cta_group::2): tiles of 256 pixels, each CTA holds block_n/2 weight rows
     int wide_stores;            // 1: every segment's rows and channel offset are 32-byte aligned (256-bit epilogue stores)

@@ -157,6 +157,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
     const int rb = 2 * p.kc;                                   // bytes per operand row
     // im2col: [stages x (W | P)]            halo: [2 x window][w_stages x W]
     const int stage_bytes = p.w_stage_bytes + p.p_stage_bytes;
+    const int w_tap_bytes = kWRows * rb;                         // one tap's weight tile; a halo-mode W stage holds p.w_group of them
     uint8_t* win_base = smem;
     uint8_t* wt_base = smem + 2 * (size_t)p.p_stage_bytes;
     Bars* bars = (Bars*)(kHalo ? wt_base + (size_t)p.w_stages * p.w_stage_bytes : smem + (size_t)p.stages * stage_bytes);
@@ -229,11 +230,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                         ptx::tma_load_im2col_elect(dst + (size_t)i * kHaloLoadRows * rb, &tm_p, &bars->a_full[as], chunk * p.kc, wp - p.pad_w,
                                         hp - p.pad_h, img, 0, 0, false);
                     }
-                    for (int tap = 0; tap < taps; ++tap) {
+                    for (int tap0 = 0; tap0 < taps; tap0 += p.w_group) {   // w_group taps' weight tiles per stage and barrier round trip
+                        const int g_taps = min(p.w_group, taps - tap0);
                         timed_wait(&bars->b_empty[bs], bph ^ 1, profiling, &t_wait);
-                        ptx::mbar_expect_tx_elect(&bars->b_full[bs], (uint32_t)p.w_stage_bytes);
-                        ptx::tma_load_2d_elect(wt_base + (size_t)bs * p.w_stage_bytes, &tm_w, &bars->b_full[bs], tap * p.Cin + chunk * p.kc,
-                                         m_tile * kWRows, false);
+                        ptx::mbar_expect_tx_elect(&bars->b_full[bs], (uint32_t)(g_taps * w_tap_bytes));
+                        for (int t = 0; t < g_taps; ++t)
+                            ptx::tma_load_2d_elect(wt_base + (size_t)bs * p.w_stage_bytes + (size_t)t * w_tap_bytes, &tm_w, &bars->b_full[bs],
+                                                   (tap0 + t) * p.Cin + chunk * p.kc, m_tile * kWRows, false);
                         if (++bs == p.w_stages) { bs = 0; bph ^= 1; }
                     }
                     if (++as == 2) { as = 0; aph ^= 1; }
@@ -274,18 +277,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                     ptx::tc_fence_after();
                     const uint32_t win_addr = ptx::smem_u32(win_base + (size_t)as * p.p_stage_bytes);
                     const int nk = chunk == p.cin_chunks - 1 ? p.ksteps_last : ksteps;
-                    int tap = 0;
-                    for (int kh = 0; kh < p.KH; ++kh)
-                        for (int kw = 0; kw < p.KW; ++kw, ++tap) {
+                    int in_group = 0, kh = 0, kw = 0;
+                    for (int tap = 0; tap < taps; ++tap) {
+                        if (in_group == 0) {                               // a new group of taps' weights
                             timed_wait(&bars->b_full[bs], bph, profiling, &w_full);
                             ptx::tc_fence_after();
-                            const uint32_t w_lo = desc_lo(ptx::smem_u32(wt_base + (size_t)bs * p.w_stage_bytes));
-                            // tap (kh, kw) of sub-tile s: the window entered (s*np + kh*Wp + kw) rows further down
-                            const uint32_t x_lo = desc_lo(win_addr) + (uint32_t)(kh * p.Wp + kw) * ((uint32_t)rb >> 4);
-                            issue_dispatch(nk, p.S, d_tmem, (uint32_t)p.np, w_lo, x_lo, (uint32_t)(p.np * rb) >> 4, hi, idesc, (chunk | tap) != 0 ? 1u : 0u);
+                        }
+                        const uint32_t w_lo = desc_lo(ptx::smem_u32(wt_base + (size_t)bs * p.w_stage_bytes + (size_t)in_group * w_tap_bytes));
+                        // tap (kh, kw) of sub-tile s: the window entered (s*np + kh*Wp + kw) rows further down
+                        const uint32_t x_lo = desc_lo(win_addr) + (uint32_t)(kh * p.Wp + kw) * ((uint32_t)rb >> 4);
+                        issue_dispatch(nk, p.S, d_tmem, (uint32_t)p.np, w_lo, x_lo, (uint32_t)(p.np * rb) >> 4, hi, idesc, (chunk | tap) != 0 ? 1u : 0u);
+                        if (++kw == p.KW) { kw = 0; ++kh; }
+                        if (++in_group == p.w_group || tap + 1 == taps) {  // group consumed: release the stage
+                            in_group = 0;
                             ptx::umma_commit_elect(&bars->b_empty[bs]);
                             if (++bs == p.w_stages) { bs = 0; bph ^= 1; }
                         }
+                    }
                     ptx::umma_commit_elect(&bars->a_empty[as]);
                     if (++as == 2) { as = 0; aph ^= 1; }
                 }
@@ -534,8 +542,14 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                 if (best < 0 || t < best) {
                     best = t;
                     p.halo_mode = 1; p.kc = kc; p.cin_chunks = chunks; p.np = np; p.S = S; p.stages = 0;
-                    p.w_stages = (int)(room / w_bytes > kMaxStages ? kMaxStages : room / w_bytes);
-                    p.w_stage_bytes = (int)w_bytes; p.p_stage_bytes = (int)p_bytes; p.p_loads = loads;
+                    // weight tiles of several taps share a stage (one barrier round trip per group), as many as leave three stages
+                    int grp = (int)(room / (3 * w_bytes));
+                    if (grp > taps) grp = taps;
+                    if (grp < 1) grp = 1;
+                    p.w_group = grp; p.w_stage_bytes = (int)(grp * w_bytes);
+                    p.w_stages = (int)(room / p.w_stage_bytes > kMaxStages ? kMaxStages : room / p.w_stage_bytes);
+                    if (p.w_stages < 2) { p.w_group = 1; p.w_stage_bytes = (int)w_bytes; p.w_stages = (int)(room / w_bytes > kMaxStages ? kMaxStages : room / w_bytes); }
+                    p.p_stage_bytes = (int)p_bytes; p.p_loads = loads;
                     p.acc_stages = 2 * S * np <= kTmemCols ? 2 : 1;
                 }
             }

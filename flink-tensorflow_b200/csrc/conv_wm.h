@@ -28,6 +28,7 @@ struct ConvParams {
     int S;                      // np-pixel sub-tiles per CTA tile (each with its own accumulator)
     int p_loads;                // im2col loads of kHaloLoadRows rows that fill one window
     int w_stages;               // halo mode: weight-tile ring depth
+    int w_group;                // halo mode: filter taps whose weight tiles share one stage
     int acc_stages;             // 1 or 2 TMEM accumulator sets of S * np columns
     int ksteps_last;            // K=16 steps holding real channels in the LAST channel chunk (the all-zero rest is skipped)
     unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
