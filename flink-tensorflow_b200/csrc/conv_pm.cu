@@ -644,10 +644,10 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     for (int kc = 64; kc >= 32; kc -= 32) {
         const int chunks = (g.Cin + kc - 1) / kc, rb = 2 * kc, ksteps = kc / 16;
         const int total_ksteps = (chunks - 1) * ksteps + (g.Cin - kc * (chunks - 1) + 15) / 16;   // all-zero K steps are skipped
-        // 32-channel K blocks (SWIZZLE_64B rows) only for Cin <= 32: measured, an MMA on 64-byte rows costs about twice
-        // one on 128-byte rows, so halving the MMA count gains nothing; what remains is the halved operand window of
-        // the 32-channel stem layers.  A fixed rule, so that every candidate kernel of a layer walks K in the same order
-        // and produces the same bits.
+        // 32-channel K blocks (64-byte rows, SWIZZLE_64B) only for Cin <= 32, where they halve the operand window without
+        // adding K blocks.  For wider inputs they split K into more blocks, and a block's fixed cost (barrier round trip,
+        // commit) outweighs the MMAs saved; the MMA itself runs as fast on 64-byte rows as on 128-byte ones (probed).
+        // A fixed rule, so that every candidate kernel of a layer walks K in the same order and produces the same bits.
         const bool kc32_saves = allow_kc32 && g.Cin <= 32;
         if ((kc == 32) != kc32_saves) continue;
         const double real_frac = (double)g.Cin / (chunks * kc);
