@@ -63,26 +63,9 @@ __device__ __forceinline__ void timed_wait(uint64_t* bar, uint32_t parity, bool 
     *acc += clock64() - t0;
 }
 
-__device__ __forceinline__ void tma_load_im2col(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
-                                                int off_w, int off_h) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(
-            ptx::smem_u32(dst)),
-        "l"(m), "r"(ptx::smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
-        : "memory");
-}
-
-// K-major, 128B-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart.
-__device__ __forceinline__ uint64_t smem_desc(uint32_t smem_addr, int row_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);      // start address, 16-byte units
-    d |= (uint64_t)1 << 16;                            // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)((8 * row_bytes) >> 4) << 32;       // stride byte offset: one 8-row group
-    d |= (uint64_t)1 << 46;                            // descriptor version (Blackwell)
-    d |= (uint64_t)(row_bytes == 128 ? 2 : 4) << 61;   // SWIZZLE_128B / SWIZZLE_64B
-    return d;
-}
-// The same descriptor in two 32-bit halves (see the halo kernel's MMA loop).
+// K-major swizzled operand descriptor in two 32-bit halves: rows of row_bytes (128 -> SWIZZLE_128B, 64 -> SWIZZLE_64B), 8-row groups
+// contiguous.  hi = stride byte offset (one 8-row group) | descriptor version (bit 46) | layout type (bits 61-63);
+// lo = start address in 16-byte units | leading byte offset field = 1.  Only lo changes between MMAs.
 __device__ __forceinline__ uint32_t desc_hi(int row_bytes) {
     return (uint32_t)((8 * row_bytes) >> 4) | (1u << 14) | ((uint32_t)(row_bytes == 128 ? 2 : 4) << 29);
 }
@@ -243,14 +226,6 @@ __device__ __forceinline__ void epilogue_row(const ConvParams& p, const float* b
     }
 }
 
-__device__ __forceinline__ void tma_load_im2col_pair(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
-                                                     int off_w, int off_h) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.im2col.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(
-            ptx::smem_u32(dst)),
-        "l"(m), "r"(ptx::smem_u32(bar) & ptx::kPeerMask), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
-        : "memory");
-}
 
 // kPair = false: one CTA per 128-pixel tile.  kPair = true: a cluster of two CTAs on one TPC works on 256 pixels with
 // cta_group::2 MMAs -- CTA r loads the im2col rows of ITS 128 pixels and rows [r*block_n/2, (r+1)*block_n/2) of the weight

@@ -76,25 +76,7 @@ __device__ __forceinline__ void timed_wait(uint64_t* bar, uint32_t parity, bool 
     *acc += clock64() - t0;
 }
 
-__device__ __forceinline__ void tma_load_im2col(void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
-                                                int off_w, int off_h) {
-    asm volatile(
-        "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};" ::"r"(
-            ptx::smem_u32(dst)),
-        "l"(m), "r"(ptx::smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"((uint16_t)off_w), "h"((uint16_t)off_h)
-        : "memory");
-}
 
-// K-major swizzled operand tile: rows of row_bytes (128 -> SWIZZLE_128B, 64 -> SWIZZLE_64B), 8-row groups contiguous.
-__device__ __forceinline__ uint64_t smem_desc(uint32_t smem_addr, int row_bytes) {
-    uint64_t d = 0;
-    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);                 // start address, 16-byte units
-    d |= (uint64_t)1 << 16;                                       // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)((8 * row_bytes) >> 4) << 32;                  // stride byte offset: one 8-row group
-    d |= (uint64_t)1 << 46;                                       // descriptor version (Blackwell)
-    d |= (uint64_t)(row_bytes == 128 ? 2 : 4) << 61;              // SWIZZLE_128B / SWIZZLE_64B
-    return d;
-}
 // The same descriptor in two 32-bit halves: the high word (stride, version, swizzle) never changes inside a kernel, the low
 // word is 0x10000 | (address >> 4), so another tap, sub-tile or K step is one 32-bit add (see conv_pm.cu).
 __device__ __forceinline__ uint32_t desc_hi(int row_bytes) {
