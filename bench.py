@@ -199,11 +199,13 @@ def pinned_array(lib, np, nbytes, dtype):
     return p, np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,)).view(dtype)
 
 
-def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_label", sync=None):
+def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_label", sync=None, wire=False, offered_rate=None):
     """Records through ftf_submit/ftf_poll at saturation (micro-batches of 64, 2 ms deadline); latency = submit -> result
     polled.  kind "normalize_label": BASELINE config 5 on one GPU, raw 640x480 RGB records (normalise -> Inception-v3 ->
     top-5 on the device).  kind "inception": config 4's records, normalised 299x299x3 fp32 images (Inception-v3 -> top-5),
-    the per-record map() the reference's InceptionModel.label runs."""
+    the per-record map() the reference's InceptionModel.label runs.
+    wire: every record sits in the pinned ring as a TensorValue wire image (TensorValue.java:142-187) and is decoded in place
+    (ftf_tv_decode, no copy) before it is submitted.  offered_rate: records/s the source emits (None = saturation)."""
     from flink_tensorflow_b200.host import _as_ftf, FtfTensor, _check
     cfg = ftf.default_config(device=device, max_batch=INC["batch"], max_delay_us=2000, top_k=INC["top_k"], out_h=299, out_w=299,
                              mean=128.0, scale=128.0, num_classes=INC["classes"], seed=INC["seed"])
@@ -224,6 +226,27 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
         dims = (C.c_int64 * 3)(299, 299, 3)
         dtype, pipeline = ftf.DataType.FLOAT, "fp32 299x299x3 -> bf16 -> Inception-v3 -> softmax/top-5"
     recs = [FtfTensor(dtype, 3, dims, ring.ctypes.data + i * rec_bytes, rec_bytes) for i in range(n_buf)]
+    wire_p = None
+    if wire:
+        # the same payloads as Flink wire images in a second pinned ring: 0x01 | BE header | payload (37 header bytes here)
+        wlen = int(lib.ftf_tv_binary_length(3, rec_bytes))
+        wstride = (wlen + 255) // 256 * 256
+        wire_p, wring = pinned_array(lib, np, n_buf * wstride, np.uint8)
+        written = C.c_int64()
+        for i in range(n_buf):
+            _check(lib.ftf_tv_encode(C.byref(recs[i]), wring.ctypes.data + i * wstride, wlen, C.byref(written)), r.handle)
+            assert written.value == wlen
+        wire_ptrs = [wring.ctypes.data + i * wstride for i in range(n_buf)]
+        dims_buf = (C.c_int64 * 32)()
+        decoded = FtfTensor()
+
+    def submit(i):
+        slot = i % n_buf
+        if wire:                                               # parse the wire image where it lies; the payload is not copied
+            _check(lib.ftf_tv_decode(wire_ptrs[slot], wlen, C.byref(decoded), dims_buf), r.handle)
+            _check(lib.ftf_submit(r.handle, i, C.byref(decoded)), r.handle)
+        else:
+            _check(lib.ftf_submit(r.handle, i, C.byref(recs[slot])), r.handle)
     keys = (C.c_char_p * 2)(b"top_k_indices", b"top_k_scores")
     tags = (C.c_uint64 * 256)()
     outs = (FtfTensor * 512)()
@@ -243,7 +266,7 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
     for i in range(n_warm):
         while i - done >= n_buf - INC["batch"]:
             drain(True)
-        _check(lib.ftf_submit(r.handle, i, C.byref(recs[i % n_buf])), r.handle)
+        submit(i)
         if i == 0:
             _check(lib.ftf_poll_select(r.handle, 2, keys), r.handle)
     _check(lib.ftf_flush(r.handle), r.handle)
@@ -254,10 +277,15 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
         sync()
     r2 = r.stats()
     t0 = time.perf_counter()
+    period = 1.0 / offered_rate if offered_rate else 0.0
     for i in range(n_records):
         while i - done >= n_buf - INC["batch"]:                # back-pressure: never overwrite an unpolled record
             drain(True)
-        _check(lib.ftf_submit(r.handle, i, C.byref(recs[i % n_buf])), r.handle)
+        if period:                                             # a source that emits at a fixed rate: poll while waiting
+            due = t0 + i * period
+            while time.perf_counter() < due:
+                drain(False)
+        submit(i)
         if i % 16 == 15:
             drain(False)
     _check(lib.ftf_flush(r.handle), r.handle)
@@ -267,7 +295,9 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
     st = r.stats()
     r.close()
     lib.ftf_host_free(p)
-    return {"records_per_s": n_records / dt, "records": n_records, "latency_us_p50": st["queue_latency_us_p50"],
+    if wire_p:
+        lib.ftf_host_free(wire_p)
+    return {"records_per_s": n_records / dt, "offered_records_per_s": offered_rate, "record_format": "TensorValue wire image, decoded in place" if wire else "raw tensor", "records": n_records, "latency_us_p50": st["queue_latency_us_p50"],
             "latency_us_p99": st["queue_latency_us_p99"], "max_batch": INC["batch"], "max_delay_us": 2000,
             "h2d_bytes_per_record": rec_bytes, "d2h_bytes_per_record": 2 * INC["top_k"] * 4, "pipeline": pipeline, "seconds": dt,
             "api": "ftf_submit/ftf_poll, pinned record payloads", "launches": int(st["kernel_launches"] - r2["kernel_launches"]),
@@ -458,7 +488,12 @@ def run_ours(args):
                "api": "ftf_submit/ftf_poll (C ABI): one fp32 299x299x3 record per call from pinned host memory, micro-batches of 64, "
                       "top-5 indices and scores read back per record"}
     if wl == "inception" and not args.quick:
-        extra["streaming"] = streaming_bench(ftf, lib, np, local_rank)
+        # BASELINE config 5 on this rank's GPU: 640x480 u8 records as TensorValue wire images -> normalise -> Inception-v3 ->
+        # top-5; >= 10^5 records at saturation, then a source emitting at half that rate (latency at a sustainable load)
+        sat = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * 1600, wire=True)
+        half = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * 800, wire=True, offered_rate=0.5 * sat["records_per_s"])
+        extra["streaming"] = sat
+        extra["streaming_half_rate"] = half
     if rank != 0:
         return
     # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -----------------------------------------
