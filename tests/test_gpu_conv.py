@@ -238,6 +238,40 @@ def test_whole_network_on_one_kernel_family(ftf, oracle, monkeypatch, kind):
     assert np.array_equal(res["top_k_indices"].to_array(), wi)
 
 
+def test_two_label_runners_share_one_gpu(ftf, monkeypatch):
+    """Two Flink subtasks on one GPU: two runners created and driven concurrently from two threads give the bits a single
+    runner gives (model-chosen kernels, so that both pick the same ones whatever the timing noise)."""
+    import threading
+    monkeypatch.setenv("FTF_CONV_TUNE", "0")
+    x = np.random.default_rng(11).standard_normal((4, 299, 299, 3)).astype(np.float32)
+    cfg = ftf.default_config(max_batch=4, top_k=5, num_classes=1000, seed=2024)
+    ref = ftf.Runner("builtin:inception_v3", None, None, cfg)
+    try:
+        want = ref.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits"])["logits"].to_array()
+    finally:
+        ref.close()
+    results, errors = [None, None], []
+
+    def subtask(i):
+        try:
+            r = ftf.Runner("builtin:inception_v3", None, None, cfg)
+            try:
+                for _ in range(5):
+                    results[i] = r.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits"])["logits"].to_array()
+            finally:
+                r.close()
+        except Exception as ex:  # noqa: BLE001
+            errors.append(ex)
+
+    threads = [threading.Thread(target=subtask, args=(i,)) for i in range(2)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    assert np.array_equal(results[0], want) and np.array_equal(results[1], want)
+
+
 def test_label_results_do_not_depend_on_batch(ftf, label_runner):
     x = np.random.default_rng(8).standard_normal((4, 299, 299, 3)).astype(np.float32)
     full = label_runner.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits"])["logits"].to_array()
