@@ -61,19 +61,30 @@ __device__ __forceinline__ float finish(float top, float bot, float yl, const Re
     return kMulRecip ? __fmul_rn(d, p.inv_scale) : __fdiv_rn(d, p.scale);
 }
 
-// The interpolation of kN output columns (c0 + j*kThreads) over the rows of one band; see the kernel below.
+// ---- TMA-staged band kernel -------------------------------------------------------------------
+// Persistent: a CTA of kBS threads walks bands blockIdx.x, blockIdx.x + gridDim.x, ... through two shared-memory stages guarded
+// by full/empty mbarriers: warp 0 refills a stage as soon as all warps have released it, and no warp ever waits for another
+// one (no __syncthreads in the loop), so the warps drift apart and hide each other's shared-memory latency.
+//
+// A thread owns kN output columns (col = threadIdx.x + j*kBS, kN warp-uniform): their x terms and shared-memory offsets are
+// computed ONCE per kernel -- they do not depend on the band -- and live in registers; the row loop is branch-free
+// straight-line code: per output value 4 address adds, 4 byte loads, the conversions, the 11 rounded fp32 operations of the
+// reference's formula and one store.  kBS is chosen by the launcher so that out_w*3 columns split into whole groups with as
+// few idle lanes as possible (897 columns: 3 x 320 instead of 4 x 256).
 // u8 -> f32 uses the 2^23 trick: m(b) = bits 0x4B000000|b = 2^23 + b exactly.  A tap that only enters a difference needs
 // no conversion at all, since m(tr) - m(tl) = tr - tl exactly; the left taps are converted with one FADD each.
-template <int kN, bool kMulRecip, typename OutT>
-__device__ __forceinline__ void band_columns(const ResizeParams& p, uint32_t sbase, int c0, int ow3, int rows, int oy0, int iy0,
-                                             OutT* __restrict__ orow) {
+template <int kN, int kBS, bool kMulRecip, typename OutT>
+__device__ __forceinline__ void run_bands(const ResizeParams& p, OutT* __restrict__ out, long long total_bands, int stage_bytes,
+                                          uint32_t smem_a, uint64_t* full, uint64_t* empty, const CUtensorMap* tmap, uint8_t* smem) {
+    const int ow3 = p.out_w * 3;
+    const int c0 = (int)threadIdx.x;
     uint32_t off_lo[kN], off_hi[kN];
     float xl[kN];
     bool live[kN];
 #pragma unroll
     for (int j = 0; j < kN; ++j) {
-        live[j] = c0 + j * kThreads < ow3;
-        const int col = min(c0 + j * kThreads, ow3 - 1);                   // a dead lane recomputes the last column, unstored
+        live[j] = c0 + j * kBS < ow3;
+        const int col = min(c0 + j * kBS, ow3 - 1);                        // a dead lane recomputes the last column, unstored
         const int px = col / 3, c = col - px * 3;
         const float fx = __fmul_rn((float)px, p.ws);
         const int lo = (int)fx;
@@ -82,64 +93,17 @@ __device__ __forceinline__ void band_columns(const ResizeParams& p, uint32_t sba
         const int blo = lo * 3 + c, bhi = hi * 3 + c;
         // chunk index = byte / cw without an integer division: (b + 0.5)/cw is at least 0.5/cw away from an integer
         const int klo = (int)(((float)blo + 0.5f) * p.inv_cw), khi = (int)(((float)bhi + 0.5f) * p.inv_cw);
-        off_lo[j] = sbase + (uint32_t)(klo * p.chunk_stride + (blo - klo * p.cw));
-        off_hi[j] = sbase + (uint32_t)(khi * p.chunk_stride + (bhi - khi * p.cw));
+        off_lo[j] = smem_a + (uint32_t)(klo * p.chunk_stride + (blo - klo * p.cw));
+        off_hi[j] = smem_a + (uint32_t)(khi * p.chunk_stride + (bhi - khi * p.cw));
     }
-    for (int r = 0; r < rows; ++r, orow += ow3) {
-        const float py = __fmul_rn((float)(oy0 + r), p.hs);                // the row terms: a few uniform operations
-        const int ylo = (int)py;
-        const int yhi = min(ylo + 1, p.in_h - 1);
-        const uint32_t r0 = (uint32_t)((ylo - iy0) * p.cw), r1 = (uint32_t)((yhi - iy0) * p.cw);
-        const float yl = __fsub_rn(py, (float)ylo);
-#pragma unroll
-        for (int j = 0; j < kN; ++j) {
-            const float mtl = __uint_as_float(0x4B000000u | lds_u8(r0 + off_lo[j])), mtr = __uint_as_float(0x4B000000u | lds_u8(r0 + off_hi[j]));
-            const float mbl = __uint_as_float(0x4B000000u | lds_u8(r1 + off_lo[j])), mbr = __uint_as_float(0x4B000000u | lds_u8(r1 + off_hi[j]));
-            const float tl = __fsub_rn(mtl, 8388608.0f), bl = __fsub_rn(mbl, 8388608.0f);
-            const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(mtr, mtl), xl[j]));
-            const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(mbr, mbl), xl[j]));
-            const OutT v = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
-            if (live[j]) orow[j * kThreads] = v;
-        }
-    }
-}
-
-// ---- TMA-staged band kernel -------------------------------------------------------------------
-// Persistent: a CTA walks bands blockIdx.x, blockIdx.x + gridDim.x, ... through two shared-memory stages guarded by
-// full/empty mbarriers: warp 0 refills a stage as soon as all eight warps have released it, and no warp ever waits for
-// another one (no __syncthreads in the loop), so the warps drift apart and hide each other's shared-memory latency.
-template <bool kMulRecip, typename OutT>
-__global__ void __launch_bounds__(kThreads, 4)
-resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p, long long total_bands,
-                     int stage_bytes) {
-    extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t full[2], empty[2];
-
-    // run by all lanes of warp 0 on warp-uniform values; one elected lane issues each instruction (see ptx.cuh)
-    auto issue = [&](long long blk, int stage) {       // fetch the input rows of band `blk`
+    auto issue = [&](long long blk, int stage) {       // warp 0, all lanes, one elected lane per instruction (see ptx.cuh)
         const long long img = blk / p.bands;
         const int band = (int)(blk - img * p.bands);
         const int iy0 = (int)__fmul_rn((float)(band * p.th), p.hs);
         ptx::mbar_expect_tx_elect(&full[stage], (uint32_t)(p.n_chunks * p.cw * p.br));
         for (int k = 0; k < p.n_chunks; ++k)
-            ptx::tma_load_3d_elect(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, &tmap, &full[stage], k * p.cw, iy0, (int)img);
+            ptx::tma_load_3d_elect(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, tmap, &full[stage], k * p.cw, iy0, (int)img);
     };
-
-    if (threadIdx.x == 0) {
-        ptx::mbar_init(&full[0], 1);
-        ptx::mbar_init(&full[1], 1);
-        ptx::mbar_init(&empty[0], kThreads / 32);
-        ptx::mbar_init(&empty[1], kThreads / 32);
-        ptx::fence_mbar_init();
-    }
-    __syncthreads();
-    if (threadIdx.x < 32) {
-        if ((long long)blockIdx.x < total_bands) issue(blockIdx.x, 0);
-        if ((long long)blockIdx.x + gridDim.x < total_bands) issue((long long)blockIdx.x + gridDim.x, 1);
-    }
-
-    const int ow3 = p.out_w * 3;
-    const uint32_t smem_a = ptx::smem_u32(smem);             // 32-bit shared-window addresses: no generic-pointer arithmetic
     int it = 0;
     for (long long blk = blockIdx.x; blk < total_bands; blk += gridDim.x, ++it) {
         const int stage = it & 1;
@@ -150,30 +114,78 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
         const int rows = min(p.th, p.out_h - oy0);
         const int iy0 = (int)__fmul_rn((float)oy0, p.hs);  // first input row of the band
         ptx::mbar_wait(&full[stage], phase);
-        const uint32_t sbase = smem_a + (uint32_t)(stage * stage_bytes);
-        OutT* obase = out + ((size_t)img * p.out_h + oy0) * ow3;
-        // A thread owns up to kCols output columns (col = c0 + j*kThreads): their x terms and shared-memory offsets live in
-        // registers for the whole band, and the row loop is specialised on how many of them the WARP has (the last group of
-        // a row is usually partial), so its body is branch-free straight-line code: per output value 4 address adds,
-        // 4 byte loads, the conversions, the 11 rounded fp32 operations of the reference's formula and one store.
-        for (int c0 = threadIdx.x; c0 - (int)(threadIdx.x & 31) < ow3; c0 += kThreads * kCols) {
-            const int warp_c0 = c0 - (int)(threadIdx.x & 31);                 // first column of this warp's group
-            const int nj = min(kCols, (ow3 - warp_c0 + kThreads - 1) / kThreads);   // columns with at least one live lane
-            OutT* orow = obase + c0;
-            switch (nj) {
-            case 4: band_columns<4, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
-            case 3: band_columns<3, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
-            case 2: band_columns<2, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
-            default: band_columns<1, kMulRecip>(p, sbase, c0, ow3, rows, oy0, iy0, orow); break;
+        const uint32_t sbase = (uint32_t)(stage * stage_bytes);
+        OutT* orow = out + ((size_t)img * p.out_h + oy0) * ow3 + c0;
+        // the row terms of the band (at most 8 rows): lane r computes row r's once, the row loop fetches them by shuffle
+        uint32_t my_r0, my_r1;
+        float my_yl;
+        {
+            const float py = __fmul_rn((float)(oy0 + (int)(threadIdx.x & 31)), p.hs);
+            const int ylo = (int)py;
+            const int yhi = min(ylo + 1, p.in_h - 1);
+            my_r0 = sbase + (uint32_t)((ylo - iy0) * p.cw);
+            my_r1 = sbase + (uint32_t)((yhi - iy0) * p.cw);
+            my_yl = __fsub_rn(py, (float)ylo);
+        }
+        for (int r = 0; r < rows; ++r, orow += ow3) {
+            const uint32_t r0 = __shfl_sync(0xffffffffu, my_r0, r), r1 = __shfl_sync(0xffffffffu, my_r1, r);
+            const float yl = __shfl_sync(0xffffffffu, my_yl, r);
+#pragma unroll
+            for (int j = 0; j < kN; ++j) {
+                const float mtl = __uint_as_float(0x4B000000u | lds_u8(r0 + off_lo[j])), mtr = __uint_as_float(0x4B000000u | lds_u8(r0 + off_hi[j]));
+                const float mbl = __uint_as_float(0x4B000000u | lds_u8(r1 + off_lo[j])), mbr = __uint_as_float(0x4B000000u | lds_u8(r1 + off_hi[j]));
+                const float tl = __fsub_rn(mtl, 8388608.0f), bl = __fsub_rn(mbl, 8388608.0f);
+                const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(mtr, mtl), xl[j]));
+                const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(mbr, mbl), xl[j]));
+                const OutT v = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
+                if (live[j]) orow[j * kBS] = v;
             }
         }
-        // this warp is done with the stage; thread 0 refills it (band it+2) once every warp has said so
+        // this warp is done with the stage; warp 0 refills it (band it+2) once every warp has said so
         __syncwarp();
         if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&empty[stage]);
-        if (threadIdx.x < 32 && blk + 2ll * gridDim.x < total_bands) {     // warp 0 refills
+        if (threadIdx.x < 32 && blk + 2ll * gridDim.x < total_bands) {
             ptx::mbar_wait(&empty[stage], phase);
             issue(blk + 2ll * gridDim.x, stage);
         }
+    }
+}
+
+template <int kBS, bool kMulRecip, typename OutT>
+__global__ void __launch_bounds__(kBS, (kBS <= 256 ? 4 : 3))
+resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p, long long total_bands,
+                     int stage_bytes) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full[2], empty[2];
+    if (threadIdx.x == 0) {
+        ptx::mbar_init(&full[0], 1);
+        ptx::mbar_init(&full[1], 1);
+        ptx::mbar_init(&empty[0], kBS / 32);
+        ptx::mbar_init(&empty[1], kBS / 32);
+        ptx::fence_mbar_init();
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {                                     // the first two bands
+        for (int s = 0; s < 2; ++s) {
+            const long long blk = (long long)blockIdx.x + (long long)s * gridDim.x;
+            if (blk >= total_bands) break;
+            const long long img = blk / p.bands;
+            const int band = (int)(blk - img * p.bands);
+            const int iy0 = (int)__fmul_rn((float)(band * p.th), p.hs);
+            ptx::mbar_expect_tx_elect(&full[s], (uint32_t)(p.n_chunks * p.cw * p.br));
+            for (int k = 0; k < p.n_chunks; ++k)
+                ptx::tma_load_3d_elect(smem + (size_t)s * stage_bytes + (size_t)k * p.chunk_stride, &tmap, &full[s], k * p.cw, iy0, (int)img);
+        }
+    }
+    const uint32_t smem_a = ptx::smem_u32(smem);             // 32-bit shared-window addresses: no generic-pointer arithmetic
+    const int warp_c0 = (int)(threadIdx.x & ~31u);            // first column of this warp
+    const int ow3 = p.out_w * 3;
+    const int nj = warp_c0 < ow3 ? min(kCols, (ow3 - warp_c0 + kBS - 1) / kBS) : 0;   // columns with at least one live lane in this warp
+    switch (nj) {
+    case 4: run_bands<4, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;
+    case 3: run_bands<3, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;
+    case 2: run_bands<2, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;
+    default: run_bands<1, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;   // also warps without columns: they keep the barriers in step
     }
 }
 
@@ -234,11 +246,33 @@ template <typename OutT>
 int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool use_tma, size_t smem,
                  const CUtensorMap* tmap, int sms, cudaStream_t s, std::string* err) {
     if (use_tma) {
-        auto kern = recip ? resize_norm_band_tma<true, OutT> : resize_norm_band_tma<false, OutT>;
-        FTF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem)), err);
+        // block size: out_w*3 columns in kc <= kCols whole groups of bs threads with the fewest idle lanes
+        const int ow3 = p.out_w * 3;
+        static const int kSizes[] = {320, 288, 256, 224, 192};
+        int bs = 256, best_waste = 1 << 30;
+        for (int cand : kSizes) {
+            const int kc = (ow3 + cand - 1) / cand;
+            if (kc > kCols) continue;
+            const int waste = kc * cand - ow3;
+            if (waste * bs < best_waste * cand) { best_waste = waste; bs = cand; }        // relative waste
+        }
         const long long bands = p.n * p.bands;
-        const long long resident = (long long)sms * 4;      // persistent: 4 CTAs per SM, two stages each
-        kern<<<(unsigned)(bands < resident ? bands : resident), kThreads, 2 * smem, s>>>(*tmap, out, p, bands, (int)smem);
+        const long long resident = (long long)sms * (bs <= 256 ? 4 : 3);                  // persistent CTAs, two stages each
+        const unsigned grid = (unsigned)(bands < resident ? bands : resident);
+#define FTF_K2_LAUNCH(BS)                                                                                              \
+        {                                                                                                              \
+            auto kern = recip ? resize_norm_band_tma<BS, true, OutT> : resize_norm_band_tma<BS, false, OutT>;          \
+            FTF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem)), err);   \
+            kern<<<grid, BS, 2 * smem, s>>>(*tmap, out, p, bands, (int)smem);                                          \
+        }
+        switch (bs) {
+        case 320: FTF_K2_LAUNCH(320) break;
+        case 288: FTF_K2_LAUNCH(288) break;
+        case 224: FTF_K2_LAUNCH(224) break;
+        case 192: FTF_K2_LAUNCH(192) break;
+        default: FTF_K2_LAUNCH(256) break;
+        }
+#undef FTF_K2_LAUNCH
     } else {
         auto kern = recip ? resize_norm_direct<true, OutT> : resize_norm_direct<false, OutT>;
         const long long total = p.n * p.out_h * p.out_w * 3;
@@ -294,7 +328,7 @@ int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out
         }
         p.bands = (out_h + p.th - 1) / p.th;
         p.inv_cw = 1.0f / (float)p.cw;
-        if (!fits || n * (long long)p.bands > 0x7fffffffLL) use_tma = false;
+        if (!fits || n * (long long)p.bands > 0x7fffffffLL || (long long)out_w * 3 > 320ll * kCols) use_tma = false;
     }
     if (use_tma) {
         auto encode = get_tensor_map_encode_tiled();
