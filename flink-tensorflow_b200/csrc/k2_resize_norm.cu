@@ -70,7 +70,7 @@ __device__ __forceinline__ float finish(float top, float bot, float yl, const Re
 // computed ONCE per kernel -- they do not depend on the band -- and live in registers; the row loop is branch-free
 // straight-line code: per output value 4 address adds, 4 byte loads, the conversions, the 11 rounded fp32 operations of the
 // reference's formula and one store.  kBS is chosen by the launcher so that out_w*3 columns split into whole groups with as
-// few idle lanes as possible (897 columns: 3 x 320 instead of 4 x 256).
+// few idle lanes as possible among 256, 224 and 192 threads (four CTAs per SM).
 // u8 -> f32 uses the 2^23 trick: m(b) = bits 0x4B000000|b = 2^23 + b exactly.  A tap that only enters a difference needs
 // no conversion at all, since m(tr) - m(tl) = tr - tl exactly; the left taps are converted with one FADD each.
 template <int kN, int kBS, bool kMulRecip, typename OutT>
@@ -248,16 +248,18 @@ int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool 
     if (use_tma) {
         // block size: out_w*3 columns in kc <= kCols whole groups of bs threads with the fewest idle lanes
         const int ow3 = p.out_w * 3;
-        static const int kSizes[] = {320, 288, 256, 224, 192};
-        int bs = 256, best_waste = 1 << 30;
+        // (320- and 288-thread blocks waste fewer lanes on 897 columns but leave room for only three CTAs per SM: measured slower)
+        static const int kSizes[] = {256, 224, 192};
+        int bs = 256;
+        long long best_waste = 1ll << 40;
         for (int cand : kSizes) {
             const int kc = (ow3 + cand - 1) / cand;
             if (kc > kCols) continue;
-            const int waste = kc * cand - ow3;
+            const long long waste = (long long)kc * cand - ow3;
             if (waste * bs < best_waste * cand) { best_waste = waste; bs = cand; }        // relative waste
         }
         const long long bands = p.n * p.bands;
-        const long long resident = (long long)sms * (bs <= 256 ? 4 : 3);                  // persistent CTAs, two stages each
+        const long long resident = (long long)sms * 4;                                    // persistent CTAs, two stages each
         const unsigned grid = (unsigned)(bands < resident ? bands : resident);
 #define FTF_K2_LAUNCH(BS)                                                                                              \
         {                                                                                                              \
@@ -266,8 +268,6 @@ int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool 
             kern<<<grid, BS, 2 * smem, s>>>(*tmap, out, p, bands, (int)smem);                                          \
         }
         switch (bs) {
-        case 320: FTF_K2_LAUNCH(320) break;
-        case 288: FTF_K2_LAUNCH(288) break;
         case 224: FTF_K2_LAUNCH(224) break;
         case 192: FTF_K2_LAUNCH(192) break;
         default: FTF_K2_LAUNCH(256) break;
@@ -328,7 +328,7 @@ int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out
         }
         p.bands = (out_h + p.th - 1) / p.th;
         p.inv_cw = 1.0f / (float)p.cw;
-        if (!fits || n * (long long)p.bands > 0x7fffffffLL || (long long)out_w * 3 > 320ll * kCols) use_tma = false;
+        if (!fits || n * (long long)p.bands > 0x7fffffffLL || (long long)out_w * 3 > 256ll * kCols) use_tma = false;
     }
     if (use_tma) {
         auto encode = get_tensor_map_encode_tiled();
