@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py -- one JSON line per run (see the round contract).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload half_plus_two|normalize|inception]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--workload half_plus_two|normalize|inception|jpeg]
   python bench.py --impl reference ...          the reference's CPU path (oracle stand-in) on the host cores
   torchrun --nproc-per-node N bench.py --gpus N one rank per GPU, records sharded, no collective on the data path
 
@@ -125,6 +125,56 @@ def torchvision_cpu(threads, unit, seconds=10.0):
         return {"unavailable": str(ex)[:200]}
 
 
+JPEG = {"batch": 256, "h": 480, "w": 640, "quality": 85, "subsampling": "4:2:0", "distinct": 16}
+
+
+def jpeg_files(np, seed, n=None):
+    """Synthetic photo-like 640x480 images (smooth colour fields + sensor-like noise) written as baseline JPEG by Pillow
+    (quality 85, 4:2:0, standard Huffman tables, no restart markers: what a camera or `convert` writes by default)."""
+    import io
+    from PIL import Image
+    rng = np.random.default_rng(seed)
+    h, w = JPEG["h"], JPEG["w"]
+    y, x = np.mgrid[0:h, 0:w]
+    files = []
+    for _ in range(JPEG["distinct"]):
+        p = rng.uniform(0, 6.28, 3)
+        img = np.stack([128 + 90 * np.sin(x / rng.uniform(20, 60) + p[c]) * np.cos(y / rng.uniform(15, 50)) for c in range(3)], -1)
+        img = np.clip(img + rng.normal(0, 10, (h, w, 3)), 0, 255).astype(np.uint8)
+        b = io.BytesIO()
+        Image.fromarray(img).save(b, "JPEG", quality=JPEG["quality"])
+        files.append(b.getvalue())
+    n = JPEG["batch"] if n is None else n
+    return [files[i % len(files)] for i in range(n)]
+
+
+def cpu_jpeg(np, oracle, files, threads, seconds):
+    """The oracle's decoder over `files`, one file per task on `threads` host threads (ctypes drops the GIL)."""
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(oracle.jpeg_decode, files[:threads]))
+        t0, done = time.perf_counter(), 0
+        while time.perf_counter() - t0 < seconds:
+            list(ex.map(oracle.jpeg_decode, files))
+            done += len(files)
+        return done / (time.perf_counter() - t0)
+
+
+def cpu_pillow(np, files, threads, seconds):
+    """libjpeg-turbo (SIMD) through Pillow on all host threads: the library TF's DecodeJpeg wraps, the strongest CPU stand-in."""
+    import io
+    from concurrent.futures import ThreadPoolExecutor
+    from PIL import Image
+    dec = lambda f: np.asarray(Image.open(io.BytesIO(f)).convert("RGB")).shape
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(dec, files[:threads]))
+        t0, done = time.perf_counter(), 0
+        while time.perf_counter() - t0 < seconds:
+            list(ex.map(dec, files))
+            done += len(files)
+        return done / (time.perf_counter() - t0)
+
+
 def run_reference(args):
     import numpy as np
     import oracle
@@ -148,6 +198,14 @@ def run_reference(args):
         units, unit, metric, sample = float(b), "images/s", "ImageNormalization images/sec", "32 of the 256 images per step"
         config = {"workload": "ImageNormalization 640x480 -> 299x299 batch 256 (BASELINE config 3)", "sample_images": b}
         dtype = "f32"
+    elif wl == "jpeg":
+        from concurrent.futures import ThreadPoolExecutor
+        files = jpeg_files(np, 1234, 64)
+        pool = ThreadPoolExecutor(threads)
+        step = lambda: list(pool.map(oracle.jpeg_decode, files))
+        units, unit, metric, sample = float(len(files)), "images/s", "DecodeJpeg images/sec", "64 of the 256 files per step"
+        config = {"workload": "DecodeJpeg 640x480 baseline JPEG (quality 85, 4:2:0) batch 256", "sample_images": len(files)}
+        dtype = "u8"
     else:
         import oracle.inception as oinc                       # noqa: F401  (exists once the conv path lands)
         net = oinc.Net(INC["classes"], INC["seed"])
@@ -174,6 +232,8 @@ def run_reference(args):
                     "cannot run without a JVM; it omits the reference's per-record JNI/dispatch overhead"}
     if wl == "inception":
         line["cpu_torchvision_onednn"] = torchvision_cpu(threads, unit)
+    if wl == "jpeg":
+        line["cpu_pillow_libjpeg_turbo"] = {"value": cpu_pillow(np, files, threads, 5.0), "unit": unit, "cores": threads}
     print(json.dumps(line), flush=True)
 
 
@@ -361,6 +421,21 @@ def run_ours(args):
                               "(BASELINE config 3)", "l2": "input+output 511 MB per step, larger than L2",
                   "parallelism": f"dp{world} (records sharded, no collective)", **NORM}
         bound, peak, peak_unit = "hbm", pk["hbm"], "GB/s"
+    elif wl == "jpeg":
+        files = jpeg_files(np, 1234 + rank)
+        jb = device.JpegBatch(local_rank)
+        jb.load(files)
+        rgb = torch.empty(jb.rgb_bytes, dtype=torch.uint8, device="cuda")
+        step = lambda: jb.decode(out=rgb)
+        step(); jb.status()
+        units_per_step, unit, metric, dtype = float(len(files)), "images/s", "DecodeJpeg images/sec", "u8"
+        file_bytes = sum(len(f) for f in files)
+        algo_bytes = float(file_bytes + jb.rgb_bytes)
+        config = {"workload": "DecodeJpeg: 640x480 baseline JPEG files (quality 85, 4:2:0, no restart markers) -> RGB u8, batch 256 "
+                              "per GPU (the node in front of BASELINE config 3's resize)", "file_bytes_per_image": file_bytes // len(files),
+                  "segments": jb.segments, "l2": "coefficients + planes + RGB of one step (about 590 MB) exceed L2; no flush",
+                  "parallelism": f"dp{world} (records sharded, no collective)", **JPEG}
+        bound, peak, peak_unit = "hbm", pk["hbm"], "GB/s"
     else:
         bsz = INC["batch"]
         cfg = ftf.default_config(device=local_rank, max_batch=bsz, top_k=INC["top_k"], num_classes=INC["classes"], seed=INC["seed"])
@@ -422,6 +497,17 @@ def run_ours(args):
         tv.data_type, tv.shape, tv.buffer = ftf.DataType.FLOAT, (HPT_N, 1), hx.view(np.uint8)
         in_key, out_key = "x", "y"
         h2d = d2h = 4 * HPT_N
+    elif wl == "jpeg":
+        # the files through the public call: STRING tensor of JPEG files -> decode -> resize/normalise -> Inception-v3 -> top-5
+        r = ftf.Runner("builtin:normalize_label", None, None,
+                       ftf.default_config(device=local_rank, max_batch=64, top_k=INC["top_k"], num_classes=INC["classes"], seed=INC["seed"],
+                                          out_h=299, out_w=299, mean=128.0, scale=128.0))
+        tv = ftf.messages_to_tensor(files)
+        p, hx = pinned_array(lib, np, tv.buffer.nbytes, np.uint8)
+        hx[:] = tv.buffer
+        tv.buffer = hx
+        in_key, out_key = "inputs", "top_k_indices"
+        h2d, d2h = int(tv.buffer.nbytes), len(files) * (2 * INC["classes"] * 4 + 2 * INC["top_k"] * 4)
     elif wl == "inception":
         r = lab
         nb = INC["batch"] * 299 * 299 * 3 * 4
@@ -451,7 +537,7 @@ def run_ours(args):
     def e2e_step():
         _check(lib.ftf_run(r.handle, 1, ikeys, tin, 1, okeys, tout), r.handle)
         # the result (runner-owned pinned memory) is read by the host: first and last element
-        res = np.ctypeslib.as_array(C.cast(tout[0].data, C.POINTER(C.c_int32 if wl == "inception" else C.c_float)),
+        res = np.ctypeslib.as_array(C.cast(tout[0].data, C.POINTER(C.c_int32 if wl in ("inception", "jpeg") else C.c_float)),
                                     shape=(tout[0].nbytes // 4,))
         return float(res[0]) + float(res[-1])
     for _ in range(2):
@@ -471,6 +557,9 @@ def run_ours(args):
     e2e = {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
            "ms_per_step": e2e_ms, "steps": e2e_steps, "gpu_launches": int(e2e_launches),
            "api": "ftf_run (C ABI) with pinned host buffers, chunked H2D/kernel/D2H pipeline"}
+    if wl == "jpeg":
+        e2e["api"] = ("ftf_run (C ABI) on builtin:normalize_label with a STRING tensor of 256 JPEG files in host memory: header parse, "
+                      "upload of the entropy-coded bytes, J1-J3, resize/normalise, Inception-v3, top-5 read back")
     if wl == "inception":
         # The reference labels images record by record inside a map() (InceptionModel.label); the drop-in for that call
         # is ftf_submit/ftf_poll, which micro-batches 64 records, uploads each as it arrives and overlaps the upload of
@@ -511,6 +600,11 @@ def run_ours(args):
                 reps += 1
             cpu = {"value": 8.0 * n * reps / 1e9 / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
                    "sample": f"{reps} passes over 2^26 floats (1/4 of the workload), all host threads"}
+        elif wl == "jpeg":
+            cpu = {"value": cpu_jpeg(np, oracle, files[:64], threads, 8.0), "unit": unit, "cores": threads, "kind": "port",
+                   "sample": "passes over 64 of the 256 files for 8 s, C oracle, one file per task on all host threads"}
+            extra["cpu_pillow_libjpeg_turbo"] = {"value": cpu_pillow(np, files[:64], threads, 5.0), "unit": unit, "cores": threads,
+                                                 "note": "libjpeg-turbo (SIMD) through Pillow, the library TF's DecodeJpeg wraps"}
         elif wl == "inception":
             import oracle.inception as oinc
             net = oinc.Net(INC["classes"], INC["seed"], 0)
@@ -563,7 +657,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--quick", action="store_true", help="development A/B runs: skip the CPU baseline and the streaming leg")
-    ap.add_argument("--workload", default="inception", choices=["half_plus_two", "normalize", "inception"])
+    ap.add_argument("--workload", default="inception", choices=["half_plus_two", "normalize", "inception", "jpeg"])
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -10,7 +10,7 @@ _abi.load_library()
 from .host import (DataType, GenericModel, GraphMethod, HalfPlusTwo, ImageNormalization,  # noqa: E402,F401
                    ImageNormalizationMethod, InceptionModel, LabeledImage, LabelMethod, MiniCluster,
                    ModelFunction, PredictMethod, RegressionMethod, RichModel, Runner, TensorFlowModel,
-                   TensorName, TensorValue, VersionMismatchException, default_config, example,
+                   TensorName, TensorValue, VersionMismatchException, bytes_to_tensor, default_config, example,
                    map_with_model, messages_to_tensor)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

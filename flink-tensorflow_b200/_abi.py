@@ -79,6 +79,17 @@ SYMBOLS = {
     "ftf_debug_activation": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int32)]),
     "ftf_label_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,
                                 C.c_void_p]),
+    "ftf_jpeg_info": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "ftf_jpeg_batch_create": (C.c_int, [C.c_int32, C.POINTER(C.c_void_p)]),
+    "ftf_jpeg_batch_destroy": (None, [C.c_void_p]),
+    "ftf_jpeg_batch_error": (C.c_char_p, [C.c_void_p]),
+    "ftf_jpeg_batch_load": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.POINTER(C.c_int64),
+                                      C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_void_p]),
+    "ftf_jpeg_batch_rgb_bytes": (C.c_int64, [C.c_void_p]),
+    "ftf_jpeg_batch_scan_bytes": (C.c_int64, [C.c_void_p]),
+    "ftf_jpeg_batch_segments": (C.c_int32, [C.c_void_p]),
+    "ftf_jpeg_batch_decode_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "ftf_jpeg_batch_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int32]),
     "ftf_runner_stream": (C.c_void_p, [C.c_void_p]),
     "ftf_launch_count": (C.c_uint64, []),
     "ftf_version": (C.c_char_p, []),

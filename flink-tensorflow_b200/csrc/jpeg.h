@@ -1,0 +1,38 @@
+// jpeg.h -- baseline JPEG decoding on the GPU: the DecodeJpeg(channels=3) node in front of the normalisation graph
+// (EX/common/GraphBuilder.java:41-47; EX/inception/ImageNormalization.scala:56-57 feeds it the file bytes read by
+// EX/inception/ImageInputFormat.scala:63-80).  The host only reads the marker segments (a few hundred bytes per file);
+// entropy decoding, inverse DCT, upsampling and colour conversion run in csrc/jpeg.cu.
+#pragma once
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "jpeg_core.h"
+
+namespace ftf {
+namespace jpeg {
+
+// What the marker segments of one file say (host side).
+struct Parsed {
+    int width = 0, height = 0, ncomp = 0;
+    int hs = 1, vs = 1;
+    int restart = 0;                       // MCUs per restart interval, 0 = none
+    int tq[3] = {0, 0, 0}, td[3] = {0, 0, 0}, ta[3] = {0, 0, 0};
+    uint16_t quant[4][64];                 // row-major
+    bool quant_present[4] = {false, false, false, false};
+    HuffTable dc[4], ac[4];
+    bool dc_present[4] = {false, false, false, false}, ac_present[4] = {false, false, false, false};
+    int64_t scan_begin = 0;                // first entropy-coded byte
+};
+
+// Reads SOI .. SOS of one file.  Returns an FTF status; *err says what was wrong or unsupported.
+int parse_headers(const uint8_t* d, int64_t n, Parsed* out, std::string* err);
+
+// Geometry shared by the host planner and the kernels.
+void fill_geometry(const Parsed& p, ImageDesc* im);
+
+// Splits the entropy-coded bytes [p.scan_begin, n) at the RSTn markers (only when the file has a restart interval;
+// otherwise the whole scan is one segment and no byte of it is read on the host).  Offsets are relative to d.
+void find_segments(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, std::vector<Segment>* out);
+
+}  // namespace jpeg
+}  // namespace ftf

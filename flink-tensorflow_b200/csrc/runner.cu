@@ -111,9 +111,21 @@ int fix_geometry(ftf_runner* r, const ftf_tensor& t, bool single_record) {
     }
     case Kind::kNormalize:
     case Kind::kNormalizeLabel: {
+        if (t.dtype == FTF_STRING) {
+            // JPEG files, the reference's ImageFileTensor (EX/inception/package.scala:12-29): sizes come from each file
+            if (t.rank > 1) return fail(r, FTF_INVALID_ARGUMENT, "normalize expects a scalar or vector of STRING (JPEG files)");
+            if (r->kind == Kind::kNormalize) {
+                OutSpec o; o.key = "outputs"; o.dtype = FTF_FLOAT;
+                o.rec_dims = {r->cfg.out_h, r->cfg.out_w, 3};
+                o.rec_bytes = (size_t)r->cfg.out_h * r->cfg.out_w * 3 * 4;
+                outs.push_back(o);
+            }
+            in_bytes = 0;
+            break;
+        }
         const int base = single_record ? t.rank - 3 : t.rank - 3;
         if (t.dtype != FTF_UINT8 || (t.rank != 3 && t.rank != 4) || t.dims[t.rank - 1] != 3)
-            return fail(r, FTF_INVALID_ARGUMENT, "normalize expects a UINT8 tensor shaped [N,H,W,3] or [H,W,3]");
+            return fail(r, FTF_INVALID_ARGUMENT, "normalize expects a UINT8 tensor shaped [N,H,W,3] or [H,W,3], or a STRING tensor of JPEG files");
         const int64_t h = t.dims[base], w = t.dims[base + 1];
         if (h <= 0 || w <= 0 || h > 65535 || w > 65535)
             return fail(r, FTF_INVALID_ARGUMENT, "normalize: image height/width out of range");
@@ -166,7 +178,21 @@ int wait_slot(ftf_runner* r, Slot& s) {
 int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h_dst, bool uploaded = false) {
     std::string* err = &r->err;
     int rc;
-    if ((rc = s.d_in.ensure((size_t)n * r->in_rec_bytes, err))) return rc;
+    const bool jpg = s.jpeg_n > 0;         // d_in already holds this batch's images, decoded from files by decode_files
+    if (jpg) uploaded = true;
+    else if ((rc = s.d_in.ensure((size_t)n * r->in_rec_bytes, err))) return rc;
+    // resize + normalise of the batch in d_in: one launch, or one per image when decoded files differ in size
+    auto normalise = [&](int oh, int ow, void* outp, int out_dtype) -> int {
+        if (!jpg) return launch_resize_norm((const uint8_t*)s.d_in.p, n, r->in_h, r->in_w, oh, ow, r->cfg.mean, r->cfg.scale, outp, out_dtype, s.stream, err);
+        if (s.jpeg_uniform) return launch_resize_norm((const uint8_t*)s.d_in.p, n, s.jh[0], s.jw[0], oh, ow, r->cfg.mean, r->cfg.scale, outp, out_dtype, s.stream, err);
+        const size_t rec = (size_t)oh * ow * 3 * (out_dtype == FTF_FLOAT ? 4 : 2);
+        for (int64_t i = 0; i < n; ++i) {
+            const int rc1 = launch_resize_norm((const uint8_t*)s.d_in.p + s.joff[i], 1, s.jh[i], s.jw[i], oh, ow, r->cfg.mean, r->cfg.scale,
+                                               (uint8_t*)outp + (size_t)i * rec, out_dtype, s.stream, err);
+            if (rc1) return rc1;
+        }
+        return FTF_OK;
+    };
     for (size_t j = 0; j < r->outs.size(); ++j)
         if ((rc = s.d_out[j].ensure((size_t)n * r->outs[j].rec_bytes, err))) return rc;
     if (!uploaded) {     // micro-batched records were uploaded one by one as they were submitted
@@ -179,8 +205,7 @@ int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h
         rc = launch_affine_f32((const float*)s.d_in.p, (float*)s.d_out[0].p, n, r->affine.a, r->affine.b, s.stream, err);
         break;
     case Kind::kNormalize:
-        rc = launch_resize_norm((const uint8_t*)s.d_in.p, n, r->in_h, r->in_w, r->cfg.out_h, r->cfg.out_w,
-                                r->cfg.mean, r->cfg.scale, s.d_out[0].p, FTF_FLOAT, s.stream, err);
+        rc = normalise(r->cfg.out_h, r->cfg.out_w, s.d_out[0].p, FTF_FLOAT);
         break;
     case Kind::kLabel:
     case Kind::kNormalizeLabel: {
@@ -191,8 +216,7 @@ int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h
         if (r->kind == Kind::kLabel)
             rc = launch_cast_f32_bf16((const float*)s.d_in.p, img.p, (int64_t)n * img_elems, s.stream, err);
         else
-            rc = launch_resize_norm((const uint8_t*)s.d_in.p, n, r->in_h, r->in_w, kInceptionSide, kInceptionSide,
-                                    r->cfg.mean, r->cfg.scale, img.p, FTF_BFLOAT16, s.stream, err);
+            rc = normalise(kInceptionSide, kInceptionSide, img.p, FTF_BFLOAT16);
         if (rc) break;
         FTF_CUDA(cudaEventRecord(s.done, s.stream), err);
         FTF_CUDA(cudaStreamWaitEvent(r->net_stream, s.done, 0), err);
@@ -220,6 +244,36 @@ int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h
     return FTF_OK;
 }
 
+// Decodes n JPEG files into s.d_in on the slot's stream (J1-J3, csrc/jpeg.cu) and notes their geometry in the slot.
+int decode_files(ftf_runner* r, Slot& s, int n, const uint8_t* const* files, const int64_t* lens) {
+    int rc;
+    s.jpeg_n = 0;
+    if (!s.jpeg && (rc = ftf_jpeg_batch_create(r->device, &s.jpeg))) return fail(r, rc, thread_error());
+    s.joff.resize((size_t)n); s.jh.resize((size_t)n); s.jw.resize((size_t)n);
+    if ((rc = ftf_jpeg_batch_load(s.jpeg, n, files, lens, s.joff.data(), s.jh.data(), s.jw.data(), s.stream)))
+        return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
+    const int64_t bytes = ftf_jpeg_batch_rgb_bytes(s.jpeg);
+    if ((rc = s.d_in.ensure((size_t)bytes, &r->err))) return rc;
+    const uint64_t before = launches_so_far();
+    if ((rc = ftf_jpeg_batch_decode_dev(s.jpeg, (uint8_t*)s.d_in.p, bytes, s.stream))) return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
+    r->stats.kernel_launches += launches_so_far() - before;
+    r->stats.h2d_bytes += (uint64_t)ftf_jpeg_batch_scan_bytes(s.jpeg);
+    s.jpeg_uniform = true;
+    for (int i = 0; i < n; ++i)
+        if (s.jh[i] != s.jh[0] || s.jw[i] != s.jw[0] || s.joff[i] != (int64_t)i * s.jh[0] * s.jw[0] * 3) s.jpeg_uniform = false;
+    s.jpeg_n = n;
+    return FTF_OK;
+}
+
+// A finished slot whose input was JPEG files: did the device find a corrupt entropy-coded segment?
+int files_status(ftf_runner* r, Slot& s) {
+    if (s.jpeg_n <= 0 || !s.jpeg) return FTF_OK;
+    const int rc = ftf_jpeg_batch_status(s.jpeg, nullptr, 0);
+    s.jpeg_n = 0;
+    if (rc) return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
+    return FTF_OK;
+}
+
 bool pinned(const void* p) {
     cudaPointerAttributes a;
     if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
@@ -239,6 +293,7 @@ void destroy_runner(ftf_runner* r) {
     r->net.reset();
     for (auto& s : r->slots) {
         s.h_in.free_now(); s.d_in.free_now(); s.d_img.free_now();
+        if (s.jpeg) { ftf_jpeg_batch_destroy(s.jpeg); s.jpeg = nullptr; }
         for (auto& b : s.h_out) b.free_now();
         for (auto& b : s.d_out) b.free_now();
         if (s.done) cudaEventDestroy(s.done);
@@ -263,6 +318,13 @@ int launch_open(ftf_runner* r) {
         if ((rc = s.h_out[j].ensure((size_t)s.n * r->outs[j].rec_bytes, &r->err))) return rc;
     std::vector<void*> dst(r->outs.size());
     for (size_t j = 0; j < dst.size(); ++j) dst[j] = s.h_out[j].p;
+    if (s.files_n > 0) {
+        std::vector<const uint8_t*> fp((size_t)s.n);
+        std::vector<int64_t> fl((size_t)s.n);
+        for (int64_t i = 0; i < s.n; ++i) { fp[i] = s.files[i].data(); fl[i] = (int64_t)s.files[i].size(); }
+        if ((rc = decode_files(r, s, (int)s.n, fp.data(), fl.data()))) return rc;
+        s.files_n = 0;
+    } else s.jpeg_n = 0;
     rc = enqueue(r, s, s.n, s.h_in.p, dst.data(), /*uploaded=*/true);
     if (rc) { if (rc == FTF_INTERNAL) r->dead = true; return rc; }
     r->in_flight.push_back(r->open_slot);
@@ -427,6 +489,7 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
 
     // ---- how many records, and where the per-record payload starts ------------------------------
     int64_t n = 0;
+    bool files_in = false;                 // the input is a STRING tensor of JPEG files
     std::vector<int64_t> lead_dims;        // output dims before the per-record dims
     if (r->kind == Kind::kAffine) {
         if (r->affine.input_is_examples) {
@@ -440,6 +503,12 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
             n = numel(*x);
             if (x->nbytes != n * 4) return fail(r, FTF_INVALID_ARGUMENT, "input payload size does not match its shape");
         }
+    } else if (x->dtype == FTF_STRING && r->kind != Kind::kLabel) {
+        // JPEG files: ImageNormalization.scala:56-57 feeds the file bytes and the graph starts with DecodeJpeg
+        if ((rc = fix_geometry(r, *x, false))) return rc;
+        n = x->rank == 0 ? 1 : x->dims[0];
+        lead_dims = {n};
+        files_in = true;
     } else {
         if ((rc = fix_geometry(r, *x, false))) return rc;
         const int rec_rank = 3;
@@ -479,8 +548,10 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
         if (n <= chunk && n >= 64) chunk = (n / 2 + 7) / 8 * 8;
         if (const char* e = getenv("FTF_RUN_CHUNK")) chunk = std::max<int64_t>(1, std::min<int64_t>(r->net->max_batch(), atoll(e)));   // measurement switch
     }
+    if (files_in && !is_label_kind(r->kind)) chunk = 128;
     const bool parse = r->kind == Kind::kAffine && r->affine.input_is_examples;
-    const bool direct = !parse && n > 0 && pinned(x->data);
+    const bool direct = !parse && !files_in && n > 0 && pinned(x->data);
+    int files_rc = FTF_OK;
     cudaError_t e;
     if ((e = cudaEventRecord(r->ev_begin, r->slots[r->next_slot].stream)) != cudaSuccess) return cuda_fail(e, "cudaEventRecord", &r->err);
     for (int64_t c0 = 0; c0 < n; c0 += chunk) {
@@ -488,9 +559,19 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
         Slot& s = r->slots[r->next_slot];
         r->next_slot = (r->next_slot + 1) % kSlots;
         if ((rc = wait_slot(r, s))) return rc;
+        if (files_rc == FTF_OK) files_rc = files_status(r, s); else s.jpeg_n = 0;
         const void* src;
-        if (direct) src = (const uint8_t*)x->data + (size_t)c0 * r->in_rec_bytes;
+        if (files_in) {
+            std::vector<const uint8_t*> fp((size_t)cn);
+            std::vector<int64_t> fl((size_t)cn);
+            for (int64_t i = 0; i < cn; ++i)
+                if (string_tensor_item((const uint8_t*)x->data, x->nbytes, n, c0 + i, &fp[i], &fl[i]) != FTF_OK)
+                    return fail(r, FTF_INVALID_ARGUMENT, "malformed STRING tensor at element " + std::to_string(c0 + i));
+            if ((rc = decode_files(r, s, (int)cn, fp.data(), fl.data()))) return rc;
+            src = nullptr;
+        } else if (direct) { s.jpeg_n = 0; src = (const uint8_t*)x->data + (size_t)c0 * r->in_rec_bytes; }
         else {
+            s.jpeg_n = 0;
             if ((rc = s.h_in.ensure((size_t)cn * r->in_rec_bytes, &r->err))) return rc;
             if (parse) {
                 for (int64_t i = 0; i < cn; ++i) {
@@ -516,7 +597,12 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
             return cuda_fail(e, "cudaStreamWaitEvent", &r->err);
     if ((e = cudaEventRecord(r->ev_end, r->slots[0].stream)) != cudaSuccess) return cuda_fail(e, "cudaEventRecord", &r->err);
     if ((e = cudaEventSynchronize(r->ev_end)) != cudaSuccess) { r->dead = true; return cuda_fail(e, "model run", &r->err); }
-    for (auto& s : r->slots) s.busy = false;
+    std::string files_msg = r->err;
+    for (auto& s : r->slots) {
+        s.busy = false;
+        if (files_rc == FTF_OK) { files_rc = files_status(r, s); files_msg = r->err; } else s.jpeg_n = 0;
+    }
+    if (files_rc) return fail(r, files_rc, files_msg);
     float ms = 0.0f;
     if (cudaEventElapsedTime(&ms, r->ev_begin, r->ev_end) == cudaSuccess) r->stats.last_run_device_ms = ms; else cudaGetLastError();
     r->stats.runs += 1;
@@ -548,6 +634,8 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
     float parsed = 0.0f;
     const void* payload = rec->data;
     size_t bytes = 0;
+    const uint8_t* file = nullptr;         // set when the record is a JPEG file
+    int64_t file_len = 0;
     if (r->kind == Kind::kAffine) {
         if (r->affine.input_is_examples) {
             const int64_t cnt = rec->rank == 0 ? 1 : (rec->rank == 1 ? rec->dims[0] : -1);
@@ -560,6 +648,17 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
         } else if (rec->dtype != FTF_FLOAT || numel(*rec) != 1 || rec->nbytes != 4)
             return fail(r, FTF_INVALID_ARGUMENT, "a record is one FLOAT value");
         bytes = 4;
+    } else if (rec->dtype == FTF_STRING && r->kind != Kind::kLabel) {
+        // one JPEG file per record (ImageFileTensor).  Its header is checked now, so a malformed or unsupported file is
+        // refused here and never joins a batch; its entropy-coded bytes are decoded on the device when the batch closes.
+        const int64_t cnt = rec->rank == 0 ? 1 : (rec->rank == 1 ? rec->dims[0] : -1);
+        if (cnt != 1) return fail(r, FTF_INVALID_ARGUMENT, "a record is one JPEG file (STRING scalar or [1])");
+        if (string_tensor_item((const uint8_t*)rec->data, rec->nbytes, 1, 0, &file, &file_len) != FTF_OK)
+            return fail(r, FTF_INVALID_ARGUMENT, "malformed STRING tensor");
+        int32_t fh, fw, fc;
+        if ((rc = ftf_jpeg_info(file, file_len, &fh, &fw, &fc))) return fail(r, rc, thread_error());
+        if (r->outs.empty() || r->in_rec_bytes != 0) { if ((rc = fix_geometry(r, *rec, true))) return rc; }
+        bytes = 0;
     } else {
         if (rec->rank == 4 && rec->dims[0] != 1) return fail(r, FTF_INVALID_ARGUMENT, "a record is one image");
         if ((rc = fix_geometry(r, *rec, true))) return rc;
@@ -573,7 +672,7 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
         if ((rc = wait_slot(r, cand))) return rc;
         r->open_slot = r->next_slot;
         r->next_slot = (r->next_slot + 1) % kSlots;
-        cand.n = 0; cand.emitted = 0; cand.tags.clear(); cand.t_submit.clear();
+        cand.n = 0; cand.emitted = 0; cand.tags.clear(); cand.t_submit.clear(); cand.files_n = 0;
         const int cap = is_label_kind(r->kind) ? std::min(r->cfg.max_batch, r->net->max_batch()) : r->cfg.max_batch;
         // device staging of every slot on the first batch (an allocation later would stall the batches in flight); the
         // pinned host staging only if a payload ever arrives in pageable memory (see below)
@@ -591,6 +690,19 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
     // The record starts its way to HBM now, on the slot's stream, so that the upload overlaps the batches in flight.
     // A payload in pinned memory (ftf_host_alloc) is read in place by the copy engine -- the caller keeps it untouched
     // until the record's result has been polled; any other payload is first copied into the pinned slot.
+    if (s.n > 0 && (file != nullptr) != (s.files_n > 0))
+        return fail(r, FTF_INVALID_ARGUMENT, "records of one micro-batch must share one format (raw RGB or JPEG files)");
+    if (file) {
+        if (s.files.size() <= (size_t)s.n) s.files.resize((size_t)s.n + 1);
+        s.files[(size_t)s.n].assign(file, file + file_len);
+        s.files_n += 1;
+        s.tags.push_back(tag);
+        s.t_submit.push_back(std::chrono::steady_clock::now());
+        s.n += 1;
+        const int capf = is_label_kind(r->kind) ? std::min(r->cfg.max_batch, r->net->max_batch()) : r->cfg.max_batch;
+        if (s.n >= capf) return launch_open(r);
+        return FTF_OK;
+    }
     const void* src = payload;
     if (!(payload == rec->data && pinned(payload))) {
         const int cap0 = is_label_kind(r->kind) ? std::min(r->cfg.max_batch, r->net->max_batch()) : r->cfg.max_batch;
@@ -629,6 +741,7 @@ extern "C" int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor
     if (rc) return rc;
     if (!n_ready || cap < 0 || (cap && (!tags || !outs))) return fail(r, FTF_INVALID_ARGUMENT, "poll: null output arrays");
     *n_ready = 0;
+    int poll_rc = FTF_OK;
     const size_t no = r->outs.size();
     // a batch also closes max_delay_us after its first record (and at once when the caller blocks on it)
     if (r->open_slot >= 0 && r->slots[r->open_slot].n > 0) {
@@ -646,6 +759,9 @@ extern "C" int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor
         cudaError_t e = may_block ? cudaEventSynchronize(s.done) : cudaEventQuery(s.done);
         if (e == cudaErrorNotReady) { cudaGetLastError(); break; }
         if (e != cudaSuccess) { r->dead = true; return cuda_fail(e, "poll", &r->err); }
+        // a batch of JPEG records: a corrupt entropy-coded segment is only known now; the batch's results are still
+        // handed out (the damaged image decodes as far as libjpeg would have got) and the call reports the failure
+        if (s.emitted == 0 && s.jpeg_n > 0) { const int frc = files_status(r, s); if (frc && !poll_rc) poll_rc = frc; }
         may_block = false;
         const auto now = std::chrono::steady_clock::now();
         while (s.emitted < s.n && *n_ready < cap) {
@@ -666,7 +782,7 @@ extern "C" int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor
         if (s.emitted == s.n) { r->in_flight.pop_front(); s.busy = false; }
     }
     if (r->latencies_us.size() > (1u << 20)) r->latencies_us.erase(r->latencies_us.begin(), r->latencies_us.begin() + (1u << 19));
-    return FTF_OK;
+    return poll_rc;
 }
 
 extern "C" int ftf_poll_select(ftf_runner* r, int32_t n_keys, const char* const* keys) {

@@ -103,3 +103,97 @@ def global_avgpool(x):
     y = torch.empty((n, c), dtype=torch.bfloat16, device=x.device)
     _check(_abi.load_library().ftf_global_avgpool_bf16_dev(x.data_ptr(), n, h * w, c, y.data_ptr(), _stream()))
     return y
+
+
+def jpeg_info(data):
+    """(height, width, components) from the marker segments of one JPEG file; host only."""
+    h, w, c = C.c_int32(), C.c_int32(), C.c_int32()
+    buf = np.frombuffer(data, np.uint8)
+    _check(_abi.load_library().ftf_jpeg_info(buf.ctypes.data if buf.size else None, buf.size, C.byref(h), C.byref(w), C.byref(c)))
+    return h.value, w.value, c.value
+
+
+class JpegBatch:
+    """J1-J3 behind ftf_jpeg_batch_*: a reusable batch of JPEG files decoded on the current CUDA device."""
+
+    def __init__(self, device=None):
+        self._lib = _abi.load_library()
+        self._h = C.c_void_p()
+        dev = torch.cuda.current_device() if device is None else device
+        _check(self._lib.ftf_jpeg_batch_create(dev, C.byref(self._h)))
+        self.n = 0
+
+    def _ck(self, rc):
+        if rc:
+            msg = self._lib.ftf_jpeg_batch_error(self._h)
+            from .host import _ERRORS
+            raise _ERRORS.get(rc, RuntimeError)((msg or b"").decode("utf-8", "replace") + f" [status {rc}]")
+
+    def load(self, files):
+        """files: list of bytes.  Parses the headers, stages and uploads the entropy-coded data on the current stream."""
+        n = len(files)
+        self._keep = [np.frombuffer(f, np.uint8) for f in files]
+        ptrs = (C.c_void_p * max(1, n))(*[k.ctypes.data for k in self._keep])
+        lens = (C.c_int64 * max(1, n))(*[k.size for k in self._keep])
+        offs = (C.c_int64 * max(1, n))()
+        hs = (C.c_int32 * max(1, n))()
+        ws = (C.c_int32 * max(1, n))()
+        self._ck(self._lib.ftf_jpeg_batch_load(self._h, n, ptrs, lens, offs, hs, ws, _stream()))
+        self.n = n
+        self.offsets = [offs[i] for i in range(n)]
+        self.shapes = [(hs[i], ws[i]) for i in range(n)]
+        return self
+
+    @property
+    def rgb_bytes(self):
+        return self._lib.ftf_jpeg_batch_rgb_bytes(self._h)
+
+    @property
+    def uploaded_bytes(self):
+        return self._lib.ftf_jpeg_batch_scan_bytes(self._h)
+
+    @property
+    def segments(self):
+        return self._lib.ftf_jpeg_batch_segments(self._h)
+
+    def decode(self, out=None):
+        """Enqueues the three kernels on the current stream; returns the flat uint8 output tensor."""
+        if out is None:
+            out = torch.empty(max(1, self.rgb_bytes), dtype=torch.uint8, device="cuda")
+        _need_cuda(out)
+        self._ck(self._lib.ftf_jpeg_batch_decode_dev(self._h, out.data_ptr(), out.numel(), _stream()))
+        return out
+
+    def status(self):
+        """Waits for the decode; per-image status codes.  Raises ValueError for the first corrupt image."""
+        st = (C.c_int32 * max(1, self.n))()
+        rc = self._lib.ftf_jpeg_batch_status(self._h, st, self.n)
+        self.last_status = [st[i] for i in range(self.n)]
+        self._ck(rc)
+        return self.last_status
+
+    def images(self, flat):
+        """Views of the decoded images, uint8 [h,w,3] each, into the flat output tensor."""
+        return [flat[o: o + h * w * 3].view(h, w, 3) for o, (h, w) in zip(self.offsets, self.shapes)]
+
+    def close(self):
+        if self._h:
+            self._lib.ftf_jpeg_batch_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def decode_jpeg(files):
+    """DecodeJpeg(channels=3) for a list of files -> list of CUDA uint8 [h,w,3] tensors."""
+    b = JpegBatch()
+    try:
+        flat = b.load(files).decode()
+        b.status()
+        return b.images(flat)
+    finally:
+        b.close()

@@ -138,6 +138,13 @@ def messages_to_tensor(messages):
     return TensorValue(DataType.STRING, (n,), out[:got])
 
 
+def bytes_to_tensor(data):
+    """One byte string -> 0-D STRING tensor (TS/ByteStrings.scala:22-25: Tensor.create(bytes)); this is how the reference
+    wraps an image file into its ImageFileTensor (EX/inception/ImageInputFormat.scala:63-80)."""
+    tv = messages_to_tensor([bytes(data)])
+    return TensorValue(DataType.STRING, (), tv.buffer)
+
+
 def example(**features):
     """tf.Example with float_list features (FTT/util/TestData.scala:22-34), serialized by hand."""
     def ld(field, payload):

@@ -216,6 +216,36 @@ int ftf_pool_branch_bf16_static_dev(const void* in, int32_t n, int32_t h, int32_
 /* K6: global average pool, bf16 [n,hw,c] -> bf16 [n,c] (fp32 mean over the pixels). */
 int ftf_global_avgpool_bf16_dev(const void* in, int32_t n, int32_t hw, int32_t c, void* out, void* stream);
 
+/* ---- JPEG decoding on the GPU: the DecodeJpeg(channels=3) node the reference's normalisation graph starts with
+ * (EX/common/GraphBuilder.java:41-47, EX/inception/ImageNormalization.scala:56-57; the file bytes come from
+ * EX/inception/ImageInputFormat.scala:63-80).  8-bit baseline / extended-sequential Huffman files, 1 or 3 components,
+ * 4:4:4 / 4:2:2 / 4:2:0, optional restart intervals; results are bit-identical to libjpeg's defaults (integer slow IDCT,
+ * fancy upsampling).  Progressive/arithmetic/CMYK/multi-scan files: FTF_UNIMPLEMENTED.  Malformed headers:
+ * FTF_INVALID_ARGUMENT at load; a corrupt entropy-coded segment is found on the device and reported by
+ * ftf_jpeg_batch_status ("Invalid JPEG data" in TF).  ftf_run on "builtin:image_normalization" and
+ * "builtin:normalize_label" accepts a STRING tensor of files (the reference's ImageFileTensor) and runs these kernels
+ * in front of K2. */
+/* header fields of one file; host only (no device needed) */
+int ftf_jpeg_info(const uint8_t* file, int64_t len, int32_t* height, int32_t* width, int32_t* components);
+typedef struct ftf_jpeg_batch ftf_jpeg_batch;
+int ftf_jpeg_batch_create(int32_t device, ftf_jpeg_batch** out);
+void ftf_jpeg_batch_destroy(ftf_jpeg_batch* b);                  /* NULL-safe */
+const char* ftf_jpeg_batch_error(const ftf_jpeg_batch* b);
+/* Reads the marker segments of n files (host memory), stages their entropy-coded bytes and starts the upload on
+ * `stream`.  Optional outputs, n entries each: byte offset of image i in the decoded output, its height and width.
+ * Images are laid out in order, each 16-byte aligned, uint8 [h,w,3]. */
+int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* const* files, const int64_t* lens,
+                        int64_t* rgb_offsets, int32_t* heights, int32_t* widths, void* stream);
+int64_t ftf_jpeg_batch_rgb_bytes(const ftf_jpeg_batch* b);      /* size of the decoded output of the loaded batch   */
+int64_t ftf_jpeg_batch_scan_bytes(const ftf_jpeg_batch* b);     /* bytes uploaded for the loaded batch              */
+int32_t ftf_jpeg_batch_segments(const ftf_jpeg_batch* b);       /* independently decodable segments (= J1 threads)  */
+/* Enqueues J1-J3 on `stream` (the stream of the load, or one ordered after it): rgb_out is device memory of at least
+ * ftf_jpeg_batch_rgb_bytes().  May be called repeatedly for one load. */
+int ftf_jpeg_batch_decode_dev(ftf_jpeg_batch* b, uint8_t* rgb_out, int64_t cap, void* stream);
+/* Waits for the last decode and reports per image FTF_OK or FTF_INVALID_ARGUMENT (per_image may be NULL); returns
+ * the first failure. */
+int ftf_jpeg_batch_status(ftf_jpeg_batch* b, int32_t* per_image, int32_t n);
+
 /* Label path on device buffers: images [n,299,299,3] (f32 or bf16 per in_dtype) -> logits [n,classes]
  * f32, probs, top-k.  Runs on the runner's stream; the weights are the runner's. Any of
  * logits/probs/idx/score may be NULL. */

@@ -132,3 +132,22 @@ def tensor_name(s):
     idx = C.c_int()
     rc = lib().orc_tensor_name(s.encode(), op, len(op), C.byref(idx))
     return rc, op.value.decode(), idx.value
+
+
+def jpeg_info(data):
+    """(height, width, components) of a baseline JPEG file, or raises ValueError(status)."""
+    h, w, c = C.c_int32(), C.c_int32(), C.c_int32()
+    rc = lib().orc_jpeg_info(data, C.c_int64(len(data)), C.byref(h), C.byref(w), C.byref(c))
+    if rc:
+        raise ValueError(rc)
+    return h.value, w.value, c.value
+
+
+def jpeg_decode(data):
+    """DecodeJpeg(channels=3): file bytes -> uint8 [H,W,3]."""
+    h, w, _ = jpeg_info(data)
+    out = np.empty((h, w, 3), np.uint8)
+    rc = lib().orc_jpeg_decode(data, C.c_int64(len(data)), _p(out))
+    if rc:
+        raise ValueError(rc)
+    return out

@@ -1,0 +1,172 @@
+"""DecodeJpeg on the GPU (J1-J3, csrc/jpeg.cu) through the C ABI: bit-exact against the libjpeg-turbo fixtures and the
+oracle, alone and in front of the normalisation and labeling models.  Needs a B200 (-m gpu)."""
+import io
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def dev(ftf):
+    import torch
+    assert torch.cuda.is_available()
+    from flink_tensorflow_b200 import device
+    return device
+
+
+@pytest.fixture(scope="module")
+def cases():
+    z = np.load(os.path.join(ROOT, "tests", "golden", "jpeg", "cases.npz"))
+    names = sorted(k[:-4] for k in z.files if k.endswith(".jpg") and not k.startswith("refuse_"))
+    return {n: (z[n + ".jpg"].tobytes(), z[n + ".rgb"]) for n in names}
+
+
+def _bits(a):
+    return np.ascontiguousarray(a, np.float32).view(np.uint32)
+
+
+def _photo(rng, h=480, w=640, noise=10.0):
+    y, x = np.mgrid[0:h, 0:w]
+    p = rng.uniform(0, 6.28, 3)
+    img = np.stack([128 + 90 * np.sin(x / rng.uniform(20, 60) + p[c]) * np.cos(y / rng.uniform(15, 50)) for c in range(3)], -1)
+    return np.clip(img + rng.normal(0, noise, (h, w, 3)), 0, 255).astype(np.uint8)
+
+
+def _jpeg(arr, **kw):
+    from PIL import Image
+    b = io.BytesIO()
+    Image.fromarray(arr).save(b, "JPEG", **kw)
+    return b.getvalue()
+
+
+def test_every_fixture_in_one_ragged_batch(dev, cases):
+    """All fixtures (4:4:4 / 4:2:2 / 4:2:0 / grey, odd sizes down to 1x1, optimised tables, restart markers) as ONE batch:
+    every image equals what libjpeg-turbo decoded."""
+    import torch
+    names = list(cases)
+    b = dev.JpegBatch()
+    flat = b.load([cases[n][0] for n in names]).decode()
+    assert b.status() == [0] * len(names)
+    assert b.segments > len(names)                      # restart intervals became extra segments
+    for n, img in zip(names, b.images(flat)):
+        assert np.array_equal(img.cpu().numpy(), cases[n][1]), n
+    # a second load on the same object (smaller, other tables) and two decodes of one load
+    flat2 = b.load([cases["gray_48x64"][0], cases["444_q98"][0]]).decode()
+    flat3 = b.decode()
+    b.status()
+    torch.cuda.synchronize()
+    assert torch.equal(flat2, flat3)
+    assert np.array_equal(b.images(flat2)[1].cpu().numpy(), cases["444_q98"][1])
+    b.close()
+
+
+@pytest.mark.parametrize("kw", [dict(quality=85), dict(quality=92, subsampling=0), dict(quality=60, subsampling=1),
+                                dict(quality=75, restart_marker_rows=1), dict(quality=90, optimize=True)])
+def test_photo_sized_batch_matches_oracle(dev, oracle, kw):
+    rng = np.random.default_rng(77)
+    files = [_jpeg(_photo(rng), **kw) for _ in range(12)]
+    imgs = dev.decode_jpeg(files)
+    for f, g in zip(files, imgs):
+        assert np.array_equal(g.cpu().numpy(), oracle.jpeg_decode(f))
+
+
+def test_corrupt_entropy_data_is_reported_per_image(dev, oracle):
+    rng = np.random.default_rng(3)
+    good = [_jpeg(_photo(rng, 96, 128), quality=80, optimize=True) for _ in range(3)]
+    i = good[1].index(b"\xff\xda")
+    start = i + 2 + int.from_bytes(good[1][i + 2:i + 4], "big")
+    bad = good[1][:start + 50] + b"\xfe" * 200 + good[1][start + 250:]
+    b = dev.JpegBatch()
+    flat = b.load([good[0], bad, good[2]]).decode()
+    try:
+        st = b.status()
+    except ValueError as e:
+        assert "image 1" in str(e)
+        st = b.last_status
+    # an optimised table has no all-ones code, so the run of 0xFE bytes cannot decode
+    assert st == [0, 3, 0]
+    ims = b.images(flat)
+    assert np.array_equal(ims[0].cpu().numpy(), oracle.jpeg_decode(good[0]))
+    assert np.array_equal(ims[2].cpu().numpy(), oracle.jpeg_decode(good[2]))
+    with pytest.raises(NotImplementedError):
+        b.load([_jpeg(_photo(rng, 32, 32), progressive=True)])
+    with pytest.raises(ValueError, match="image 1"):
+        b.load([good[0], b"\xff\xd8 nonsense"])
+    b.close()
+
+
+def test_truncated_file_decodes_like_libjpeg_with_zero_bits(dev, oracle):
+    rng = np.random.default_rng(8)
+    f = _jpeg(_photo(rng, 80, 112), quality=80)
+    cut = f[: len(f) * 2 // 3]
+    got = dev.decode_jpeg([cut])[0].cpu().numpy()
+    assert np.array_equal(got, oracle.jpeg_decode(cut))
+
+
+def test_normalization_model_takes_image_files(ftf, oracle):
+    """The reference's own call: ImageFileTensor (file bytes as a 0-D STRING tensor) -> normalize -> [1,224,224,3]
+    (EX/inception/ImageInputFormat.scala:63-80, ImageNormalization.scala:56-65), constants 224/117/1."""
+    rng = np.random.default_rng(19)
+    files = [_jpeg(_photo(rng), quality=85) for _ in range(5)]
+    m = ftf.ImageNormalization()
+    m.open()
+    try:
+        with m.normalize(ftf.bytes_to_tensor(files[0])) as out:
+            assert out.shape == (1, 224, 224, 3) and out.data_type == ftf.DataType.FLOAT
+            want0 = oracle.resize_bilinear_norm_u8(oracle.jpeg_decode(files[0])[None], 224, 224, 117.0, 1.0)
+            assert np.array_equal(_bits(out.to_array()), _bits(want0))
+        with m.normalize(ftf.messages_to_tensor(files)) as out:             # a vector of files: one batch
+            want = np.concatenate([oracle.resize_bilinear_norm_u8(oracle.jpeg_decode(f)[None], 224, 224, 117.0, 1.0) for f in files])
+            assert np.array_equal(_bits(out.to_array()), _bits(want))
+        ragged = [_jpeg(_photo(rng, h, w), quality=80, subsampling=s) for (h, w, s) in ((100, 150, 2), (33, 47, 0), (240, 320, 1))]
+        with m.normalize(ftf.messages_to_tensor(ragged)) as out:            # files of different sizes
+            want = np.concatenate([oracle.resize_bilinear_norm_u8(oracle.jpeg_decode(f)[None], 224, 224, 117.0, 1.0) for f in ragged])
+            assert np.array_equal(_bits(out.to_array()), _bits(want))
+        with pytest.raises(ValueError, match="DecodeJpeg"):
+            with m.normalize(ftf.bytes_to_tensor(b"GIF89a not a jpeg")):
+                pass
+        img = np.random.default_rng(2).integers(0, 256, (2, 60, 80, 3), dtype=np.uint8)
+        with m.normalize(ftf.TensorValue.from_array(img)) as out:           # raw RGB still works on the same session
+            assert np.array_equal(_bits(out.to_array()), _bits(oracle.resize_bilinear_norm_u8(img, 224, 224, 117.0, 1.0)))
+    finally:
+        m.close()
+
+
+def test_file_records_through_submit_poll(ftf, oracle):
+    """One JPEG file per record through the micro-batched path: order kept, values equal the oracle's."""
+    rng = np.random.default_rng(23)
+    files = [_jpeg(_photo(rng, 120, 160), quality=80) for _ in range(11)]
+    cfg = ftf.default_config(max_batch=4, max_delay_us=500, out_h=32, out_w=24, mean=117.0, scale=1.0)
+    r = ftf.Runner("builtin:image_normalization", None, None, cfg)
+    for i, f in enumerate(files):
+        r.submit(500 + i, ftf.bytes_to_tensor(f))
+    with pytest.raises(NotImplementedError):
+        r.submit(999, ftf.bytes_to_tensor(_jpeg(_photo(rng, 32, 32), progressive=True)))   # refused, joins no batch
+    r.flush()
+    res = []
+    while len(res) < len(files):
+        res += r.poll(block=True)
+    assert [t for t, _ in res] == list(range(500, 500 + len(files)))
+    for (_, tv), f in zip(res, files):
+        want = oracle.resize_bilinear_norm_u8(oracle.jpeg_decode(f)[None], 32, 24, 117.0, 1.0)[0]
+        assert np.array_equal(_bits(tv.to_array()), _bits(want))
+    r.close()
+
+
+def test_files_and_decoded_pixels_label_alike(ftf, oracle):
+    """normalize_label fed JPEG files gives exactly what it gives when fed the oracle-decoded pixels of those files."""
+    rng = np.random.default_rng(29)
+    files = [_jpeg(_photo(rng), quality=85) for _ in range(3)]
+    cfg = ftf.default_config(max_batch=4, top_k=5, out_h=299, out_w=299, mean=128.0, scale=128.0, seed=2024)
+    r = ftf.Runner("builtin:normalize_label", None, None, cfg)
+    a = r.run({"inputs": ftf.messages_to_tensor(files)}, ["logits", "top_k_indices"])
+    pix = np.stack([oracle.jpeg_decode(f) for f in files])
+    b = r.run({"inputs": ftf.TensorValue.from_array(pix)}, ["logits", "top_k_indices"])
+    assert np.array_equal(_bits(a["logits"].to_array()), _bits(b["logits"].to_array()))
+    assert np.array_equal(a["top_k_indices"].to_array(), b["top_k_indices"].to_array())
+    r.close()
