@@ -3,15 +3,19 @@
 // examples/src/main/scala/org/apache/flink/contrib/tensorflow/examples).  TF-Java runs it in libjpeg on one core per record;
 // here a batch of files is decoded by three kernels and the RGB images never leave HBM before the resize kernel reads them.
 //
-//   J1 jpeg_huffman_kernel   one thread per independently decodable segment (restart interval, else whole scan):
-//                            canonical Huffman decode with a 9-bit lookahead table, byte unstuffing on the fly,
-//                            coefficients scattered (de-zigzagged) into a zeroed int16 buffer.  A latency-bound
-//                            kernel: its parallelism is segments per batch, so segments are spread one per warp
-//                            until there are more segments than the GPU holds warps.
+//   J1a jpeg_huffman_kernel  one CTA per independently decodable segment (restart interval, else the whole scan), one
+//                            thread per 1024-bit chunk of it: every chunk is decoded from a guessed state, the guesses
+//                            are corrected along the chain until they are the true states (a Huffman decoder started
+//                            in the wrong place falls into step after a few symbols), then a last pass scatters the
+//                            coefficients (de-zigzagged) into a zeroed int16 buffer.  Canonical Huffman decode with a
+//                            9-bit lookahead table on a byte-unstuffed stream (the host removes the stuffing while it
+//                            copies the file into pinned memory).
+//   J1b jpeg_dc_kernel       DC differences -> DC values: warp scan per (segment, component).
 //   J2 jpeg_idct_kernel      one thread per 8x8 block: dequantise + libjpeg's integer slow IDCT, entirely in
 //                            registers, 16-byte coefficient loads, 8-byte row stores into the component plane.
-//   J3 jpeg_colour_kernel    one thread per 4 pixels: triangle-filter chroma upsampling (2x1, 2x2), fixed-point
-//                            YCbCr -> RGB, three 32-bit stores of packed RGB.
+//   J3 jpeg_colour_kernel    one thread per 8 pixels: planes read as aligned words, triangle-filter chroma upsampling
+//                            (2x1, 2x2) with every source sample fetched once, fixed-point YCbCr -> RGB, six 32-bit
+//                            stores of packed RGB.
 // Integer arithmetic throughout: results are bit-identical to libjpeg(-turbo), checked against oracle/jpeg_oracle.c
 // and the Pillow-made fixtures in tests/golden/jpeg.
 #include "jpeg.h"
@@ -23,17 +27,98 @@ using namespace ftf::jpeg;
 
 namespace {
 
-__global__ void __launch_bounds__(128)
-jpeg_huffman_kernel(const Segment* __restrict__ segs, int nseg, int lanes, const ImageDesc* __restrict__ images,
+// J1a: one CTA per segment, one thread per chunk of kChunkBits (see decode_chunk in jpeg_core.h for the scheme).
+// Segments with more chunks than the CTA has threads are walked in waves: a wave starts from the true state the
+// previous wave ended in.
+__global__ void __launch_bounds__(1024)
+jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restrict__ images,
                     const HuffTable* __restrict__ tables, const uint8_t* __restrict__ scan,
                     int16_t* __restrict__ coef, int32_t* __restrict__ status) {
-    const int warp = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5);
-    const int lane = (int)(threadIdx.x & 31);
-    if (lane >= lanes) return;
-    const int s = warp * lanes + lane;
+    __shared__ ScanState s_exit[1024];
+    __shared__ int s_warp[32];
+    const Segment sg = segs[blockIdx.x];
+    const ImageDesc& im = images[sg.image];
+    const int T = (int)blockDim.x, tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
+    const int total_blocks = sg.n_mcus * bpm;
+    ScanState wave_entry;
+    wave_entry.pos = 0; wave_entry.k = 0; wave_entry.b = 0;
+    int blocks_before = 0, bad = 0;
+    for (int c0 = 0; c0 < sg.n_chunks; c0 += T) {
+        const int j = c0 + tid;
+        const bool active = j < sg.n_chunks;
+        const uint32_t limit = (uint32_t)(j + 1) * kChunkBits;
+        ScanState in;
+        in.pos = (uint32_t)j * kChunkBits; in.k = 0; in.b = 0;
+        if (tid == 0) in = wave_entry;
+        ScanState out = in;
+        int n = 0;
+        // 1. guess
+        if (active) out = decode_chunk<false>(sg, im, tables, scan, in, limit, 0, 0, nullptr, &n, nullptr);
+        s_exit[tid] = out;
+        // 2. until every chunk started from the state its predecessor left
+        for (;;) {
+            __syncthreads();
+            bool changed = false;
+            ScanState prev = in;
+            if (active && tid > 0) { prev = s_exit[tid - 1]; changed = !same_state(prev, in); }
+            if (!__syncthreads_or(changed)) break;
+            if (changed) {
+                in = prev;
+                out = decode_chunk<false>(sg, im, tables, scan, in, limit, 0, 0, nullptr, &n, nullptr);
+                s_exit[tid] = out;
+            }
+        }
+        // 3. which block does each chunk start in: exclusive prefix sum of the blocks completed per chunk
+        int incl = active ? n : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        int warp_before = 0, wave_total = 0;
+        for (int w = 0; w < (T + 31) / 32; ++w) {
+            const int v = s_warp[w];
+            if (w < warp) warp_before += v;
+            wave_total += v;
+        }
+        const int ordinal = blocks_before + warp_before + incl - (active ? n : 0);
+        if (active && ordinal < total_blocks) {
+            int n2 = 0;
+            decode_chunk<true>(sg, im, tables, scan, in, j == sg.n_chunks - 1 ? 0xffffffffu : limit, ordinal, total_blocks, coef, &n2, &bad);
+        }
+        if (c0 + T < sg.n_chunks) {             // another wave follows: it starts where this one ended
+            wave_entry = s_exit[T - 1];
+            blocks_before += wave_total;
+            __syncthreads();
+        }
+    }
+    if (bad) atomicOr(&status[sg.image], 1);
+}
+
+// J1b: DC differences -> DC values.  One warp per (segment, component): every lane sums a run of the component's
+// blocks, a warp scan turns the sums into offsets, every lane rewrites its run.
+__global__ void __launch_bounds__(128)
+jpeg_dc_kernel(const Segment* __restrict__ segs, int nseg, const ImageDesc* __restrict__ images, int16_t* __restrict__ coef) {
+    const int w = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = (int)(threadIdx.x & 31);
+    const int s = w / 3, c = w - s * 3;
     if (s >= nseg) return;
     const Segment sg = segs[s];
-    if (decode_segment(sg, images[sg.image], tables, scan, coef)) atomicOr(&status[sg.image], 1);
+    const ImageDesc& im = images[sg.image];
+    if (c >= im.ncomp) return;
+    const int count = sg.n_mcus * (c == 0 ? im.hs * im.vs : 1);
+    const int run = (count + 31) / 32;
+    const int t0 = min(lane * run, count), t1 = min(t0 + run, count);
+    const int sum = dc_run_sum(sg, im, coef, c, t0, t1);
+    int incl = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    dc_run_apply(sg, im, coef, c, t0, t1, incl - sum);
 }
 
 __global__ void __launch_bounds__(128)
@@ -66,18 +151,18 @@ jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restric
 __global__ void __launch_bounds__(256)
 jpeg_colour_kernel(const ImageDesc* __restrict__ images, const uint8_t* __restrict__ planes, uint8_t* __restrict__ rgb) {
     const ImageDesc& im = images[blockIdx.y];
-    const int groups = (im.width + 3) >> 2;
+    const int groups = (im.width + 7) >> 3;
     const int t = (int)(blockIdx.x * blockDim.x + threadIdx.x);
     if (t >= groups * im.height) return;
-    const int y = t / groups, x0 = (t - y * groups) * 4;
-    const int nx = im.width - x0 < 4 ? im.width - x0 : 4;
-    union { uint8_t b[12]; uint32_t w[3]; } px;
-    px.w[0] = px.w[1] = px.w[2] = 0;
-    for (int i = 0; i < nx; ++i) pixel_rgb(im, planes, y, x0 + i, px.b + 3 * i);
+    const int y = t / groups, x0 = (t - y * groups) * 8;
+    const int nx = im.width - x0 < 8 ? im.width - x0 : 8;
+    union { uint8_t b[24]; uint32_t w[6]; } px;
+    pixels8_rgb(im, planes, y, x0, px.b);
     uint8_t* dst = rgb + im.rgb_off + ((int64_t)y * im.width + x0) * 3;
-    if (nx == 4 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
+    if (nx == 8 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
         uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
-        d32[0] = px.w[0]; d32[1] = px.w[1]; d32[2] = px.w[2];
+#pragma unroll
+        for (int i = 0; i < 6; ++i) d32[i] = px.w[i];
     } else {
         for (int i = 0; i < 3 * nx; ++i) dst[i] = px.b[i];
     }
@@ -99,7 +184,7 @@ struct ftf_jpeg_batch {
     std::vector<uint16_t> quants;
     size_t scan_bytes = 0, meta_bytes = 0, off_seg = 0, off_tab = 0, off_q = 0;
     int64_t coef_elems = 0, plane_bytes = 0, rgb_bytes = 0;
-    int max_blocks = 0, max_groups = 0;
+    int max_blocks = 0, max_groups = 0, max_chunks = 1;
     bool decoded = false;
 };
 
@@ -179,7 +264,6 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
     b->decoded = false;
     b->coef_elems = 0; b->plane_bytes = 0; b->rgb_bytes = 0; b->max_blocks = 0; b->max_groups = 0;
     std::vector<Parsed>* parsed = new std::vector<Parsed>((size_t)n);
-    std::vector<int64_t> scan_off((size_t)n);
     size_t scan_total = 0;
     int rc = FTF_OK;
     for (int i = 0; i < n && rc == FTF_OK; ++i) {
@@ -211,33 +295,30 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
         if (widths) widths[i] = im.width;
         b->rgb_bytes += align_up((size_t)im.width * im.height * 3, 16);
         if (im.n_blocks > b->max_blocks) b->max_blocks = im.n_blocks;
-        const int groups = ((im.width + 3) >> 2) * im.height;
+        const int groups = ((im.width + 7) >> 3) * im.height;
         if (groups > b->max_groups) b->max_groups = groups;
-        scan_off[i] = (int64_t)scan_total;
-        scan_total += align_up((size_t)(lens[i] - p.scan_begin), 16);
-        const size_t first_seg = b->segments.size();
-        find_segments(files[i], lens[i], p, im, i, &b->segments);
-        for (size_t k = first_seg; k < b->segments.size(); ++k) {      // file offsets -> offsets into the batch buffer
-            b->segments[k].begin += scan_off[i] - p.scan_begin;
-            b->segments[k].end += scan_off[i] - p.scan_begin;
-        }
+        scan_total += (size_t)stage_bound(lens[i], p, im);
         b->images.push_back(im);
     }
     if (rc == FTF_OK && n > 0) {
+        if ((rc = b->h_scan.ensure(scan_total + 16, &b->err)) == 0) {
+            int64_t w = 0;                              // the one host pass over the compressed bytes: unstuff + split + stage
+            for (int i = 0; i < n; ++i)
+                w += stage_scan(files[i], lens[i], (*parsed)[i], b->images[i], i, (uint8_t*)b->h_scan.p + w, w, &b->segments);
+            scan_total = (size_t)w;
+            b->max_chunks = 1;
+            for (const Segment& sgm : b->segments) if (sgm.n_chunks > b->max_chunks) b->max_chunks = sgm.n_chunks;
+        }
         b->scan_bytes = scan_total;
         b->off_seg = align_up(b->images.size() * sizeof(ImageDesc), 16);
         b->off_tab = align_up(b->off_seg + b->segments.size() * sizeof(Segment), 16);
         b->off_q = align_up(b->off_tab + b->tables.size() * sizeof(HuffTable), 16);
         b->meta_bytes = b->off_q + b->quants.size() * sizeof(uint16_t);
-        if ((rc = b->h_scan.ensure(scan_total + 16, &b->err)) == 0 && (rc = b->h_meta.ensure(b->meta_bytes, &b->err)) == 0 &&
+        if (rc == 0 && (rc = b->h_meta.ensure(b->meta_bytes, &b->err)) == 0 &&
             (rc = b->d_scan.ensure(scan_total + 16, &b->err)) == 0 && (rc = b->d_meta.ensure(b->meta_bytes, &b->err)) == 0 &&
             (rc = b->d_coef.ensure((size_t)b->coef_elems * 2, &b->err)) == 0 &&
             (rc = b->d_planes.ensure((size_t)b->plane_bytes, &b->err)) == 0 &&
             (rc = b->d_status.ensure((size_t)n * 4, &b->err)) == 0 && (rc = b->h_status.ensure((size_t)n * 4, &b->err)) == 0) {
-            for (int i = 0; i < n; ++i) {
-                const Parsed& p = (*parsed)[i];
-                memcpy((uint8_t*)b->h_scan.p + scan_off[i], files[i] + p.scan_begin, (size_t)(lens[i] - p.scan_begin));
-            }
             uint8_t* m = (uint8_t*)b->h_meta.p;
             memcpy(m, b->images.data(), b->images.size() * sizeof(ImageDesc));
             memcpy(m + b->off_seg, b->segments.data(), b->segments.size() * sizeof(Segment));
@@ -272,19 +353,16 @@ extern "C" int ftf_jpeg_batch_decode_dev(ftf_jpeg_batch* b, uint8_t* rgb_out, in
     const uint16_t* d_quant = (const uint16_t*)(m + b->off_q);
     FTF_CUDA(cudaMemsetAsync(b->d_coef.p, 0, (size_t)b->coef_elems * 2, st), &b->err);
     FTF_CUDA(cudaMemsetAsync(b->d_status.p, 0, (size_t)n * 4, st), &b->err);
-    // one segment per warp while the GPU has warps to spare; beyond that pack lanes
-    const int warps_wanted = device_sm_count(b->device) * 48;
-    int lanes = (nseg + warps_wanted - 1) / warps_wanted;
-    lanes = lanes < 1 ? 1 : lanes > 32 ? 32 : lanes;
-    const int warps = (nseg + lanes - 1) / lanes;
-    const int wpb = lanes == 1 ? 1 : 4;          // lone lanes: one warp per block, so that they spread over all SMs
-    jpeg_huffman_kernel<<<(warps + wpb - 1) / wpb, wpb * 32, 0, st>>>(d_segs, nseg, lanes, d_images, d_tabs, (const uint8_t*)b->d_scan.p,
-                                                                   (int16_t*)b->d_coef.p, (int32_t*)b->d_status.p);
+    int threads = (b->max_chunks + 31) / 32 * 32;
+    threads = threads > 1024 ? 1024 : threads;
+    jpeg_huffman_kernel<<<nseg, threads, 0, st>>>(d_segs, d_images, d_tabs, (const uint8_t*)b->d_scan.p, (int16_t*)b->d_coef.p,
+                                                  (int32_t*)b->d_status.p);
+    jpeg_dc_kernel<<<(nseg * 3 + 3) / 4, 128, 0, st>>>(d_segs, nseg, d_images, (int16_t*)b->d_coef.p);
     jpeg_idct_kernel<<<dim3((b->max_blocks + 127) / 128, n), 128, 0, st>>>(d_images, d_quant, (const int16_t*)b->d_coef.p,
                                                                             (uint8_t*)b->d_planes.p);
     jpeg_colour_kernel<<<dim3((b->max_groups + 255) / 256, n), 256, 0, st>>>(d_images, (const uint8_t*)b->d_planes.p, rgb_out);
     FTF_CUDA(cudaGetLastError(), &b->err);
-    count_launch(3);
+    count_launch(4);
     FTF_CUDA(cudaMemcpyAsync(b->h_status.p, b->d_status.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st), &b->err);
     FTF_CUDA(cudaEventRecord(b->done, st), &b->err);
     b->decoded = true;

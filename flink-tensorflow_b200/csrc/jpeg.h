@@ -30,9 +30,15 @@ int parse_headers(const uint8_t* d, int64_t n, Parsed* out, std::string* err);
 // Geometry shared by the host planner and the kernels.
 void fill_geometry(const Parsed& p, ImageDesc* im);
 
-// Splits the entropy-coded bytes [p.scan_begin, n) at the RSTn markers (only when the file has a restart interval;
-// otherwise the whole scan is one segment and no byte of it is read on the host).  Offsets are relative to d.
-void find_segments(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, std::vector<Segment>* out);
+// Upper bound of what stage_scan writes for this file.
+int64_t stage_bound(int64_t n, const Parsed& p, const ImageDesc& im);
+
+// Copies the entropy-coded bytes [p.scan_begin, n) of one file to dst with the 0xFF00 byte stuffing removed, one clean
+// stream per restart interval (or one for the whole scan), each 4-byte aligned and followed by >= 8 zero bytes, and
+// appends one Segment per stream (begin = dst_offset + position in dst).  Returns the bytes written.  This is the one
+// pass the host makes over the compressed data; it doubles as the copy into pinned staging memory.
+int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, uint8_t* dst,
+                   int64_t dst_offset, std::vector<Segment>* out);
 
 }  // namespace jpeg
 }  // namespace ftf

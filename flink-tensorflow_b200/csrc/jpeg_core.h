@@ -48,12 +48,16 @@ struct ImageDesc {
     int64_t rgb_off;              // bytes
 };
 
-// One independently decodable stretch of a scan: a restart interval, or the whole scan.
+constexpr int kChunkBits = 1024;   // the unit of parallel entropy decoding (see decode_chunk)
+
+// One independently decodable stretch of a scan: a restart interval, or the whole scan.  The host stages its bytes with
+// the 0xFF00 byte stuffing removed ("clean" stream), 4-byte aligned and followed by at least 8 zero bytes.
 struct Segment {
     int32_t image;
     int32_t first_mcu, n_mcus;
-    int32_t pad;
-    int64_t begin, end;           // bytes of the batch's scan buffer
+    int32_t n_chunks;             // max(1, ceil(nbits / kChunkBits))
+    int64_t begin;                // byte offset of the clean stream in the batch's scan buffer
+    int64_t nbits;                // bits of clean stream; past them the decoder reads zeros, as libjpeg does at a marker
 };
 
 // zig-zag position -> row-major position (T.81 figure A.6)
@@ -72,93 +76,177 @@ FTF_HD uint8_t natural_order(int k) {
 #endif
 }
 
-// MSB-first bit reader over entropy-coded bytes with the 0xFF00 stuffing removed on the fly; at a marker (or the end
-// of the segment) the stream continues as zero bits, which is what libjpeg feeds its decoder there.
-struct BitReader {
-    const uint8_t* p;
-    const uint8_t* end;
+#ifdef __CUDA_ARCH__
+#define FTF_BE32(x) __byte_perm((x), 0, 0x0123)
+#else
+#define FTF_BE32(x) __builtin_bswap32(x)
+#endif
+
+// MSB-first view of a clean stream: 64 bits starting at a 32-bit boundary are kept in a register pair and slide forward
+// one aligned word at a time, so a symbol costs one load per 32 bits consumed.
+struct BitWindow {
+    const uint32_t* words;
     uint64_t buf;
-    int cnt;
-    FTF_HD void init(const uint8_t* b, const uint8_t* e) { p = b; end = e; buf = 0; cnt = 0; }
-    FTF_HD void fill() {
-        while (cnt <= 56) {
-            uint32_t b = 0;
-            if (p < end) {
-                b = FTF_LDG(p);
-                if (b == 0xFF) {
-                    const uint32_t b2 = (p + 1 < end) ? (uint32_t)FTF_LDG(p + 1) : 0xD9u;
-                    if (b2 == 0) p += 2;
-                    else { b = 0; end = p; }
-                } else ++p;
-            }
-            buf |= (uint64_t)b << (56 - cnt);
-            cnt += 8;
-        }
+    uint32_t base;      // bit position of buf's top bit (a multiple of 32)
+    uint32_t nbits;
+    FTF_HD void seek(const uint32_t* w, uint32_t nb, uint32_t pos) {
+        words = w; nbits = nb; base = pos & ~31u; buf = 0;
+        if (pos < nbits) buf = ((uint64_t)FTF_BE32(FTF_LDG(words + (base >> 5))) << 32) | FTF_BE32(FTF_LDG(words + (base >> 5) + 1));
     }
-    FTF_HD uint32_t peek(int n) const { return (uint32_t)(buf >> (64 - n)); }
-    FTF_HD void skip(int n) { buf <<= n; cnt -= n; }
+    // the 32 bits that start at pos (pos never goes backwards and advances by less than 32 between calls)
+    FTF_HD uint32_t at(uint32_t pos) {
+        if (pos >= nbits) return 0;
+        if (pos - base >= 32) {
+            base += 32;
+            buf = (buf << 32) | FTF_BE32(FTF_LDG(words + (base >> 5) + 1));
+        }
+        return (uint32_t)((buf << (pos - base)) >> 32);
+    }
 };
 
-// T.81 F.2.2.3 DECODE; returns the symbol or -1 for a code no table entry matches.  Needs >= 16 bits in the reader.
-FTF_HD int decode_symbol(BitReader& br, const HuffTable* __restrict__ t) {
-    const uint32_t e = FTF_LDG(&t->lut[br.peek(kLutBits)]);
-    if (e) { br.skip((int)(e >> 8)); return (int)(e & 0xFF); }
-    const int32_t code16 = (int32_t)br.peek(16);
+// T.81 F.2.2.3 DECODE on a 32-bit window: code length (0 = no such code) and symbol.
+FTF_HD int lookup_symbol(uint32_t w, const HuffTable* __restrict__ t, int* sym) {
+    const uint32_t e = FTF_LDG(&t->lut[w >> (32 - kLutBits)]);
+    if (e) { *sym = (int)(e & 0xFF); return (int)(e >> 8); }
+    const int32_t code16 = (int32_t)(w >> 16);
     int l = kLutBits + 1;
     while (l <= 16 && (code16 >> (16 - l)) > FTF_LDG(&t->maxcode[l])) ++l;
-    if (l > 16) return -1;
-    br.skip(l);
-    return (int)FTF_LDG(&t->vals[(code16 >> (16 - l)) + FTF_LDG(&t->valoff[l])]);
+    if (l > 16) return 0;
+    *sym = (int)FTF_LDG(&t->vals[(code16 >> (16 - l)) + FTF_LDG(&t->valoff[l])]);
+    return l;
 }
 
-// T.81 F.2.2.1 EXTEND applied to the next t bits
-FTF_HD int receive_extend(BitReader& br, int t) {
-    const int v = (int)br.peek(t);
-    br.skip(t);
-    return v < (1 << (t - 1)) ? v - (1 << t) + 1 : v;
+// T.81 F.2.2.1 EXTEND of the s (1..15) bits that follow the first len bits of the window
+FTF_HD int extend_bits(uint32_t w, int len, int s) {
+    const int v = (int)((w << len) >> (32 - s));
+    return v < (1 << (s - 1)) ? v - (1 << s) + 1 : v;
 }
 
-// Decodes one segment: every block of its MCUs, non-zero coefficients stored at their row-major position in the
-// (pre-zeroed) coefficient buffer.  Returns 0, or 1 when the data is not a valid Huffman stream for these tables.
-FTF_HD int decode_segment(const Segment& sg, const ImageDesc& im, const HuffTable* __restrict__ tables,
-                          const uint8_t* __restrict__ scan, int16_t* __restrict__ coef) {
-    BitReader br;
-    br.init(scan + sg.begin, scan + sg.end);
-    int pred[3] = {0, 0, 0};
-    int mx = sg.first_mcu % im.mcus_x, my = sg.first_mcu / im.mcus_x;
-    for (int m = 0; m < sg.n_mcus; ++m) {
-        for (int c = 0; c < im.ncomp; ++c) {
-            const HuffTable* dc = tables + im.dc[c];
-            const HuffTable* ac = tables + im.ac[c];
-            const int ch = c == 0 ? im.hs : 1, cv = c == 0 ? im.vs : 1;
-            for (int v = 0; v < cv; ++v)
-                for (int h = 0; h < ch; ++h) {
-                    int16_t* blk = coef + im.coef_off[c] + ((int64_t)(my * cv + v) * im.bw[c] + (mx * ch + h)) * 64;
-                    br.fill();
-                    const int t = decode_symbol(br, dc);
-                    if (t < 0 || t > 16) return 1;
-                    if (t) pred[c] += receive_extend(br, t);
-                    blk[0] = (int16_t)pred[c];
-                    for (int k = 1; k < 64; ++k) {
-                        br.fill();
-                        const int rs = decode_symbol(br, ac);
-                        if (rs < 0) return 1;
-                        const int r = rs >> 4, s = rs & 15;
-                        if (s) {
-                            k += r;
-                            const int val = receive_extend(br, s);
-                            if (k > 63) return 1;
-                            blk[natural_order(k)] = (int16_t)val;
-                        } else {
-                            if (r != 15) break;
-                            k += 15;
-                        }
-                    }
-                }
-        }
-        if (++mx == im.mcus_x) { mx = 0; ++my; }
+// Where an entropy decoder stands between two symbols: the bit it reads next, the zig-zag index it decodes next
+// (0: the block's DC symbol) and which block of the MCU it is in.
+struct ScanState {
+    uint32_t pos;
+    uint16_t k, b;
+};
+FTF_HD bool same_state(const ScanState& a, const ScanState& b) { return a.pos == b.pos && a.k == b.k && a.b == b.b; }
+
+// Component and position inside the MCU of block b (luma blocks first, row-major; then Cb, Cr).
+FTF_HD int16_t* block_ptr(const ImageDesc& im, int16_t* __restrict__ coef, int my, int mx, int b) {
+    const int nluma = im.hs * im.vs;
+    if (b < nluma) {
+        const int v = b / im.hs, h = b - v * im.hs;
+        return coef + im.coef_off[0] + ((int64_t)(my * im.vs + v) * im.bw[0] + (mx * im.hs + h)) * 64;
     }
-    return 0;
+    const int c = b - nluma + 1;
+    return coef + im.coef_off[c] + ((int64_t)my * im.bw[c] + mx) * 64;
+}
+
+// Parallel entropy decoding.  A Huffman stream has no index, but a decoder started at a wrong place falls into step with
+// the true one after a few symbols, so a segment is cut into chunks of kChunkBits and every chunk gets a thread:
+//   1. each thread decodes its chunk from a guessed state (the chunk's first bit, start of an MCU) and publishes the state
+//      it leaves the chunk in -- chunk 0 starts from the true state;
+//   2. a thread whose predecessor published a state other than the one it started from decodes again from that state;
+//      repeated until nothing changes, at which point every entry state is the true one (by induction from chunk 0);
+//   3. a prefix sum over the blocks completed per chunk tells every thread which block it starts in, and a last pass
+//      decodes once more and stores the coefficients.  DC values are stored as differences; dc_* below add them up.
+// decode_chunk is one such pass over the symbols that start in [st.pos, limit).  kWrite = false: counts completed blocks
+// and returns the exit state; a bit pattern that is no code (possible only from a wrong state or in a corrupt file) is
+// skipped one bit at a time.  kWrite = true: also stores coefficients for blocks [ordinal, total_blocks) of the segment,
+// and reports a pattern that is no code, or a run past the 64th coefficient, through *bad.
+template <bool kWrite>
+FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const HuffTable* __restrict__ tables,
+                              const uint8_t* __restrict__ scan, ScanState st, uint32_t limit, int ordinal, int total_blocks,
+                              int16_t* __restrict__ coef, int* n_done, int* bad) {
+    const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
+    const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
+    BitWindow bw;
+    bw.seek(reinterpret_cast<const uint32_t*>(scan + sg.begin), (uint32_t)sg.nbits, st.pos);
+    uint32_t pos = st.pos;
+    int k = st.k, b = st.b, done = 0;
+    int mx = 0, my = 0;
+    int16_t* blk = nullptr;
+    if (kWrite) {
+        const int mcu = sg.first_mcu + ordinal / bpm;
+        my = mcu / im.mcus_x; mx = mcu - my * im.mcus_x;
+        blk = block_ptr(im, coef, my, mx, b);
+    }
+    int c = b < nluma ? 0 : b - nluma + 1;
+    const HuffTable* dc = tables + im.dc[c];
+    const HuffTable* ac = tables + im.ac[c];
+    while (pos < limit && (!kWrite || ordinal < total_blocks)) {
+        const uint32_t w = bw.at(pos);
+        int sym = 0;
+        const int len = lookup_symbol(w, k == 0 ? dc : ac, &sym);
+        if (len == 0) {
+            if (kWrite) { *bad = 1; break; }
+            pos += 1;
+            continue;
+        }
+        if (k == 0) {
+            if (sym > 15) {                 // a DC symbol is a bit count
+                if (kWrite) { *bad = 1; break; }
+                sym = 0;
+            }
+            const int s = sym;
+            if (kWrite) blk[0] = (int16_t)(s ? extend_bits(w, len, s) : 0);
+            pos += (uint32_t)(len + s);
+            k = 1;
+        } else {
+            const int r = sym >> 4, s = sym & 15;
+            if (s) {
+                k += r;
+                if (k > 63) {
+                    if (kWrite) { *bad = 1; break; }
+                    k = 63;
+                }
+                if (kWrite) blk[natural_order(k)] = (int16_t)extend_bits(w, len, s);
+                pos += (uint32_t)(len + s);
+                k += 1;
+            } else {
+                pos += (uint32_t)len;
+                k = r == 15 ? k + 16 : 64;
+            }
+        }
+        if (k >= 64) {                      // block complete
+            k = 0; ++done; ++ordinal;
+            if (++b == bpm) {
+                b = 0;
+                if (kWrite && ++mx == im.mcus_x) { mx = 0; ++my; }
+            }
+            c = b < nluma ? 0 : b - nluma + 1;
+            dc = tables + im.dc[c];
+            ac = tables + im.ac[c];
+            if (kWrite) blk = block_ptr(im, coef, my, mx, b);
+        }
+    }
+    *n_done = done;
+    ScanState out;
+    out.pos = pos; out.k = (uint16_t)k; out.b = (uint16_t)b;
+    return out;
+}
+
+// DC prediction (T.81 F.2.2.1: DC = previous DC of the component + difference, reset at every restart): component c's
+// blocks of one segment in scan order are cut into runs; dc_run_sum adds up one run's differences, dc_run_apply rewrites
+// the run with the running totals once the sums of the runs before it are known.
+FTF_HD int16_t* dc_slot(const Segment& sg, const ImageDesc& im, int16_t* __restrict__ coef, int c, int t) {
+    const int ch = c == 0 ? im.hs : 1, cv = c == 0 ? im.vs : 1, per = ch * cv;
+    const int mcu = sg.first_mcu + t / per, sub = t - (t / per) * per;
+    const int my = mcu / im.mcus_x, mx = mcu - my * im.mcus_x;
+    const int v = sub / ch, h = sub - v * ch;
+    return coef + im.coef_off[c] + ((int64_t)(my * cv + v) * im.bw[c] + (mx * ch + h)) * 64;
+}
+FTF_HD int dc_run_sum(const Segment& sg, const ImageDesc& im, int16_t* __restrict__ coef, int c, int t0, int t1) {
+    int sum = 0;
+    for (int t = t0; t < t1; ++t) sum += *dc_slot(sg, im, coef, c, t);
+    return sum;
+}
+FTF_HD void dc_run_apply(const Segment& sg, const ImageDesc& im, int16_t* __restrict__ coef, int c, int t0, int t1, int before) {
+    int run = before;
+    for (int t = t0; t < t1; ++t) {
+        int16_t* p = dc_slot(sg, im, coef, c, t);
+        run += *p;
+        *p = (int16_t)run;
+    }
 }
 
 // ---- inverse DCT: libjpeg's integer "slow" method (13-bit constants, first pass keeps 2 extra bits) -----------------
@@ -259,6 +347,87 @@ FTF_HD void pixel_rgb(const ImageDesc& im, const uint8_t* __restrict__ planes, i
     const int cb = chroma_at(planes + im.plane_off[1], im.bw[1] * 8, im.dw[1], im.dh[1], im.hs, im.vs, y, x);
     const int cr = chroma_at(planes + im.plane_off[2], im.bw[2] * 8, im.dw[2], im.dh[2], im.hs, im.vs, y, x);
     ycc_to_rgb(yy, cb, cr, rgb);
+}
+
+FTF_HD uint32_t load_u32(const uint8_t* p) { return *reinterpret_cast<const uint32_t*>(p); }
+
+// The chroma samples of the 8 pixels (y, x0 .. x0+7), x0 a multiple of 8: chroma_at for each of them, with the plane
+// read as aligned words and every source sample fetched once.  The triangle filters replicate the edge sample, so the
+// neighbours outside [0, dw) are the clamped ones.
+FTF_HD void chroma8(const uint8_t* __restrict__ pl, int st, int dw, int dh, int hs, int vs, int y, int x0, int (&o)[8]) {
+    if (hs == 1) {
+        const uint8_t* r = pl + (int64_t)y * st + x0;
+        const uint32_t a = load_u32(r), b = load_u32(r + 4);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { o[i] = (int)((a >> (8 * i)) & 0xFF); o[4 + i] = (int)((b >> (8 * i)) & 0xFF); }
+        return;
+    }
+    if (dw <= 2) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = chroma_at(pl, st, dw, dh, hs, vs, y, x0 + i);
+        return;
+    }
+    const int cx0 = x0 >> 1;
+    const int cy = vs == 2 ? y >> 1 : y;
+    int ny = cy;
+    if (vs == 2) {
+        ny = (y & 1) ? cy + 1 : cy - 1;
+        ny = ny < 0 ? 0 : ny > dh - 1 ? dh - 1 : ny;
+    }
+    const uint8_t* r0 = pl + (int64_t)cy * st;
+    const uint8_t* r1 = pl + (int64_t)ny * st;
+    int s[6];                                // column terms of samples cx0-1 .. cx0+4
+    if (cx0 >= 1 && cx0 + 4 <= dw - 1) {
+        const uint32_t a = load_u32(r0 + cx0), b = load_u32(r1 + cx0);
+        if (vs == 2) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) s[1 + i] = 3 * (int)((a >> (8 * i)) & 0xFF) + (int)((b >> (8 * i)) & 0xFF);
+            s[0] = 3 * r0[cx0 - 1] + r1[cx0 - 1];
+            s[5] = 3 * r0[cx0 + 4] + r1[cx0 + 4];
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) s[1 + i] = (int)((a >> (8 * i)) & 0xFF);
+            s[0] = r0[cx0 - 1];
+            s[5] = r0[cx0 + 4];
+        }
+    } else {
+#pragma unroll
+        for (int i = 0; i < 6; ++i) {
+            int cx = cx0 - 1 + i;
+            cx = cx < 0 ? 0 : cx > dw - 1 ? dw - 1 : cx;
+            s[i] = vs == 2 ? 3 * r0[cx] + r1[cx] : (int)r0[cx];
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (vs == 2) {
+            o[2 * i] = (3 * s[1 + i] + s[i] + 8) >> 4;
+            o[2 * i + 1] = (3 * s[1 + i] + s[2 + i] + 7) >> 4;
+        } else {
+            o[2 * i] = (3 * s[1 + i] + s[i] + 1) >> 2;
+            o[2 * i + 1] = (3 * s[1 + i] + s[2 + i] + 2) >> 2;
+        }
+    }
+}
+
+// The 8 pixels (y, x0 .. x0+7) of image `im`, x0 a multiple of 8, as 24 RGB bytes (pixels past the width are computed
+// from the planes' padding and dropped by the caller).
+FTF_HD void pixels8_rgb(const ImageDesc& im, const uint8_t* __restrict__ planes, int y, int x0, uint8_t* rgb) {
+    const uint8_t* yp = planes + im.plane_off[0] + (int64_t)y * (im.bw[0] * 8) + x0;
+    const uint32_t ya = load_u32(yp), yb = load_u32(yp + 4);
+    if (im.ncomp == 1) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint8_t v = (uint8_t)(((i < 4 ? ya : yb) >> (8 * (i & 3))) & 0xFF);
+            rgb[3 * i] = rgb[3 * i + 1] = rgb[3 * i + 2] = v;
+        }
+        return;
+    }
+    int cb[8], cr[8];
+    chroma8(planes + im.plane_off[1], im.bw[1] * 8, im.dw[1], im.dh[1], im.hs, im.vs, y, x0, cb);
+    chroma8(planes + im.plane_off[2], im.bw[2] * 8, im.dw[2], im.dh[2], im.hs, im.vs, y, x0, cr);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) ycc_to_rgb((int)(((i < 4 ? ya : yb) >> (8 * (i & 3))) & 0xFF), cb[i], cr[i], rgb + 3 * i);
 }
 
 }  // namespace jpeg

@@ -159,37 +159,51 @@ void fill_geometry(const Parsed& p, ImageDesc* im) {
     }
 }
 
-void find_segments(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, std::vector<Segment>* out) {
+static int segment_count(const Parsed& p, const ImageDesc& im) {
     const int total = im.mcus_x * im.mcus_y;
-    Segment s{};
-    s.image = image;
-    if (p.restart <= 0 || p.restart >= total) {
-        s.first_mcu = 0; s.n_mcus = total; s.begin = p.scan_begin; s.end = n;
-        out->push_back(s);
-        return;
-    }
-    int64_t pos = p.scan_begin;
+    return (p.restart > 0 && p.restart < total) ? (total + p.restart - 1) / p.restart : 1;
+}
+
+int64_t stage_bound(int64_t n, const Parsed& p, const ImageDesc& im) {
+    return (n - p.scan_begin) + 16ll * segment_count(p, im) + 16;
+}
+
+int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, uint8_t* dst,
+                   int64_t dst_offset, std::vector<Segment>* out) {
+    const int total = im.mcus_x * im.mcus_y;
+    const int nseg = segment_count(p, im);
+    const int per = nseg > 1 ? p.restart : total;
+    int64_t pos = p.scan_begin, w = 0;
     bool ended = false;
-    for (int first = 0; first < total; first += p.restart) {
-        s.first_mcu = first;
-        s.n_mcus = total - first < p.restart ? total - first : p.restart;
-        s.begin = pos;
-        int64_t e = pos;
-        while (!ended) {            // next marker that is not a stuffed 0xFF00 or a fill byte
-            const uint8_t* f = e < n ? (const uint8_t*)memchr(d + e, 0xFF, (size_t)(n - e)) : nullptr;
-            if (!f || f + 1 >= d + n) { e = n; ended = true; break; }
-            e = f - d;
-            const int m = f[1];
-            if (m == 0x00) { e += 2; continue; }
-            if (m == 0xFF) { e += 1; continue; }
-            if (m >= 0xD0 && m <= 0xD7) { pos = e + 2; break; }
-            ended = true;           // EOI or another marker: the scan ends here
-            break;
+    for (int k = 0; k < nseg; ++k) {
+        Segment s{};
+        s.image = image;
+        s.first_mcu = k * per;
+        s.n_mcus = total - s.first_mcu < per ? total - s.first_mcu : per;
+        s.begin = dst_offset + w;
+        const int64_t w0 = w;
+        while (!ended) {
+            const uint8_t* f = pos < n ? (const uint8_t*)memchr(d + pos, 0xFF, (size_t)(n - pos)) : nullptr;
+            const int64_t upto = f ? f - d : n;
+            memcpy(dst + w, d + pos, (size_t)(upto - pos));
+            w += upto - pos;
+            pos = upto;
+            if (!f || pos + 1 >= n) { ended = true; break; }          // data runs out: the rest reads as zero bits
+            const int m = d[pos + 1];
+            if (m == 0x00) { dst[w++] = 0xFF; pos += 2; continue; }   // stuffed byte
+            if (m == 0xFF) { pos += 1; continue; }                    // fill byte in front of a marker
+            if (m >= 0xD0 && m <= 0xD7 && nseg > 1) { pos += 2; break; }   // RSTn closes this interval
+            ended = true;                                             // EOI or any other marker ends the scan
         }
-        s.end = e;
-        if (ended) pos = e;         // later intervals (missing from a truncated file) decode from zero bits
+        s.nbits = (w - w0) * 8;
+        s.n_chunks = (int32_t)((s.nbits + kChunkBits - 1) / kChunkBits);
+        if (s.n_chunks < 1) s.n_chunks = 1;
+        const int64_t padded = (w + 3) / 4 * 4 + 8;
+        memset(dst + w, 0, (size_t)(padded - w));
+        w = padded;
         out->push_back(s);
     }
+    return w;
 }
 
 }  // namespace jpeg

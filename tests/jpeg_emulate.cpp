@@ -3,11 +3,16 @@
 // checked against the oracle on a machine without a GPU.  Built and used by tests/test_jpeg_cpu.py only; it is not
 // part of libftf_b200.so and nothing in the library calls it.
 #include "../flink-tensorflow_b200/csrc/jpeg_parse.cpp"
+#include <algorithm>
 #include <vector>
 
 using namespace ftf::jpeg;
 
-extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, int32_t* n_segments) {
+static int g_rounds = 0;
+extern "C" int emu_last_rounds() { return g_rounds; }      // correction rounds of the last decode (all segments)
+
+// threads: chunks per wave (the CTA size of J1a); 0 = 1024
+extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, int32_t* n_segments, int32_t threads) {
     Parsed* p = new Parsed();
     std::string err;
     int rc = parse_headers(file, len, p, &err);
@@ -27,20 +32,86 @@ extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, i
     }
     im.rgb_off = 0;
     std::vector<Segment> segs;
-    find_segments(file, len, *p, im, 0, &segs);
+    std::vector<uint8_t> scan((size_t)stage_bound(len, *p, im) + 16);
+    stage_scan(file, len, *p, im, 0, scan.data(), 0, &segs);
     if (n_segments) *n_segments = (int)segs.size();
     std::vector<int16_t> coef((size_t)coef_elems, 0);
-    std::vector<uint8_t> planes((size_t)plane_bytes + 8);
+    std::vector<uint8_t> planes((size_t)plane_bytes + 16);
     int bad = 0;
-    for (const Segment& s : segs) bad |= decode_segment(s, im, tables.data(), file, coef.data());   // J1, one thread each
+    const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
+    g_rounds = 0;
+    for (const Segment& sg : segs) {                                  // J1a: one CTA per segment, `threads` chunks per wave
+        const int T = threads > 0 ? threads : 1024, total_blocks = sg.n_mcus * bpm;
+        ScanState wave_entry{0, 0, 0};
+        int blocks_before = 0;
+        for (int c0 = 0; c0 < sg.n_chunks; c0 += T) {
+            const int m = std::min(T, sg.n_chunks - c0);
+            std::vector<ScanState> in((size_t)m), out((size_t)m);
+            std::vector<int> n((size_t)m, 0);
+            for (int t = 0; t < m; ++t) {                             // 1. guess
+                in[t] = ScanState{(uint32_t)(c0 + t) * kChunkBits, 0, 0};
+                if (t == 0) in[t] = wave_entry;
+                out[t] = decode_chunk<false>(sg, im, tables.data(), scan.data(), in[t], (uint32_t)(c0 + t + 1) * kChunkBits, 0, 0,
+                                             nullptr, &n[t], nullptr);
+            }
+            for (;;) {                                                // 2. correct along the chain, all threads in lock step
+                std::vector<ScanState> prev(out);
+                bool any = false;
+                for (int t = 1; t < m; ++t)
+                    if (!same_state(prev[t - 1], in[t])) {
+                        any = true;
+                        in[t] = prev[t - 1];
+                        out[t] = decode_chunk<false>(sg, im, tables.data(), scan.data(), in[t], (uint32_t)(c0 + t + 1) * kChunkBits, 0, 0,
+                                                     nullptr, &n[t], nullptr);
+                    }
+                if (!any) break;
+                ++g_rounds;
+            }
+            int ordinal = blocks_before;                              // 3. prefix sum + the storing pass
+            for (int t = 0; t < m; ++t) {
+                if (ordinal < total_blocks) {
+                    int n2 = 0;
+                    const bool last = c0 + t == sg.n_chunks - 1;
+                    decode_chunk<true>(sg, im, tables.data(), scan.data(), in[t], last ? 0xffffffffu : (uint32_t)(c0 + t + 1) * kChunkBits,
+                                       ordinal, total_blocks, coef.data(), &n2, &bad);
+                }
+                ordinal += n[t];
+            }
+            wave_entry = out[(size_t)m - 1];
+            blocks_before = ordinal;
+        }
+        for (int c = 0; c < im.ncomp; ++c) {                          // J1b: 32 lanes, each a run of the component's blocks
+            const int count = sg.n_mcus * (c == 0 ? im.hs * im.vs : 1), run = (count + 31) / 32;
+            int sums[32], before = 0;
+            for (int lane = 0; lane < 32; ++lane) {
+                const int t0 = std::min(lane * run, count), t1 = std::min(t0 + run, count);
+                sums[lane] = dc_run_sum(sg, im, coef.data(), c, t0, t1);
+            }
+            for (int lane = 0; lane < 32; ++lane) {
+                const int t0 = std::min(lane * run, count), t1 = std::min(t0 + run, count);
+                dc_run_apply(sg, im, coef.data(), c, t0, t1, before);
+                before += sums[lane];
+            }
+        }
+    }
     for (int c = 0; c < im.ncomp; ++c)                                                              // J2
         for (int b = 0; b < im.bw[c] * im.bh[c]; ++b) {
             const int by = b / im.bw[c], bx = b % im.bw[c];
             idct_block(coef.data() + im.coef_off[c] + (int64_t)b * 64, quant.data() + im.quant[c] * 64,
                        planes.data() + im.plane_off[c] + ((int64_t)by * 8 * im.bw[c] + bx) * 8, im.bw[c] * 8);
         }
-    for (int y = 0; y < im.height; ++y)                                                             // J3
-        for (int x = 0; x < im.width; ++x) pixel_rgb(im, planes.data(), y, x, rgb + ((int64_t)y * im.width + x) * 3);
+    for (int y = 0; y < im.height; ++y)                                                             // J3: 8 pixels per thread
+        for (int x0 = 0; x0 < im.width; x0 += 8) {
+            uint8_t px[24];
+            pixels8_rgb(im, planes.data(), y, x0, px);
+            const int nx = std::min(8, im.width - x0);
+            memcpy(rgb + ((int64_t)y * im.width + x0) * 3, px, (size_t)nx * 3);
+            uint8_t one[3];                                          // the per-pixel form must agree
+            for (int i = 0; i < nx; ++i) {
+                pixel_rgb(im, planes.data(), y, x0 + i, one);
+                if (memcmp(one, px + 3 * i, 3)) bad |= 2;
+            }
+        }
     delete p;
     return bad ? 3 : 0;
 }

@@ -22,15 +22,16 @@ def cases():
 def emu(tmp_path_factory):
     """tests/jpeg_emulate.cpp: csrc/jpeg_core.h + csrc/jpeg_parse.cpp compiled by g++ (no CUDA), one loop per kernel."""
     out = str(tmp_path_factory.mktemp("emu") / "libjpeg_emu.so")
-    subprocess.run(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-o", out, os.path.join(ROOT, "tests", "jpeg_emulate.cpp")],
+    subprocess.run(["g++", "-O2", "-std=c++17", "-Wno-unknown-pragmas", "-shared", "-fPIC", "-o", out, os.path.join(ROOT, "tests", "jpeg_emulate.cpp")],
                    check=True)
     lib = C.CDLL(out)
 
-    def decode(data, shape):
+    def decode(data, shape, threads=0):
         rgb = np.zeros(shape, np.uint8)
         nseg = C.c_int32()
-        rc = lib.emu_jpeg_decode(data, C.c_int64(len(data)), rgb.ctypes.data_as(C.c_void_p), C.byref(nseg))
+        rc = lib.emu_jpeg_decode(data, C.c_int64(len(data)), rgb.ctypes.data_as(C.c_void_p), C.byref(nseg), threads)
         return rc, rgb, nseg.value
+    decode.rounds = lib.emu_last_rounds
     return decode
 
 
@@ -51,19 +52,21 @@ def test_oracle_matches_libjpeg_fixtures(oracle, cases):
 
 
 def test_kernel_functions_on_cpu_match_fixtures(emu, cases):
-    """The code the three kernels run per thread (Huffman segment, 8x8 block, pixel), bit-exact on every fixture;
-    files with restart markers split into several segments."""
-    for name, (data, want) in cases.items():
-        rc, rgb, nseg = emu(data, want.shape)
-        if name.startswith("refuse_"):
-            assert rc == 12
-            continue
-        assert rc == 0, name
-        assert np.array_equal(rgb, want), name
-        if "rst" in name:
-            assert nseg > 1, name
-        else:
-            assert nseg == 1, name
+    """The code the kernels run per thread (Huffman chunk, DC run, 8x8 block, pixel) and the chunk-parallel decoding
+    scheme around it, bit-exact on every fixture; files with restart markers split into several segments.  CTA sizes
+    of 1 and 2 chunks force the multi-wave path and the longest correction chains."""
+    for threads in (0, 2, 1):
+        for name, (data, want) in cases.items():
+            rc, rgb, nseg = emu(data, want.shape, threads)
+            if name.startswith("refuse_"):
+                assert rc == 12
+                continue
+            assert rc == 0, name
+            assert np.array_equal(rgb, want), (name, threads)
+            if "rst" in name:
+                assert nseg > 1, name
+            else:
+                assert nseg == 1, name
 
 
 def test_kernel_functions_on_cpu_match_oracle_on_photo_sized_image(emu, oracle):
@@ -76,9 +79,14 @@ def test_kernel_functions_on_cpu_match_oracle_on_photo_sized_image(emu, oracle):
     b = io.BytesIO()
     Image.fromarray(img).save(b, "JPEG", quality=85)
     data = b.getvalue()
-    rc, rgb, _ = emu(data, (480, 640, 3))
-    assert rc == 0
-    assert np.array_equal(rgb, oracle.jpeg_decode(data))
+    want = oracle.jpeg_decode(data)
+    for threads in (0, 64):                        # one wave of 1024 chunks; waves of 64
+        rc, rgb, _ = emu(data, (480, 640, 3), threads)
+        assert rc == 0
+        assert np.array_equal(rgb, want)
+    # a wrongly started decoder falls into step quickly: far fewer correction rounds than chunks
+    emu(data, (480, 640, 3), 0)
+    assert emu.rounds() < 40 < len(data) * 8 // 1024
 
 
 def test_jpeg_info_and_header_errors(ftf, cases):
