@@ -30,15 +30,22 @@ namespace {
 // J1a: one CTA per segment, one thread per chunk of kChunkBits (see decode_chunk in jpeg_core.h for the scheme).
 // Segments with more chunks than the CTA has threads are walked in waves: a wave starts from the true state the
 // previous wave ended in.
-__global__ void __launch_bounds__(1024)
+template <int kMaxThreads, int kMinBlocks>
+__global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
 jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restrict__ images,
                     const HuffTable* __restrict__ tables, const uint8_t* __restrict__ scan,
-                    int16_t* __restrict__ coef, int32_t* __restrict__ status) {
-    __shared__ ScanState s_exit[1024];
+                    int16_t* __restrict__ coef, int16_t* __restrict__ dcv, int32_t* __restrict__ status) {
+    extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ int s_warp[32];
     const Segment sg = segs[blockIdx.x];
     const ImageDesc& im = images[sg.image];
     const int T = (int)blockDim.x, tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // dynamic shared memory: exit states [T] | checkpoint states [kCheckpoints][T] | checkpoint block counts [kCheckpoints][T]
+    ScanState* s_exit = reinterpret_cast<ScanState*>(smem_raw);
+    Checkpoints cp;
+    cp.state = s_exit + T + tid;
+    cp.done = reinterpret_cast<uint16_t*>(s_exit + (size_t)T * (1 + kCheckpoints)) + tid;
+    cp.stride = T;
     const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
     const int total_blocks = sg.n_mcus * bpm;
     ScanState wave_entry;
@@ -54,7 +61,7 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
         ScanState out = in;
         int n = 0;
         // 1. guess
-        if (active) out = decode_chunk<false>(sg, im, tables, scan, in, limit, 0, 0, nullptr, &n, nullptr);
+        if (active) out = decode_chunk<kGuess>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr, cp);
         s_exit[tid] = out;
         // 2. until every chunk started from the state its predecessor left
         for (;;) {
@@ -65,7 +72,7 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
             if (!__syncthreads_or(changed)) break;
             if (changed) {
                 in = prev;
-                out = decode_chunk<false>(sg, im, tables, scan, in, limit, 0, 0, nullptr, &n, nullptr);
+                out = decode_chunk<kCorrect>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr, cp, out);
                 s_exit[tid] = out;
             }
         }
@@ -87,7 +94,7 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
         const int ordinal = blocks_before + warp_before + incl - (active ? n : 0);
         if (active && ordinal < total_blocks) {
             int n2 = 0;
-            decode_chunk<true>(sg, im, tables, scan, in, j == sg.n_chunks - 1 ? 0xffffffffu : limit, ordinal, total_blocks, coef, &n2, &bad);
+            decode_chunk<kStore>(sg, im, tables, scan, in, j == sg.n_chunks - 1 ? 0xffffffffu : limit, ordinal, total_blocks, coef, dcv, &n2, &bad);
         }
         if (c0 + T < sg.n_chunks) {             // another wave follows: it starts where this one ended
             wave_entry = s_exit[T - 1];
@@ -98,32 +105,38 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
     if (bad) atomicOr(&status[sg.image], 1);
 }
 
-// J1b: DC differences -> DC values.  One warp per (segment, component): every lane sums a run of the component's
-// blocks, a warp scan turns the sums into offsets, every lane rewrites its run.
+// J1b: DC differences -> DC values.  One warp per (segment, component): an inclusive scan over the component's
+// contiguous stretch of the DC array, 32 elements per step with a carry.
 __global__ void __launch_bounds__(128)
-jpeg_dc_kernel(const Segment* __restrict__ segs, int nseg, const ImageDesc* __restrict__ images, int16_t* __restrict__ coef) {
+jpeg_dc_kernel(const Segment* __restrict__ segs, int nseg, const ImageDesc* __restrict__ images, int16_t* __restrict__ dcv) {
     const int w = (int)((blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = (int)(threadIdx.x & 31);
     const int s = w / 3, c = w - s * 3;
     if (s >= nseg) return;
     const Segment sg = segs[s];
     const ImageDesc& im = images[sg.image];
     if (c >= im.ncomp) return;
-    const int count = sg.n_mcus * (c == 0 ? im.hs * im.vs : 1);
-    const int run = (count + 31) / 32;
-    const int t0 = min(lane * run, count), t1 = min(t0 + run, count);
-    const int sum = dc_run_sum(sg, im, coef, c, t0, t1);
-    int incl = sum;
+    int64_t first;
+    int count;
+    dc_range(sg, im, c, &first, &count);
+    int16_t* p = dcv + first;
+    int carry = 0;
+    for (int t0 = 0; t0 < count; t0 += 32) {
+        const int t = t0 + lane;
+        int v = t < count ? (int)p[t] : 0;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, v, o);
+            if (lane >= o) v += u;
+        }
+        v += carry;
+        if (t < count) p[t] = (int16_t)v;
+        carry = __shfl_sync(0xffffffffu, v, 31);
     }
-    dc_run_apply(sg, im, coef, c, t0, t1, incl - sum);
 }
 
 __global__ void __launch_bounds__(128)
 jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restrict__ quant,
-                 const int16_t* __restrict__ coef, uint8_t* __restrict__ planes) {
+                 const int16_t* __restrict__ coef, const int16_t* __restrict__ dcv, uint8_t* __restrict__ planes) {
     const ImageDesc& im = images[blockIdx.y];
     int b = (int)(blockIdx.x * blockDim.x + threadIdx.x);
     if (b >= im.n_blocks) return;
@@ -145,6 +158,7 @@ jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restric
         reinterpret_cast<int4*>(cf)[i] = __ldg(cp + i);
         reinterpret_cast<int4*>(q)[i] = __ldg(qp + i);
     }
+    cf[0] = dc_of_block(im, dcv, c, by, bx);
     idct_block(cf, q, planes + im.plane_off[c] + ((int64_t)by * 8 * bw + bx) * 8, bw * 8);
 }
 
@@ -177,15 +191,15 @@ struct ftf_jpeg_batch {
     int device = 0;
     std::string err;
     cudaEvent_t done = nullptr;
-    Buf h_scan, h_meta, h_status, d_scan, d_meta, d_coef, d_planes, d_status;
+    Buf h_scan, h_meta, h_status, d_scan, d_meta, d_coef, d_dc, d_planes, d_status;
     std::vector<ImageDesc> images;
     std::vector<Segment> segments;
     std::vector<HuffTable> tables;
     std::vector<uint16_t> quants;
     size_t scan_bytes = 0, meta_bytes = 0, off_seg = 0, off_tab = 0, off_q = 0;
-    int64_t coef_elems = 0, plane_bytes = 0, rgb_bytes = 0;
+    int64_t coef_elems = 0, plane_bytes = 0, rgb_bytes = 0, dc_elems = 0;
     int max_blocks = 0, max_groups = 0, max_chunks = 1;
-    bool decoded = false;
+    bool decoded = false, attr_set = false;
 };
 
 namespace {
@@ -244,7 +258,7 @@ extern "C" void ftf_jpeg_batch_destroy(ftf_jpeg_batch* b) {
     if (!b) return;
     cudaSetDevice(b->device);
     if (b->done) { cudaEventSynchronize(b->done); cudaEventDestroy(b->done); }
-    for (Buf* f : {&b->h_scan, &b->h_meta, &b->h_status, &b->d_scan, &b->d_meta, &b->d_coef, &b->d_planes, &b->d_status})
+    for (Buf* f : {&b->h_scan, &b->h_meta, &b->h_status, &b->d_scan, &b->d_meta, &b->d_coef, &b->d_dc, &b->d_planes, &b->d_status})
         f->free_now();
     cudaGetLastError();
     delete b;
@@ -262,7 +276,7 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
     FTF_CUDA(cudaEventSynchronize(b->done), &b->err);
     b->images.clear(); b->segments.clear(); b->tables.clear(); b->quants.clear();
     b->decoded = false;
-    b->coef_elems = 0; b->plane_bytes = 0; b->rgb_bytes = 0; b->max_blocks = 0; b->max_groups = 0;
+    b->coef_elems = 0; b->plane_bytes = 0; b->rgb_bytes = 0; b->dc_elems = 0; b->max_blocks = 0; b->max_groups = 0;
     std::vector<Parsed>* parsed = new std::vector<Parsed>((size_t)n);
     size_t scan_total = 0;
     int rc = FTF_OK;
@@ -288,6 +302,8 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
             b->coef_elems += (int64_t)im.bw[c] * im.bh[c] * 64;
             im.plane_off[c] = b->plane_bytes;
             b->plane_bytes += (int64_t)im.bw[c] * im.bh[c] * 64;
+            im.dc_off[c] = b->dc_elems;
+            b->dc_elems += (int64_t)im.bw[c] * im.bh[c];
         }
         im.rgb_off = b->rgb_bytes;
         if (rgb_offsets) rgb_offsets[i] = im.rgb_off;
@@ -317,6 +333,7 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
         if (rc == 0 && (rc = b->h_meta.ensure(b->meta_bytes, &b->err)) == 0 &&
             (rc = b->d_scan.ensure(scan_total + 16, &b->err)) == 0 && (rc = b->d_meta.ensure(b->meta_bytes, &b->err)) == 0 &&
             (rc = b->d_coef.ensure((size_t)b->coef_elems * 2, &b->err)) == 0 &&
+            (rc = b->d_dc.ensure((size_t)b->dc_elems * 2, &b->err)) == 0 &&
             (rc = b->d_planes.ensure((size_t)b->plane_bytes, &b->err)) == 0 &&
             (rc = b->d_status.ensure((size_t)n * 4, &b->err)) == 0 && (rc = b->h_status.ensure((size_t)n * 4, &b->err)) == 0) {
             uint8_t* m = (uint8_t*)b->h_meta.p;
@@ -352,14 +369,26 @@ extern "C" int ftf_jpeg_batch_decode_dev(ftf_jpeg_batch* b, uint8_t* rgb_out, in
     const HuffTable* d_tabs = (const HuffTable*)(m + b->off_tab);
     const uint16_t* d_quant = (const uint16_t*)(m + b->off_q);
     FTF_CUDA(cudaMemsetAsync(b->d_coef.p, 0, (size_t)b->coef_elems * 2, st), &b->err);
+    FTF_CUDA(cudaMemsetAsync(b->d_dc.p, 0, (size_t)b->dc_elems * 2, st), &b->err);
     FTF_CUDA(cudaMemsetAsync(b->d_status.p, 0, (size_t)n * 4, st), &b->err);
+    // CTA size: one thread per chunk up to 1024; up to 640 threads the kernel is built for two CTAs per SM (48 registers)
     int threads = (b->max_chunks + 31) / 32 * 32;
     threads = threads > 1024 ? 1024 : threads;
-    jpeg_huffman_kernel<<<nseg, threads, 0, st>>>(d_segs, d_images, d_tabs, (const uint8_t*)b->d_scan.p, (int16_t*)b->d_coef.p,
-                                                  (int32_t*)b->d_status.p);
-    jpeg_dc_kernel<<<(nseg * 3 + 3) / 4, 128, 0, st>>>(d_segs, nseg, d_images, (int16_t*)b->d_coef.p);
+    const size_t hsm = (size_t)threads * (sizeof(ScanState) * (1 + kCheckpoints) + sizeof(uint16_t) * kCheckpoints);
+    if (!b->attr_set) {                  // once per batch object: the attribute belongs to the function on this device
+        FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<640, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 640 * 78), &b->err);
+        FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * 78), &b->err);
+        b->attr_set = true;
+    }
+    if (threads <= 640)
+        jpeg_huffman_kernel<640, 2><<<nseg, threads, hsm, st>>>(d_segs, d_images, d_tabs, (const uint8_t*)b->d_scan.p, (int16_t*)b->d_coef.p,
+                                                             (int16_t*)b->d_dc.p, (int32_t*)b->d_status.p);
+    else
+        jpeg_huffman_kernel<1024, 1><<<nseg, threads, hsm, st>>>(d_segs, d_images, d_tabs, (const uint8_t*)b->d_scan.p, (int16_t*)b->d_coef.p,
+                                                              (int16_t*)b->d_dc.p, (int32_t*)b->d_status.p);
+    jpeg_dc_kernel<<<(nseg * 3 + 3) / 4, 128, 0, st>>>(d_segs, nseg, d_images, (int16_t*)b->d_dc.p);
     jpeg_idct_kernel<<<dim3((b->max_blocks + 127) / 128, n), 128, 0, st>>>(d_images, d_quant, (const int16_t*)b->d_coef.p,
-                                                                            (uint8_t*)b->d_planes.p);
+                                                                            (const int16_t*)b->d_dc.p, (uint8_t*)b->d_planes.p);
     jpeg_colour_kernel<<<dim3((b->max_groups + 255) / 256, n), 256, 0, st>>>(d_images, (const uint8_t*)b->d_planes.p, rgb_out);
     FTF_CUDA(cudaGetLastError(), &b->err);
     count_launch(4);

@@ -45,6 +45,7 @@ struct ImageDesc {
     int32_t n_blocks;
     int64_t coef_off[3];          // int16 elements
     int64_t plane_off[3];         // bytes
+    int64_t dc_off[3];            // int16 elements of the batch's DC array: the component's blocks in scan order
     int64_t rgb_off;              // bytes
 };
 
@@ -141,6 +142,24 @@ FTF_HD int16_t* block_ptr(const ImageDesc& im, int16_t* __restrict__ coef, int m
     return coef + im.coef_off[c] + ((int64_t)my * im.bw[c] + mx) * 64;
 }
 
+// DC terms live apart from the other coefficients, per component in scan order (MCU by MCU, luma blocks row-major inside
+// the MCU), so that turning differences into values is a scan over contiguous memory.
+FTF_HD int dc_index(const ImageDesc& im, int mcu, int b) {
+    const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
+    return b < nluma ? mcu * nluma + b : mcu;
+}
+FTF_HD int16_t* dc_slot(const ImageDesc& im, int16_t* __restrict__ dcv, int mcu, int b) {
+    const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
+    const int c = b < nluma ? 0 : b - nluma + 1;
+    return dcv + im.dc_off[c] + dc_index(im, mcu, b);
+}
+// the DC value of block (by, bx) of component c, for the inverse DCT
+FTF_HD int16_t dc_of_block(const ImageDesc& im, const int16_t* __restrict__ dcv, int c, int by, int bx) {
+    const int ch = c == 0 ? im.hs : 1, cv = c == 0 ? im.vs : 1;
+    const int my = by / cv, v = by - my * cv, mx = bx / ch, h = bx - mx * ch;
+    return dcv[im.dc_off[c] + (int64_t)(my * im.mcus_x + mx) * (ch * cv) + v * ch + h];
+}
+
 // Parallel entropy decoding.  A Huffman stream has no index, but a decoder started at a wrong place falls into step with
 // the true one after a few symbols, so a segment is cut into chunks of kChunkBits and every chunk gets a thread:
 //   1. each thread decodes its chunk from a guessed state (the chunk's first bit, start of an MCU) and publishes the state
@@ -152,17 +171,37 @@ FTF_HD int16_t* block_ptr(const ImageDesc& im, int16_t* __restrict__ coef, int m
 // decode_chunk is one such pass over the symbols that start in [st.pos, limit).  kWrite = false: counts completed blocks
 // and returns the exit state; a bit pattern that is no code (possible only from a wrong state or in a corrupt file) is
 // skipped one bit at a time.  kWrite = true: also stores coefficients for blocks [ordinal, total_blocks) of the segment,
-// and reports a pattern that is no code, or a run past the 64th coefficient, through *bad.
-template <bool kWrite>
+// (DC differences go to the DC array, see dc_slot) and reports a pattern that is no code, or a run past the 64th
+// coefficient, through *bad.
+// Correction passes rarely need the whole chunk: the re-started decoder usually meets the path of the previous attempt
+// after a few symbols, and from there on everything (exit state, blocks completed) is already known.  Every attempt
+// therefore leaves its state at kCheckpoints positions of the chunk (the first symbol at or after every kCheckpointBits),
+// and a correction pass stops at the first checkpoint where it finds itself in the recorded state.
+constexpr int kCheckpointBits = 128;
+constexpr int kCheckpoints = kChunkBits / kCheckpointBits - 1;
+struct Checkpoints {
+    ScanState* state;     // [kCheckpoints], element i at state[i * stride]
+    uint16_t* done;       // blocks completed before the checkpoint
+    int stride;
+};
+enum { kGuess = 0, kCorrect = 1, kStore = 2 };
+
+// kMode kGuess / kCorrect: the counting passes (record / compare-and-record checkpoints; kCorrect takes the previous
+// attempt's exit state and block count in *exit_io / *n_done and may return them adjusted).  kStore: the storing pass.
+template <int kMode>
 FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const HuffTable* __restrict__ tables,
                               const uint8_t* __restrict__ scan, ScanState st, uint32_t limit, int ordinal, int total_blocks,
-                              int16_t* __restrict__ coef, int* n_done, int* bad) {
+                              int16_t* __restrict__ coef, int16_t* __restrict__ dcv, int* n_done, int* bad,
+                              Checkpoints cp = Checkpoints{nullptr, nullptr, 0}, ScanState old_exit = ScanState{0, 0, 0}) {
+    constexpr bool kWrite = kMode == kStore;
     const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
     const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
     BitWindow bw;
     bw.seek(reinterpret_cast<const uint32_t*>(scan + sg.begin), (uint32_t)sg.nbits, st.pos);
     uint32_t pos = st.pos;
     int k = st.k, b = st.b, done = 0;
+    uint32_t next_cp = limit - kChunkBits + kCheckpointBits;      // counting passes only
+    int ci = 0;
     int mx = 0, my = 0;
     int16_t* blk = nullptr;
     if (kWrite) {
@@ -188,7 +227,7 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
                 sym = 0;
             }
             const int s = sym;
-            if (kWrite) blk[0] = (int16_t)(s ? extend_bits(w, len, s) : 0);
+            if (kWrite) *dc_slot(im, dcv, my * im.mcus_x + mx, b) = (int16_t)(s ? extend_bits(w, len, s) : 0);
             pos += (uint32_t)(len + s);
             k = 1;
         } else {
@@ -218,6 +257,21 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
             ac = tables + im.ac[c];
             if (kWrite) blk = block_ptr(im, coef, my, mx, b);
         }
+        if (!kWrite && pos >= next_cp && ci < kCheckpoints) {
+            ScanState cur;
+            cur.pos = pos; cur.k = (uint16_t)k; cur.b = (uint16_t)b;
+            if (kMode == kCorrect && same_state(cur, cp.state[ci * cp.stride])) {
+                // back on the previous attempt's path: its remainder stands, only the block counts shift
+                const int delta = done - (int)cp.done[ci * cp.stride];
+                for (int i = ci; i < kCheckpoints; ++i) cp.done[i * cp.stride] = (uint16_t)((int)cp.done[i * cp.stride] + delta);
+                *n_done += delta;
+                return old_exit;
+            }
+            cp.state[ci * cp.stride] = cur;
+            cp.done[ci * cp.stride] = (uint16_t)done;
+            ++ci;
+            next_cp += kCheckpointBits;
+        }
     }
     *n_done = done;
     ScanState out;
@@ -225,28 +279,12 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
     return out;
 }
 
-// DC prediction (T.81 F.2.2.1: DC = previous DC of the component + difference, reset at every restart): component c's
-// blocks of one segment in scan order are cut into runs; dc_run_sum adds up one run's differences, dc_run_apply rewrites
-// the run with the running totals once the sums of the runs before it are known.
-FTF_HD int16_t* dc_slot(const Segment& sg, const ImageDesc& im, int16_t* __restrict__ coef, int c, int t) {
-    const int ch = c == 0 ? im.hs : 1, cv = c == 0 ? im.vs : 1, per = ch * cv;
-    const int mcu = sg.first_mcu + t / per, sub = t - (t / per) * per;
-    const int my = mcu / im.mcus_x, mx = mcu - my * im.mcus_x;
-    const int v = sub / ch, h = sub - v * ch;
-    return coef + im.coef_off[c] + ((int64_t)(my * cv + v) * im.bw[c] + (mx * ch + h)) * 64;
-}
-FTF_HD int dc_run_sum(const Segment& sg, const ImageDesc& im, int16_t* __restrict__ coef, int c, int t0, int t1) {
-    int sum = 0;
-    for (int t = t0; t < t1; ++t) sum += *dc_slot(sg, im, coef, c, t);
-    return sum;
-}
-FTF_HD void dc_run_apply(const Segment& sg, const ImageDesc& im, int16_t* __restrict__ coef, int c, int t0, int t1, int before) {
-    int run = before;
-    for (int t = t0; t < t1; ++t) {
-        int16_t* p = dc_slot(sg, im, coef, c, t);
-        run += *p;
-        *p = (int16_t)run;
-    }
+// DC prediction (T.81 F.2.2.1: DC = previous DC of the component + difference, reset at every restart): an in-place
+// inclusive scan over the component's stretch of the DC array that belongs to one segment.  dc_range gives the stretch.
+FTF_HD void dc_range(const Segment& sg, const ImageDesc& im, int c, int64_t* first, int* count) {
+    const int per = c == 0 ? (im.ncomp == 1 ? 1 : im.hs * im.vs) : 1;
+    *first = im.dc_off[c] + (int64_t)sg.first_mcu * per;
+    *count = sg.n_mcus * per;
 }
 
 // ---- inverse DCT: libjpeg's integer "slow" method (13-bit constants, first pass keeps 2 extra bits) -----------------

@@ -29,13 +29,14 @@ extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, i
         im.ac[c] = (int)tables.size(); tables.push_back(p->ac[p->ta[c]]);
         im.coef_off[c] = coef_elems; coef_elems += (int64_t)im.bw[c] * im.bh[c] * 64;
         im.plane_off[c] = plane_bytes; plane_bytes += (int64_t)im.bw[c] * im.bh[c] * 64;
+        im.dc_off[c] = im.coef_off[c] / 64;
     }
     im.rgb_off = 0;
     std::vector<Segment> segs;
     std::vector<uint8_t> scan((size_t)stage_bound(len, *p, im) + 16);
     stage_scan(file, len, *p, im, 0, scan.data(), 0, &segs);
     if (n_segments) *n_segments = (int)segs.size();
-    std::vector<int16_t> coef((size_t)coef_elems, 0);
+    std::vector<int16_t> coef((size_t)coef_elems, 0), dcv((size_t)coef_elems / 64, 0);
     std::vector<uint8_t> planes((size_t)plane_bytes + 16);
     int bad = 0;
     const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
@@ -48,11 +49,14 @@ extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, i
             const int m = std::min(T, sg.n_chunks - c0);
             std::vector<ScanState> in((size_t)m), out((size_t)m);
             std::vector<int> n((size_t)m, 0);
+            std::vector<ScanState> cps((size_t)m * kCheckpoints);              // [kCheckpoints][m], as in shared memory
+            std::vector<uint16_t> cpn((size_t)m * kCheckpoints);
+            auto cp_of = [&](int t) { return Checkpoints{cps.data() + t, cpn.data() + t, m}; };
             for (int t = 0; t < m; ++t) {                             // 1. guess
                 in[t] = ScanState{(uint32_t)(c0 + t) * kChunkBits, 0, 0};
                 if (t == 0) in[t] = wave_entry;
-                out[t] = decode_chunk<false>(sg, im, tables.data(), scan.data(), in[t], (uint32_t)(c0 + t + 1) * kChunkBits, 0, 0,
-                                             nullptr, &n[t], nullptr);
+                out[t] = decode_chunk<kGuess>(sg, im, tables.data(), scan.data(), in[t], (uint32_t)(c0 + t + 1) * kChunkBits, 0, 0,
+                                              nullptr, nullptr, &n[t], nullptr, cp_of(t));
             }
             for (;;) {                                                // 2. correct along the chain, all threads in lock step
                 std::vector<ScanState> prev(out);
@@ -61,8 +65,8 @@ extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, i
                     if (!same_state(prev[t - 1], in[t])) {
                         any = true;
                         in[t] = prev[t - 1];
-                        out[t] = decode_chunk<false>(sg, im, tables.data(), scan.data(), in[t], (uint32_t)(c0 + t + 1) * kChunkBits, 0, 0,
-                                                     nullptr, &n[t], nullptr);
+                        out[t] = decode_chunk<kCorrect>(sg, im, tables.data(), scan.data(), in[t], (uint32_t)(c0 + t + 1) * kChunkBits, 0, 0,
+                                                        nullptr, nullptr, &n[t], nullptr, cp_of(t), out[t]);
                     }
                 if (!any) break;
                 ++g_rounds;
@@ -72,31 +76,25 @@ extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, i
                 if (ordinal < total_blocks) {
                     int n2 = 0;
                     const bool last = c0 + t == sg.n_chunks - 1;
-                    decode_chunk<true>(sg, im, tables.data(), scan.data(), in[t], last ? 0xffffffffu : (uint32_t)(c0 + t + 1) * kChunkBits,
-                                       ordinal, total_blocks, coef.data(), &n2, &bad);
+                    decode_chunk<kStore>(sg, im, tables.data(), scan.data(), in[t], last ? 0xffffffffu : (uint32_t)(c0 + t + 1) * kChunkBits,
+                                       ordinal, total_blocks, coef.data(), dcv.data(), &n2, &bad);
                 }
                 ordinal += n[t];
             }
             wave_entry = out[(size_t)m - 1];
             blocks_before = ordinal;
         }
-        for (int c = 0; c < im.ncomp; ++c) {                          // J1b: 32 lanes, each a run of the component's blocks
-            const int count = sg.n_mcus * (c == 0 ? im.hs * im.vs : 1), run = (count + 31) / 32;
-            int sums[32], before = 0;
-            for (int lane = 0; lane < 32; ++lane) {
-                const int t0 = std::min(lane * run, count), t1 = std::min(t0 + run, count);
-                sums[lane] = dc_run_sum(sg, im, coef.data(), c, t0, t1);
-            }
-            for (int lane = 0; lane < 32; ++lane) {
-                const int t0 = std::min(lane * run, count), t1 = std::min(t0 + run, count);
-                dc_run_apply(sg, im, coef.data(), c, t0, t1, before);
-                before += sums[lane];
-            }
+        for (int c = 0; c < im.ncomp; ++c) {                          // J1b: inclusive scan of the segment's DC stretch
+            int64_t first;
+            int count, carry = 0;
+            dc_range(sg, im, c, &first, &count);
+            for (int t = 0; t < count; ++t) { carry += dcv[(size_t)first + t]; dcv[(size_t)first + t] = (int16_t)carry; }
         }
     }
     for (int c = 0; c < im.ncomp; ++c)                                                              // J2
         for (int b = 0; b < im.bw[c] * im.bh[c]; ++b) {
             const int by = b / im.bw[c], bx = b % im.bw[c];
+            coef[(size_t)(im.coef_off[c] + (int64_t)b * 64)] = dc_of_block(im, dcv.data(), c, by, bx);
             idct_block(coef.data() + im.coef_off[c] + (int64_t)b * 64, quant.data() + im.quant[c] * 64,
                        planes.data() + im.plane_off[c] + ((int64_t)by * 8 * im.bw[c] + bx) * 8, im.bw[c] * 8);
         }
