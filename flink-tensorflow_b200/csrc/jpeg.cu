@@ -27,6 +27,8 @@ using namespace ftf::jpeg;
 
 namespace {
 
+constexpr size_t kHuffSmemPerThread = sizeof(ScanState) * (2 + kCheckpoints) + sizeof(int) + sizeof(uint16_t) * (kCheckpoints + 1);
+
 // J1a: one CTA per segment, one thread per chunk of kChunkBits (see decode_chunk in jpeg_core.h for the scheme).
 // Segments with more chunks than the CTA has threads are walked in waves: a wave starts from the true state the
 // previous wave ended in.
@@ -40,12 +42,14 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
     const Segment sg = segs[blockIdx.x];
     const ImageDesc& im = images[sg.image];
     const int T = (int)blockDim.x, tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // dynamic shared memory: exit states [T] | checkpoint states [kCheckpoints][T] | checkpoint block counts [kCheckpoints][T]
+    // dynamic shared memory, all indexed by the chunk's position in the wave: exit states, entry states, checkpoint states
+    // [kCheckpoints][T], blocks completed, checkpoint block counts [kCheckpoints][T], work list of a correction round
     ScanState* s_exit = reinterpret_cast<ScanState*>(smem_raw);
-    Checkpoints cp;
-    cp.state = s_exit + T + tid;
-    cp.done = reinterpret_cast<uint16_t*>(s_exit + (size_t)T * (1 + kCheckpoints)) + tid;
-    cp.stride = T;
+    ScanState* s_in = s_exit + T;
+    ScanState* s_cps = s_in + T;
+    int* s_n = reinterpret_cast<int*>(s_cps + (size_t)T * kCheckpoints);
+    uint16_t* s_cpn = reinterpret_cast<uint16_t*>(s_n + T);
+    uint16_t* s_list = s_cpn + (size_t)T * kCheckpoints;
     const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
     const int total_blocks = sg.n_mcus * bpm;
     ScanState wave_entry;
@@ -61,21 +65,45 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
         ScanState out = in;
         int n = 0;
         // 1. guess
-        if (active) out = decode_chunk<kGuess>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr, cp);
+        if (active) out = decode_chunk<kGuess>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr,
+                                               Checkpoints{s_cps + tid, s_cpn + tid, T});
         s_exit[tid] = out;
-        // 2. until every chunk started from the state its predecessor left
+        s_n[tid] = n;
+        // 2. until every chunk started from the state its predecessor left.  The chunks that have to be decoded again are
+        // gathered into a list and handed to the first threads of the CTA, so that late rounds with few such chunks run
+        // in few, full warps.
         for (;;) {
             __syncthreads();
             bool changed = false;
             ScanState prev = in;
             if (active && tid > 0) { prev = s_exit[tid - 1]; changed = !same_state(prev, in); }
-            if (!__syncthreads_or(changed)) break;
+            const unsigned bal = __ballot_sync(0xffffffffu, changed);
+            if (lane == 0) s_warp[warp] = __popc(bal);
+            __syncthreads();
+            int before = 0, total = 0;
+            for (int w = 0; w < (T + 31) / 32; ++w) {
+                const int v = s_warp[w];
+                if (w < warp) before += v;
+                total += v;
+            }
+            if (total == 0) break;
             if (changed) {
                 in = prev;
-                out = decode_chunk<kCorrect>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr, cp, out);
-                s_exit[tid] = out;
+                s_in[tid] = prev;
+                s_list[before + __popc(bal & ((1u << lane) - 1u))] = (uint16_t)tid;
+            }
+            __syncthreads();
+            if (tid < total) {
+                const int c = s_list[tid];
+                int cn = s_n[c];
+                const ScanState e = decode_chunk<kCorrect>(sg, im, tables, scan, s_in[c], (uint32_t)(c0 + c + 1) * kChunkBits, 0, 0, nullptr,
+                                                           nullptr, &cn, nullptr, Checkpoints{s_cps + c, s_cpn + c, T}, s_exit[c]);
+                s_exit[c] = e;
+                s_n[c] = cn;
             }
         }
+        __syncthreads();                   // the round loop's last look at s_warp is over before the scan reuses it
+        n = s_n[tid];
         // 3. which block does each chunk start in: exclusive prefix sum of the blocks completed per chunk
         int incl = active ? n : 0;
 #pragma unroll
@@ -374,10 +402,10 @@ extern "C" int ftf_jpeg_batch_decode_dev(ftf_jpeg_batch* b, uint8_t* rgb_out, in
     // CTA size: one thread per chunk up to 1024; up to 640 threads the kernel is built for two CTAs per SM (48 registers)
     int threads = (b->max_chunks + 31) / 32 * 32;
     threads = threads > 1024 ? 1024 : threads;
-    const size_t hsm = (size_t)threads * (sizeof(ScanState) * (1 + kCheckpoints) + sizeof(uint16_t) * kCheckpoints);
+    const size_t hsm = (size_t)threads * kHuffSmemPerThread;
     if (!b->attr_set) {                  // once per batch object: the attribute belongs to the function on this device
-        FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<640, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 640 * 78), &b->err);
-        FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * 78), &b->err);
+        FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<640, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 640 * (int)kHuffSmemPerThread), &b->err);
+        FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * (int)kHuffSmemPerThread), &b->err);
         b->attr_set = true;
     }
     if (threads <= 640)

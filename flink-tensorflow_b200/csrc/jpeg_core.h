@@ -204,47 +204,43 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
     int ci = 0;
     int mx = 0, my = 0;
     int16_t* blk = nullptr;
+    int16_t* dcp = nullptr;
     if (kWrite) {
         const int mcu = sg.first_mcu + ordinal / bpm;
         my = mcu / im.mcus_x; mx = mcu - my * im.mcus_x;
         blk = block_ptr(im, coef, my, mx, b);
+        dcp = dc_slot(im, dcv, mcu, b);
     }
     int c = b < nluma ? 0 : b - nluma + 1;
     const HuffTable* dc = tables + im.dc[c];
     const HuffTable* ac = tables + im.ac[c];
     while (pos < limit && (!kWrite || ordinal < total_blocks)) {
         const uint32_t w = bw.at(pos);
+        const bool is_dc = k == 0;
         int sym = 0;
-        const int len = lookup_symbol(w, k == 0 ? dc : ac, &sym);
-        if (len == 0) {
+        const int len = lookup_symbol(w, is_dc ? dc : ac, &sym);
+        if (len == 0 || (is_dc && sym > 15)) {          // no such code / a DC symbol is a bit count
             if (kWrite) { *bad = 1; break; }
             pos += 1;
             continue;
         }
-        if (k == 0) {
-            if (sym > 15) {                 // a DC symbol is a bit count
+        // one path for both kinds of symbol: a DC symbol is a run of 0 and a size, landing on index 0
+        const int r = is_dc ? 0 : sym >> 4, s = is_dc ? sym : sym & 15;
+        if (s != 0 || is_dc) {
+            k += r;
+            if (k > 63) {
                 if (kWrite) { *bad = 1; break; }
-                sym = 0;
+                k = 63;
             }
-            const int s = sym;
-            if (kWrite) *dc_slot(im, dcv, my * im.mcus_x + mx, b) = (int16_t)(s ? extend_bits(w, len, s) : 0);
+            if (kWrite) {
+                int16_t* dst = is_dc ? dcp : blk + natural_order(k);
+                *dst = (int16_t)(s ? extend_bits(w, len, s) : 0);
+            }
             pos += (uint32_t)(len + s);
-            k = 1;
+            k += 1;
         } else {
-            const int r = sym >> 4, s = sym & 15;
-            if (s) {
-                k += r;
-                if (k > 63) {
-                    if (kWrite) { *bad = 1; break; }
-                    k = 63;
-                }
-                if (kWrite) blk[natural_order(k)] = (int16_t)extend_bits(w, len, s);
-                pos += (uint32_t)(len + s);
-                k += 1;
-            } else {
-                pos += (uint32_t)len;
-                k = r == 15 ? k + 16 : 64;
-            }
+            pos += (uint32_t)len;
+            k = r == 15 ? k + 16 : 64;
         }
         if (k >= 64) {                      // block complete
             k = 0; ++done; ++ordinal;
@@ -255,7 +251,10 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
             c = b < nluma ? 0 : b - nluma + 1;
             dc = tables + im.dc[c];
             ac = tables + im.ac[c];
-            if (kWrite) blk = block_ptr(im, coef, my, mx, b);
+            if (kWrite) {
+                blk = block_ptr(im, coef, my, mx, b);
+                dcp = dc_slot(im, dcv, my * im.mcus_x + mx, b);
+            }
         }
         if (!kWrite && pos >= next_cp && ci < kCheckpoints) {
             ScanState cur;
