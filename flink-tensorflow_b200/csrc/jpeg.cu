@@ -223,6 +223,7 @@ struct ftf_jpeg_batch {
     std::vector<ImageDesc> images;
     std::vector<Segment> segments;
     std::vector<HuffTable> tables;
+    std::vector<HuffSpec> specs;          // the definitions tables[] were built from, same order
     std::vector<uint16_t> quants;
     size_t scan_bytes = 0, meta_bytes = 0, off_seg = 0, off_tab = 0, off_q = 0;
     int64_t coef_elems = 0, plane_bytes = 0, rgb_bytes = 0, dc_elems = 0;
@@ -302,7 +303,7 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
     FTF_CUDA(cudaSetDevice(b->device), &b->err);
     // the previous load's staging may still be in flight on another stream
     FTF_CUDA(cudaEventSynchronize(b->done), &b->err);
-    b->images.clear(); b->segments.clear(); b->tables.clear(); b->quants.clear();
+    b->images.clear(); b->segments.clear(); b->tables.clear(); b->specs.clear(); b->quants.clear();
     b->decoded = false;
     b->coef_elems = 0; b->plane_bytes = 0; b->rgb_bytes = 0; b->dc_elems = 0; b->max_blocks = 0; b->max_groups = 0;
     std::vector<Parsed>* parsed = new std::vector<Parsed>((size_t)n);
@@ -324,8 +325,12 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
                 if (memcmp(&b->quants[(size_t)k * 64], q, 128) == 0) { found = k; break; }
             if (found < 0) { found = nq; b->quants.insert(b->quants.end(), q, q + 64); }
             im.quant[c] = found;
-            im.dc[c] = pool_index(b->tables, p.dc[p.td[c]]);
-            im.ac[c] = pool_index(b->tables, p.ac[p.ta[c]]);
+            for (int which = 0; which < 2; ++which) {      // decoder tables are built once per distinct definition
+                const HuffSpec& sp = which ? p.ac[p.ta[c]] : p.dc[p.td[c]];
+                const int idx = pool_index(b->specs, sp);
+                if (idx == (int)b->tables.size()) { b->tables.emplace_back(); build_table(sp, &b->tables.back()); }
+                (which ? im.ac : im.dc)[c] = idx;
+            }
             im.coef_off[c] = b->coef_elems;
             b->coef_elems += (int64_t)im.bw[c] * im.bh[c] * 64;
             im.plane_off[c] = b->plane_bytes;

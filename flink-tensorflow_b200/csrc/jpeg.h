@@ -11,6 +11,15 @@
 namespace ftf {
 namespace jpeg {
 
+// A Huffman table as a DHT segment defines it (T.81 B.2.4.2): how many codes of each length, then the values.
+struct HuffSpec {
+    uint8_t counts[17];
+    uint8_t values[256];
+    int32_t nvalues;
+};
+// Decoder form of a (validated) table definition.
+void build_table(const HuffSpec& spec, HuffTable* t);
+
 // What the marker segments of one file say (host side).
 struct Parsed {
     int width = 0, height = 0, ncomp = 0;
@@ -19,7 +28,7 @@ struct Parsed {
     int tq[3] = {0, 0, 0}, td[3] = {0, 0, 0}, ta[3] = {0, 0, 0};
     uint16_t quant[4][64];                 // row-major
     bool quant_present[4] = {false, false, false, false};
-    HuffTable dc[4], ac[4];
+    HuffSpec dc[4], ac[4];                 // as the file defines them; build_table makes the decoder form
     bool dc_present[4] = {false, false, false, false}, ac_present[4] = {false, false, false, false};
     int64_t scan_begin = 0;                // first entropy-coded byte
 };
@@ -34,7 +43,7 @@ void fill_geometry(const Parsed& p, ImageDesc* im);
 int64_t stage_bound(int64_t n, const Parsed& p, const ImageDesc& im);
 
 // Copies the entropy-coded bytes [p.scan_begin, n) of one file to dst with the 0xFF00 byte stuffing removed, one clean
-// stream per restart interval (or one for the whole scan), each 4-byte aligned and followed by >= 8 zero bytes, and
+// stream per restart interval (or one for the whole scan), each 4-byte aligned and followed by >= 16 zero bytes, and
 // appends one Segment per stream (begin = dst_offset + position in dst).  Returns the bytes written.  This is the one
 // pass the host makes over the compressed data; it doubles as the copy into pinned staging memory.
 int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, uint8_t* dst,

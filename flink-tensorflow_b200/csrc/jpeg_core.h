@@ -22,10 +22,11 @@
 namespace ftf {
 namespace jpeg {
 
-constexpr int kLutBits = 9;
+constexpr int kLutBits = 12;
 
 // One Huffman table, decoder form.  lut: the next kLutBits bits of the stream -> (code length << 8 | symbol), 0 when
-// the code is longer than kLutBits; then the canonical-code walk of T.81 F.2.2.3 over maxcode / valoff.
+// the code is longer than kLutBits (rare at 12 bits: a lane that misses stalls its whole warp); then the canonical-code
+// walk of T.81 F.2.2.3 over maxcode / valoff.
 struct HuffTable {
     uint16_t lut[1 << kLutBits];
     int32_t maxcode[18];     // largest code of each length (-1: none); [17] = INT32_MAX ends the walk
@@ -52,7 +53,7 @@ struct ImageDesc {
 constexpr int kChunkBits = 1024;   // the unit of parallel entropy decoding (see decode_chunk)
 
 // One independently decodable stretch of a scan: a restart interval, or the whole scan.  The host stages its bytes with
-// the 0xFF00 byte stuffing removed ("clean" stream), 4-byte aligned and followed by at least 8 zero bytes.
+// the 0xFF00 byte stuffing removed ("clean" stream), 4-byte aligned and followed by at least 16 zero bytes.
 struct Segment {
     int32_t image;
     int32_t first_mcu, n_mcus;
@@ -84,7 +85,8 @@ FTF_HD uint8_t natural_order(int k) {
 #endif
 
 // MSB-first view of a clean stream: 64 bits starting at a 32-bit boundary are kept in a register pair and slide forward
-// one aligned word at a time, so a symbol costs one load per 32 bits consumed.
+// one aligned word at a time.  The word after them is fetched every call whether or not it is needed yet: lanes of a
+// warp cross word boundaries at different symbols, and a fetch inside a branch would serialise them.
 struct BitWindow {
     const uint32_t* words;
     uint64_t buf;
@@ -97,10 +99,10 @@ struct BitWindow {
     // the 32 bits that start at pos (pos never goes backwards and advances by less than 32 between calls)
     FTF_HD uint32_t at(uint32_t pos) {
         if (pos >= nbits) return 0;
-        if (pos - base >= 32) {
-            base += 32;
-            buf = (buf << 32) | FTF_BE32(FTF_LDG(words + (base >> 5) + 1));
-        }
+        const uint32_t next = FTF_BE32(FTF_LDG(words + (base >> 5) + 2));     // within the 16 zero bytes after the stream
+        const bool adv = pos - base >= 32;
+        buf = adv ? (buf << 32) | next : buf;
+        base = adv ? base + 32 : base;
         return (uint32_t)((buf << (pos - base)) >> 32);
     }
 };

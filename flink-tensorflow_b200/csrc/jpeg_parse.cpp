@@ -19,34 +19,42 @@ int bad(std::string* err, int code, const char* msg) {
     return code;
 }
 
-// counts[1..16], values -> decoder form
-int build_table(const uint8_t* counts, const uint8_t* values, int nvalues, HuffTable* t) {
+// a prefix code needs no more codes of a length than the shorter codes leave room for
+bool valid_spec(const HuffSpec& sp) {
+    int code = 0;
+    for (int l = 1; l <= 16; ++l) {
+        code += sp.counts[l];
+        if (code > (1 << l)) return false;
+        code <<= 1;
+    }
+    return true;
+}
+
+}  // namespace
+
+void build_table(const HuffSpec& sp, HuffTable* t) {
     memset(t, 0, sizeof(*t));
-    memcpy(t->vals, values, (size_t)nvalues);
+    memcpy(t->vals, sp.values, (size_t)sp.nvalues);
     int code = 0, k = 0;
     for (int l = 1; l <= 16; ++l) {
-        const int cnt = counts[l];
+        const int cnt = sp.counts[l];
         t->valoff[l] = k - code;
         if (l <= kLutBits) {
             for (int i = 0; i < cnt; ++i) {
-                const int first = (code + i) << (kLutBits - l);
-                if (first + (1 << (kLutBits - l)) > (1 << kLutBits)) return 1;
-                for (int j = 0; j < (1 << (kLutBits - l)); ++j) t->lut[first + j] = (uint16_t)((l << 8) | values[k + i]);
+                const int first = (code + i) << (kLutBits - l), span = 1 << (kLutBits - l);
+                const uint16_t e = (uint16_t)((l << 8) | sp.values[k + i]);
+                for (int j = 0; j < span; ++j) t->lut[first + j] = e;
             }
         }
         code += cnt;
         k += cnt;
         t->maxcode[l] = cnt ? code - 1 : -1;
-        if (code > (1 << l)) return 1;                 // more codes of this length than the prefix leaves room for
         code <<= 1;
     }
     t->maxcode[0] = -1;
     t->maxcode[17] = 0x7fffffff;
     t->valoff[0] = 0;
-    return 0;
 }
-
-}  // namespace
 
 int parse_headers(const uint8_t* d, int64_t n, Parsed* out, std::string* err) {
     if (!d || n < 4 || d[0] != 0xFF || d[1] != 0xD8) return bad(err, FTF_INVALID_ARGUMENT, "not a JPEG file (no SOI marker)");
@@ -86,8 +94,13 @@ int parse_headers(const uint8_t* d, int64_t n, Parsed* out, std::string* err) {
                 int cnt = 0;
                 for (int i = 1; i <= 16; ++i) cnt += q[i];
                 if (tc > 1 || th > 3 || cnt > 256 || rem < 17 + cnt) return bad(err, FTF_INVALID_ARGUMENT, "bad Huffman table segment");
-                HuffTable* t = tc ? &out->ac[th] : &out->dc[th];
-                if (build_table(q, q + 17, cnt, t)) return bad(err, FTF_INVALID_ARGUMENT, "Huffman table is not a prefix code");
+                HuffSpec* t = tc ? &out->ac[th] : &out->dc[th];
+                memset(t, 0, sizeof(*t));
+                memcpy(t->counts, q, 17);
+                t->counts[0] = 0;
+                memcpy(t->values, q + 17, (size_t)cnt);
+                t->nvalues = cnt;
+                if (!valid_spec(*t)) return bad(err, FTF_INVALID_ARGUMENT, "Huffman table is not a prefix code");
                 (tc ? out->ac_present : out->dc_present)[th] = true;
                 q += 17 + cnt; rem -= 17 + cnt;
             }
@@ -165,7 +178,7 @@ static int segment_count(const Parsed& p, const ImageDesc& im) {
 }
 
 int64_t stage_bound(int64_t n, const Parsed& p, const ImageDesc& im) {
-    return (n - p.scan_begin) + 16ll * segment_count(p, im) + 16;
+    return (n - p.scan_begin) + 24ll * segment_count(p, im) + 16;
 }
 
 int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, uint8_t* dst,
@@ -198,7 +211,7 @@ int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc
         s.nbits = (w - w0) * 8;
         s.n_chunks = (int32_t)((s.nbits + kChunkBits - 1) / kChunkBits);
         if (s.n_chunks < 1) s.n_chunks = 1;
-        const int64_t padded = (w + 3) / 4 * 4 + 8;
+        const int64_t padded = (w + 3) / 4 * 4 + 16;
         memset(dst + w, 0, (size_t)(padded - w));
         w = padded;
         out->push_back(s);

@@ -25,8 +25,8 @@ extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, i
     for (int c = 0; c < p->ncomp; ++c) {
         im.quant[c] = c;
         quant.insert(quant.end(), p->quant[p->tq[c]], p->quant[p->tq[c]] + 64);
-        im.dc[c] = (int)tables.size(); tables.push_back(p->dc[p->td[c]]);
-        im.ac[c] = (int)tables.size(); tables.push_back(p->ac[p->ta[c]]);
+        im.dc[c] = (int)tables.size(); tables.emplace_back(); build_table(p->dc[p->td[c]], &tables.back());
+        im.ac[c] = (int)tables.size(); tables.emplace_back(); build_table(p->ac[p->ta[c]], &tables.back());
         im.coef_off[c] = coef_elems; coef_elems += (int64_t)im.bw[c] * im.bh[c] * 64;
         im.plane_off[c] = plane_bytes; plane_bytes += (int64_t)im.bw[c] * im.bh[c] * 64;
         im.dc_off[c] = im.coef_off[c] / 64;
