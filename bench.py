@@ -270,7 +270,21 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
     cfg = ftf.default_config(device=device, max_batch=INC["batch"], max_delay_us=2000, top_k=INC["top_k"], out_h=299, out_w=299,
                              mean=128.0, scale=128.0, num_classes=INC["classes"], seed=INC["seed"])
     n_buf = 4 * INC["batch"]                                   # records stay untouched until polled: a ring of pinned payloads
-    if kind == "normalize_label":
+    if kind == "jpeg_label":
+        # BASELINE config 5 with the records the reference's source emits: image FILES (ImageInputFormat.scala:63-80 reads the
+        # file, ImageFileTensor wraps its bytes), here 640x480 baseline JPEGs as 0-D STRING tensors in pinned memory
+        r = ftf.Runner("builtin:normalize_label", None, None, cfg)
+        blobs = [ftf.bytes_to_tensor(f).buffer for f in jpeg_files(np, 3, JPEG["distinct"])]
+        stride = (max(b.nbytes for b in blobs) + 255) // 256 * 256
+        p, ring = pinned_array(lib, np, n_buf * stride, np.uint8)
+        recs = []
+        for i in range(n_buf):
+            b = blobs[i % len(blobs)]
+            ring[i * stride: i * stride + b.nbytes] = b
+            recs.append(FtfTensor(ftf.DataType.STRING, 0, None, ring.ctypes.data + i * stride, b.nbytes))
+        rec_bytes = int(sum(b.nbytes for b in blobs) / len(blobs))
+        pipeline = "640x480 JPEG file -> Huffman/IDCT/colour -> resize+normalise (bf16) -> Inception-v3 -> softmax/top-5"
+    elif kind == "normalize_label":
         r = ftf.Runner("builtin:normalize_label", None, None, cfg)
         rec_bytes = 480 * 640 * 3
         p, ring = pinned_array(lib, np, n_buf * rec_bytes, np.uint8)
@@ -285,7 +299,8 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
         ring = ring32.view(np.uint8)
         dims = (C.c_int64 * 3)(299, 299, 3)
         dtype, pipeline = ftf.DataType.FLOAT, "fp32 299x299x3 -> bf16 -> Inception-v3 -> softmax/top-5"
-    recs = [FtfTensor(dtype, 3, dims, ring.ctypes.data + i * rec_bytes, rec_bytes) for i in range(n_buf)]
+    if kind != "jpeg_label":
+        recs = [FtfTensor(dtype, 3, dims, ring.ctypes.data + i * rec_bytes, rec_bytes) for i in range(n_buf)]
     wire_p = None
     if wire:
         # the same payloads as Flink wire images in a second pinned ring: 0x01 | BE header | payload (37 header bytes here)
@@ -357,7 +372,8 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
     lib.ftf_host_free(p)
     if wire_p:
         lib.ftf_host_free(wire_p)
-    return {"records_per_s": n_records / dt, "offered_records_per_s": offered_rate, "record_format": "TensorValue wire image, decoded in place" if wire else "raw tensor", "records": n_records, "latency_us_p50": st["queue_latency_us_p50"],
+    return {"records_per_s": n_records / dt, "offered_records_per_s": offered_rate,
+            "record_format": "TensorValue wire image, decoded in place" if wire else ("JPEG file as a 0-D STRING tensor" if kind == "jpeg_label" else "raw tensor"), "records": n_records, "latency_us_p50": st["queue_latency_us_p50"],
             "latency_us_p99": st["queue_latency_us_p99"], "max_batch": INC["batch"], "max_delay_us": 2000,
             "h2d_bytes_per_record": rec_bytes, "d2h_bytes_per_record": 2 * INC["top_k"] * 4, "pipeline": pipeline, "seconds": dt,
             "api": "ftf_submit/ftf_poll, pinned record payloads", "launches": int(st["kernel_launches"] - r2["kernel_launches"]),
@@ -558,6 +574,10 @@ def run_ours(args):
            "ms_per_step": e2e_ms, "steps": e2e_steps, "gpu_launches": int(e2e_launches),
            "api": "ftf_run (C ABI) with pinned host buffers, chunked H2D/kernel/D2H pipeline"}
     if wl == "jpeg":
+        # the per-record path with files as records (what the reference's source emits), next to the blocking call
+        sres = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * (100 if args.quick else 400), kind="jpeg_label", sync=barrier)
+        barrier()
+        extra["streaming_files"] = sres
         e2e["api"] = ("ftf_run (C ABI) on builtin:normalize_label with a STRING tensor of 256 JPEG files in host memory: header parse, "
                       "upload of the entropy-coded bytes, J1-J3, resize/normalise, Inception-v3, top-5 read back")
     if wl == "inception":

@@ -21,6 +21,7 @@
 #include "jpeg.h"
 #include "runner.h"
 #include <string.h>
+#include <algorithm>
 
 using namespace ftf;
 using namespace ftf::jpeg;
@@ -228,7 +229,8 @@ struct ftf_jpeg_batch {
     size_t scan_bytes = 0, meta_bytes = 0, off_seg = 0, off_tab = 0, off_q = 0;
     int64_t coef_elems = 0, plane_bytes = 0, rgb_bytes = 0, dc_elems = 0;
     int max_blocks = 0, max_groups = 0, max_chunks = 1;
-    bool decoded = false, attr_set = false;
+    bool decoded = false, attr_set = false, committed = false;
+    Parsed parsed;                        // scratch of batch_add
 };
 
 namespace {
@@ -295,92 +297,115 @@ extern "C" void ftf_jpeg_batch_destroy(ftf_jpeg_batch* b) {
 
 extern "C" const char* ftf_jpeg_batch_error(const ftf_jpeg_batch* b) { return b ? b->err.c_str() : thread_error(); }
 
+namespace ftf {
+namespace jpeg {
+
+int batch_begin(ftf_jpeg_batch* b) {
+    if (!b) return FTF_INVALID_ARGUMENT;
+    FTF_CUDA(cudaSetDevice(b->device), &b->err);
+    // the previous batch's uploads and kernels may still be reading the staging buffers
+    FTF_CUDA(cudaEventSynchronize(b->done), &b->err);
+    b->images.clear(); b->segments.clear(); b->tables.clear(); b->specs.clear(); b->quants.clear();
+    b->decoded = false; b->committed = false;
+    b->coef_elems = 0; b->plane_bytes = 0; b->rgb_bytes = 0; b->dc_elems = 0; b->max_blocks = 0; b->max_groups = 0;
+    b->max_chunks = 1; b->scan_bytes = 0;
+    return FTF_OK;
+}
+
+int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* height, int32_t* width, int64_t* rgb_offset) {
+    Parsed& p = b->parsed;
+    p = Parsed();
+    std::string perr;
+    const int i = (int)b->images.size();
+    int rc = parse_headers(file, len, &p, &perr);
+    if (rc) return bfail(b, rc, "image " + std::to_string(i) + ": " + perr);
+    ImageDesc im;
+    fill_geometry(p, &im);
+    // room in the pinned staging buffer (grown with its contents kept; sized generously so that this is rare)
+    const size_t need = b->scan_bytes + (size_t)stage_bound(len, p, im);
+    if (need > b->h_scan.cap) {
+        Buf bigger;
+        bigger.host = true;
+        if ((rc = bigger.ensure(std::max<size_t>(need * 2, 8u << 20), &b->err))) return rc;
+        if (b->scan_bytes) memcpy(bigger.p, b->h_scan.p, b->scan_bytes);
+        b->h_scan.free_now();
+        b->h_scan = bigger;
+    }
+    for (int c = 0; c < p.ncomp; ++c) {
+        // tables are pooled per batch: files from one encoder share them, so look at the last few entries
+        const uint16_t* q = p.quant[p.tq[c]];
+        int found = -1;
+        const int nq = (int)(b->quants.size() / 64);
+        for (int k = nq - 1; k >= 0 && k >= nq - 8; --k)
+            if (memcmp(&b->quants[(size_t)k * 64], q, 128) == 0) { found = k; break; }
+        if (found < 0) { found = nq; b->quants.insert(b->quants.end(), q, q + 64); }
+        im.quant[c] = found;
+        for (int which = 0; which < 2; ++which) {      // decoder tables are built once per distinct definition
+            const HuffSpec& sp = which ? p.ac[p.ta[c]] : p.dc[p.td[c]];
+            const int idx = pool_index(b->specs, sp);
+            if (idx == (int)b->tables.size()) { b->tables.emplace_back(); build_table(sp, &b->tables.back()); }
+            (which ? im.ac : im.dc)[c] = idx;
+        }
+        im.coef_off[c] = b->coef_elems;
+        b->coef_elems += (int64_t)im.bw[c] * im.bh[c] * 64;
+        im.plane_off[c] = b->plane_bytes;
+        b->plane_bytes += (int64_t)im.bw[c] * im.bh[c] * 64;
+        im.dc_off[c] = b->dc_elems;
+        b->dc_elems += (int64_t)im.bw[c] * im.bh[c];
+    }
+    im.rgb_off = b->rgb_bytes;
+    if (rgb_offset) *rgb_offset = im.rgb_off;
+    if (height) *height = im.height;
+    if (width) *width = im.width;
+    b->rgb_bytes += align_up((size_t)im.width * im.height * 3, 16);
+    if (im.n_blocks > b->max_blocks) b->max_blocks = im.n_blocks;
+    const int groups = ((im.width + 7) >> 3) * im.height;
+    if (groups > b->max_groups) b->max_groups = groups;
+    // the one host pass over the compressed bytes: unstuff + split at restart markers + copy into pinned memory
+    const size_t first_seg = b->segments.size();
+    b->scan_bytes += (size_t)stage_scan(file, len, p, im, i, (uint8_t*)b->h_scan.p + b->scan_bytes, (int64_t)b->scan_bytes, &b->segments);
+    for (size_t k = first_seg; k < b->segments.size(); ++k)
+        if (b->segments[k].n_chunks > b->max_chunks) b->max_chunks = b->segments[k].n_chunks;
+    b->images.push_back(im);
+    return FTF_OK;
+}
+
+int batch_commit(ftf_jpeg_batch* b, cudaStream_t st) {
+    const size_t n = b->images.size();
+    if (n == 0) { b->committed = true; return FTF_OK; }
+    int rc;
+    b->off_seg = align_up(n * sizeof(ImageDesc), 16);
+    b->off_tab = align_up(b->off_seg + b->segments.size() * sizeof(Segment), 16);
+    b->off_q = align_up(b->off_tab + b->tables.size() * sizeof(HuffTable), 16);
+    b->meta_bytes = b->off_q + b->quants.size() * sizeof(uint16_t);
+    if ((rc = b->h_meta.ensure(b->meta_bytes, &b->err)) || (rc = b->d_scan.ensure(b->scan_bytes + 16, &b->err)) ||
+        (rc = b->d_meta.ensure(b->meta_bytes, &b->err)) || (rc = b->d_coef.ensure((size_t)b->coef_elems * 2, &b->err)) ||
+        (rc = b->d_dc.ensure((size_t)b->dc_elems * 2, &b->err)) || (rc = b->d_planes.ensure((size_t)b->plane_bytes, &b->err)) ||
+        (rc = b->d_status.ensure(n * 4, &b->err)) || (rc = b->h_status.ensure(n * 4, &b->err)))
+        return rc;
+    uint8_t* m = (uint8_t*)b->h_meta.p;
+    memcpy(m, b->images.data(), n * sizeof(ImageDesc));
+    memcpy(m + b->off_seg, b->segments.data(), b->segments.size() * sizeof(Segment));
+    memcpy(m + b->off_tab, b->tables.data(), b->tables.size() * sizeof(HuffTable));
+    memcpy(m + b->off_q, b->quants.data(), b->quants.size() * sizeof(uint16_t));
+    FTF_CUDA(cudaMemcpyAsync(b->d_scan.p, b->h_scan.p, b->scan_bytes, cudaMemcpyHostToDevice, st), &b->err);
+    FTF_CUDA(cudaMemcpyAsync(b->d_meta.p, b->h_meta.p, b->meta_bytes, cudaMemcpyHostToDevice, st), &b->err);
+    FTF_CUDA(cudaEventRecord(b->done, st), &b->err);
+    b->committed = true;
+    return FTF_OK;
+}
+
+}  // namespace jpeg
+}  // namespace ftf
+
 extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* const* files, const int64_t* lens,
                                    int64_t* rgb_offsets, int32_t* heights, int32_t* widths, void* stream) {
     if (!b) return FTF_INVALID_ARGUMENT;
     if (n < 0 || (n > 0 && (!files || !lens))) return bfail(b, FTF_INVALID_ARGUMENT, "ftf_jpeg_batch_load: null argument");
-    cudaStream_t st = (cudaStream_t)stream;
-    FTF_CUDA(cudaSetDevice(b->device), &b->err);
-    // the previous load's staging may still be in flight on another stream
-    FTF_CUDA(cudaEventSynchronize(b->done), &b->err);
-    b->images.clear(); b->segments.clear(); b->tables.clear(); b->specs.clear(); b->quants.clear();
-    b->decoded = false;
-    b->coef_elems = 0; b->plane_bytes = 0; b->rgb_bytes = 0; b->dc_elems = 0; b->max_blocks = 0; b->max_groups = 0;
-    std::vector<Parsed>* parsed = new std::vector<Parsed>((size_t)n);
-    size_t scan_total = 0;
-    int rc = FTF_OK;
-    for (int i = 0; i < n && rc == FTF_OK; ++i) {
-        Parsed& p = (*parsed)[i];
-        std::string perr;
-        rc = parse_headers(files[i], lens[i], &p, &perr);
-        if (rc) { bfail(b, rc, "image " + std::to_string(i) + ": " + perr); break; }
-        ImageDesc im;
-        fill_geometry(p, &im);
-        for (int c = 0; c < p.ncomp; ++c) {
-            // tables are pooled per batch: files from one encoder share them, so look at the last few entries
-            const uint16_t* q = p.quant[p.tq[c]];
-            int found = -1;
-            const int nq = (int)(b->quants.size() / 64);
-            for (int k = nq - 1; k >= 0 && k >= nq - 8; --k)
-                if (memcmp(&b->quants[(size_t)k * 64], q, 128) == 0) { found = k; break; }
-            if (found < 0) { found = nq; b->quants.insert(b->quants.end(), q, q + 64); }
-            im.quant[c] = found;
-            for (int which = 0; which < 2; ++which) {      // decoder tables are built once per distinct definition
-                const HuffSpec& sp = which ? p.ac[p.ta[c]] : p.dc[p.td[c]];
-                const int idx = pool_index(b->specs, sp);
-                if (idx == (int)b->tables.size()) { b->tables.emplace_back(); build_table(sp, &b->tables.back()); }
-                (which ? im.ac : im.dc)[c] = idx;
-            }
-            im.coef_off[c] = b->coef_elems;
-            b->coef_elems += (int64_t)im.bw[c] * im.bh[c] * 64;
-            im.plane_off[c] = b->plane_bytes;
-            b->plane_bytes += (int64_t)im.bw[c] * im.bh[c] * 64;
-            im.dc_off[c] = b->dc_elems;
-            b->dc_elems += (int64_t)im.bw[c] * im.bh[c];
-        }
-        im.rgb_off = b->rgb_bytes;
-        if (rgb_offsets) rgb_offsets[i] = im.rgb_off;
-        if (heights) heights[i] = im.height;
-        if (widths) widths[i] = im.width;
-        b->rgb_bytes += align_up((size_t)im.width * im.height * 3, 16);
-        if (im.n_blocks > b->max_blocks) b->max_blocks = im.n_blocks;
-        const int groups = ((im.width + 7) >> 3) * im.height;
-        if (groups > b->max_groups) b->max_groups = groups;
-        scan_total += (size_t)stage_bound(lens[i], p, im);
-        b->images.push_back(im);
-    }
-    if (rc == FTF_OK && n > 0) {
-        if ((rc = b->h_scan.ensure(scan_total + 16, &b->err)) == 0) {
-            int64_t w = 0;                              // the one host pass over the compressed bytes: unstuff + split + stage
-            for (int i = 0; i < n; ++i)
-                w += stage_scan(files[i], lens[i], (*parsed)[i], b->images[i], i, (uint8_t*)b->h_scan.p + w, w, &b->segments);
-            scan_total = (size_t)w;
-            b->max_chunks = 1;
-            for (const Segment& sgm : b->segments) if (sgm.n_chunks > b->max_chunks) b->max_chunks = sgm.n_chunks;
-        }
-        b->scan_bytes = scan_total;
-        b->off_seg = align_up(b->images.size() * sizeof(ImageDesc), 16);
-        b->off_tab = align_up(b->off_seg + b->segments.size() * sizeof(Segment), 16);
-        b->off_q = align_up(b->off_tab + b->tables.size() * sizeof(HuffTable), 16);
-        b->meta_bytes = b->off_q + b->quants.size() * sizeof(uint16_t);
-        if (rc == 0 && (rc = b->h_meta.ensure(b->meta_bytes, &b->err)) == 0 &&
-            (rc = b->d_scan.ensure(scan_total + 16, &b->err)) == 0 && (rc = b->d_meta.ensure(b->meta_bytes, &b->err)) == 0 &&
-            (rc = b->d_coef.ensure((size_t)b->coef_elems * 2, &b->err)) == 0 &&
-            (rc = b->d_dc.ensure((size_t)b->dc_elems * 2, &b->err)) == 0 &&
-            (rc = b->d_planes.ensure((size_t)b->plane_bytes, &b->err)) == 0 &&
-            (rc = b->d_status.ensure((size_t)n * 4, &b->err)) == 0 && (rc = b->h_status.ensure((size_t)n * 4, &b->err)) == 0) {
-            uint8_t* m = (uint8_t*)b->h_meta.p;
-            memcpy(m, b->images.data(), b->images.size() * sizeof(ImageDesc));
-            memcpy(m + b->off_seg, b->segments.data(), b->segments.size() * sizeof(Segment));
-            memcpy(m + b->off_tab, b->tables.data(), b->tables.size() * sizeof(HuffTable));
-            memcpy(m + b->off_q, b->quants.data(), b->quants.size() * sizeof(uint16_t));
-            cudaError_t e = cudaMemcpyAsync(b->d_scan.p, b->h_scan.p, scan_total, cudaMemcpyHostToDevice, st);
-            if (e == cudaSuccess) e = cudaMemcpyAsync(b->d_meta.p, b->h_meta.p, b->meta_bytes, cudaMemcpyHostToDevice, st);
-            if (e == cudaSuccess) e = cudaEventRecord(b->done, st);
-            if (e != cudaSuccess) rc = cuda_fail(e, "ftf_jpeg_batch_load upload", &b->err);
-        }
-    }
-    delete parsed;
+    int rc = batch_begin(b);
+    for (int i = 0; i < n && rc == FTF_OK; ++i)
+        rc = batch_add(b, files[i], lens[i], heights ? heights + i : nullptr, widths ? widths + i : nullptr, rgb_offsets ? rgb_offsets + i : nullptr);
+    if (rc == FTF_OK) rc = batch_commit(b, (cudaStream_t)stream);
     if (rc) { b->images.clear(); b->segments.clear(); }
     return rc;
 }
@@ -392,6 +417,7 @@ extern "C" int32_t ftf_jpeg_batch_segments(const ftf_jpeg_batch* b) { return b ?
 extern "C" int ftf_jpeg_batch_decode_dev(ftf_jpeg_batch* b, uint8_t* rgb_out, int64_t cap, void* stream) {
     if (!b) return FTF_INVALID_ARGUMENT;
     if (b->images.empty()) return FTF_OK;
+    if (!b->committed) return bfail(b, FTF_FAILED_PRECONDITION, "ftf_jpeg_batch_decode_dev: the batch has not been uploaded");
     if (!rgb_out || cap < b->rgb_bytes) return bfail(b, FTF_INVALID_ARGUMENT, "ftf_jpeg_batch_decode_dev: output buffer too small");
     cudaStream_t st = (cudaStream_t)stream;
     FTF_CUDA(cudaSetDevice(b->device), &b->err);

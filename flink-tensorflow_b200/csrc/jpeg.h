@@ -51,3 +51,16 @@ int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc
 
 }  // namespace jpeg
 }  // namespace ftf
+
+// The pieces of ftf_jpeg_batch_load, for callers that receive their files one at a time (ftf_submit): a file is parsed
+// and staged when it arrives, the batch is uploaded when it closes.  batch_add copies what it needs: the caller's buffer
+// is free again when it returns.
+struct ftf_jpeg_batch;
+struct CUstream_st;
+namespace ftf {
+namespace jpeg {
+int batch_begin(ftf_jpeg_batch* b);
+int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* height, int32_t* width, int64_t* rgb_offset);
+int batch_commit(ftf_jpeg_batch* b, CUstream_st* stream);
+}  // namespace jpeg
+}  // namespace ftf

@@ -22,11 +22,11 @@
 namespace ftf {
 namespace jpeg {
 
-constexpr int kLutBits = 12;
+constexpr int kLutBits = 9;
 
 // One Huffman table, decoder form.  lut: the next kLutBits bits of the stream -> (code length << 8 | symbol), 0 when
-// the code is longer than kLutBits (rare at 12 bits: a lane that misses stalls its whole warp); then the canonical-code
-// walk of T.81 F.2.2.3 over maxcode / valoff.
+// the code is longer than kLutBits; then the canonical-code walk of T.81 F.2.2.3 over maxcode / valoff.  (Measured: 12-bit
+// tables, 8 KB each, lose more to L1 misses than they save on the walk; 9 bits keep all of a batch's tables L1-resident.)
 struct HuffTable {
     uint16_t lut[1 << kLutBits];
     int32_t maxcode[18];     // largest code of each length (-1: none); [17] = INT32_MAX ends the walk
@@ -85,8 +85,7 @@ FTF_HD uint8_t natural_order(int k) {
 #endif
 
 // MSB-first view of a clean stream: 64 bits starting at a 32-bit boundary are kept in a register pair and slide forward
-// one aligned word at a time.  The word after them is fetched every call whether or not it is needed yet: lanes of a
-// warp cross word boundaries at different symbols, and a fetch inside a branch would serialise them.
+// one aligned word at a time, so a symbol costs one load per 32 bits consumed.
 struct BitWindow {
     const uint32_t* words;
     uint64_t buf;
@@ -99,10 +98,10 @@ struct BitWindow {
     // the 32 bits that start at pos (pos never goes backwards and advances by less than 32 between calls)
     FTF_HD uint32_t at(uint32_t pos) {
         if (pos >= nbits) return 0;
-        const uint32_t next = FTF_BE32(FTF_LDG(words + (base >> 5) + 2));     // within the 16 zero bytes after the stream
-        const bool adv = pos - base >= 32;
-        buf = adv ? (buf << 32) | next : buf;
-        base = adv ? base + 32 : base;
+        if (pos - base >= 32) {
+            base += 32;
+            buf = (buf << 32) | FTF_BE32(FTF_LDG(words + (base >> 5) + 1));
+        }
         return (uint32_t)((buf << (pos - base)) >> 32);
     }
 };

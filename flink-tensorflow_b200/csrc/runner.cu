@@ -7,6 +7,7 @@
 // Records travel  caller buffer -> pinned slot -> HBM -> kernels -> HBM -> pinned result.  Three slots, one
 // CUDA stream each, so the upload of chunk c+1 overlaps the kernels of chunk c and the download of c-1.
 #include "runner.h"
+#include "jpeg.h"
 #include "inception.h"
 #include "conv_tc.h"
 #include "pools.h"
@@ -244,14 +245,29 @@ int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h
     return FTF_OK;
 }
 
-// Decodes n JPEG files into s.d_in on the slot's stream (J1-J3, csrc/jpeg.cu) and notes their geometry in the slot.
-int decode_files(ftf_runner* r, Slot& s, int n, const uint8_t* const* files, const int64_t* lens) {
+// JPEG records of a slot (J1-J3, csrc/jpeg.cu): files_begin opens the slot's batch, files_add parses one file and stages
+// its entropy-coded bytes in pinned memory (the caller's buffer is free again afterwards), files_launch uploads the batch and
+// decodes it into s.d_in on the slot's stream.
+int files_begin(ftf_runner* r, Slot& s) {
     int rc;
     s.jpeg_n = 0;
     if (!s.jpeg && (rc = ftf_jpeg_batch_create(r->device, &s.jpeg))) return fail(r, rc, thread_error());
-    s.joff.resize((size_t)n); s.jh.resize((size_t)n); s.jw.resize((size_t)n);
-    if ((rc = ftf_jpeg_batch_load(s.jpeg, n, files, lens, s.joff.data(), s.jh.data(), s.jw.data(), s.stream)))
-        return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
+    if ((rc = jpeg::batch_begin(s.jpeg))) return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
+    s.joff.clear(); s.jh.clear(); s.jw.clear();
+    return FTF_OK;
+}
+int files_add(ftf_runner* r, Slot& s, const uint8_t* file, int64_t len) {
+    int32_t h = 0, w = 0;
+    int64_t off = 0;
+    const int rc = jpeg::batch_add(s.jpeg, file, len, &h, &w, &off);
+    if (rc) return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
+    s.joff.push_back(off); s.jh.push_back(h); s.jw.push_back(w);
+    return FTF_OK;
+}
+int files_launch(ftf_runner* r, Slot& s) {
+    int rc;
+    const int n = (int)s.jh.size();
+    if ((rc = jpeg::batch_commit(s.jpeg, s.stream))) return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
     const int64_t bytes = ftf_jpeg_batch_rgb_bytes(s.jpeg);
     if ((rc = s.d_in.ensure((size_t)bytes, &r->err))) return rc;
     const uint64_t before = launches_so_far();
@@ -263,6 +279,12 @@ int decode_files(ftf_runner* r, Slot& s, int n, const uint8_t* const* files, con
         if (s.jh[i] != s.jh[0] || s.jw[i] != s.jw[0] || s.joff[i] != (int64_t)i * s.jh[0] * s.jw[0] * 3) s.jpeg_uniform = false;
     s.jpeg_n = n;
     return FTF_OK;
+}
+int decode_files(ftf_runner* r, Slot& s, int n, const uint8_t* const* files, const int64_t* lens) {
+    int rc = files_begin(r, s);
+    for (int i = 0; i < n && !rc; ++i) rc = files_add(r, s, files[i], lens[i]);
+    if (!rc) rc = files_launch(r, s);
+    return rc;
 }
 
 // A finished slot whose input was JPEG files: did the device find a corrupt entropy-coded segment?
@@ -319,10 +341,7 @@ int launch_open(ftf_runner* r) {
     std::vector<void*> dst(r->outs.size());
     for (size_t j = 0; j < dst.size(); ++j) dst[j] = s.h_out[j].p;
     if (s.files_n > 0) {
-        std::vector<const uint8_t*> fp((size_t)s.n);
-        std::vector<int64_t> fl((size_t)s.n);
-        for (int64_t i = 0; i < s.n; ++i) { fp[i] = s.files[i].data(); fl[i] = (int64_t)s.files[i].size(); }
-        if ((rc = decode_files(r, s, (int)s.n, fp.data(), fl.data()))) return rc;
+        if ((rc = files_launch(r, s))) return rc;
         s.files_n = 0;
     } else s.jpeg_n = 0;
     rc = enqueue(r, s, s.n, s.h_in.p, dst.data(), /*uploaded=*/true);
@@ -649,14 +668,12 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
             return fail(r, FTF_INVALID_ARGUMENT, "a record is one FLOAT value");
         bytes = 4;
     } else if (rec->dtype == FTF_STRING && r->kind != Kind::kLabel) {
-        // one JPEG file per record (ImageFileTensor).  Its header is checked now, so a malformed or unsupported file is
-        // refused here and never joins a batch; its entropy-coded bytes are decoded on the device when the batch closes.
+        // one JPEG file per record (ImageFileTensor).  Its header is read and its entropy-coded bytes are staged now (a
+        // malformed or unsupported file is refused here and joins no batch); the device decodes when the batch closes.
         const int64_t cnt = rec->rank == 0 ? 1 : (rec->rank == 1 ? rec->dims[0] : -1);
         if (cnt != 1) return fail(r, FTF_INVALID_ARGUMENT, "a record is one JPEG file (STRING scalar or [1])");
         if (string_tensor_item((const uint8_t*)rec->data, rec->nbytes, 1, 0, &file, &file_len) != FTF_OK)
             return fail(r, FTF_INVALID_ARGUMENT, "malformed STRING tensor");
-        int32_t fh, fw, fc;
-        if ((rc = ftf_jpeg_info(file, file_len, &fh, &fw, &fc))) return fail(r, rc, thread_error());
         if (r->outs.empty() || r->in_rec_bytes != 0) { if ((rc = fix_geometry(r, *rec, true))) return rc; }
         bytes = 0;
     } else {
@@ -693,8 +710,8 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
     if (s.n > 0 && (file != nullptr) != (s.files_n > 0))
         return fail(r, FTF_INVALID_ARGUMENT, "records of one micro-batch must share one format (raw RGB or JPEG files)");
     if (file) {
-        if (s.files.size() <= (size_t)s.n) s.files.resize((size_t)s.n + 1);
-        s.files[(size_t)s.n].assign(file, file + file_len);
+        if (s.n == 0 && (rc = files_begin(r, s))) return rc;
+        if ((rc = files_add(r, s, file, file_len))) return rc;      // header trouble: the record joins no batch
         s.files_n += 1;
         s.tags.push_back(tag);
         s.t_submit.push_back(std::chrono::steady_clock::now());

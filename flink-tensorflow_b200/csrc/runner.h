@@ -44,10 +44,9 @@ struct Slot {
     std::vector<uint64_t> tags;
     std::vector<std::chrono::steady_clock::time_point> t_submit;
     int64_t emitted = 0;
-    // records that arrive as JPEG files (the reference's ImageFileTensor): decoder state of this slot, the file bytes of
-    // the open micro-batch, and the geometry of the decoded images sitting in d_in (jpeg_n > 0)
+    // records that arrive as JPEG files (the reference's ImageFileTensor): decoder state of this slot (it stages the
+    // files of the open micro-batch as they arrive), and the geometry of the decoded images sitting in d_in (jpeg_n > 0)
     ftf_jpeg_batch* jpeg = nullptr;
-    std::vector<std::vector<uint8_t>> files;
     int64_t files_n = 0;               // how many records of the open micro-batch are files
     int64_t jpeg_n = 0;
     bool jpeg_uniform = true;
