@@ -317,6 +317,8 @@ int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* heig
     p = Parsed();
     std::string perr;
     const int i = (int)b->images.size();
+    if (len > (int64_t)1 << 28)            // bit positions inside a segment are 32-bit
+        return bfail(b, FTF_UNIMPLEMENTED, "image " + std::to_string(i) + ": DecodeJpeg: files larger than 256 MiB are not supported");
     int rc = parse_headers(file, len, &p, &perr);
     if (rc) return bfail(b, rc, "image " + std::to_string(i) + ": " + perr);
     ImageDesc im;

@@ -115,3 +115,35 @@ def test_corrupt_entropy_data_is_reported_by_the_emulated_kernel(emu, cases):
     broken = data[:start] + b"\xfe" * 64 + data[start + 64:]
     rc, _, _ = emu(broken, want.shape)
     assert rc in (0, 3)          # either decodes as garbage or trips the invalid-code check; must not crash
+
+
+def test_damaged_files_never_hang_or_crash_the_kernel_functions(emu, cases, ftf):
+    """Random damage to headers and entropy-coded bytes: the host reader refuses or accepts, and whatever it accepts the
+    (emulated) kernels decode to completion -- every loop of decode_chunk advances, the correction rounds are bounded by
+    the number of chunks."""
+    from flink_tensorflow_b200 import device
+    rng = np.random.default_rng(99)
+    picks = ["420_opt", "444_rst_blocks", "422_q30", "gray_rst", "420_40x41_q75"]
+    decoded = refused = 0
+    for name in picks:
+        data, want = cases[name]
+        sos = data.index(b"\xff\xda")
+        for trial in range(40):
+            b = bytearray(data)
+            lo = sos if trial % 2 else 2                       # odd trials: entropy data only; even: anywhere
+            for _ in range(int(rng.integers(1, 6))):
+                b[int(rng.integers(lo, len(b)))] = int(rng.integers(0, 256))
+            if trial % 7 == 0:
+                b = b[: int(rng.integers(lo + 1, len(b)))]     # and truncated
+            b = bytes(b)
+            try:
+                h, w, _ = device.jpeg_info(b)
+            except (ValueError, NotImplementedError):
+                refused += 1
+                continue
+            if h * w > 1 << 20:                                # a damaged size field: keep the test small
+                continue
+            rc, rgb, _ = emu(b, (h, w, 3))
+            assert rc in (0, 3)
+            decoded += 1
+    assert decoded > 100 and refused > 0
