@@ -40,9 +40,18 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
                     int16_t* __restrict__ coef, int16_t* __restrict__ dcv, int32_t* __restrict__ status) {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     __shared__ int s_warp[32];
+    // the image's lookahead tables in shared memory ([component][dc, ac]): every symbol starts with a gather from one of
+    // them, and 32 lanes gathering 2-byte entries from global memory cost up to 32 L1 wavefronts where shared memory
+    // costs a few bank conflicts
+    __shared__ uint16_t s_lut[6 << kLutBits];
     const Segment sg = segs[blockIdx.x];
     const ImageDesc& im = images[sg.image];
     const int T = (int)blockDim.x, tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < (im.ncomp * 2) << kLutBits; i += T) {
+        const int t = i >> kLutBits, c = t >> 1;
+        s_lut[i] = tables[(t & 1) ? im.ac[c] : im.dc[c]].lut[i & ((1 << kLutBits) - 1)];
+    }
+    __syncthreads();
     // dynamic shared memory, all indexed by the chunk's position in the wave: exit states, entry states, checkpoint states
     // [kCheckpoints][T], blocks completed, checkpoint block counts [kCheckpoints][T], work list of a correction round
     ScanState* s_exit = reinterpret_cast<ScanState*>(smem_raw);
@@ -67,7 +76,7 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
         int n = 0;
         // 1. guess
         if (active) out = decode_chunk<kGuess>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr,
-                                               Checkpoints{s_cps + tid, s_cpn + tid, T});
+                                               Checkpoints{s_cps + tid, s_cpn + tid, T}, ScanState{0, 0, 0}, s_lut);
         s_exit[tid] = out;
         s_n[tid] = n;
         // 2. until every chunk started from the state its predecessor left.  The chunks that have to be decoded again are
@@ -98,7 +107,7 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
                 const int c = s_list[tid];
                 int cn = s_n[c];
                 const ScanState e = decode_chunk<kCorrect>(sg, im, tables, scan, s_in[c], (uint32_t)(c0 + c + 1) * kChunkBits, 0, 0, nullptr,
-                                                           nullptr, &cn, nullptr, Checkpoints{s_cps + c, s_cpn + c, T}, s_exit[c]);
+                                                           nullptr, &cn, nullptr, Checkpoints{s_cps + c, s_cpn + c, T}, s_exit[c], s_lut);
                 s_exit[c] = e;
                 s_n[c] = cn;
             }
@@ -123,102 +132,10 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
         const int ordinal = blocks_before + warp_before + incl - (active ? n : 0);
         if (active && ordinal < total_blocks) {
             int n2 = 0;
-            decode_chunk<kStore>(sg, im, tables, scan, in, j == sg.n_chunks - 1 ? 0xffffffffu : limit, ordinal, total_blocks, coef, dcv, &n2, &bad);
+            decode_chunk<kStore>(sg, im, tables, scan, in, j == sg.n_chunks - 1 ? 0xffffffffu : limit, ordinal, total_blocks, coef, dcv, &n2, &bad, Checkpoints{nullptr, nullptr, 0}, ScanState{0, 0, 0}, s_lut);
         }
         if (c0 + T < sg.n_chunks) {             // another wave follows: it starts where this one ended
             wave_entry = s_exit[T - 1];
-            blocks_before += wave_total;
-            __syncthreads();
-        }
-    }
-    if (bad) atomicOr(&status[sg.image], 1);
-}
-
-// J1a, second form: the corrections run inside each warp first.  A warp's lanes pass their exit states along by shuffle
-// and redo their chunks until the warp agrees with itself, at its own pace and without a CTA barrier; only the state that
-// crosses a warp boundary goes through shared memory, and a CTA-wide round is needed only when that state changes
-// (a re-started decoder falls into step within a chunk or two, so a boundary correction rarely travels far into the next
-// warp).  Same passes, same results; fewer barriers and no warp waits for another warp's long chain.
-template <int kMaxThreads, int kMinBlocks>
-__global__ void __launch_bounds__(kMaxThreads, kMinBlocks)
-jpeg_huffman_warp_kernel(const Segment* __restrict__ segs, const ImageDesc* __restrict__ images,
-                         const HuffTable* __restrict__ tables, const uint8_t* __restrict__ scan,
-                         int16_t* __restrict__ coef, int16_t* __restrict__ dcv, int32_t* __restrict__ status) {
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    __shared__ int s_warp[32];
-    __shared__ ScanState s_last[32];         // exit state of each warp's last chunk
-    const Segment sg = segs[blockIdx.x];
-    const ImageDesc& im = images[sg.image];
-    const int T = (int)blockDim.x, tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = (T + 31) / 32;
-    ScanState* s_cps = reinterpret_cast<ScanState*>(smem_raw);
-    uint16_t* s_cpn = reinterpret_cast<uint16_t*>(s_cps + (size_t)T * kCheckpoints);
-    const Checkpoints cp{s_cps + tid, s_cpn + tid, T};
-    const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
-    const int total_blocks = sg.n_mcus * bpm;
-    ScanState wave_entry;
-    wave_entry.pos = 0; wave_entry.k = 0; wave_entry.b = 0;
-    int blocks_before = 0, bad = 0;
-    for (int c0 = 0; c0 < sg.n_chunks; c0 += T) {
-        const int j = c0 + tid;
-        const bool active = j < sg.n_chunks;
-        const uint32_t limit = (uint32_t)(j + 1) * kChunkBits;
-        ScanState in;
-        in.pos = (uint32_t)j * kChunkBits; in.k = 0; in.b = 0;
-        if (tid == 0) in = wave_entry;
-        ScanState out = in;
-        int n = 0;
-        if (active) out = decode_chunk<kGuess>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr, cp);
-        for (;;) {
-            // inside the warp: lane l starts from what lane l-1 left, until nothing moves (lane 0 keeps its entry for now)
-            for (;;) {
-                ScanState prev;
-                prev.pos = __shfl_up_sync(0xffffffffu, out.pos, 1);
-                const uint32_t kb = __shfl_up_sync(0xffffffffu, (uint32_t)out.k | ((uint32_t)out.b << 16), 1);
-                prev.k = (uint16_t)(kb & 0xffff); prev.b = (uint16_t)(kb >> 16);
-                const bool changed = active && lane > 0 && !same_state(prev, in);
-                if (!__any_sync(0xffffffffu, changed)) break;
-                if (changed) {
-                    in = prev;
-                    out = decode_chunk<kCorrect>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr, cp, out);
-                }
-            }
-            // across warps: the last active lane publishes, lane 0 of the next warp compares
-            const int last_lane = min(31, sg.n_chunks - 1 - c0 - warp * 32);     // < 0: no active lane in this warp
-            if (lane == last_lane) s_last[warp] = out;
-            __syncthreads();
-            bool moved = false;
-            if (lane == 0 && warp > 0 && active) {
-                const ScanState prev = s_last[warp - 1];
-                if (!same_state(prev, in)) {
-                    moved = true;
-                    in = prev;
-                    out = decode_chunk<kCorrect>(sg, im, tables, scan, in, limit, 0, 0, nullptr, nullptr, &n, nullptr, cp, out);
-                }
-            }
-            if (!__syncthreads_or(moved)) break;
-        }
-        // which block does each chunk start in: exclusive prefix sum of the blocks completed per chunk
-        int incl = active ? n : 0;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
-        }
-        if (lane == 31) s_warp[warp] = incl;
-        __syncthreads();
-        int warp_before = 0, wave_total = 0;
-        for (int w = 0; w < nwarps; ++w) {
-            const int v = s_warp[w];
-            if (w < warp) warp_before += v;
-            wave_total += v;
-        }
-        const int ordinal = blocks_before + warp_before + incl - (active ? n : 0);
-        if (active && ordinal < total_blocks) {
-            int n2 = 0;
-            decode_chunk<kStore>(sg, im, tables, scan, in, j == sg.n_chunks - 1 ? 0xffffffffu : limit, ordinal, total_blocks, coef, dcv, &n2, &bad);
-        }
-        if (c0 + T < sg.n_chunks) {             // another wave follows: it starts where this one ended
-            wave_entry = s_last[nwarps - 1];
             blocks_before += wave_total;
             __syncthreads();
         }
@@ -321,7 +238,7 @@ struct ftf_jpeg_batch {
     size_t scan_bytes = 0, meta_bytes = 0, off_seg = 0, off_tab = 0, off_q = 0;
     int64_t coef_elems = 0, plane_bytes = 0, rgb_bytes = 0, dc_elems = 0;
     int max_blocks = 0, max_groups = 0, max_chunks = 1;
-    bool decoded = false, attr_set = false, attr_set_w = false, committed = false;
+    bool decoded = false, attr_set = false, committed = false;
     Parsed parsed;                        // scratch of batch_add
 };
 
@@ -533,21 +450,7 @@ extern "C" int ftf_jpeg_batch_decode_dev(ftf_jpeg_batch* b, uint8_t* rgb_out, in
         FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * (int)kHuffSmemPerThread), &b->err);
         b->attr_set = true;
     }
-    static const bool warp_form = getenv("FTF_JPEG_BLOCK_ROUNDS") == nullptr;      // measurement switch: the first form of J1a
-    if (warp_form) {
-        const size_t wsm = (size_t)threads * kCheckpoints * (sizeof(ScanState) + sizeof(uint16_t));
-        if (!b->attr_set_w) {
-            FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_warp_kernel<640, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 640 * 70), &b->err);
-            FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_warp_kernel<1024, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1024 * 70), &b->err);
-            b->attr_set_w = true;
-        }
-        if (threads <= 640)
-            jpeg_huffman_warp_kernel<640, 2><<<nseg, threads, wsm, st>>>(d_segs, d_images, d_tabs, (const uint8_t*)b->d_scan.p, (int16_t*)b->d_coef.p,
-                                                                      (int16_t*)b->d_dc.p, (int32_t*)b->d_status.p);
-        else
-            jpeg_huffman_warp_kernel<1024, 1><<<nseg, threads, wsm, st>>>(d_segs, d_images, d_tabs, (const uint8_t*)b->d_scan.p, (int16_t*)b->d_coef.p,
-                                                                       (int16_t*)b->d_dc.p, (int32_t*)b->d_status.p);
-    } else if (threads <= 640)
+    if (threads <= 640)
         jpeg_huffman_kernel<640, 2><<<nseg, threads, hsm, st>>>(d_segs, d_images, d_tabs, (const uint8_t*)b->d_scan.p, (int16_t*)b->d_coef.p,
                                                              (int16_t*)b->d_dc.p, (int32_t*)b->d_status.p);
     else

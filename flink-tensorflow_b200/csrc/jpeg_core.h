@@ -107,8 +107,9 @@ struct BitWindow {
 };
 
 // T.81 F.2.2.3 DECODE on a 32-bit window: code length (0 = no such code) and symbol.
-FTF_HD int lookup_symbol(uint32_t w, const HuffTable* __restrict__ t, int* sym) {
-    const uint32_t e = FTF_LDG(&t->lut[w >> (32 - kLutBits)]);
+// lut: the table's lookahead entries, possibly a copy in shared memory (hence a plain load, not a read-only-path one)
+FTF_HD int lookup_symbol(uint32_t w, const uint16_t* lut, const HuffTable* __restrict__ t, int* sym) {
+    const uint32_t e = lut[w >> (32 - kLutBits)];
     if (e) { *sym = (int)(e & 0xFF); return (int)(e >> 8); }
     const int32_t code16 = (int32_t)(w >> 16);
     int l = kLutBits + 1;
@@ -193,7 +194,8 @@ template <int kMode>
 FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const HuffTable* __restrict__ tables,
                               const uint8_t* __restrict__ scan, ScanState st, uint32_t limit, int ordinal, int total_blocks,
                               int16_t* __restrict__ coef, int16_t* __restrict__ dcv, int* n_done, int* bad,
-                              Checkpoints cp = Checkpoints{nullptr, nullptr, 0}, ScanState old_exit = ScanState{0, 0, 0}) {
+                              Checkpoints cp = Checkpoints{nullptr, nullptr, 0}, ScanState old_exit = ScanState{0, 0, 0},
+                              const uint16_t* luts = nullptr) {      // luts: [component][dc, ac][1 << kLutBits] copies, or null
     constexpr bool kWrite = kMode == kStore;
     const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
     const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
@@ -215,11 +217,13 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
     int c = b < nluma ? 0 : b - nluma + 1;
     const HuffTable* dc = tables + im.dc[c];
     const HuffTable* ac = tables + im.ac[c];
+    const uint16_t* dcl = luts ? luts + ((2 * c) << kLutBits) : dc->lut;
+    const uint16_t* acl = luts ? luts + ((2 * c + 1) << kLutBits) : ac->lut;
     while (pos < limit && (!kWrite || ordinal < total_blocks)) {
         const uint32_t w = bw.at(pos);
         const bool is_dc = k == 0;
         int sym = 0;
-        const int len = lookup_symbol(w, is_dc ? dc : ac, &sym);
+        const int len = lookup_symbol(w, is_dc ? dcl : acl, is_dc ? dc : ac, &sym);
         if (len == 0 || (is_dc && sym > 15)) {          // no such code / a DC symbol is a bit count
             if (kWrite) { *bad = 1; break; }
             pos += 1;
@@ -252,6 +256,8 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
             c = b < nluma ? 0 : b - nluma + 1;
             dc = tables + im.dc[c];
             ac = tables + im.ac[c];
+            dcl = luts ? luts + ((2 * c) << kLutBits) : dc->lut;
+            acl = luts ? luts + ((2 * c + 1) << kLutBits) : ac->lut;
             if (kWrite) {
                 blk = block_ptr(im, coef, my, mx, b);
                 dcp = dc_slot(im, dcv, my * im.mcus_x + mx, b);
