@@ -380,6 +380,51 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
             "checksum": int(checksum[0])}
 
 
+def blocking_two_subtasks(ftf, lib, np, device, seconds=1.5):
+    """Two task threads, each with its own label runner on the same GPU (two Flink slots per GPU), each calling the blocking
+    ftf_run over a stacked [64,299,299,3] fp32 tensor in pinned memory: one thread's upload overlaps the other's kernels."""
+    import threading
+    from flink_tensorflow_b200.host import _as_ftf, FtfTensor, _check
+    nb = INC["batch"] * 299 * 299 * 3 * 4
+    runners, bufs, counts = [], [], [0, 0]
+    for t in range(2):
+        cfg = ftf.default_config(device=device, max_batch=INC["batch"], top_k=INC["top_k"], num_classes=INC["classes"], seed=INC["seed"])
+        runners.append(ftf.Runner("builtin:inception_v3", None, None, cfg))
+        p, hx = pinned_array(lib, np, nb, np.float32)
+        hx[:] = np.random.default_rng(11 + t).standard_normal(nb // 4, dtype=np.float32)
+        bufs.append((p, hx))
+    stop = threading.Event()
+    go = threading.Barrier(3)
+
+    def task(t):
+        r, (p, hx) = runners[t], bufs[t]
+        t_in, keep = _as_ftf(ftf.DataType.FLOAT, (INC["batch"], 299, 299, 3), hx.view(np.uint8))
+        ik, ok = (C.c_char_p * 1)(b"inputs"), (C.c_char_p * 1)(b"top_k_indices")
+        tin, tout = (FtfTensor * 1)(t_in), (FtfTensor * 1)()
+        for _ in range(2):
+            _check(lib.ftf_run(r.handle, 1, ik, tin, 1, ok, tout), r.handle)
+        go.wait()
+        while not stop.is_set():
+            _check(lib.ftf_run(r.handle, 1, ik, tin, 1, ok, tout), r.handle)
+            counts[t] += 1
+    th = [threading.Thread(target=task, args=(t,)) for t in range(2)]
+    for x in th:
+        x.start()
+    go.wait()
+    t0 = time.perf_counter()
+    time.sleep(seconds)
+    stop.set()
+    for x in th:
+        x.join()
+    dt = time.perf_counter() - t0
+    for r in runners:
+        r.close()
+    for p, _ in bufs:
+        lib.ftf_host_free(p)
+    return {"value": sum(counts) * INC["batch"] / dt, "unit": "images/s", "calls": sum(counts), "seconds": dt,
+            "api": "ftf_run (C ABI) from two task threads with one runner each on one GPU (two Flink slots per GPU)"}
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -590,6 +635,8 @@ def run_ours(args):
         barrier()
         s_ms = max_over_ranks(sres["seconds"] * 1e3)
         extra["e2e_blocking_run"] = e2e
+        if world == 1 and not args.quick:
+            extra["e2e_blocking_run_two_subtasks"] = blocking_two_subtasks(ftf, lib, np, local_rank)
         e2e = {"value": sres["records"] * world / (s_ms / 1e3), "unit": unit,
                "h2d_bytes_per_step": INC["batch"] * sres["h2d_bytes_per_record"], "d2h_bytes_per_step": INC["batch"] * sres["d2h_bytes_per_record"],
                "ms_per_step": s_ms / n_b, "steps": n_b, "gpu_launches": sres["launches"],

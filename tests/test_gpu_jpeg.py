@@ -75,6 +75,29 @@ def test_photo_sized_batch_matches_oracle(dev, oracle, kw):
         assert np.array_equal(g.cpu().numpy(), oracle.jpeg_decode(f))
 
 
+def test_full_batch_is_independent_of_batch_composition(dev, oracle):
+    """The bench's size (256 files of 640x480): an image decodes to the same bytes whatever batch it travels in (alone,
+    in a batch of 7, in the full batch), and a sample of the full batch equals the oracle."""
+    import torch
+    rng = np.random.default_rng(55)
+    distinct = [_jpeg(_photo(rng), quality=85) for _ in range(8)] + [_jpeg(_photo(rng), quality=70, restart_marker_rows=2)]
+    files = [distinct[i % len(distinct)] for i in range(256)]
+    b = dev.JpegBatch()
+    flat = b.load(files).decode()
+    assert b.status() == [0] * 256
+    full = [im.clone() for im in b.images(flat)]
+    for i in range(len(distinct), 256):                       # repeats of a file give the same image
+        assert torch.equal(full[i], full[i % len(distinct)])
+    for i in (0, 3, 8):
+        assert np.array_equal(full[i].cpu().numpy(), oracle.jpeg_decode(files[i]))
+    alone = dev.decode_jpeg([files[5]])[0]
+    assert torch.equal(alone, full[5])
+    seven = dev.decode_jpeg(files[2:9])
+    for k, im in enumerate(seven):
+        assert torch.equal(im, full[2 + k])
+    b.close()
+
+
 def test_corrupt_entropy_data_is_reported_per_image(dev, oracle):
     rng = np.random.default_rng(3)
     good = [_jpeg(_photo(rng, 96, 128), quality=80, optimize=True) for _ in range(3)]
