@@ -48,6 +48,7 @@ struct ResizeParams {
     int n_chunks;
     int chunk_stride;        // bytes between chunk regions in smem (128-byte multiple)
     long long n;             // images
+    int step_img, step_band; // gridDim.x bands further on: += step_img images, += step_band bands (wrapping at `bands`)
 };
 
 template <typename T> __device__ __forceinline__ T to_out(float v);
@@ -73,9 +74,9 @@ __device__ __forceinline__ float finish(float top, float bot, float yl, const Re
 // few idle lanes as possible among 256, 224 and 192 threads (four CTAs per SM).
 // u8 -> f32 uses the 2^23 trick: m(b) = bits 0x4B000000|b = 2^23 + b exactly.  A tap that only enters a difference needs
 // no conversion at all, since m(tr) - m(tl) = tr - tl exactly; the left taps are converted with one FADD each.
-template <int kN, int kBS, bool kMulRecip, typename OutT>
+template <int kN, int kBS, bool kMulRecip, bool kPartial, typename OutT>
 __device__ __forceinline__ void run_bands(const ResizeParams& p, OutT* __restrict__ out, long long total_bands, int stage_bytes,
-                                          uint32_t smem_a, uint64_t* full, uint64_t* empty, const CUtensorMap* tmap, uint8_t* smem) {
+                                          uint32_t smem_a, uint64_t* full, uint64_t* empty, const CUtensorMap* tmap, uint8_t* smem, uint4* rows_sm) {
     const int ow3 = p.out_w * 3;
     const int c0 = (int)threadIdx.x;
     uint32_t off_lo[kN], off_hi[kN];
@@ -96,40 +97,51 @@ __device__ __forceinline__ void run_bands(const ResizeParams& p, OutT* __restric
         off_lo[j] = smem_a + (uint32_t)(klo * p.chunk_stride + (blo - klo * p.cw));
         off_hi[j] = smem_a + (uint32_t)(khi * p.chunk_stride + (bhi - khi * p.cw));
     }
-    auto issue = [&](long long blk, int stage) {       // warp 0, all lanes, one elected lane per instruction (see ptx.cuh)
-        const long long img = blk / p.bands;
-        const int band = (int)(blk - img * p.bands);
+    // (image, band) of a CTA's bands advance by host-computed steps: the 64-bit division they replace cost more than a
+    // whole output row per band
+    auto advance = [&](int& img, int& band) {
+        img += p.step_img; band += p.step_band;
+        if (band >= p.bands) { band -= p.bands; ++img; }
+    };
+    auto issue = [&](int img, int band, int stage) {   // warp 0, all lanes, one elected lane per instruction (see ptx.cuh)
         const int iy0 = (int)__fmul_rn((float)(band * p.th), p.hs);
         ptx::mbar_expect_tx_elect(&full[stage], (uint32_t)(p.n_chunks * p.cw * p.br));
         for (int k = 0; k < p.n_chunks; ++k)
             ptx::tma_load_3d_elect(smem + (size_t)stage * stage_bytes + (size_t)k * p.chunk_stride, tmap, &full[stage], k * p.cw, iy0, (int)img);
     };
     int it = 0;
-    for (long long blk = blockIdx.x; blk < total_bands; blk += gridDim.x, ++it) {
+    int img = (int)(blockIdx.x / (unsigned)p.bands), band = (int)(blockIdx.x % (unsigned)p.bands);
+    int nimg = img, nband = band;                      // the band two steps ahead, which warp 0 fetches
+    advance(nimg, nband); advance(nimg, nband);
+    for (unsigned blk = blockIdx.x; blk < (unsigned)total_bands; blk += gridDim.x, ++it, advance(img, band), advance(nimg, nband)) {
         const int stage = it & 1;
         const uint32_t phase = (uint32_t)((it >> 1) & 1);
-        const long long img = blk / p.bands;
-        const int band = (int)(blk - img * p.bands);
         const int oy0 = band * p.th;
         const int rows = min(p.th, p.out_h - oy0);
         const int iy0 = (int)__fmul_rn((float)oy0, p.hs);  // first input row of the band
         ptx::mbar_wait(&full[stage], phase);
         const uint32_t sbase = (uint32_t)(stage * stage_bytes);
         OutT* orow = out + ((size_t)img * p.out_h + oy0) * ow3 + c0;
-        // the row terms of the band (at most 8 rows): lane r computes row r's once, the row loop fetches them by shuffle
-        uint32_t my_r0, my_r1;
-        float my_yl;
-        {
+        // the row terms of the band (at most 8 rows): lane r computes row r's once and leaves them in the warp's corner of
+        // shared memory; the row loop reads them back as broadcasts.  (Fetching them by shuffle made the loop body a
+        // possibly-divergent region for the compiler, which then kept uniform values -- the global-memory descriptor among
+        // them -- in vector registers and moved them to uniform ones again before every store.)
+        if ((threadIdx.x & 31) < 8) {
             const float py = __fmul_rn((float)(oy0 + (int)(threadIdx.x & 31)), p.hs);
             const int ylo = (int)py;
             const int yhi = min(ylo + 1, p.in_h - 1);
-            my_r0 = sbase + (uint32_t)((ylo - iy0) * p.cw);
-            my_r1 = sbase + (uint32_t)((yhi - iy0) * p.cw);
-            my_yl = __fsub_rn(py, (float)ylo);
+            uint4 t;
+            t.x = sbase + (uint32_t)((ylo - iy0) * p.cw);
+            t.y = sbase + (uint32_t)((yhi - iy0) * p.cw);
+            t.z = __float_as_uint(__fsub_rn(py, (float)ylo));
+            t.w = 0;
+            rows_sm[threadIdx.x & 31] = t;
         }
+        __syncwarp();
         for (int r = 0; r < rows; ++r, orow += ow3) {
-            const uint32_t r0 = __shfl_sync(0xffffffffu, my_r0, r), r1 = __shfl_sync(0xffffffffu, my_r1, r);
-            const float yl = __shfl_sync(0xffffffffu, my_yl, r);
+            const uint4 t = rows_sm[r];
+            const uint32_t r0 = t.x, r1 = t.y;
+            const float yl = __uint_as_float(t.z);
 #pragma unroll
             for (int j = 0; j < kN; ++j) {
                 const float mtl = __uint_as_float(0x4B000000u | lds_u8(r0 + off_lo[j])), mtr = __uint_as_float(0x4B000000u | lds_u8(r0 + off_hi[j]));
@@ -138,15 +150,15 @@ __device__ __forceinline__ void run_bands(const ResizeParams& p, OutT* __restric
                 const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(mtr, mtl), xl[j]));
                 const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(mbr, mbl), xl[j]));
                 const OutT v = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
-                if (live[j]) orow[j * kBS] = v;
+                if (!kPartial || j < kN - 1 || live[j]) orow[j * kBS] = v;     // only a warp's last group can hold dead lanes
             }
         }
         // this warp is done with the stage; warp 0 refills it (band it+2) once every warp has said so
         __syncwarp();
         if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&empty[stage]);
-        if (threadIdx.x < 32 && blk + 2ll * gridDim.x < total_bands) {
+        if (threadIdx.x < 32 && (unsigned long long)blk + 2ull * gridDim.x < (unsigned long long)total_bands) {
             ptx::mbar_wait(&empty[stage], phase);
-            issue(blk + 2ll * gridDim.x, stage);
+            issue(nimg, nband, stage);
         }
     }
 }
@@ -157,6 +169,8 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
                      int stage_bytes) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full[2], empty[2];
+    __shared__ uint4 rows_all[(kBS / 32) * 8];          // per warp: the row terms of its current band
+    uint4* rows_sm = rows_all + (threadIdx.x >> 5) * 8;
     if (threadIdx.x == 0) {
         ptx::mbar_init(&full[0], 1);
         ptx::mbar_init(&full[1], 1);
@@ -181,12 +195,21 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
     const int warp_c0 = (int)(threadIdx.x & ~31u);            // first column of this warp
     const int ow3 = p.out_w * 3;
     const int nj = warp_c0 < ow3 ? min(kCols, (ow3 - warp_c0 + kBS - 1) / kBS) : 0;   // columns with at least one live lane in this warp
+    // a warp whose last column group is cut by the end of the row stores under a predicate; every other warp runs code
+    // without one (the predicate cost an ISETP and two R2UR per stored value)
+    const bool partial = nj > 0 && warp_c0 + (nj - 1) * kBS + 32 > ow3;
+#define FTF_K2_RUN(N)                                                                                                   \
+    if (partial) run_bands<N, kBS, kMulRecip, true>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem, rows_sm);  \
+    else run_bands<N, kBS, kMulRecip, false>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem, rows_sm);
     switch (nj) {
-    case 4: run_bands<4, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;
-    case 3: run_bands<3, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;
-    case 2: run_bands<2, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;
-    default: run_bands<1, kBS, kMulRecip>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem); break;   // also warps without columns: they keep the barriers in step
+    case 4: FTF_K2_RUN(4) break;
+    case 3: FTF_K2_RUN(3) break;
+    case 2: FTF_K2_RUN(2) break;
+    default:                      // also warps without columns: they keep the barriers in step
+        run_bands<1, kBS, kMulRecip, true>(p, out, total_bands, stage_bytes, smem_a, full, empty, &tmap, smem, rows_sm);
+        break;
     }
+#undef FTF_K2_RUN
 }
 
 // ---- direct kernel: any alignment, any size; one thread per output element ---------------------
@@ -261,6 +284,7 @@ int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool 
         const long long bands = p.n * p.bands;
         const long long resident = (long long)sms * 4;                                    // persistent CTAs, two stages each
         const unsigned grid = (unsigned)(bands < resident ? bands : resident);
+        p.step_img = (int)(grid / (unsigned)p.bands); p.step_band = (int)(grid % (unsigned)p.bands);
 #define FTF_K2_LAUNCH(BS)                                                                                              \
         {                                                                                                              \
             auto kern = recip ? resize_norm_band_tma<BS, true, OutT> : resize_norm_band_tma<BS, false, OutT>;          \
