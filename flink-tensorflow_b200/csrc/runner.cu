@@ -429,16 +429,9 @@ extern "C" int ftf_create(const char* model, const char* signature_key, const ch
     if ((e = cudaSetDevice(cfg.device)) != cudaSuccess) return fail(nullptr, FTF_INTERNAL, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
     ftf_runner* raw = r.release();
     auto bail = [&](int code, const std::string& msg) { destroy_runner(raw); return fail(nullptr, code, msg); };
-    // The slot streams carry a batch's uploads and its pre-processing (JPEG decoding, resize); for label runners they rank
-    // above the network's stream, so that when a convolution kernel of the batch in flight retires, the block scheduler
-    // hands the free SMs to the next batch's (latency-bound) decode first instead of queueing it behind the whole network.
-    int prio_lo = 0, prio_hi = 0;
-    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
-    static const bool flat_prio = getenv("FTF_FLAT_PRIORITY") != nullptr;      // measurement switch
-    const int slot_prio = (is_label_kind(raw->kind) && !flat_prio) ? prio_hi : 0;
     for (auto& s : raw->slots) {
         s.h_in.host = true;
-        if ((e = cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, slot_prio)) != cudaSuccess ||
+        if ((e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)) != cudaSuccess ||
             (e = cudaEventCreateWithFlags(&s.done, cudaEventDisableTiming)) != cudaSuccess)
             return bail(FTF_INTERNAL, std::string("stream/event creation: ") + cudaGetErrorString(e));
     }
