@@ -374,7 +374,15 @@ int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* heig
     if (groups > b->max_groups) b->max_groups = groups;
     // the one host pass over the compressed bytes: unstuff + split at restart markers + copy into pinned memory
     const size_t first_seg = b->segments.size();
-    b->scan_bytes += (size_t)stage_scan(file, len, p, im, i, (uint8_t*)b->h_scan.p + b->scan_bytes, (int64_t)b->scan_bytes, &b->segments);
+    bool truncated = false;
+    const size_t staged = (size_t)stage_scan(file, len, p, im, i, (uint8_t*)b->h_scan.p + b->scan_bytes, (int64_t)b->scan_bytes, &b->segments, &truncated);
+    if (truncated) {
+        // the reference's graph leaves DecodeJpeg's try_recover_truncated at false (GraphBuilder.java:41-47 sets channels
+        // only): TF refuses a file that ends before its end-of-image marker instead of padding it
+        b->segments.resize(first_seg);
+        return bfail(b, FTF_INVALID_ARGUMENT, "image " + std::to_string(i) + ": DecodeJpeg: invalid JPEG data (the file ends inside the scan)");
+    }
+    b->scan_bytes += staged;
     for (size_t k = first_seg; k < b->segments.size(); ++k)
         if (b->segments[k].n_chunks > b->max_chunks) b->max_chunks = b->segments[k].n_chunks;
     b->images.push_back(im);

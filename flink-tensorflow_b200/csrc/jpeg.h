@@ -46,8 +46,9 @@ int64_t stage_bound(int64_t n, const Parsed& p, const ImageDesc& im);
 // stream per restart interval (or one for the whole scan), each 4-byte aligned and followed by >= 16 zero bytes, and
 // appends one Segment per stream (begin = dst_offset + position in dst).  Returns the bytes written.  This is the one
 // pass the host makes over the compressed data; it doubles as the copy into pinned staging memory.
+// *truncated: the file ended inside the scan, before any closing marker (the decoder would read zero bits from there on).
 int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, uint8_t* dst,
-                   int64_t dst_offset, std::vector<Segment>* out);
+                   int64_t dst_offset, std::vector<Segment>* out, bool* truncated = nullptr);
 
 }  // namespace jpeg
 }  // namespace ftf

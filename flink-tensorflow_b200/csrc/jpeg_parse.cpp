@@ -182,7 +182,8 @@ int64_t stage_bound(int64_t n, const Parsed& p, const ImageDesc& im) {
 }
 
 int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc& im, int image, uint8_t* dst,
-                   int64_t dst_offset, std::vector<Segment>* out) {
+                   int64_t dst_offset, std::vector<Segment>* out, bool* truncated) {
+    if (truncated) *truncated = false;
     const int total = im.mcus_x * im.mcus_y;
     const int nseg = segment_count(p, im);
     const int per = nseg > 1 ? p.restart : total;
@@ -201,7 +202,11 @@ int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc
             memcpy(dst + w, d + pos, (size_t)(upto - pos));
             w += upto - pos;
             pos = upto;
-            if (!f || pos + 1 >= n) { ended = true; break; }          // data runs out: the rest reads as zero bits
+            if (!f || pos + 1 >= n) {                                 // the file ends inside the scan, without a marker
+                ended = true;
+                if (truncated) *truncated = true;
+                break;
+            }
             const int m = d[pos + 1];
             if (m == 0x00) { dst[w++] = 0xFF; pos += 2; continue; }   // stuffed byte
             if (m == 0xFF) { pos += 1; continue; }                    // fill byte in front of a marker

@@ -221,7 +221,8 @@ int ftf_global_avgpool_bf16_dev(const void* in, int32_t n, int32_t hw, int32_t c
  * EX/inception/ImageInputFormat.scala:63-80).  8-bit baseline / extended-sequential Huffman files, 1 or 3 components,
  * 4:4:4 / 4:2:2 / 4:2:0, optional restart intervals; results are bit-identical to libjpeg's defaults (integer slow IDCT,
  * fancy upsampling).  Progressive/arithmetic/CMYK/multi-scan files: FTF_UNIMPLEMENTED.  Malformed headers:
- * FTF_INVALID_ARGUMENT at load; a corrupt entropy-coded segment is found on the device and reported by
+ * FTF_INVALID_ARGUMENT at load, and so is a file that ends inside its scan (the reference leaves DecodeJpeg's
+ * try_recover_truncated at false); a corrupt entropy-coded segment is found on the device and reported by
  * ftf_jpeg_batch_status ("Invalid JPEG data" in TF).  ftf_run on "builtin:image_normalization" and
  * "builtin:normalize_label" accepts a STRING tensor of files (the reference's ImageFileTensor) and runs these kernels
  * in front of K2. */

@@ -53,7 +53,7 @@ typedef struct {
     jo_comp comp[3];
     /* bit reader */
     uint32_t bitbuf;
-    int bitcnt, hit_marker;
+    int bitcnt, hit_marker, truncated;
 } jo_dec;
 
 static int u16(const uint8_t* p) { return (p[0] << 8) | p[1]; }
@@ -82,10 +82,12 @@ static int get_bit(jo_dec* s) {
         if (!s->hit_marker && s->pos < s->n) {
             b = s->d[s->pos];
             if (b == 0xFF) {
-                int b2 = s->pos + 1 < s->n ? s->d[s->pos + 1] : 0xD9;
-                if (b2 == 0) s->pos += 2;
+                if (s->pos + 1 >= s->n) { s->truncated = 1; s->hit_marker = 1; b = 0; }
+                else if (s->d[s->pos + 1] == 0) s->pos += 2;
                 else { s->hit_marker = 1; b = 0; }
             } else s->pos += 1;
+        } else if (!s->hit_marker) {
+            s->truncated = 1;              /* the data ran out before any marker */
         }
         s->bitbuf = (uint32_t)b;
         s->bitcnt = 8;
@@ -264,8 +266,10 @@ static int decode_scan(jo_dec* s) {
                 }
                 if (s->pos + 1 < s->n && s->d[s->pos] == 0xFF && s->d[s->pos + 1] == 0xD0 + rst) {
                     s->pos += 2; s->hit_marker = 0;
-                } else if (s->pos + 1 >= s->n || s->d[s->pos + 1] == 0xD9) {
-                    s->hit_marker = 1;              /* truncated: the rest decodes from zero bits */
+                } else if (s->pos + 1 >= s->n) {
+                    s->hit_marker = 1; s->truncated = 1;
+                } else if (s->d[s->pos + 1] == 0xD9) {
+                    s->hit_marker = 1;              /* EOI early: the rest decodes from zero bits */
                 } else return JO_INVALID;
                 rst = (rst + 1) & 7;
                 pred[0] = pred[1] = pred[2] = 0;
@@ -375,6 +379,14 @@ int orc_jpeg_decode(const uint8_t* d, int64_t n, uint8_t* rgb) {
             c->plane = (uint8_t*)malloc((size_t)c->bw * c->bh * 64);
         }
         rc = decode_scan(s);
+        /* TF's DecodeJpeg runs with try_recover_truncated = false (the reference sets only `channels`,
+         * GraphBuilder.java:41-47): a file that ends before its closing marker is an error, not a padded image */
+        if (!rc && !s->hit_marker) {          /* libjpeg goes on to read the closing marker */
+            int64_t q = s->pos;
+            while (q + 1 < s->n && !(s->d[q] == 0xFF && s->d[q + 1] != 0 && s->d[q + 1] != 0xFF)) ++q;
+            if (q + 1 >= s->n) s->truncated = 1;
+        }
+        if (!rc && s->truncated) rc = JO_INVALID;
     }
     if (!rc) {
         for (int i = 0; i < s->ncomp; ++i) {

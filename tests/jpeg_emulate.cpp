@@ -34,7 +34,9 @@ extern "C" int emu_jpeg_decode(const uint8_t* file, int64_t len, uint8_t* rgb, i
     im.rgb_off = 0;
     std::vector<Segment> segs;
     std::vector<uint8_t> scan((size_t)stage_bound(len, *p, im) + 16);
-    stage_scan(file, len, *p, im, 0, scan.data(), 0, &segs);
+    bool truncated = false;
+    stage_scan(file, len, *p, im, 0, scan.data(), 0, &segs, &truncated);
+    if (truncated) { delete p; return 3; }
     if (n_segments) *n_segments = (int)segs.size();
     std::vector<int16_t> coef((size_t)coef_elems, 0), dcv((size_t)coef_elems / 64, 0);
     std::vector<uint8_t> planes((size_t)plane_bytes + 16);

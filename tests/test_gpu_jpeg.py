@@ -155,12 +155,19 @@ def test_damaged_files_decode_to_completion_like_the_oracle(dev, oracle):
     b.close()
 
 
-def test_truncated_file_decodes_like_libjpeg_with_zero_bits(dev, oracle):
+def test_truncated_file_is_refused_like_tf_with_default_attributes(dev, oracle):
+    """The reference's graph leaves try_recover_truncated at false: a file that ends inside its scan is invalid JPEG data,
+    for the oracle and for the product; one that lost only its end-of-image marker too.  A premature end-of-image marker
+    is libjpeg's warning case: the rest of the image decodes from zero bits."""
     rng = np.random.default_rng(8)
     f = _jpeg(_photo(rng, 80, 112), quality=80)
-    cut = f[: len(f) * 2 // 3]
-    got = dev.decode_jpeg([cut])[0].cpu().numpy()
-    assert np.array_equal(got, oracle.jpeg_decode(cut))
+    for cut in (f[: len(f) * 2 // 3], f[:-2]):
+        with pytest.raises(ValueError):
+            oracle.jpeg_decode(cut)
+        with pytest.raises(ValueError, match="ends inside the scan"):
+            dev.decode_jpeg([cut])
+    early = f[: len(f) * 2 // 3] + b"\xff\xd9"
+    assert np.array_equal(dev.decode_jpeg([early])[0].cpu().numpy(), oracle.jpeg_decode(early))
 
 
 def test_normalization_model_takes_image_files(ftf, oracle):
