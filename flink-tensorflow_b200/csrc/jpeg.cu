@@ -11,12 +11,11 @@
 //                            9-bit lookahead table on a byte-unstuffed stream (the host removes the stuffing while it
 //                            copies the file into pinned memory).
 //   J1b jpeg_dc_kernel       DC differences -> DC values: warp scan per (segment, component).
-//   J2 jpeg_idct_kernel      one thread per 8x8 block: a warp's coefficients staged through shared memory with
-//                            coalesced loads, dequantise + libjpeg's integer slow IDCT entirely in registers, 8-byte
-//                            row stores into the component plane.
+//   J2 jpeg_idct_kernel      one thread per 8x8 block: dequantise + libjpeg's integer slow IDCT, entirely in
+//                            registers, 16-byte coefficient loads, 8-byte row stores into the component plane.
 //   J3 jpeg_colour_kernel    one thread per 8 pixels: planes read as aligned words, triangle-filter chroma upsampling
-//                            (2x1, 2x2) with every source sample fetched once, fixed-point YCbCr -> RGB; a warp's
-//                            768 bytes of packed RGB leave through shared memory as 16-byte stores.
+//                            (2x1, 2x2) with every source sample fetched once, fixed-point YCbCr -> RGB, six 32-bit
+//                            stores of packed RGB.
 // Integer arithmetic throughout: results are bit-identical to libjpeg(-turbo), checked against oracle/jpeg_oracle.c
 // and the Pillow-made fixtures in tests/golden/jpeg.
 #include "jpeg.h"
@@ -176,29 +175,10 @@ jpeg_dc_kernel(const Segment* __restrict__ segs, int nseg, const ImageDesc* __re
 __global__ void __launch_bounds__(128)
 jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restrict__ quant,
                  const int16_t* __restrict__ coef, const int16_t* __restrict__ dcv, uint8_t* __restrict__ planes) {
-    // a warp's 32 blocks of coefficients (4 KB, contiguous: an image's components follow each other) staged with coalesced
-    // loads; rows padded to 144 bytes so that both the staging stores and each lane's 16-byte reads are conflict-free.
-    // Read straight from global memory, every lane would pull from its own 128-byte line: 32 wavefronts per load.
-    __shared__ __align__(16) uint8_t s_coef[4][32 * 144];
     const ImageDesc& im = images[blockIdx.y];
-    const int lane = (int)(threadIdx.x & 31), warp = (int)(threadIdx.x >> 5);
-    const int b0 = (int)(blockIdx.x * blockDim.x + threadIdx.x);         // block index across the image's components
-    const bool valid = b0 < im.n_blocks;
-    const bool staged = __all_sync(0xffffffffu, valid);
-    int16_t cf[64];
-    if (staged) {
-        const int4* src = reinterpret_cast<const int4*>(coef + im.coef_off[0] + (int64_t)(b0 - lane) * 64);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int q = k * 32 + lane;
-            *reinterpret_cast<int4*>(&s_coef[warp][(q >> 3) * 144 + (q & 7) * 16]) = __ldg(src + q);
-        }
-        __syncwarp();
-#pragma unroll
-        for (int i = 0; i < 8; ++i) reinterpret_cast<int4*>(cf)[i] = *reinterpret_cast<const int4*>(&s_coef[warp][lane * 144 + i * 16]);
-    }
-    if (!valid) return;
-    int b = b0, c = 0;
+    int b = (int)(blockIdx.x * blockDim.x + threadIdx.x);
+    if (b >= im.n_blocks) return;
+    int c = 0;
     const int nb0 = im.bw[0] * im.bh[0];
     if (b >= nb0) {
         b -= nb0; c = 1;
@@ -207,12 +187,13 @@ jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restric
     }
     const int bw = im.bw[c];
     const int by = b / bw, bx = b - by * bw;
+    int16_t cf[64];
     uint16_t q[64];
     const int4* cp = reinterpret_cast<const int4*>(coef + im.coef_off[c] + (int64_t)b * 64);
     const int4* qp = reinterpret_cast<const int4*>(quant + (int64_t)im.quant[c] * 64);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        if (!staged) reinterpret_cast<int4*>(cf)[i] = __ldg(cp + i);
+        reinterpret_cast<int4*>(cf)[i] = __ldg(cp + i);
         reinterpret_cast<int4*>(q)[i] = __ldg(qp + i);
     }
     cf[0] = dc_of_block(im, dcv, c, by, bx);
@@ -221,35 +202,14 @@ jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restric
 
 __global__ void __launch_bounds__(256)
 jpeg_colour_kernel(const ImageDesc* __restrict__ images, const uint8_t* __restrict__ planes, uint8_t* __restrict__ rgb) {
-    __shared__ __align__(16) uint32_t s_px[8][32 * 6];       // a warp's 32 x 24 bytes of RGB on their way to 16-byte stores
     const ImageDesc& im = images[blockIdx.y];
     const int groups = (im.width + 7) >> 3;
-    const int total = groups * im.height;
     const int t = (int)(blockIdx.x * blockDim.x + threadIdx.x);
-    const int lane = (int)(threadIdx.x & 31), warp = (int)(threadIdx.x >> 5);
-    const bool valid = t < total;
-    union { uint8_t b[24]; uint32_t w[6]; } px;
-    int y = 0, x0 = 0;
-    if (valid) {
-        y = t / groups; x0 = (t - y * groups) * 8;
-        pixels8_rgb(im, planes, y, x0, px.b);
-    }
-    // Widths that are a multiple of 8: thread t's 24 bytes sit at byte 24 * t of the image, rows included, so a full warp
-    // owns 768 contiguous, 16-byte aligned bytes.  They go through shared memory and leave as 48 16-byte stores; stored
-    // straight from the registers they would be six 4-byte stores per lane, each touching six lines of the output.
-    const bool dense = (im.width & 7) == 0 && __all_sync(0xffffffffu, valid);
-    if (dense) {
-#pragma unroll
-        for (int i = 0; i < 6; ++i) s_px[warp][lane * 6 + i] = px.w[i];
-        __syncwarp();
-        uint4* dst = reinterpret_cast<uint4*>(rgb + im.rgb_off + (int64_t)(t - lane) * 24);
-        const uint4* src = reinterpret_cast<const uint4*>(s_px[warp]);
-        dst[lane] = src[lane];
-        if (lane < 16) dst[32 + lane] = src[32 + lane];
-        return;
-    }
-    if (!valid) return;
+    if (t >= groups * im.height) return;
+    const int y = t / groups, x0 = (t - y * groups) * 8;
     const int nx = im.width - x0 < 8 ? im.width - x0 : 8;
+    union { uint8_t b[24]; uint32_t w[6]; } px;
+    pixels8_rgb(im, planes, y, x0, px.b);
     uint8_t* dst = rgb + im.rgb_off + ((int64_t)y * im.width + x0) * 3;
     if (nx == 8 && (reinterpret_cast<uintptr_t>(dst) & 3) == 0) {
         uint32_t* d32 = reinterpret_cast<uint32_t*>(dst);
