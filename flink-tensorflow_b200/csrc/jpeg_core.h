@@ -50,7 +50,13 @@ struct ImageDesc {
     int64_t rgb_off;              // bytes
 };
 
-constexpr int kChunkBits = 1024;   // the unit of parallel entropy decoding (see decode_chunk)
+#ifndef FTF_JPEG_CHUNK_BITS
+#define FTF_JPEG_CHUNK_BITS 1024
+#endif
+#ifndef FTF_JPEG_CHECKPOINT_BITS
+#define FTF_JPEG_CHECKPOINT_BITS 128
+#endif
+constexpr int kChunkBits = FTF_JPEG_CHUNK_BITS;   // the unit of parallel entropy decoding (see decode_chunk)
 
 // One independently decodable stretch of a scan: a restart interval, or the whole scan.  The host stages its bytes with
 // the 0xFF00 byte stuffing removed ("clean" stream), 4-byte aligned and followed by at least 16 zero bytes.
@@ -179,7 +185,7 @@ FTF_HD int16_t dc_of_block(const ImageDesc& im, const int16_t* __restrict__ dcv,
 // after a few symbols, and from there on everything (exit state, blocks completed) is already known.  Every attempt
 // therefore leaves its state at kCheckpoints positions of the chunk (the first symbol at or after every kCheckpointBits),
 // and a correction pass stops at the first checkpoint where it finds itself in the recorded state.
-constexpr int kCheckpointBits = 128;
+constexpr int kCheckpointBits = FTF_JPEG_CHECKPOINT_BITS;
 constexpr int kCheckpoints = kChunkBits / kCheckpointBits - 1;
 struct Checkpoints {
     ScanState* state;     // [kCheckpoints], element i at state[i * stride]
