@@ -726,6 +726,12 @@ def main():
     ap.add_argument("--quick", action="store_true", help="development A/B runs: skip the CPU baseline and the streaming leg")
     ap.add_argument("--workload", default="inception", choices=["half_plus_two", "normalize", "inception", "jpeg"])
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: whatever libraries print at the C level on the way (NCCL's version banner
+    # under NCCL_DEBUG=VERSION, for one) is sent to stderr, and print() gets the real stdout back
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
