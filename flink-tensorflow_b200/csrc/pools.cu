@@ -44,62 +44,6 @@ maxpool3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ o
     ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
 }
 
-// The same pool with a 2x2 patch of outputs per thread: the four windows cover 5x5 inputs, so a thread issues 25 loads for
-// four outputs where the kernel above issues 36.  Neighbouring windows overlap by a column and a row, and those overlaps
-// were the kernel's cost: it ran at the L2 -> SM fill rate (2.25 input reads per input element), not at HBM's.  Inputs
-// beyond the image are clamped to the last row / column; only outputs that do not exist see them.
-__global__ void __launch_bounds__(256)
-maxpool3x3s2_quad(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int C, int OH, int OW,
-                  int out_ld, int out_off, unsigned long long* tl) {
-    ptx::tl_stamp_min(tl);
-    ptx::pdl_launch_dependents();
-    ptx::pdl_wait();
-    ptx::tl_stamp_min(tl ? tl + 2 : nullptr);
-    const unsigned cg = (unsigned)C / 8u, OH2 = ((unsigned)OH + 1u) / 2u, OW2 = ((unsigned)OW + 1u) / 2u;
-    const unsigned total = (unsigned)n * OH2 * OW2 * cg;
-    const unsigned stride = gridDim.x * blockDim.x;
-    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += stride) {
-        const unsigned g = t % cg, q = t / cg;
-        const unsigned ox = 2u * (q % OW2), rest = q / OW2;
-        const unsigned oy = 2u * (rest % OH2), img = rest / OH2;
-        const __nv_bfloat16* base = in + (size_t)img * H * W * C + g * 8;
-        __nv_bfloat162 acc[2][2][4];
-#pragma unroll
-        for (int ry = 0; ry < 5; ++ry) {
-            const unsigned iy = min(2u * oy + (unsigned)ry, (unsigned)H - 1u);
-            uint4 v[5];
-#pragma unroll
-            for (int cx = 0; cx < 5; ++cx) {
-                const unsigned ix = min(2u * ox + (unsigned)cx, (unsigned)W - 1u);
-                v[cx] = __ldg(reinterpret_cast<const uint4*>(base + ((size_t)iy * W + ix) * C));
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const __nv_bfloat162 c2 = reinterpret_cast<const __nv_bfloat162*>(&v[2])[j];
-                const __nv_bfloat162 h0 = __hmax2(__hmax2(reinterpret_cast<const __nv_bfloat162*>(&v[0])[j],
-                                                          reinterpret_cast<const __nv_bfloat162*>(&v[1])[j]), c2);
-                const __nv_bfloat162 h1 = __hmax2(__hmax2(reinterpret_cast<const __nv_bfloat162*>(&v[3])[j],
-                                                          reinterpret_cast<const __nv_bfloat162*>(&v[4])[j]), c2);
-                if (ry == 0) { acc[0][0][j] = h0; acc[0][1][j] = h1; }
-                else if (ry < 2) { acc[0][0][j] = __hmax2(acc[0][0][j], h0); acc[0][1][j] = __hmax2(acc[0][1][j], h1); }
-                else if (ry == 2) {
-                    acc[0][0][j] = __hmax2(acc[0][0][j], h0); acc[0][1][j] = __hmax2(acc[0][1][j], h1);
-                    acc[1][0][j] = h0; acc[1][1][j] = h1;
-                } else { acc[1][0][j] = __hmax2(acc[1][0][j], h0); acc[1][1][j] = __hmax2(acc[1][1][j], h1); }
-            }
-        }
-#pragma unroll
-        for (int dy = 0; dy < 2; ++dy)
-#pragma unroll
-            for (int dx = 0; dx < 2; ++dx)
-                if (oy + dy < (unsigned)OH && ox + dx < (unsigned)OW) {
-                    const size_t pix = ((size_t)img * OH + oy + dy) * OW + ox + dx;
-                    *reinterpret_cast<uint4*>(out + pix * out_ld + out_off + g * 8) = *reinterpret_cast<uint4*>(acc[dy][dx]);
-                }
-    }
-    ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
-}
-
 // out = bf16(relu(avgpool3x3_s1_p1(pre) * (1/9) + bias)); pre is the fp32 1x1-conv output [n,H,W,C]; taps summed
 // row-major in fp32; divisor 9 at the borders too (count_include_pad).  4 channels per thread; the nine loads are
 // issued together, out-of-image taps read the centre pixel and contribute +0.
@@ -181,17 +125,9 @@ int launch_maxpool3x3s2(const void* in, void* out, int n, int H, int W, int C, i
     const int OH = (H - 3) / 2 + 1, OW = (W - 3) / 2 + 1;
     const long long total = (long long)n * OH * OW * (C / 8);
     if (total >= (1ll << 31)) { if (err) *err = "maxpool3x3s2: tensor too large"; return FTF_INVALID_ARGUMENT; }
-    static const bool single = getenv("FTF_MAXPOOL_SINGLE") != nullptr;       // measurement switch: one output per thread
-    if (single) {
-        const long long want = (total + 255) / 256, cap = grid_cap(s);
-        FTF_CUDA(launch_pdl(maxpool3x3s2, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, H, W, C,
-                            OH, OW, out_ld, out_off, tl), err);
-    } else {
-        const long long quads = (long long)n * ((OH + 1) / 2) * ((OW + 1) / 2) * (C / 8);
-        const long long want = (quads + 255) / 256, cap = grid_cap(s);
-        FTF_CUDA(launch_pdl(maxpool3x3s2_quad, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, H, W,
-                            C, OH, OW, out_ld, out_off, tl), err);
-    }
+    const long long want = (total + 255) / 256, cap = grid_cap(s);
+    FTF_CUDA(launch_pdl(maxpool3x3s2, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, H, W, C,
+                        OH, OW, out_ld, out_off, tl), err);
     count_launch();
     return FTF_OK;
 }
