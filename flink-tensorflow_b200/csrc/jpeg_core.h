@@ -347,11 +347,26 @@ FTF_HD void idct_block(const int16_t* __restrict__ coef, const uint16_t* __restr
         idct_1d(ws[r * 8], ws[r * 8 + 1], ws[r * 8 + 2], ws[r * 8 + 3], ws[r * 8 + 4], ws[r * 8 + 5], ws[r * 8 + 6],
                 ws[r * 8 + 7], o);
         uint32_t lo = 0, hi = 0;
+#ifdef __CUDA_ARCH__
+        // idct_range_limit without its select chain: the table depends on x modulo 1024 only, and for the representative
+        // y of x in [-512, 511] it is clamp(y + 128, 0, 255).  y + 128 = (((x + 512) & 1023) - 384), the +512 rides on the
+        // descale's rounding constant, and the clamp is the saturation of the pack instruction.
+        int v[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+            v[c] = (int)((((int32_t)((uint32_t)o[c] + ((1u << 17) + (512u << 18)))) >> 18) & 1023) - 384;
+        uint32_t t;
+        asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(v[3]), "r"(v[2]), "r"(0));
+        asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(lo) : "r"(v[1]), "r"(v[0]), "r"(t));
+        asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(t) : "r"(v[7]), "r"(v[6]), "r"(0));
+        asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(hi) : "r"(v[5]), "r"(v[4]), "r"(t));
+#else
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             lo |= idct_range_limit((o[c] + (1 << 17)) >> 18) << (8 * c);
             hi |= idct_range_limit((o[4 + c] + (1 << 17)) >> 18) << (8 * c);
         }
+#endif
         uint32_t* row = reinterpret_cast<uint32_t*>(out + (int64_t)r * stride);
         row[0] = lo;
         row[1] = hi;
@@ -404,7 +419,8 @@ FTF_HD uint32_t load_u32(const uint8_t* p) { return *reinterpret_cast<const uint
 // The chroma samples of the 8 pixels (y, x0 .. x0+7), x0 a multiple of 8: chroma_at for each of them, with the plane
 // read as aligned words and every source sample fetched once.  The triangle filters replicate the edge sample, so the
 // neighbours outside [0, dw) are the clamped ones.
-FTF_HD void chroma8(const uint8_t* __restrict__ pl, int st, int dw, int dh, int hs, int vs, int y, int x0, int (&o)[8]) {
+template <int hs, int vs>
+FTF_HD void chroma8(const uint8_t* __restrict__ pl, int st, int dw, int dh, int y, int x0, int (&o)[8]) {
     if (hs == 1) {
         const uint8_t* r = pl + (int64_t)y * st + x0;
         const uint32_t a = load_u32(r), b = load_u32(r + 4);
@@ -461,11 +477,13 @@ FTF_HD void chroma8(const uint8_t* __restrict__ pl, int st, int dw, int dh, int 
 }
 
 // The 8 pixels (y, x0 .. x0+7) of image `im`, x0 a multiple of 8, as 24 RGB bytes (pixels past the width are computed
-// from the planes' padding and dropped by the caller).
-FTF_HD void pixels8_rgb(const ImageDesc& im, const uint8_t* __restrict__ planes, int y, int x0, uint8_t* rgb) {
+// from the planes' padding and dropped by the caller).  One instance per sampling layout (hs x vs luma samples per chroma
+// sample; 0 x 0: one component), so that the layout is not a question asked per sample.
+template <int hs, int vs>
+FTF_HD void pixels8_rgb_t(const ImageDesc& im, const uint8_t* __restrict__ planes, int y, int x0, uint8_t* rgb) {
     const uint8_t* yp = planes + im.plane_off[0] + (int64_t)y * (im.bw[0] * 8) + x0;
     const uint32_t ya = load_u32(yp), yb = load_u32(yp + 4);
-    if (im.ncomp == 1) {
+    if (hs == 0) {
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const uint8_t v = (uint8_t)(((i < 4 ? ya : yb) >> (8 * (i & 3))) & 0xFF);
@@ -474,8 +492,9 @@ FTF_HD void pixels8_rgb(const ImageDesc& im, const uint8_t* __restrict__ planes,
         return;
     }
     int cb[8], cr[8];
-    chroma8(planes + im.plane_off[1], im.bw[1] * 8, im.dw[1], im.dh[1], im.hs, im.vs, y, x0, cb);
-    chroma8(planes + im.plane_off[2], im.bw[2] * 8, im.dw[2], im.dh[2], im.hs, im.vs, y, x0, cr);
+    constexpr int chs = hs == 0 ? 1 : hs, cvs = vs == 0 ? 1 : vs;
+    chroma8<chs, cvs>(planes + im.plane_off[1], im.bw[1] * 8, im.dw[1], im.dh[1], y, x0, cb);
+    chroma8<chs, cvs>(planes + im.plane_off[2], im.bw[2] * 8, im.dw[2], im.dh[2], y, x0, cr);
 #ifdef __CUDA_ARCH__
     // The same arithmetic as ycc_to_rgb with fewer instructions: y enters as y << 16 (one byte permute), the -128 level
     // shifts and the rounding term are constants added once, the >> 16 then yields y + (term >> 16) exactly because
@@ -501,6 +520,13 @@ FTF_HD void pixels8_rgb(const ImageDesc& im, const uint8_t* __restrict__ planes,
 #pragma unroll
     for (int i = 0; i < 8; ++i) ycc_to_rgb((int)(((i < 4 ? ya : yb) >> (8 * (i & 3))) & 0xFF), cb[i], cr[i], rgb + 3 * i);
 #endif
+}
+
+FTF_HD void pixels8_rgb(const ImageDesc& im, const uint8_t* __restrict__ planes, int y, int x0, uint8_t* rgb) {
+    if (im.ncomp == 1) pixels8_rgb_t<0, 0>(im, planes, y, x0, rgb);
+    else if (im.hs == 1) pixels8_rgb_t<1, 1>(im, planes, y, x0, rgb);
+    else if (im.vs == 1) pixels8_rgb_t<2, 1>(im, planes, y, x0, rgb);
+    else pixels8_rgb_t<2, 2>(im, planes, y, x0, rgb);
 }
 
 }  // namespace jpeg
