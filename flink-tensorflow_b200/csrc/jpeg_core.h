@@ -113,10 +113,15 @@ struct BitWindow {
 };
 
 // T.81 F.2.2.3 DECODE on a 32-bit window: code length (0 = no such code) and symbol.
-// lut: the table's lookahead entries, possibly a copy in shared memory (hence a plain load, not a read-only-path one)
+FTF_HD int lookup_long_code(uint32_t w, const HuffTable* __restrict__ t, int* sym);
+// lut: the table's lookahead entries, possibly a copy in shared memory (hence a plain load, not a read-only-path one).
+// The table itself is only needed for codes longer than the lookahead.
 FTF_HD int lookup_symbol(uint32_t w, const uint16_t* lut, const HuffTable* __restrict__ t, int* sym) {
     const uint32_t e = lut[w >> (32 - kLutBits)];
     if (e) { *sym = (int)(e & 0xFF); return (int)(e >> 8); }
+    return lookup_long_code(w, t, sym);
+}
+FTF_HD int lookup_long_code(uint32_t w, const HuffTable* __restrict__ t, int* sym) {
     const int32_t code16 = (int32_t)(w >> 16);
     int l = kLutBits + 1;
     while (l <= 16 && (code16 >> (16 - l)) > FTF_LDG(&t->maxcode[l])) ++l;
@@ -221,15 +226,21 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
         dcp = dc_slot(im, dcv, mcu, b);
     }
     int c = b < nluma ? 0 : b - nluma + 1;
-    const HuffTable* dc = tables + im.dc[c];
-    const HuffTable* ac = tables + im.ac[c];
-    const uint16_t* dcl = luts ? luts + ((2 * c) << kLutBits) : dc->lut;
-    const uint16_t* acl = luts ? luts + ((2 * c + 1) << kLutBits) : ac->lut;
+    // between blocks only the component index is carried: with the lookahead tables in shared memory a symbol needs that
+    // index alone, and the table pointers (one per component and kind) are looked up by the rare long code
     while (pos < limit && (!kWrite || ordinal < total_blocks)) {
         const uint32_t w = bw.at(pos);
         const bool is_dc = k == 0;
         int sym = 0;
-        const int len = lookup_symbol(w, is_dc ? dcl : acl, is_dc ? dc : ac, &sym);
+        int len;
+        if (luts) {
+            const uint32_t e = luts[((2 * c + (is_dc ? 0 : 1)) << kLutBits) + (w >> (32 - kLutBits))];
+            if (e) { sym = (int)(e & 0xFF); len = (int)(e >> 8); }
+            else len = lookup_long_code(w, tables + (is_dc ? im.dc[c] : im.ac[c]), &sym);
+        } else {
+            const HuffTable* t = tables + (is_dc ? im.dc[c] : im.ac[c]);
+            len = lookup_symbol(w, t->lut, t, &sym);
+        }
         if (len == 0 || (is_dc && sym > 15)) {          // no such code / a DC symbol is a bit count
             if (kWrite) { *bad = 1; break; }
             pos += 1;
@@ -260,10 +271,6 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
                 if (kWrite && ++mx == im.mcus_x) { mx = 0; ++my; }
             }
             c = b < nluma ? 0 : b - nluma + 1;
-            dc = tables + im.dc[c];
-            ac = tables + im.ac[c];
-            dcl = luts ? luts + ((2 * c) << kLutBits) : dc->lut;
-            acl = luts ? luts + ((2 * c + 1) << kLutBits) : ac->lut;
             if (kWrite) {
                 blk = block_ptr(im, coef, my, mx, b);
                 dcp = dc_slot(im, dcv, my * im.mcus_x + mx, b);
