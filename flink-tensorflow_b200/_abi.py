@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libftf_b200.so")
+LIB_PATH = os.environ.get("FTF_LIB_PATH") or os.path.join(_HERE, "libftf_b200.so")   # the override serves A/B measurements of two builds
 
 OK, INVALID_ARGUMENT, NOT_FOUND, RESOURCE_EXHAUSTED = 0, 3, 5, 8
 FAILED_PRECONDITION, OUT_OF_RANGE, UNIMPLEMENTED, INTERNAL, VERSION_MISMATCH = 9, 11, 12, 13, 100
