@@ -42,14 +42,14 @@ jpeg_huffman_kernel(const Segment* __restrict__ segs, const ImageDesc* __restric
     __shared__ int s_warp[32];
     // the image's lookahead tables in shared memory ([component][dc, ac]): every symbol starts with a gather from one of
     // them, and 32 lanes gathering 2-byte entries from global memory cost up to 32 L1 wavefronts where shared memory
-    // costs a few bank conflicts; the second-level tables for the long codes come along
-    __shared__ uint16_t s_lut[6 * kLutEntries];
+    // costs a few bank conflicts
+    __shared__ uint16_t s_lut[6 << kLutBits];
     const Segment sg = segs[blockIdx.x];
     const ImageDesc& im = images[sg.image];
     const int T = (int)blockDim.x, tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < im.ncomp * 2 * kLutEntries; i += T) {
-        const int t = i / kLutEntries, c = t >> 1;
-        s_lut[i] = tables[(t & 1) ? im.ac[c] : im.dc[c]].lut[i - t * kLutEntries];
+    for (int i = tid; i < (im.ncomp * 2) << kLutBits; i += T) {
+        const int t = i >> kLutBits, c = t >> 1;
+        s_lut[i] = tables[(t & 1) ? im.ac[c] : im.dc[c]].lut[i & ((1 << kLutBits) - 1)];
     }
     __syncthreads();
     // dynamic shared memory, all indexed by the chunk's position in the wave: exit states, entry states, checkpoint states

@@ -27,14 +27,8 @@ constexpr int kLutBits = 9;
 // One Huffman table, decoder form.  lut: the next kLutBits bits of the stream -> (code length << 8 | symbol), 0 when
 // the code is longer than kLutBits; then the canonical-code walk of T.81 F.2.2.3 over maxcode / valoff.  (Measured: 12-bit
 // tables, 8 KB each, lose more to L1 misses than they save on the walk; 9 bits keep all of a batch's tables L1-resident.)
-constexpr int kSubBits = 16 - kLutBits;      // a second lookup covers the rest of the longest code
-constexpr int kSubTables = 8;
-constexpr int kLutEntries = (1 << kLutBits) + kSubTables * (1 << kSubBits);
 struct HuffTable {
-    // lut[0 .. 2^kLutBits): by the next kLutBits bits.  Bit 15 set: the code is longer, and the low bits name one of
-    // kSubTables second-level tables (they follow, 2^kSubBits entries each, indexed by the next kSubBits bits, entries of
-    // the same form with the full code length); 0: no entry, walk the code lengths.
-    uint16_t lut[kLutEntries];
+    uint16_t lut[1 << kLutBits];
     int32_t maxcode[18];     // largest code of each length (-1: none); [17] = INT32_MAX ends the walk
     int32_t valoff[17];      // index of the first value of that length minus its first code
     uint8_t vals[256];
@@ -123,8 +117,7 @@ FTF_HD int lookup_long_code(uint32_t w, const HuffTable* __restrict__ t, int* sy
 // lut: the table's lookahead entries, possibly a copy in shared memory (hence a plain load, not a read-only-path one).
 // The table itself is only needed for codes longer than the lookahead.
 FTF_HD int lookup_symbol(uint32_t w, const uint16_t* lut, const HuffTable* __restrict__ t, int* sym) {
-    uint32_t e = lut[w >> (32 - kLutBits)];
-    if (e & 0x8000u) e = lut[(1 << kLutBits) + ((e & 0xFFu) << kSubBits) + ((w >> 16) & ((1u << kSubBits) - 1u))];
+    const uint32_t e = lut[w >> (32 - kLutBits)];
     if (e) { *sym = (int)(e & 0xFF); return (int)(e >> 8); }
     return lookup_long_code(w, t, sym);
 }
@@ -213,7 +206,7 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
                               const uint8_t* __restrict__ scan, ScanState st, uint32_t limit, int ordinal, int total_blocks,
                               int16_t* __restrict__ coef, int16_t* __restrict__ dcv, int* n_done, int* bad,
                               Checkpoints cp = Checkpoints{nullptr, nullptr, 0}, ScanState old_exit = ScanState{0, 0, 0},
-                              const uint16_t* luts = nullptr) {      // luts: [component][dc, ac][kLutEntries] copies, or null
+                              const uint16_t* luts = nullptr) {      // luts: [component][dc, ac][1 << kLutBits] copies, or null
     constexpr bool kWrite = kMode == kStore;
     const int bpm = im.ncomp == 1 ? 1 : im.hs * im.vs + 2;
     const int nluma = im.ncomp == 1 ? 1 : im.hs * im.vs;
@@ -241,9 +234,7 @@ FTF_HD ScanState decode_chunk(const Segment& sg, const ImageDesc& im, const Huff
         int sym = 0;
         int len;
         if (luts) {
-            const uint16_t* lut = luts + (2 * c + (is_dc ? 0 : 1)) * kLutEntries;
-            uint32_t e = lut[w >> (32 - kLutBits)];
-            if (e & 0x8000u) e = lut[(1 << kLutBits) + ((e & 0xFFu) << kSubBits) + ((w >> 16) & ((1u << kSubBits) - 1u))];
+            const uint32_t e = luts[((2 * c + (is_dc ? 0 : 1)) << kLutBits) + (w >> (32 - kLutBits))];
             if (e) { sym = (int)(e & 0xFF); len = (int)(e >> 8); }
             else len = lookup_long_code(w, tables + (is_dc ? im.dc[c] : im.ac[c]), &sym);
         } else {

@@ -35,28 +35,15 @@ bool valid_spec(const HuffSpec& sp) {
 void build_table(const HuffSpec& sp, HuffTable* t) {
     memset(t, 0, sizeof(*t));
     memcpy(t->vals, sp.values, (size_t)sp.nvalues);
-    int code = 0, k = 0, subs = 0;
+    int code = 0, k = 0;
     for (int l = 1; l <= 16; ++l) {
         const int cnt = sp.counts[l];
         t->valoff[l] = k - code;
-        for (int i = 0; i < cnt; ++i) {
-            const uint16_t e = (uint16_t)((l << 8) | sp.values[k + i]);
-            if (l <= kLutBits) {
+        if (l <= kLutBits) {
+            for (int i = 0; i < cnt; ++i) {
                 const int first = (code + i) << (kLutBits - l), span = 1 << (kLutBits - l);
+                const uint16_t e = (uint16_t)((l << 8) | sp.values[k + i]);
                 for (int j = 0; j < span; ++j) t->lut[first + j] = e;
-            } else {
-                // a long code: its first kLutBits bits select a second-level table, the rest an entry span in it
-                const int prefix = (code + i) >> (l - kLutBits);
-                uint16_t& top = t->lut[prefix];
-                if (top == 0) {
-                    if (subs == kSubTables) continue;              // no room: this prefix is left to the code walk
-                    top = (uint16_t)(0x8000 | subs++);
-                }
-                if (!(top & 0x8000)) continue;
-                const int rest = (code + i) & ((1 << (l - kLutBits)) - 1);
-                const int first = rest << (16 - l), span = 1 << (16 - l);
-                uint16_t* sub = t->lut + (1 << kLutBits) + ((top & 0xFF) << kSubBits);
-                for (int j = 0; j < span; ++j) sub[first + j] = e;
             }
         }
         code += cnt;
