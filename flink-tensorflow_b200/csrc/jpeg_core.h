@@ -54,7 +54,7 @@ struct ImageDesc {
 #define FTF_JPEG_CHUNK_BITS 1024
 #endif
 #ifndef FTF_JPEG_CHECKPOINT_BITS
-#define FTF_JPEG_CHECKPOINT_BITS 128
+#define FTF_JPEG_CHECKPOINT_BITS 256      /* measured: 256 (three checkpoints) beats 128 and 512 by 1-2 % */
 #endif
 constexpr int kChunkBits = FTF_JPEG_CHUNK_BITS;   // the unit of parallel entropy decoding (see decode_chunk)
 
