@@ -11,7 +11,7 @@
 //   top = tl + (tr-tl)*xl; bot = bl + (br-bl)*xl; v = top + (bot-top)*yl; out = (v-mean)/scale
 //
 // Layout: in u8 [n,in_h,in_w,3] (HWC rows of in_w*3 bytes), out f32/bf16 [n,out_h,out_w,3].
-// HBM-bound: each input byte and each output element crosses HBM once.  A CTA owns a band of `th`
+// HBM-bound: each input byte and each output element crosses HBM once.  A CTA owns a band of `th` (5)
 // full-width output rows of one image: the input rows the band touches are fetched by TMA
 // (cp.async.bulk.tensor, <=256-byte wide column chunks of a 3-D tensor map) into shared memory, the
 // 4-tap lerp reads shared memory, and the band's output is one contiguous, fully coalesced range.
@@ -48,6 +48,7 @@ struct ResizeParams {
     int n_chunks;
     int chunk_stride;        // bytes between chunk regions in smem (128-byte multiple)
     long long n;             // images
+    int stages;              // shared-memory stages per CTA (2 or 3)
     int step_img, step_band; // gridDim.x bands further on: += step_img images, += step_band bands (wrapping at `bands`)
 };
 
@@ -111,11 +112,11 @@ __device__ __forceinline__ void run_bands(const ResizeParams& p, OutT* __restric
     };
     int it = 0;
     int img = (int)(blockIdx.x / (unsigned)p.bands), band = (int)(blockIdx.x % (unsigned)p.bands);
-    int nimg = img, nband = band;                      // the band two steps ahead, which warp 0 fetches
-    advance(nimg, nband); advance(nimg, nband);
+    int nimg = img, nband = band;                      // the band p.stages steps ahead, which warp 0 fetches
+    for (int s = 0; s < p.stages; ++s) advance(nimg, nband);
+    int stage = 0;
+    uint32_t phase = 0;
     for (unsigned blk = blockIdx.x; blk < (unsigned)total_bands; blk += gridDim.x, ++it, advance(img, band), advance(nimg, nband)) {
-        const int stage = it & 1;
-        const uint32_t phase = (uint32_t)((it >> 1) & 1);
         const int oy0 = band * p.th;
         const int rows = min(p.th, p.out_h - oy0);
         const int iy0 = (int)__fmul_rn((float)oy0, p.hs);  // first input row of the band
@@ -138,28 +139,49 @@ __device__ __forceinline__ void run_bands(const ResizeParams& p, OutT* __restric
             rows_sm[threadIdx.x & 31] = t;
         }
         __syncwarp();
+        // When output row r+1 starts at the input row where row r ended (ylo(r+1) == yhi(r): four rows in ten at this scale),
+        // its upper horizontal lerp is the previous row's lower one, computed from the same bytes by the same operations:
+        // it is carried over instead of being loaded and computed again.
+        float carry[kN];
+        uint32_t prev_r1 = 0xffffffffu;
         for (int r = 0; r < rows; ++r, orow += ow3) {
             const uint4 t = rows_sm[r];
             const uint32_t r0 = t.x, r1 = t.y;
             const float yl = __uint_as_float(t.z);
+            if (r0 == prev_r1) {
 #pragma unroll
-            for (int j = 0; j < kN; ++j) {
-                const float mtl = __uint_as_float(0x4B000000u | lds_u8(r0 + off_lo[j])), mtr = __uint_as_float(0x4B000000u | lds_u8(r0 + off_hi[j]));
-                const float mbl = __uint_as_float(0x4B000000u | lds_u8(r1 + off_lo[j])), mbr = __uint_as_float(0x4B000000u | lds_u8(r1 + off_hi[j]));
-                const float tl = __fsub_rn(mtl, 8388608.0f), bl = __fsub_rn(mbl, 8388608.0f);
-                const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(mtr, mtl), xl[j]));
-                const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(mbr, mbl), xl[j]));
-                const OutT v = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
-                if (!kPartial || j < kN - 1 || live[j]) orow[j * kBS] = v;     // only a warp's last group can hold dead lanes
+                for (int j = 0; j < kN; ++j) {
+                    const float mbl = __uint_as_float(0x4B000000u | lds_u8(r1 + off_lo[j])), mbr = __uint_as_float(0x4B000000u | lds_u8(r1 + off_hi[j]));
+                    const float bl = __fsub_rn(mbl, 8388608.0f);
+                    const float top = carry[j];
+                    const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(mbr, mbl), xl[j]));
+                    carry[j] = bot;
+                    const OutT v = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
+                    if (!kPartial || j < kN - 1 || live[j]) orow[j * kBS] = v;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < kN; ++j) {
+                    const float mtl = __uint_as_float(0x4B000000u | lds_u8(r0 + off_lo[j])), mtr = __uint_as_float(0x4B000000u | lds_u8(r0 + off_hi[j]));
+                    const float mbl = __uint_as_float(0x4B000000u | lds_u8(r1 + off_lo[j])), mbr = __uint_as_float(0x4B000000u | lds_u8(r1 + off_hi[j]));
+                    const float tl = __fsub_rn(mtl, 8388608.0f), bl = __fsub_rn(mbl, 8388608.0f);
+                    const float top = __fadd_rn(tl, __fmul_rn(__fsub_rn(mtr, mtl), xl[j]));
+                    const float bot = __fadd_rn(bl, __fmul_rn(__fsub_rn(mbr, mbl), xl[j]));
+                    carry[j] = bot;
+                    const OutT v = to_out<OutT>(finish<kMulRecip>(top, bot, yl, p));
+                    if (!kPartial || j < kN - 1 || live[j]) orow[j * kBS] = v;     // only a warp's last group can hold dead lanes
+                }
             }
+            prev_r1 = r1;
         }
-        // this warp is done with the stage; warp 0 refills it (band it+2) once every warp has said so
+        // this warp is done with the stage; warp 0 refills it (band it+stages) once every warp has said so
         __syncwarp();
         if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&empty[stage]);
-        if (threadIdx.x < 32 && (unsigned long long)blk + 2ull * gridDim.x < (unsigned long long)total_bands) {
+        if (threadIdx.x < 32 && (unsigned long long)blk + (unsigned long long)p.stages * gridDim.x < (unsigned long long)total_bands) {
             ptx::mbar_wait(&empty[stage], phase);
             issue(nimg, nband, stage);
         }
+        if (++stage == p.stages) { stage = 0; phase ^= 1u; }
     }
 }
 
@@ -168,19 +190,16 @@ __global__ void __launch_bounds__(kBS, (kBS <= 256 ? 4 : 3))
 resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p, long long total_bands,
                      int stage_bytes) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t full[2], empty[2];
+    __shared__ __align__(8) uint64_t full[3], empty[3];
     __shared__ uint4 rows_all[(kBS / 32) * 8];          // per warp: the row terms of its current band
     uint4* rows_sm = rows_all + (threadIdx.x >> 5) * 8;
     if (threadIdx.x == 0) {
-        ptx::mbar_init(&full[0], 1);
-        ptx::mbar_init(&full[1], 1);
-        ptx::mbar_init(&empty[0], kBS / 32);
-        ptx::mbar_init(&empty[1], kBS / 32);
+        for (int s = 0; s < 3; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], kBS / 32); }
         ptx::fence_mbar_init();
     }
     __syncthreads();
-    if (threadIdx.x < 32) {                                     // the first two bands
-        for (int s = 0; s < 2; ++s) {
+    if (threadIdx.x < 32) {                                     // the first bands, one per stage
+        for (int s = 0; s < p.stages; ++s) {
             const long long blk = (long long)blockIdx.x + (long long)s * gridDim.x;
             if (blk >= total_bands) break;
             const long long img = blk / p.bands;
@@ -288,8 +307,8 @@ int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool 
 #define FTF_K2_LAUNCH(BS)                                                                                              \
         {                                                                                                              \
             auto kern = recip ? resize_norm_band_tma<BS, true, OutT> : resize_norm_band_tma<BS, false, OutT>;          \
-            FTF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem)), err);   \
-            kern<<<grid, BS, 2 * smem, s>>>(*tmap, out, p, bands, (int)smem);                                          \
+            FTF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(p.stages * smem)), err); \
+            kern<<<grid, BS, p.stages * smem, s>>>(*tmap, out, p, bands, (int)smem);                                   \
         }
         switch (bs) {
         case 224: FTF_K2_LAUNCH(224) break;
@@ -343,12 +362,16 @@ int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out
         p.n_chunks = (int)((row_bytes + 255) / 256);
         p.cw = (int)(((row_bytes + p.n_chunks - 1) / p.n_chunks + 15) / 16 * 16);
         bool fits = false;
-        for (int th = 8; th >= 1; th /= 2) {
+        // FTF_K2_TH / FTF_K2_STAGES: measurement switches (rows per band, stages per CTA)
+        static const int th_max = getenv("FTF_K2_TH") ? atoi(getenv("FTF_K2_TH")) : 5;   // measured on 480->299 rows: 8: 0.101 ms, 7: 0.099, 6: 0.096, 5: 0.092, 4: 0.095, 3: 0.104
+        static const int stages = getenv("FTF_K2_STAGES") ? atoi(getenv("FTF_K2_STAGES")) : 2;
+        p.stages = stages == 3 ? 3 : 2;
+        for (int th = th_max; th >= 1; th /= 2) {
             p.th = th < out_h ? th : out_h;
             p.br = band_input_rows(p.th, in_h, out_h, p.hs);
             p.chunk_stride = (p.cw * p.br + 127) / 128 * 128;
             smem = (size_t)p.chunk_stride * p.n_chunks;
-            if (p.br <= 256 && smem <= 27 * 1024) { fits = true; break; }      // two stages x four CTAs per SM
+            if (p.br <= 256 && smem * p.stages <= 54 * 1024) { fits = true; break; }      // stages x four CTAs per SM
         }
         p.bands = (out_h + p.th - 1) / p.th;
         p.inv_cw = 1.0f / (float)p.cw;
