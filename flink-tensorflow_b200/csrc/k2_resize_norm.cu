@@ -185,8 +185,11 @@ __device__ __forceinline__ void run_bands(const ResizeParams& p, OutT* __restric
     }
 }
 
+#ifndef FTF_K2_CTAS
+#define FTF_K2_CTAS 4          /* persistent CTAs per SM the band kernel is built for */
+#endif
 template <int kBS, bool kMulRecip, typename OutT>
-__global__ void __launch_bounds__(kBS, (kBS <= 256 ? 4 : 3))
+__global__ void __launch_bounds__(kBS, (kBS <= 256 ? FTF_K2_CTAS : 3))
 resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict__ out, const ResizeParams p, long long total_bands,
                      int stage_bytes) {
     extern __shared__ __align__(128) uint8_t smem[];
@@ -301,7 +304,7 @@ int launch_typed(const uint8_t* in, ResizeParams p, OutT* out, bool recip, bool 
             if (waste * bs < best_waste * cand) { best_waste = waste; bs = cand; }        // relative waste
         }
         const long long bands = p.n * p.bands;
-        const long long resident = (long long)sms * 4;                                    // persistent CTAs, two stages each
+        const long long resident = (long long)sms * FTF_K2_CTAS;                          // persistent CTAs, two stages each
         const unsigned grid = (unsigned)(bands < resident ? bands : resident);
         p.step_img = (int)(grid / (unsigned)p.bands); p.step_band = (int)(grid % (unsigned)p.bands);
 #define FTF_K2_LAUNCH(BS)                                                                                              \
@@ -371,7 +374,7 @@ int launch_resize_norm(const uint8_t* in, int64_t n, int in_h, int in_w, int out
             p.br = band_input_rows(p.th, in_h, out_h, p.hs);
             p.chunk_stride = (p.cw * p.br + 127) / 128 * 128;
             smem = (size_t)p.chunk_stride * p.n_chunks;
-            if (p.br <= 256 && smem * p.stages <= 54 * 1024) { fits = true; break; }      // stages x four CTAs per SM
+            if (p.br <= 256 && smem * p.stages <= (216 / FTF_K2_CTAS) * 1024) { fits = true; break; }      // stages x CTAs per SM
         }
         p.bands = (out_h + p.th - 1) / p.th;
         p.inv_cw = 1.0f / (float)p.cw;
