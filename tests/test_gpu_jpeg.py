@@ -199,6 +199,21 @@ def test_normalization_model_takes_image_files(ftf, oracle):
         m.close()
 
 
+def test_camera_sized_file(ftf, dev, oracle):
+    """A 3-megapixel file (several waves of chunks per Huffman CTA, the direct resize kernel behind it) against the oracle."""
+    rng = np.random.default_rng(31)
+    f = _jpeg(_photo(rng, 1500, 2000, noise=14.0), quality=90)
+    want = oracle.jpeg_decode(f)
+    assert np.array_equal(dev.decode_jpeg([f])[0].cpu().numpy(), want)
+    m = ftf.ImageNormalization()
+    m.open()
+    try:
+        with m.normalize(ftf.bytes_to_tensor(f)) as out:
+            assert np.array_equal(_bits(out.to_array()), _bits(oracle.resize_bilinear_norm_u8(want[None], 224, 224, 117.0, 1.0)))
+    finally:
+        m.close()
+
+
 def test_file_records_through_submit_poll(ftf, oracle):
     """One JPEG file per record through the micro-batched path: order kept, values equal the oracle's."""
     rng = np.random.default_rng(23)
