@@ -174,7 +174,7 @@ FTF_HD int16_t dc_of_block(const ImageDesc& im, const int16_t* __restrict__ dcv,
 }
 
 // Parallel entropy decoding.  A Huffman stream has no index, but a decoder started at a wrong place falls into step with
-// the true one after a few symbols, so a segment is cut into chunks of kChunkBits and every chunk gets a thread:
+// the true one after a while (one to two kilobits on photographs: it also has to find its place inside the MCU), so a segment is cut into chunks of kChunkBits and every chunk gets a thread:
 //   1. each thread decodes its chunk from a guessed state (the chunk's first bit, start of an MCU) and publishes the state
 //      it leaves the chunk in -- chunk 0 starts from the true state;
 //   2. a thread whose predecessor published a state other than the one it started from decodes again from that state;
@@ -186,8 +186,7 @@ FTF_HD int16_t dc_of_block(const ImageDesc& im, const int16_t* __restrict__ dcv,
 // skipped one bit at a time.  kWrite = true: also stores coefficients for blocks [ordinal, total_blocks) of the segment,
 // (DC differences go to the DC array, see dc_slot) and reports a pattern that is no code, or a run past the 64th
 // coefficient, through *bad.
-// Correction passes rarely need the whole chunk: the re-started decoder usually meets the path of the previous attempt
-// after a few symbols, and from there on everything (exit state, blocks completed) is already known.  Every attempt
+// Correction passes do not always need the whole chunk: once the re-started decoder meets the path of the previous attempt, everything (exit state, blocks completed) is already known.  Every attempt
 // therefore leaves its state at kCheckpoints positions of the chunk (the first symbol at or after every kCheckpointBits),
 // and a correction pass stops at the first checkpoint where it finds itself in the recorded state.
 constexpr int kCheckpointBits = FTF_JPEG_CHECKPOINT_BITS;
@@ -450,18 +449,21 @@ FTF_HD void chroma8(const uint8_t* __restrict__ pl, int st, int dw, int dh, int 
     const uint8_t* r0 = pl + (int64_t)cy * st;
     const uint8_t* r1 = pl + (int64_t)ny * st;
     int s[6];                                // column terms of samples cx0-1 .. cx0+4
-    if (cx0 >= 1 && cx0 + 4 <= dw - 1) {
+    if (cx0 + 3 <= dw - 1) {
+        // the four samples in the middle as one word; the two outer neighbours by clamped index, without a branch: the
+        // first and the last thread of every row would otherwise drag their whole warps through the byte-wise path
         const uint32_t a = load_u32(r0 + cx0), b = load_u32(r1 + cx0);
+        const int cl = cx0 >= 1 ? cx0 - 1 : 0, cr = cx0 + 4 <= dw - 1 ? cx0 + 4 : dw - 1;
         if (vs == 2) {
 #pragma unroll
             for (int i = 0; i < 4; ++i) s[1 + i] = 3 * (int)((a >> (8 * i)) & 0xFF) + (int)((b >> (8 * i)) & 0xFF);
-            s[0] = 3 * r0[cx0 - 1] + r1[cx0 - 1];
-            s[5] = 3 * r0[cx0 + 4] + r1[cx0 + 4];
+            s[0] = 3 * r0[cl] + r1[cl];
+            s[5] = 3 * r0[cr] + r1[cr];
         } else {
 #pragma unroll
             for (int i = 0; i < 4; ++i) s[1 + i] = (int)((a >> (8 * i)) & 0xFF);
-            s[0] = r0[cx0 - 1];
-            s[5] = r0[cx0 + 4];
+            s[0] = r0[cl];
+            s[5] = r0[cr];
         }
     } else {
 #pragma unroll
