@@ -172,7 +172,10 @@ jpeg_dc_kernel(const Segment* __restrict__ segs, int nseg, const ImageDesc* __re
     }
 }
 
-__global__ void __launch_bounds__(128)
+#ifndef FTF_J2_MINBLOCKS
+#define FTF_J2_MINBLOCKS 1
+#endif
+__global__ void __launch_bounds__(128, FTF_J2_MINBLOCKS)
 jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restrict__ quant,
                  const int16_t* __restrict__ coef, const int16_t* __restrict__ dcv, uint8_t* __restrict__ planes) {
     const ImageDesc& im = images[blockIdx.y];
@@ -200,7 +203,10 @@ jpeg_idct_kernel(const ImageDesc* __restrict__ images, const uint16_t* __restric
     idct_block(cf, q, planes + im.plane_off[c] + ((int64_t)by * 8 * bw + bx) * 8, bw * 8);
 }
 
-__global__ void __launch_bounds__(256)
+#ifndef FTF_J3_MINBLOCKS
+#define FTF_J3_MINBLOCKS 8          /* 32 registers, no spills: measured 179 -> 141 us against 40 registers / 6 CTAs per SM */
+#endif
+__global__ void __launch_bounds__(256, FTF_J3_MINBLOCKS)
 jpeg_colour_kernel(const ImageDesc* __restrict__ images, const uint8_t* __restrict__ planes, uint8_t* __restrict__ rgb) {
     const ImageDesc& im = images[blockIdx.y];
     const int groups = (im.width + 7) >> 3;
