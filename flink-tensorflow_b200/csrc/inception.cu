@@ -506,7 +506,9 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
         if (m.tl_after > 0) m.tl_dev = (unsigned long long*)m.dev_alloc(m.ops.size() * 4 * 8, true);
         if (m.rc) return m.rc;
     }
-    FTF_CUDA(cudaDeviceSynchronize(), err);
+    // the uploads above went through the legacy default stream; wait for that stream only: a device-wide synchronisation
+    // is refused (and breaks the capture) while another runner's thread is recording its CUDA graph on this GPU
+    FTF_CUDA(cudaStreamSynchronize(cudaStreamLegacy), err);
     m.err = nullptr;
     net->classes_ = num_classes; net->max_batch_ = max_batch;
     *out = std::move(net);

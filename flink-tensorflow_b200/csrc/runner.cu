@@ -311,7 +311,10 @@ int set_device(ftf_runner* r) {
 
 void destroy_runner(ftf_runner* r) {
     cudaSetDevice(r->device);
-    cudaDeviceSynchronize();
+    // wait for this runner's own streams, not for the device: other runners on the GPU may be recording a CUDA graph, and a
+    // device-wide synchronisation from this thread would be refused and would invalidate their capture
+    for (auto& s : r->slots) if (s.stream) cudaStreamSynchronize(s.stream);
+    if (r->net_stream) cudaStreamSynchronize(r->net_stream);
     r->net.reset();
     for (auto& s : r->slots) {
         s.h_in.free_now(); s.d_in.free_now(); s.d_img.free_now();
