@@ -317,11 +317,16 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
 
     def submit(i):
         slot = i % n_buf
-        if wire:                                               # parse the wire image where it lies; the payload is not copied
-            _check(lib.ftf_tv_decode(wire_ptrs[slot], wlen, C.byref(decoded), dims_buf), r.handle)
-            _check(lib.ftf_submit(r.handle, i, C.byref(decoded)), r.handle)
-        else:
-            _check(lib.ftf_submit(r.handle, i, C.byref(recs[slot])), r.handle)
+        while True:
+            if wire:                                           # parse the wire image where it lies; the payload is not copied
+                _check(lib.ftf_tv_decode(wire_ptrs[slot], wlen, C.byref(decoded), dims_buf), r.handle)
+                rc = lib.ftf_submit(r.handle, i, C.byref(decoded))
+            else:
+                rc = lib.ftf_submit(r.handle, i, C.byref(recs[slot]))
+            if rc != 8:                                        # RESOURCE_EXHAUSTED: every slot holds undelivered results
+                _check(rc, r.handle)
+                return
+            drain(True)                                        # take what is ready, then offer the record again
     keys = (C.c_char_p * 2)(b"top_k_indices", b"top_k_scores")
     tags = (C.c_uint64 * 256)()
     outs = (FtfTensor * 512)()
