@@ -317,13 +317,13 @@ def test_micro_batched_records_keep_order_and_values(ftf, oracle, model_dir):
 
 def test_micro_batch_deadline_and_images(ftf, oracle):
     import time
-    cfg = ftf.default_config(max_batch=8, max_delay_us=1000, out_h=32, out_w=24, mean=117.0, scale=1.0)
+    cfg = ftf.default_config(max_batch=8, max_delay_us=100000, out_h=32, out_w=24, mean=117.0, scale=1.0)   # 100 ms: a busy box must not close the batch early
     r = ftf.Runner("builtin:image_normalization", None, None, cfg)
     img = _images(np.random.default_rng(71), 11, 60, 80)
     for i in range(3):
         r.submit(100 + i, ftf.TensorValue.from_array(img[i]))
     assert r.poll() == []                                              # batch still open, deadline not reached
-    time.sleep(0.01)
+    time.sleep(0.15)
     res = []
     while len(res) < 3:                                                # deadline passed: poll launches the short batch
         res += r.poll()
