@@ -713,7 +713,10 @@ def run_ours(args):
                          "traffic": traffic, "peak_source": pk["src"] + (" (sustained)" if wl == "inception" else ""),
                          **({"frac_of_nominal_8TBps": achieved / 8000.0} if wl != "inception" else
                             {"frac_of_burst": achieved / pk["tf_burst"], "scope": "whole step (all kernels), algorithmic FLOPs"}),
-                         "kernel_ms": ms_step},
+                         "kernel_ms": ms_step,
+                         **({"scope": "whole four-kernel step, file bytes in + RGB bytes out; the dominant kernel (Huffman, 3/4 of the step) "
+                                      "is bound by issue slots and its serial correction chain, not by bytes (profiles/r01_jpeg_notes.md)"}
+                            if wl == "jpeg" else {})},
             "e2e": e2e,
             "gpu_launches": gpu_launches, "clocks": clk.summary(), "cpu_baseline": cpu}
     line.update(extra)
