@@ -430,6 +430,31 @@ def blocking_two_subtasks(ftf, lib, np, device, seconds=1.5):
             "api": "ftf_run (C ABI) from two task threads with one runner each on one GPU (two Flink slots per GPU)"}
 
 
+def bind_to_gpu_numa_node(torch, device):
+    """Runs this rank (and so its pinned staging buffers, which are placed on first touch) on the CPUs of the NUMA node its
+    GPU hangs off (the one shared resource of the record-sharded path is host memory / PCIe).  With eight ranks
+    feeding 44 GB/s each, records that sit on the other socket cross the inter-socket link on their way to the GPU.
+    Returns what it did, for the bench line."""
+    if os.environ.get("FTF_BENCH_NO_NUMA"):
+        return "off (FTF_BENCH_NO_NUMA)"
+    try:
+        pr = torch.cuda.get_device_properties(device)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        base = "/sys/bus/pci/devices/" + bdf
+        node = int(open(base + "/numa_node").read())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "no local CPUs allowed"
+        os.sched_setaffinity(0, cpus)
+        return f"node {node}, {len(cpus)} cpus"
+    except Exception as e:  # noqa: BLE001  (no sysfs entry, container without the attribute: run unbound)
+        return f"unavailable ({type(e).__name__})"
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -442,6 +467,8 @@ def run_ours(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the runner has no CPU path")
     torch.cuda.set_device(local_rank)
+    # one rank alone has the host to itself (and the CPU baseline below wants every core): bind only when ranks share it
+    numa = bind_to_gpu_numa_node(torch, local_rank) if world > 1 else "not bound (single rank)"
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -718,7 +745,7 @@ def run_ours(args):
                                       "is bound by issue slots and its serial correction chain, not by bytes (profiles/r01_jpeg_notes.md)"}
                             if wl == "jpeg" else {})},
             "e2e": e2e,
-            "gpu_launches": gpu_launches, "clocks": clk.summary(), "cpu_baseline": cpu}
+            "gpu_launches": gpu_launches, "clocks": clk.summary(), "cpu_baseline": cpu, "host_numa_binding": numa}
     line.update(extra)
     print(json.dumps(line), flush=True)
     if world > 1:
