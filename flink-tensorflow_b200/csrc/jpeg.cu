@@ -6,16 +6,16 @@
 //   J1a jpeg_huffman_kernel  one CTA per independently decodable segment (restart interval, else the whole scan), one
 //                            thread per 1024-bit chunk of it: every chunk is decoded from a guessed state, the guesses
 //                            are corrected along the chain until they are the true states (a Huffman decoder started
-//                            in the wrong place falls into step after a few symbols), then a last pass scatters the
-//                            coefficients (de-zigzagged) into a zeroed int16 buffer.  Canonical Huffman decode with a
-//                            9-bit lookahead table on a byte-unstuffed stream (the host removes the stuffing while it
-//                            copies the file into pinned memory).
+//                            in the wrong place falls into step with the true one after a kilobit or two), then a last
+//                            pass scatters the coefficients (de-zigzagged) into a zeroed int16 buffer.  Canonical
+//                            Huffman decode with 9-bit lookahead tables (copies in shared memory) on a byte-unstuffed
+//                            stream (the host removes the stuffing while it copies the file into pinned memory).
 //   J1b jpeg_dc_kernel       DC differences -> DC values: warp scan per (segment, component).
 //   J2 jpeg_idct_kernel      one thread per 8x8 block: dequantise + libjpeg's integer slow IDCT, entirely in
 //                            registers, 16-byte coefficient loads, 8-byte row stores into the component plane.
 //   J3 jpeg_colour_kernel    one thread per 8 pixels: planes read as aligned words, triangle-filter chroma upsampling
-//                            (2x1, 2x2) with every source sample fetched once, fixed-point YCbCr -> RGB, six 32-bit
-//                            stores of packed RGB.
+//                            (2x1, 2x2) with every source sample fetched once, fixed-point YCbCr -> RGB packed with
+//                            saturation, six 32-bit stores; 32 registers, eight CTAs per SM (it waits on its loads).
 // Integer arithmetic throughout: results are bit-identical to libjpeg(-turbo), checked against oracle/jpeg_oracle.c
 // and the Pillow-made fixtures in tests/golden/jpeg.
 #include "jpeg.h"
