@@ -147,3 +147,17 @@ def test_damaged_files_never_hang_or_crash_the_kernel_functions(emu, cases, ftf)
             assert rc in (0, 3)
             decoded += 1
     assert decoded > 100 and refused > 0
+
+
+def test_decoder_has_no_cpu_path(ftf):
+    """Without a CUDA device the batch decoder cannot even be created: FAILED_PRECONDITION, loudly."""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from flink_tensorflow_b200 import _abi
+    lib = _abi.load_library()
+    h = C.c_void_p()
+    rc = lib.ftf_jpeg_batch_create(0, C.byref(h))
+    assert rc == _abi.FAILED_PRECONDITION and not h.value
+    assert b"no CPU path" in lib.ftf_jpeg_batch_error(None)
+    lib.ftf_jpeg_batch_destroy(None)                          # NULL-safe
