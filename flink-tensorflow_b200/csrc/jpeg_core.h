@@ -306,24 +306,29 @@ FTF_HD void dc_range(const Segment& sg, const ImageDesc& im, int c, int64_t* fir
 }
 
 // ---- inverse DCT: libjpeg's integer "slow" method (13-bit constants, first pass keeps 2 extra bits) -----------------
+// The sums and products are formed on unsigned words: a damaged file can hold coefficient x quantiser products that do not
+// fit 32 bits (libjpeg computes in 64), and the result for such a file should be garbage, not undefined behaviour; for every
+// value a real image produces the arithmetic is the same.
 FTF_HD void idct_1d(const int32_t in0, const int32_t in1, const int32_t in2, const int32_t in3, const int32_t in4,
                     const int32_t in5, const int32_t in6, const int32_t in7, int32_t (&o)[8]) {
-    int32_t z1 = (in2 + in6) * 4433;
-    const int32_t tmp2 = z1 + in6 * (-15137);
-    const int32_t tmp3 = z1 + in2 * 6270;
-    const int32_t tmp0 = (int32_t)((uint32_t)(in0 + in4) << 13);
-    const int32_t tmp1 = (int32_t)((uint32_t)(in0 - in4) << 13);
-    const int32_t e0 = tmp0 + tmp3, e3 = tmp0 - tmp3, e1 = tmp1 + tmp2, e2 = tmp1 - tmp2;
-    int32_t t0 = in7, t1 = in5, t2 = in3, t3 = in1;
+    typedef uint32_t u32;
+    const u32 x0 = (u32)in0, x1 = (u32)in1, x2 = (u32)in2, x3 = (u32)in3, x4 = (u32)in4, x5 = (u32)in5, x6 = (u32)in6, x7 = (u32)in7;
+    u32 z1 = (x2 + x6) * 4433u;
+    const u32 tmp2 = z1 + x6 * (u32)(-15137);
+    const u32 tmp3 = z1 + x2 * 6270u;
+    const u32 tmp0 = (x0 + x4) << 13;
+    const u32 tmp1 = (x0 - x4) << 13;
+    const u32 e0 = tmp0 + tmp3, e3 = tmp0 - tmp3, e1 = tmp1 + tmp2, e2 = tmp1 - tmp2;
+    u32 t0 = x7, t1 = x5, t2 = x3, t3 = x1;
     z1 = t0 + t3;
-    int32_t z2 = t1 + t2, z3 = t0 + t2, z4 = t1 + t3;
-    const int32_t z5 = (z3 + z4) * 9633;
-    t0 *= 2446; t1 *= 16819; t2 *= 25172; t3 *= 12299;
-    z1 *= -7373; z2 *= -20995; z3 *= -16069; z4 *= -3196;
+    u32 z2 = t1 + t2, z3 = t0 + t2, z4 = t1 + t3;
+    const u32 z5 = (z3 + z4) * 9633u;
+    t0 *= 2446u; t1 *= 16819u; t2 *= 25172u; t3 *= 12299u;
+    z1 *= (u32)(-7373); z2 *= (u32)(-20995); z3 *= (u32)(-16069); z4 *= (u32)(-3196);
     z3 += z5; z4 += z5;
     t0 += z1 + z3; t1 += z2 + z4; t2 += z2 + z3; t3 += z1 + z4;
-    o[0] = e0 + t3; o[7] = e0 - t3; o[1] = e1 + t2; o[6] = e1 - t2;
-    o[2] = e2 + t1; o[5] = e2 - t1; o[3] = e3 + t0; o[4] = e3 - t0;
+    o[0] = (int32_t)(e0 + t3); o[7] = (int32_t)(e0 - t3); o[1] = (int32_t)(e1 + t2); o[6] = (int32_t)(e1 - t2);
+    o[2] = (int32_t)(e2 + t1); o[5] = (int32_t)(e2 - t1); o[3] = (int32_t)(e3 + t0); o[4] = (int32_t)(e3 - t0);
 }
 
 FTF_HD uint32_t idct_range_limit(int32_t x) {
@@ -339,13 +344,13 @@ FTF_HD void idct_block(const int16_t* __restrict__ coef, const uint16_t* __restr
     int32_t ws[64];
     int32_t in[64];
 #pragma unroll
-    for (int i = 0; i < 64; ++i) in[i] = (int32_t)coef[i] * (int32_t)q[i];
+    for (int i = 0; i < 64; ++i) in[i] = (int32_t)coef[i] * (int32_t)q[i];      // 16 x 16 bits: always fits
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         int32_t o[8];
         idct_1d(in[c], in[8 + c], in[16 + c], in[24 + c], in[32 + c], in[40 + c], in[48 + c], in[56 + c], o);
 #pragma unroll
-        for (int r = 0; r < 8; ++r) ws[r * 8 + c] = (o[r] + (1 << 10)) >> 11;
+        for (int r = 0; r < 8; ++r) ws[r * 8 + c] = (int32_t)((uint32_t)o[r] + (1u << 10)) >> 11;
     }
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
@@ -369,8 +374,8 @@ FTF_HD void idct_block(const int16_t* __restrict__ coef, const uint16_t* __restr
 #else
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
-            lo |= idct_range_limit((o[c] + (1 << 17)) >> 18) << (8 * c);
-            hi |= idct_range_limit((o[4 + c] + (1 << 17)) >> 18) << (8 * c);
+            lo |= idct_range_limit((int32_t)((uint32_t)o[c] + (1u << 17)) >> 18) << (8 * c);
+            hi |= idct_range_limit((int32_t)((uint32_t)o[4 + c] + (1u << 17)) >> 18) << (8 * c);
         }
 #endif
         uint32_t* row = reinterpret_cast<uint32_t*>(out + (int64_t)r * stride);
