@@ -184,6 +184,7 @@ def run_reference(args):
     threads = oracle.num_threads()
     rng = np.random.default_rng(1234)
     wl = args.workload
+    warm = None
     if wl == "half_plus_two":
         n = 1 << 26                                           # bounded sample: 1/4 of the 2^28 workload per step
         x = (rng.standard_normal(n) * 100).astype(np.float32)
@@ -209,14 +210,15 @@ def run_reference(args):
     else:
         import oracle.inception as oinc                       # noqa: F401  (exists once the conv path lands)
         net = oinc.Net(INC["classes"], INC["seed"])
-        b = 4
+        b = INC["batch"]                                      # every timed step is the whole batch-64 workload (a few seconds)
         img = rng.standard_normal((b, 299, 299, 3)).astype(np.float32)
         step = lambda: net.forward(img, threads=threads)
-        units, unit, metric, sample = float(b), "images/s", "Inception-v3 images/sec", "4 of the 64 images per step, fp32"
+        warm = lambda: net.forward(img[:4], threads=threads)  # warm-up only has to generate and cache the weights
+        units, unit, metric, sample = float(b), "images/s", "Inception-v3 images/sec", "all 64 images per timed step, fp32 (warm-up steps: 4 images)"
         config = {"workload": "Inception-v3 random-init batch 64 top-5 (BASELINE config 4)", "sample_images": b}
         dtype = "f32"
     for _ in range(args.warmup):
-        step()
+        (warm or step)()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         step()
@@ -336,9 +338,8 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
     def drain(block):
         nonlocal done
         _check(lib.ftf_poll(r.handle, 1 if block else 0, tags, outs, 256, C.byref(n_ready)), r.handle)
-        if n_ready.value:                                      # the host reads the results: top-1 index of the newest record
-            last = outs[2 * (n_ready.value - 1)]
-            checksum[0] += C.cast(last.data, C.POINTER(C.c_int32))[0]
+        for q in range(n_ready.value):                         # the host reads every result: top-1 index of each record
+            checksum[0] += C.cast(outs[2 * q].data, C.POINTER(C.c_int32))[0]
         done += n_ready.value
     checksum = [0]
     # warm-up (graph capture, allocations)
@@ -353,6 +354,7 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
     while done < n_warm:
         drain(True)
     done = 0
+    checksum[0] = 0
     if sync:
         sync()
     r2 = r.stats()
@@ -430,6 +432,148 @@ def blocking_two_subtasks(ftf, lib, np, device, seconds=1.5):
             "api": "ftf_run (C ABI) from two task threads with one runner each on one GPU (two Flink slots per GPU)"}
 
 
+def sub_leg(name, torch, device, np, lib, pk, rank, local_rank, min_ms=60.0):
+    """A compact device-resident measurement of one of the HBM-bound kernels (BASELINE configs 2 and 3), run inside the
+    default bench so that the driver's record holds it: value, ms per step, roofline fraction against the measured copy
+    rate, DRAM traffic from profiles/traffic.json, clocks sampled during the timed region (it lasts >= min_ms so that the
+    2 ms sampler sees >= 10 samples)."""
+    if name == "half_plus_two":
+        g = torch.Generator(device="cuda").manual_seed(1234 + rank)
+        x = torch.randn(HPT_N, device="cuda", generator=g) * 100
+        y = torch.empty_like(x)
+        step = lambda: device.affine_f32(x, 0.5, 2.0, out=y)
+        units, unit, algo = 8.0 * HPT_N / 1e9, "GB/s", 8.0 * HPT_N
+        what = "y = 0.5x + 2 over 2^28 fp32, 8 algorithmic B/element (BASELINE config 2)"
+    else:
+        b = NORM["batch"]
+        g = torch.Generator(device="cuda").manual_seed(42 + rank)
+        img = torch.randint(0, 256, (b, NORM["in_h"], NORM["in_w"], 3), dtype=torch.uint8, device="cuda", generator=g)
+        out = torch.empty((b, NORM["out_h"], NORM["out_w"], 3), dtype=torch.float32, device="cuda")
+        step = lambda: device.resize_norm(img, NORM["out_h"], NORM["out_w"], NORM["mean"], NORM["scale"], out=out)
+        units, unit, algo = float(b), "images/s", float(NORM_BYTES_PER_IMAGE) * b
+        what = "256 x (480x640 u8 RGB -> 299x299 f32), 1 994 412 algorithmic B/image (BASELINE config 3)"
+    for _ in range(5):
+        step()
+    ms1 = cuda_time(step, 10, torch) / 10
+    steps = max(20, int(min_ms / max(ms1, 1e-3)) + 1)
+    with ClockSampler(local_rank) as clk:
+        ms = cuda_time(step, steps, torch) / steps
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(name, {}).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    achieved = algo / (ms / 1e3) / 1e9
+    return {"workload": what, "value": units / (ms / 1e3), "unit": unit, "ms_per_step": ms, "steps": steps,
+            "l2": "tensors of one step exceed L2, no flush",
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": pk["hbm"], "unit": "GB/s", "frac": achieved / pk["hbm"],
+                         "frac_of_nominal_8TBps": achieved / 8000.0, "traffic": traffic, "peak_source": pk["src"]},
+            "clocks": clk.summary()}
+
+
+def per_record_leg(ftf, lib, np, local_rank, lab, seconds=2.0):
+    """The reference's real calling pattern (BASELINE config 1): ONE record per model call -- one tf.Example per
+    regress_x_to_y call (FTT/ml/RegressITCase.scala:54) and one image per InceptionModel.label call
+    (EX/inception/inception.scala:39-46) -- through the blocking ftf_run, host buffers in, result read by the host."""
+    from flink_tensorflow_b200.host import _as_ftf, FtfTensor, _check
+    out = {}
+    r = ftf.Runner(os.path.join(ROOT, "models", "half_plus_two"), "regress_x_to_y", None, ftf.default_config(device=local_rank))
+    rng = np.random.default_rng(1234)
+    xs = rng.uniform(-1000, 1000, 4096).astype(np.float32)
+    recs = [ftf.messages_to_tensor([ftf.example(x=float(v))]) for v in xs]
+    ik, ok = (C.c_char_p * 1)(b"inputs"), (C.c_char_p * 1)(b"outputs")
+    tout = (FtfTensor * 1)()
+    prepared = []
+    for tv in recs:
+        t, keep = _as_ftf(tv.data_type, tv.shape, tv.buffer)
+        prepared.append(((FtfTensor * 1)(t), keep))
+    lat, wrong, t0, i = [], 0, time.perf_counter(), 0
+    while time.perf_counter() - t0 < seconds:
+        tin, _ = prepared[i % len(prepared)]
+        a = time.perf_counter()
+        _check(lib.ftf_run(r.handle, 1, ik, tin, 1, ok, tout), r.handle)
+        y = C.cast(tout[0].data, C.POINTER(C.c_float))[0]
+        lat.append(time.perf_counter() - a)
+        wrong += y != np.float32(np.float32(0.5) * xs[i % len(xs)]) + np.float32(2.0)
+        i += 1
+    dt = time.perf_counter() - t0
+    r.close()
+    lat = np.sort(np.array(lat)) * 1e6
+    out["half_plus_two"] = {"calls_per_s": i / dt, "latency_us_p50": float(lat[len(lat) // 2]), "latency_us_p99": float(lat[int(len(lat) * 0.99)]),
+                            "calls": i, "wrong_answers": int(wrong), "api": "one serialized tf.Example per ftf_run on regress_x_to_y (parse, upload, K1, download)"}
+    # one image per label call on the batch-64 runner (a batch of one replays the 8-image graph bucket)
+    nb = 299 * 299 * 3 * 4
+    p, hx = pinned_array(lib, np, nb, np.float32)
+    hx[:] = rng.standard_normal(nb // 4, dtype=np.float32)
+    t_in, keep = _as_ftf(ftf.DataType.FLOAT, (1, 299, 299, 3), hx.view(np.uint8))
+    tin, ok2 = (FtfTensor * 1)(t_in), (C.c_char_p * 1)(b"top_k_indices")
+    for _ in range(3):
+        _check(lib.ftf_run(lab.handle, 1, ik, tin, 1, ok2, tout), lab.handle)
+    lat, t0, i = [], time.perf_counter(), 0
+    while time.perf_counter() - t0 < seconds:
+        a = time.perf_counter()
+        _check(lib.ftf_run(lab.handle, 1, ik, tin, 1, ok2, tout), lab.handle)
+        _ = C.cast(tout[0].data, C.POINTER(C.c_int32))[0]
+        lat.append(time.perf_counter() - a)
+        i += 1
+    dt = time.perf_counter() - t0
+    lib.ftf_host_free(p)
+    lat = np.sort(np.array(lat)) * 1e6
+    out["inception_label"] = {"calls_per_s": i / dt, "latency_us_p50": float(lat[len(lat) // 2]), "latency_us_p99": float(lat[int(len(lat) * 0.99)]),
+                              "calls": i, "api": "one fp32 299x299x3 image per ftf_run on builtin:inception_v3 (upload 1.07 MB, network, top-5 back)"}
+    return out
+
+
+def per_record_cpu(ftf, np, oracle, seconds=2.0):
+    """The CPU oracle called the way the reference calls TF: one serialized Example per call (STRING tensor -> ParseExample ->
+    a*x + b), one thread, plus one image per call through the oracle's Inception-v3 on all host threads."""
+    rng = np.random.default_rng(1234)
+    xs = rng.uniform(-1000, 1000, 4096).astype(np.float32)
+    recs = [oracle.string_tensor_encode([ftf.example(x=float(v))]) for v in xs]
+    t0, i = time.perf_counter(), 0
+    while time.perf_counter() - t0 < seconds:
+        rc, y = oracle.regress(recs[i % len(recs)], 1, "x", 0.5, 2.0)
+        i += 1
+    dt = time.perf_counter() - t0
+    out = {"half_plus_two": {"calls_per_s": i / dt, "cores": 1, "kind": "port",
+                             "sample": f"{i} one-Example calls of the C oracle through ctypes (no JNI, no TF executor dispatch: "
+                                       "faster than the reference's Session.run could be)"}}
+    import oracle.inception as oinc
+    net = oinc.Net(INC["classes"], INC["seed"], 0)
+    img = rng.standard_normal((1, 299, 299, 3)).astype(np.float32)
+    threads = oracle.num_threads()
+    net.forward(img, threads=threads)
+    t0, i = time.perf_counter(), 0
+    while time.perf_counter() - t0 < 2 * seconds:
+        net.forward(img, threads=threads)
+        i += 1
+    out["inception_label"] = {"calls_per_s": i / (time.perf_counter() - t0), "cores": threads, "kind": "port",
+                              "sample": f"{i} one-image calls of the fp32 C oracle, all host threads"}
+    return out
+
+
+def outputs_digest(ftf, lib, np, torch, lab):
+    """Top-5 and logits of ONE common seeded batch (the same on every rank), as 8 int64 words of two SHA-256 digests."""
+    import hashlib
+    from flink_tensorflow_b200.host import _check
+    bsz = INC["batch"]
+    g = torch.Generator(device="cuda").manual_seed(4242)                  # not rank-dependent
+    img = torch.randn((bsz, 299, 299, 3), device="cuda", generator=g).to(torch.bfloat16)
+    logits = torch.empty((bsz, INC["classes"]), dtype=torch.float32, device="cuda")
+    idx = torch.empty((bsz, INC["top_k"]), dtype=torch.int32, device="cuda")
+    score = torch.empty((bsz, INC["top_k"]), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    _check(lib.ftf_label_dev(lab.handle, img.data_ptr(), ftf._abi.BFLOAT16, bsz, logits.data_ptr(), None, idx.data_ptr(), score.data_ptr()), lab.handle)
+    torch.cuda.synchronize()
+    words = []
+    for t in (idx, logits):
+        d = hashlib.sha256(t.cpu().numpy().tobytes()).digest()
+        words += [int.from_bytes(d[8 * k: 8 * k + 8], "little", signed=True) for k in range(4)]
+    return words
+
+
+
 def bind_to_gpu_numa_node(torch, device):
     """Runs this rank (and so its pinned staging buffers, which are placed on first touch) on the CPUs of the NUMA node its
     GPU hangs off (the one shared resource of the record-sharded path is host memory / PCIe).  With eight ranks
@@ -442,6 +586,8 @@ def bind_to_gpu_numa_node(torch, device):
         bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
         base = "/sys/bus/pci/devices/" + bdf
         node = int(open(base + "/numa_node").read())
+        if node < 0:
+            return "unbound (numa_node = -1: the box exposes no NUMA topology for this GPU)"
         cpus = set()
         for part in open(base + "/local_cpulist").read().strip().split(","):
             lo, _, hi = part.partition("-")
@@ -450,7 +596,7 @@ def bind_to_gpu_numa_node(torch, device):
         if not cpus:
             return "no local CPUs allowed"
         os.sched_setaffinity(0, cpus)
-        return f"node {node}, {len(cpus)} cpus"
+        return f"bound to node {node}, {len(cpus)} cpus"
     except Exception as e:  # noqa: BLE001  (no sysfs entry, container without the attribute: run unbound)
         return f"unavailable ({type(e).__name__})"
 
@@ -461,7 +607,6 @@ def run_ours(args):
     import ftf_loader
     ftf = ftf_loader.load()
     from flink_tensorflow_b200 import device
-    import oracle
     lib = ftf._abi.load_library()
     rank, local_rank, world = dist_env()
     if not torch.cuda.is_available():
@@ -570,14 +715,28 @@ def run_ours(args):
         barrier()
     if prof_range:
         torch.cuda.cudart().cudaProfilerStop()
-    ms_total = max_over_ranks(ms_total)
-    ms_step = ms_total / K
-    value = units_per_step * world / (ms_step / 1e3)
+    value, ms_step = sharding.aggregate_throughput(units_per_step, ms_total / K, device="cuda")   # all ranks' units over the slowest rank's time
     if wl == "inception":
         achieved = INC_FLOP_PER_IMAGE * INC["batch"] / (ms_step / 1e3) / 1e12     # algorithmic TFLOP/s of the whole step
     else:
         achieved = algo_bytes / (ms_step / 1e3) / 1e9
     gpu_launches = int(lib.ftf_launch_count() - launches0)
+
+    if wl == "inception":
+        # Every rank labels ONE common seeded batch: do N GPUs give the single GPU's outputs?  (Each rank timed its own
+        # kernel candidates; all kernel families produce the same bits, tests/test_gpu_conv.py.)  SHA-256 of the top-5
+        # indices and of the logits, compared with rank 0's.
+        words = outputs_digest(ftf, lib, np, torch, lab)
+        mine = torch.tensor(words, dtype=torch.int64, device="cuda")
+        if world > 1:
+            allw = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allw, mine)
+        else:
+            allw = [mine]
+        extra["outputs_match_rank0"] = bool(all(torch.equal(w[:4], allw[0][:4]) for w in allw))
+        extra["logits_bits_match_rank0"] = bool(all(torch.equal(w[4:], allw[0][4:]) for w in allw))
+        extra["outputs_digest"] = {"batch": "64 images, torch CUDA generator seed 4242 on every rank", "top5_sha256_head": "%016x" % (words[0] & (2**64 - 1)),
+                                   "logits_sha256_head": "%016x" % (words[4] & (2**64 - 1)), "ranks_compared": world}
 
     # ---- end to end through ftf_run with host buffers ----------------------------------------------
     e2e_steps = max(1, min(K, 5))
@@ -600,7 +759,7 @@ def run_ours(args):
         hx[:] = tv.buffer
         tv.buffer = hx
         in_key, out_key = "inputs", "top_k_indices"
-        h2d, d2h = int(tv.buffer.nbytes), len(files) * (2 * INC["classes"] * 4 + 2 * INC["top_k"] * 4)
+        h2d, d2h = int(tv.buffer.nbytes), len(files) * INC["top_k"] * 4             # only the fetched output is downloaded
     elif wl == "inception":
         r = lab
         nb = INC["batch"] * 299 * 299 * 3 * 4
@@ -609,7 +768,7 @@ def run_ours(args):
         tv = ftf.TensorValue.__new__(ftf.TensorValue)
         tv.data_type, tv.shape, tv.buffer = ftf.DataType.FLOAT, (INC["batch"], 299, 299, 3), hx.view(np.uint8)
         in_key, out_key = "inputs", "top_k_indices"
-        h2d, d2h = nb, INC["batch"] * (2 * INC["classes"] * 4 + 2 * INC["top_k"] * 4)
+        h2d, d2h = nb, INC["batch"] * INC["top_k"] * 4                               # only the fetched output is downloaded
     else:
         r = ftf.Runner("builtin:image_normalization", None, None,
                        ftf.default_config(device=local_rank, out_h=NORM["out_h"], out_w=NORM["out_w"], mean=NORM["mean"],
@@ -644,6 +803,8 @@ def run_ours(args):
     e2e_value = units_per_step * world / (e2e_ms / 1e3)
     st = r.stats()
     e2e_launches = st["kernel_launches"]
+    if wl == "inception" and world == 1 and not args.quick:
+        extra["per_record"] = per_record_leg(ftf, lib, np, local_rank, lab)
     r.close()
     lib.ftf_host_free(p)
 
@@ -676,17 +837,42 @@ def run_ours(args):
                "api": "ftf_submit/ftf_poll (C ABI): one fp32 299x299x3 record per call from pinned host memory, micro-batches of 64, "
                       "top-5 indices and scores read back per record"}
     if wl == "inception" and not args.quick:
-        # BASELINE config 5 on this rank's GPU: 640x480 u8 records as TensorValue wire images -> normalise -> Inception-v3 ->
-        # top-5; >= 10^5 records at saturation, then a source emitting at half that rate (latency at a sustainable load)
-        sat = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * 1600, wire=True)
-        half = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * 800, wire=True, offered_rate=0.5 * sat["records_per_s"])
-        extra["streaming"] = sat
-        extra["streaming_half_rate"] = half
+        # BASELINE config 5, every rank on its own GPU with its own source thread: >= 10^5 records per rank at saturation --
+        # (a) the record the reference's source really emits, a 640x480 JPEG FILE (ImageInputFormat.scala:63-80), decoded on the
+        # GPU; (b) raw 640x480 u8 records as TensorValue wire images; then (c) a source emitting (b) at half the saturation
+        # rate (latency at a sustainable load).  Whole-job figures: records of all ranks over the slowest rank's time,
+        # latencies as the worst rank's.
+        def whole_job(res):
+            secs = max_over_ranks(res["seconds"])
+            res = dict(res)
+            res["records_per_s_this_rank"] = res.pop("records_per_s")
+            res["records_per_s"] = res["records"] * world / secs
+            res["seconds"] = secs
+            res["latency_us_p50"] = max_over_ranks(res["latency_us_p50"])
+            res["latency_us_p99"] = max_over_ranks(res["latency_us_p99"])
+            res["ranks"] = world
+            return res
+        jp = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * 1600, kind="jpeg_label", sync=barrier)
+        barrier()
+        extra["streaming_jpeg"] = whole_job(jp)
+        sat = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * 1600, wire=True, sync=barrier)
+        barrier()
+        half = streaming_bench(ftf, lib, np, local_rank, n_records=INC["batch"] * 800, wire=True, offered_rate=0.5 * sat["records_per_s"], sync=barrier)
+        barrier()
+        extra["streaming"] = whole_job(sat)
+        extra["streaming_half_rate"] = whole_job(half)
+        # configs 2 and 3 in the same run (rank-local kernels; reported from rank 0)
+        extra["half_plus_two"] = sub_leg("half_plus_two", torch, device, np, lib, pk, rank, local_rank)
+        extra["normalize"] = sub_leg("normalize", torch, device, np, lib, pk, rank, local_rank)
+        barrier()
     if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
         return
     # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -----------------------------------------
     cpu = None
     if world == 1 and not args.quick:
+        import oracle                                        # the checker is loaded for this leg only, after every GPU measurement
         threads = oracle.num_threads()
         rng = np.random.default_rng(1234)
         if wl == "half_plus_two":
@@ -716,6 +902,8 @@ def run_ours(args):
             cpu = {"value": b * reps / (time.perf_counter() - t0), "unit": unit, "cores": threads, "kind": "port",
                    "sample": f"{reps} passes over 4 images (1/16 of the batch), fp32 C oracle, all host threads"}
             extra["cpu_torchvision_onednn"] = torchvision_cpu(threads, unit)
+            if "per_record" in extra:
+                extra["per_record"]["cpu"] = per_record_cpu(ftf, np, oracle)
         else:
             b = 32
             cimg = rng.integers(0, 256, (b, NORM["in_h"], NORM["in_w"], 3), dtype=np.uint8)

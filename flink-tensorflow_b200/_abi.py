@@ -45,6 +45,7 @@ SYMBOLS = {
     "ftf_poll": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_uint64), C.POINTER(FtfTensor), C.c_int32,
                            C.POINTER(C.c_int32)]),
     "ftf_flush": (C.c_int, [C.c_void_p]),
+    "ftf_poll_status": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_char_p)]),
     "ftf_poll_select": (C.c_int, [C.c_void_p, C.c_int32, C.POINTER(C.c_char_p)]),
     "ftf_last_error": (C.c_char_p, [C.c_void_p]),
     "ftf_stats_get": (C.c_int, [C.c_void_p, C.POINTER(FtfStats)]),

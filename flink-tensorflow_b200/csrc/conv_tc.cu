@@ -2,8 +2,36 @@
 #include "conv_tc.h"
 #include <stdio.h>
 #include <stdlib.h>
+#include <map>
+#include <mutex>
+#include <vector>
 
 namespace ftf {
+
+// ------------------------------------------------------------------------------------------------
+// What the plan-time timing decided, remembered per process: (device, layer geometry, segment layout, SM share) -> the
+// variant that won.  The second runner of a process (another Flink slot on the same GPU, or on another GPU of the box)
+// plans the same layers and takes the first runner's choice instead of timing again, so that every runner of a process
+// runs the same kernels -- per-record results then do not depend on which subtask served the record -- and ftf_create
+// of the later runners does no device work for planning.
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct ChoiceKey {
+    std::vector<long long> v;
+    bool operator<(const ChoiceKey& o) const { return v < o.v; }
+};
+std::mutex g_tune_mu;                   // guards g_choice and serialises the timing runs
+std::map<ChoiceKey, int> g_choice;      // -> index into kVariants
+
+ChoiceKey choice_key(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count) {
+    ChoiceKey k;
+    // the device is deliberately NOT part of the key: all GPUs of a box are the same part, and subtasks on different GPUs
+    // must agree as well
+    k.v = {g.n_max, g.H, g.W, g.Cin, g.in_ld, g.Cout, g.KH, g.KW, g.stride, g.pad_h, g.pad_w, sm_count, n_seg, g.bias != nullptr};
+    for (int i = 0; i < n_seg; ++i) { k.v.push_back(segs[i].ld); k.v.push_back(segs[i].coff); k.v.push_back(segs[i].col_begin); k.v.push_back(segs[i].flags); }
+    return k;
+}
+}  // namespace
 
 // Median-of-5 device time of one candidate on its own buffers (ms); < 0 on error.
 static float time_candidate(const ConvPlan& cand, int n, cudaStream_t s, cudaEvent_t e0, cudaEvent_t e1) {
@@ -21,13 +49,16 @@ static float time_candidate(const ConvPlan& cand, int n, cudaStream_t s, cudaEve
 }
 
 int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
-                 std::string* err, bool tune) {
-    // FTF_CONV_KIND=pm|wm forces one kernel (tests and profiling); FTF_CONV_TUNE=0/1 overrides the caller's choice
+                 std::string* err, int mode) {
+    // FTF_CONV_KIND=pm|wm forces one kernel (tests and profiling); FTF_CONV_TUNE=0/1 overrides the caller's choice --
+    // except for callers that promise to do no device work while planning (kPlanModelOnly: the per-call entry points)
     const char* force = getenv("FTF_CONV_KIND");
     const char* tenv = getenv("FTF_CONV_TUNE");
     const bool halo_only = getenv("FTF_CONV_HALO_ONLY") != nullptr;     // profiling: drop the im2col candidate where a halo one exists
-    if (tenv) tune = tenv[0] == '1';
+    bool tune = mode == kPlanTune;
+    if (tenv && mode != kPlanModelOnly) tune = tenv[0] == '1';
     ConvPlan cands[5];
+    int cand_variant[5];
     int n_cand = 0;
     std::string first_err;
     // candidates: pixel-major (im2col / halo window / CTA pair), weight-major (im2col / halo window)
@@ -40,7 +71,8 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     const long long m_tiles = ((long long)g.n_max * ((g.H + 2 * g.pad_h - g.KH) / g.stride + 1) * ((g.W + 2 * g.pad_w - g.KW) / g.stride + 1) + 127) / 128;
     const char* pair_env = getenv("FTF_CONV_PAIR");
     const bool no_pair = pair_env ? pair_env[0] != '1' : m_tiles < 4ll * sm_count;
-    for (const Variant& v : kVariants) {
+    for (int vi = 0; vi < 5; ++vi) {
+        const Variant& v = kVariants[vi];
         if (force) {   // FTF_CONV_KIND: "pm" = one-CTA pixel-major, "pm2" = CTA-pair pixel-major, "wm" = weight-major
             const bool want_pair = force[0] == 'p' && force[2] == '2';
             if ((force[0] == 'p') != (v.kind == 0) || (v.kind == 0 && want_pair != v.pair)) continue;
@@ -55,6 +87,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         const bool is_halo = v.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
         if (v.halo && !is_halo) continue;                      // same plan as the no-halo candidate
         if (v.pair && !c.pm.p.pair) continue;
+        cand_variant[n_cand] = vi;
         ++n_cand;
     }
     if (n_cand == 0) { if (err) *err = first_err; return FTF_INVALID_ARGUMENT; }
@@ -62,14 +95,29 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         int w = 0;
         for (int i = 0; i < n_cand; ++i) {
             const bool hm = cands[i].kind ? cands[i].wm.p.halo_mode != 0 : cands[i].pm.p.halo_mode != 0;
-            if (hm) cands[w++] = cands[i];
+            if (hm) { cand_variant[w] = cand_variant[i]; cands[w++] = cands[i]; }
         }
         if (w > 0) n_cand = w;
     }
     int best = 0;
     for (int i = 1; i < n_cand; ++i)
         if (cands[i].est_cycles < cands[best].est_cycles) best = i;
-    if (tune && n_cand > 1) {
+    // A choice another runner of this process already timed for the same layer is taken as it is.  Timing itself runs
+    // under a process-wide lock: two task threads that open their models at the same moment would otherwise disturb each
+    // other's measurements and could settle on different kernels.
+    const bool cacheable = tune && !force && !halo_only && n_cand > 1;
+    ChoiceKey key;
+    bool cached = false;
+    std::unique_lock<std::mutex> tune_lock(g_tune_mu, std::defer_lock);
+    if (cacheable) {
+        key = choice_key(g, segs, n_seg, sm_count);
+        tune_lock.lock();
+        auto it = g_choice.find(key);
+        if (it != g_choice.end())
+            for (int i = 0; i < n_cand; ++i)
+                if (cand_variant[i] == it->second) { best = i; cached = true; }
+    }
+    if (tune && n_cand > 1 && !cached) {
         cudaStream_t s = nullptr;
         cudaEvent_t e0 = nullptr, e1 = nullptr;
         if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) == cudaSuccess && cudaEventCreate(&e0) == cudaSuccess &&
@@ -97,13 +145,53 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         if (e1) cudaEventDestroy(e1);
         if (s) cudaStreamDestroy(s);
         cudaGetLastError();
+        if (cacheable) g_choice[key] = cand_variant[best];
     }
     *plan = cands[best];
     if (getenv("FTF_CONV_VERBOSE")) {
         const bool hm = plan->kind ? plan->wm.p.halo_mode : plan->pm.p.halo_mode;
         fprintf(stderr, "conv %dx%d s%d Cin %d Cout %d HxW %dx%d -> %s%s kc %d (%d candidates, %s)\n", g.KH, g.KW, g.stride, g.Cin, g.Cout, g.H, g.W,
-                plan->kind ? "weight-major" : (plan->pm.p.pair ? "pixel-major pair" : "pixel-major"), hm ? " halo" : "", plan->kind ? plan->wm.p.kc : plan->pm.p.kc, n_cand, tune ? "timed" : "model");
+                plan->kind ? "weight-major" : (plan->pm.p.pair ? "pixel-major pair" : "pixel-major"), hm ? " halo" : "", plan->kind ? plan->wm.p.kc : plan->pm.p.kc, n_cand, cached ? "choice of an earlier runner" : (tune ? "timed" : "model"));
     }
+    return FTF_OK;
+}
+
+// The measurement switches a plan depends on, folded into one number (part of the key below: a test that flips one of them
+// between two calls on the same buffers must not be served the other setting's plan).
+static unsigned long long env_fingerprint() {
+    static const char* const kNames[] = {"FTF_CONV_KIND", "FTF_CONV_TUNE", "FTF_CONV_HALO_ONLY", "FTF_CONV_PAIR", "FTF_NO_HALO", "FTF_NO_KC32",
+                                         "FTF_PM_NT", "FTF_PM_S", "FTF_PM_BGROUP", "FTF_CONV_PROFILE"};
+    unsigned long long h = 0xcbf29ce484222325ull;
+    for (const char* name : kNames) {
+        const char* v = getenv(name);
+        for (const char* c = v ? v : "\x01"; *c; ++c) { h ^= (unsigned char)*c; h *= 0x100000001b3ull; }
+        h ^= 0xff; h *= 0x100000001b3ull;
+    }
+    return h;
+}
+
+int conv_tc_plan_cached(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, int device, const ConvPlan** plan,
+                        std::string* err, int mode) {
+    // per thread: a runner (and a device-level caller) is driven by one thread, so no lock; bounded, cleared when full
+    thread_local std::map<std::vector<unsigned long long>, ConvPlan> cache;
+    std::vector<unsigned long long> key = {(unsigned long long)device, (unsigned long long)(uintptr_t)g.in, (unsigned long long)(uintptr_t)g.weights,
+                                           (unsigned long long)(uintptr_t)g.bias, (unsigned long long)g.n_max, (unsigned long long)g.H, (unsigned long long)g.W,
+                                           (unsigned long long)g.Cin, (unsigned long long)g.in_ld, (unsigned long long)g.Cout, (unsigned long long)g.KH,
+                                           (unsigned long long)g.KW, (unsigned long long)g.stride, (unsigned long long)g.pad_h, (unsigned long long)g.pad_w,
+                                           (unsigned long long)sm_count, (unsigned long long)mode, env_fingerprint()};
+    for (int i = 0; i < n_seg; ++i) {
+        key.push_back((unsigned long long)(uintptr_t)segs[i].out); key.push_back((unsigned long long)segs[i].ld); key.push_back((unsigned long long)segs[i].coff);
+        key.push_back((unsigned long long)segs[i].col_begin); key.push_back((unsigned long long)segs[i].flags);
+    }
+    auto it = cache.find(key);
+    if (it == cache.end()) {
+        ConvPlan fresh;
+        const int rc = conv_tc_plan(g, segs, n_seg, sm_count, &fresh, err, mode);
+        if (rc) return rc;
+        if (cache.size() >= 256) cache.clear();
+        it = cache.emplace(std::move(key), fresh).first;
+    }
+    *plan = &it->second;
     return FTF_OK;
 }
 

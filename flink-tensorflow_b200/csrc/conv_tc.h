@@ -22,12 +22,23 @@ struct ConvPlan {
     wm::ConvPlan wm;
 };
 
-// Encodes the tensor maps and tile shapes for one convolution (called once, at network build).
-// tune: time the candidate kernels (pixel-/weight-major, with and without the halo window) on the layer's own buffers
-// for n_max images and keep the fastest; otherwise the cycle model decides.  Every candidate accumulates K in the same
-// order (channel chunk, filter tap, 16-element step).
+// How conv_tc_plan chooses between the candidate kernels.
+enum {
+    kPlanModel = 0,       // the cycle model decides (FTF_CONV_TUNE=1 in the environment upgrades this to kPlanTune)
+    kPlanTune = 1,        // time the candidates on the layer's own buffers for n_max images and keep the fastest; the
+                          // choice is remembered per process, so later runners take it without timing (FTF_CONV_TUNE=0 downgrades)
+    kPlanModelOnly = 2,   // the cycle model decides, whatever the environment says: planning then only encodes tensor
+                          // maps on the host -- no stream, no event, no launch, no synchronisation (per-call entry points)
+};
+// Encodes the tensor maps and tile shapes for one convolution (called once, at network build).  Every candidate
+// accumulates K in the same order (channel chunk, filter tap, 16-element step).
 int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
-                 std::string* err, bool tune = false);
+                 std::string* err, int mode = kPlanModel);
+// The same for the per-call entry points (ftf_conv2d_bf16_dev, ftf_pool_branch_bf16*_dev): a call that repeats an earlier one
+// of this thread -- same device, buffers, geometry and mode -- gets that call's plan back (no tensor-map encoding).
+// *plan stays valid until the thread's 256-entry table is cleared by a later call.
+int conv_tc_plan_cached(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, int device, const ConvPlan** plan,
+                        std::string* err, int mode = kPlanModel);
 // Enqueues the convolution for the first n images.
 int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
 // Diagnostic cycle counters of both kernels, summed (see conv_pm.h).

@@ -102,8 +102,13 @@ struct StemWeights {
     float w[27][32];   // [kh][kw][cin] x cout, bf16-rounded values
     float b[32];
 };
+// TIn = float: the records of the label model arrive as fp32 images (the reference's ImageTensor); each value is rounded
+// to bf16 (RNE) as it is loaded, which is what a separate cast pass in front of the network would have produced, bit for bit.
+__device__ __forceinline__ float stem_load(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ float stem_load(const float* p) { return __bfloat162float(__float2bfloat16_rn(__ldg(p))); }
+template <typename TIn>
 __global__ void __launch_bounds__(128)
-stem_conv3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int OH, int OW,
+stem_conv3x3s2(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, int n, int H, int W, int OH, int OW,
                const __grid_constant__ StemWeights sw, unsigned long long* tl) {
     ptx::tl_stamp_min(tl);
     ptx::pdl_launch_dependents();
@@ -118,12 +123,12 @@ stem_conv3x3s2(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__
     float acc[32];
 #pragma unroll
     for (int o = 0; o < 32; ++o) acc[o] = 0.0f;
-    const __nv_bfloat16* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
+    const TIn* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
 #pragma unroll
     for (int ky = 0; ky < 3; ++ky) {
         float x[9];
 #pragma unroll
-        for (int i = 0; i < 9; ++i) x[i] = __bfloat162float(base[(size_t)ky * W * 3 + i]);   // 3 pixels x 3 channels, contiguous
+        for (int i = 0; i < 9; ++i) x[i] = stem_load(base + (size_t)ky * W * 3 + i);   // 3 pixels x 3 channels, contiguous
 #pragma unroll
         for (int i = 0; i < 9; ++i)
 #pragma unroll
@@ -279,7 +284,7 @@ struct InceptionV3::Impl {
         cudaMemcpy(db, bias.data(), (size_t)total * 4, cudaMemcpyHostToDevice);
         ConvGeometry g{in.p, max_batch, in.h, in.w, in.c, in.c, dw, db, total, kh, kw, s, ph, pw};
         ConvPlan plan;
-        rc = conv_tc_plan(g, segs.data(), (int)segs.size(), share(), &plan, err, /*tune=*/true);
+        rc = conv_tc_plan(g, segs.data(), (int)segs.size(), share(), &plan, err, kPlanTune);
         if (rc) return;
         plans.push_back(plan);
         Op op{}; op.type = Op::kConv; op.lane = cur_lane; op.plan = (int)plans.size() - 1;
@@ -472,7 +477,7 @@ struct InceptionV3::Impl {
         ConvSegment sg{}; sg.out = logits; sg.ld = cols; sg.coff = 0; sg.col_begin = 0; sg.flags = kSegBias | kSegF32;
         ConvGeometry g{gap.p, max_batch, 1, 1, x.c, x.c, dw, db, cols, 1, 1, 1, 0, 0};
         ConvPlan plan;
-        rc = conv_tc_plan(g, &sg, 1, sms, &plan, err, /*tune=*/true);
+        rc = conv_tc_plan(g, &sg, 1, sms, &plan, err, kPlanTune);
         if (rc) return;
         plans.push_back(plan);
         Op op{}; op.type = Op::kConv; op.plan = (int)plans.size() - 1; op.tag = "fc";
@@ -518,7 +523,7 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
 // Enqueues every op of the network for nb images: lane 0 on `s`, the other lanes on the net's own streams,
 // fenced by events at each block's fork and join (the same calls record a graph when `s` is being captured).
 // ops [first, last) are enqueued; the stem convolution (op 0) reads `image`, the caller's batch, where it lies.
-static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* err, const void* image, size_t first, size_t last) {
+static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* err, const void* image, int image_dtype, size_t first, size_t last) {
     auto stream_of = [&](int lane) { return lane == 0 ? s : m.lane_stream[lane]; };
     for (size_t oi = first; oi < last; ++oi) {
         const Op& op = m.ops[oi];
@@ -539,8 +544,12 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
             break;
         case Op::kStem: {
             const long long pix = (long long)nb * op.OH * op.OW;
-            FTF_CUDA(launch_pdl(stem_conv3x3s2, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const __nv_bfloat16*)image,
-                                (__nv_bfloat16*)op.out, nb, op.H, op.W, op.OH, op.OW, m.stem, tl), err);
+            if (image_dtype == FTF_FLOAT)
+                FTF_CUDA(launch_pdl(stem_conv3x3s2<float>, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const float*)image,
+                                    (__nv_bfloat16*)op.out, nb, op.H, op.W, op.OH, op.OW, m.stem, tl), err);
+            else
+                FTF_CUDA(launch_pdl(stem_conv3x3s2<__nv_bfloat16>, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const __nv_bfloat16*)image,
+                                    (__nv_bfloat16*)op.out, nb, op.H, op.W, op.OH, op.OW, m.stem, tl), err);
             count_launch();
             break;
         }
@@ -601,9 +610,10 @@ static void dump_timeline(InceptionV3::Impl& m, int nb) {
     fprintf(stderr, "sum of (end - go) over kernels: %.1f us\n", busy_sum);
 }
 
-int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cudaStream_t s, std::string* err) {
+int InceptionV3::forward(const void* images, int in_dtype, int64_t n, float* logits, cudaStream_t s, std::string* err) {
     Impl& m = *impl_;
     if (n < 0 || n > m.max_batch) { if (err) *err = "inception_v3: batch exceeds max_batch"; return FTF_INVALID_ARGUMENT; }
+    if (in_dtype != FTF_FLOAT && in_dtype != FTF_BFLOAT16) { if (err) *err = "inception_v3: images must be FLOAT or BFLOAT16"; return FTF_INVALID_ARGUMENT; }
     if (n == 0) return FTF_OK;
     const int nb = (int)n;
     // The stem convolution reads the caller's images in place and is launched on its own, in front of the graph: a graph
@@ -624,15 +634,22 @@ int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cuda
     cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
     FTF_CUDA(cudaStreamIsCapturing(s, &cap), err);
     if (!use_graph || cap != cudaStreamCaptureStatusNone) {
-        const int rc = run_ops(m, nb, s, err, images_bf16, 0, n_ops);
+        const int rc = run_ops(m, nb, s, err, images, in_dtype, 0, n_ops);
         if (rc) return rc;
     } else {
-        { const int rc = run_ops(m, nb, s, err, images_bf16, 0, stem_ops); if (rc) return rc; }
-        auto it = m.graphs.find(nb);
+        { const int rc = run_ops(m, nb, s, err, images, in_dtype, 0, stem_ops); if (rc) return rc; }
+        // Micro-batches closed by the deadline or by a blocking poll have arbitrary sizes.  One graph per distinct size would
+        // pay a capture + instantiation of ~80 kernels on the record path for every new size and keep up to max_batch graphs
+        // alive; instead the sizes are bucketed (at most 16 buckets) and a batch replays the graph of the bucket above it.  The
+        // surplus rows are rows of the activation arena that hold an earlier batch's values: they are computed and never
+        // read back -- no kernel mixes records, so the real rows do not change by a bit.
+        const int step = m.max_batch <= 128 ? 8 : (m.max_batch / 16 + 7) / 8 * 8;
+        const int gb = std::min(m.max_batch, (nb + step - 1) / step * step);
+        auto it = m.graphs.find(gb);
         if (it == m.graphs.end()) {
             const uint64_t before = launches_so_far();
             FTF_CUDA(cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal), err);
-            const int rc = run_ops(m, nb, s, err, images_bf16, stem_ops, n_ops);
+            const int rc = run_ops(m, gb, s, err, images, in_dtype, stem_ops, n_ops);
             cudaGraph_t graph = nullptr;
             const cudaError_t e = cudaStreamEndCapture(s, &graph);
             if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
@@ -641,12 +658,12 @@ int InceptionV3::forward(const void* images_bf16, int64_t n, float* logits, cuda
             const cudaError_t e2 = cudaGraphInstantiate(&exec, graph, 0);
             cudaGraphDestroy(graph);
             if (e2 != cudaSuccess) return cuda_fail(e2, "cudaGraphInstantiate", err);
-            m.graph_kernels[nb] = (int)(launches_so_far() - before);
-            count_launch(-m.graph_kernels[nb]);          // recording launched nothing
-            it = m.graphs.emplace(nb, exec).first;
+            m.graph_kernels[gb] = (int)(launches_so_far() - before);
+            count_launch(-m.graph_kernels[gb]);          // recording launched nothing
+            it = m.graphs.emplace(gb, exec).first;
         }
         FTF_CUDA(cudaGraphLaunch(it->second, s), err);
-        count_launch(m.graph_kernels[nb]);
+        count_launch(m.graph_kernels[gb]);
     }
     if (tl_now) {
         FTF_CUDA(cudaStreamSynchronize(s), err);

@@ -19,8 +19,9 @@ public:
     // allocates the activation arena.  compute_dtype: FTF_BFLOAT16 (tcgen05 path).
     static int create(int device, int num_classes, uint64_t seed, int max_batch, int compute_dtype,
                       std::unique_ptr<InceptionV3>* out, std::string* err);
-    // images: [n,299,299,3] NHWC bf16 in HBM; logits: [n,classes] f32.  Enqueues on s.
-    int forward(const void* images_bf16, int64_t n, float* logits, cudaStream_t s, std::string* err);
+    // images: [n,299,299,3] NHWC in HBM, bf16 or fp32 (in_dtype FTF_BFLOAT16 / FTF_FLOAT; fp32 values are rounded to bf16 as
+    // the first convolution loads them); logits: [n,classes] f32.  Enqueues on s.
+    int forward(const void* images, int in_dtype, int64_t n, float* logits, cudaStream_t s, std::string* err);
     int num_classes() const { return classes_; }
     int max_batch() const { return max_batch_; }
     // Diagnostic: copies the named activation (layer or block name of oracle/inception_oracle.c) of the last

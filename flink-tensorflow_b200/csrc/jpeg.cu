@@ -336,8 +336,16 @@ int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* heig
         return bfail(b, FTF_UNIMPLEMENTED, "image " + std::to_string(i) + ": DecodeJpeg: files larger than 256 MiB are not supported");
     int rc = parse_headers(file, len, &p, &perr);
     if (rc) return bfail(b, rc, "image " + std::to_string(i) + ": " + perr);
+    // TF's DecodeJpeg refuses frames of 2^29 or more output bytes before it sizes anything ("Image too large"); a forged
+    // 65535x65535 header must not turn into a multi-gigabyte allocation here either
+    if ((int64_t)p.width * p.height * 3 >= ((int64_t)1 << 29))
+        return bfail(b, FTF_INVALID_ARGUMENT, "image " + std::to_string(i) + ": DecodeJpeg: image too large (" + std::to_string(p.width) + "x" +
+                     std::to_string(p.height) + ")");
     ImageDesc im;
     fill_geometry(p, &im);
+    // what a refused file must give back: the batch's sizes are only committed once the scan has been staged whole
+    const int64_t coef0 = b->coef_elems, plane0 = b->plane_bytes, dc0 = b->dc_elems, rgb0 = b->rgb_bytes;
+    const int blocks0 = b->max_blocks, groups0 = b->max_groups;
     // room in the pinned staging buffer (grown with its contents kept; sized generously so that this is rare)
     const size_t need = b->scan_bytes + (size_t)stage_bound(len, p, im);
     if (need > b->h_scan.cap) {
@@ -386,6 +394,8 @@ int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* heig
         // the reference's graph leaves DecodeJpeg's try_recover_truncated at false (GraphBuilder.java:41-47 sets channels
         // only): TF refuses a file that ends before its end-of-image marker instead of padding it
         b->segments.resize(first_seg);
+        b->coef_elems = coef0; b->plane_bytes = plane0; b->dc_elems = dc0; b->rgb_bytes = rgb0;
+        b->max_blocks = blocks0; b->max_groups = groups0;
         return bfail(b, FTF_INVALID_ARGUMENT, "image " + std::to_string(i) + ": DecodeJpeg: invalid JPEG data (the file ends inside the scan)");
     }
     b->scan_bytes += staged;

@@ -50,7 +50,9 @@ int scratch_for_device(int dev, float** out, std::string* err) {
 }  // namespace
 
 // See include/ftf.h.  The first call on a device resolves the scratch address (set-up work that belongs before any
-// stream capture); later calls only encode two tensor maps on the host and enqueue two kernels.
+// stream capture); later calls only encode two tensor maps on the host (or find them in the calling thread's plan table)
+// and enqueue two kernels.  The FTF_CONV_TUNE environment switch, which makes other planners time their candidates on
+// the device, is ignored here.
 extern "C" int ftf_pool_branch_bf16_static_dev(const void* in, int32_t n, int32_t h, int32_t w, int32_t cin, int32_t in_ld,
                                                const void* weights, const float* bias, int32_t cout, void* out,
                                                int32_t out_ld, int32_t out_off, void* stream) {
@@ -75,9 +77,11 @@ extern "C" int ftf_pool_branch_bf16_static_dev(const void* in, int32_t n, int32_
     ConvSegment sg{};
     sg.out = pre; sg.ld = cout; sg.coff = 0; sg.col_begin = 0; sg.flags = kSegF32;
     ConvGeometry g{in, n, h, w, cin, in_ld, weights, nullptr, cout, 1, 1, 1, 0, 0};
-    ConvPlan plan;
-    rc = conv_tc_plan(g, &sg, 1, device_sm_count(dev), &plan, &err);
-    if (!rc) rc = conv_tc_launch(plan, n, s, &err);
+    // kPlanModelOnly: planning is host work only (tensor-map encoding), whatever FTF_CONV_TUNE says -- no stream, event,
+    // launch or synchronisation; a repeated call finds its plan in the calling thread's table
+    const ConvPlan* plan = nullptr;
+    rc = conv_tc_plan_cached(g, &sg, 1, device_sm_count(dev), dev, &plan, &err, kPlanModelOnly);
+    if (!rc) rc = conv_tc_launch(*plan, n, s, &err);
     if (!rc) rc = launch_avgpool3x3_bias_relu(pre, bias, out, n, h, w, cout, out_ld, out_off, s, &err);
     if (rc) set_thread_error(err);
     return rc;

@@ -176,7 +176,8 @@ int wait_slot(ftf_runner* r, Slot& s) {
 
 // Enqueues one batch on a slot: upload n records from h_src, run the model, download into h_dst[j].
 // h_src must be pinned (the slot's own staging or caller memory from ftf_host_alloc).
-int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h_dst, bool uploaded = false) {
+// sel: the outputs to download (indices into r->outs); s.downloaded remembers them for ftf_poll.
+int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h_dst, const std::vector<int>& sel, bool uploaded = false) {
     std::string* err = &r->err;
     int rc;
     const bool jpg = s.jpeg_n > 0;         // d_in already holds this batch's images, decoded from files by decode_files
@@ -212,16 +213,17 @@ int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h
     case Kind::kNormalizeLabel: {
         // the activation arena is shared by the runner's batches: the net runs on one stream, fenced by events
         const size_t img_elems = (size_t)kInceptionSide * kInceptionSide * 3;
-        Buf& img = s.d_img;   // bf16 image batch, per slot so the next upload can overlap
-        if ((rc = img.ensure((size_t)n * img_elems * 2, err))) return rc;
-        if (r->kind == Kind::kLabel)
-            rc = launch_cast_f32_bf16((const float*)s.d_in.p, img.p, (int64_t)n * img_elems, s.stream, err);
-        else
-            rc = normalise(kInceptionSide, kInceptionSide, img.p, FTF_BFLOAT16);
-        if (rc) break;
+        const void* img = s.d_in.p;        // fp32 records: the first convolution reads them where they were uploaded
+        int img_dtype = FTF_FLOAT;
+        if (r->kind == Kind::kNormalizeLabel) {
+            // bf16 image batch, per slot so that the next batch's normalisation can overlap this one's network
+            if ((rc = s.d_img.ensure((size_t)n * img_elems * 2, err))) return rc;
+            if ((rc = normalise(kInceptionSide, kInceptionSide, s.d_img.p, FTF_BFLOAT16))) break;
+            img = s.d_img.p; img_dtype = FTF_BFLOAT16;
+        }
         FTF_CUDA(cudaEventRecord(s.done, s.stream), err);
         FTF_CUDA(cudaStreamWaitEvent(r->net_stream, s.done, 0), err);
-        rc = r->net->forward(img.p, n, (float*)s.d_out[1].p, r->net_stream, err);
+        rc = r->net->forward(img, img_dtype, n, (float*)s.d_out[1].p, r->net_stream, err);
         if (rc) break;
         rc = launch_softmax_topk((const float*)s.d_out[1].p, n, r->cfg.num_classes, r->cfg.num_classes, r->cfg.top_k, 1,
                                  (float*)s.d_out[0].p, (int32_t*)s.d_out[2].p, (float*)s.d_out[3].p, r->net_stream, err);
@@ -233,10 +235,12 @@ int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h
     }
     if (rc) return rc;
     r->stats.kernel_launches += launches_so_far() - before;
-    for (size_t j = 0; j < r->outs.size(); ++j) {
+    s.downloaded = 0;
+    for (int j : sel) {
         const size_t bytes = (size_t)n * r->outs[j].rec_bytes;
         FTF_CUDA(cudaMemcpyAsync(h_dst[j], s.d_out[j].p, bytes, cudaMemcpyDeviceToHost, s.stream), err);
         r->stats.d2h_bytes += bytes;
+        s.downloaded |= 1u << j;
     }
     FTF_CUDA(cudaEventRecord(s.done, s.stream), err);
     s.busy = true;
@@ -288,9 +292,10 @@ int decode_files(ftf_runner* r, Slot& s, int n, const uint8_t* const* files, con
 }
 
 // A finished slot whose input was JPEG files: did the device find a corrupt entropy-coded segment?
-int files_status(ftf_runner* r, Slot& s) {
+int files_status(ftf_runner* r, Slot& s, std::vector<int32_t>* per_record = nullptr) {
     if (s.jpeg_n <= 0 || !s.jpeg) return FTF_OK;
-    const int rc = ftf_jpeg_batch_status(s.jpeg, nullptr, 0);
+    if (per_record) per_record->assign((size_t)s.jpeg_n, FTF_OK);
+    const int rc = ftf_jpeg_batch_status(s.jpeg, per_record ? per_record->data() : nullptr, per_record ? (int32_t)per_record->size() : 0);
     s.jpeg_n = 0;
     if (rc) return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
     return FTF_OK;
@@ -347,7 +352,7 @@ int launch_open(ftf_runner* r) {
         if ((rc = files_launch(r, s))) return rc;
         s.files_n = 0;
     } else s.jpeg_n = 0;
-    rc = enqueue(r, s, s.n, s.h_in.p, dst.data(), /*uploaded=*/true);
+    rc = enqueue(r, s, s.n, s.h_in.p, dst.data(), r->poll_sel, /*uploaded=*/true);
     if (rc) { if (rc == FTF_INTERNAL) r->dead = true; return rc; }
     r->in_flight.push_back(r->open_slot);
     r->open_slot = -1;
@@ -370,8 +375,8 @@ extern "C" uint64_t ftf_launch_count(void) { return launches_so_far(); }
 
 extern "C" const char* ftf_version(void) { return "flink-tensorflow_b200 0.1 (sm_100a)"; }
 
-extern "C" int ftf_create(const char* model, const char* signature_key, const char* method_name,
-                          const ftf_config* cfg_in, ftf_runner** out) {
+static int create_runner(const char* model, const char* signature_key, const char* method_name,
+                         const ftf_config* cfg_in, ftf_runner** out) {
     if (out) *out = nullptr;
     if (!model || !out) return fail(nullptr, FTF_INVALID_ARGUMENT, "a model and an output handle must be provided");
     ftf_config cfg;
@@ -389,7 +394,9 @@ extern "C" int ftf_create(const char* model, const char* signature_key, const ch
     if (cfg.device < 0 || cfg.device >= n_dev)
         return fail(nullptr, FTF_INVALID_ARGUMENT, "device ordinal " + std::to_string(cfg.device) + " out of range");
 
-    std::unique_ptr<ftf_runner> r(new ftf_runner());
+    // from here on the runner is torn down by destroy_runner whichever way this function is left (a return or an exception)
+    if ((e = cudaSetDevice(cfg.device)) != cudaSuccess) return fail(nullptr, FTF_INTERNAL, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
+    std::unique_ptr<ftf_runner, void (*)(ftf_runner*)> r(new ftf_runner(), destroy_runner);
     r->cfg = cfg;
     r->device = cfg.device;
     const std::string m(model);
@@ -429,9 +436,8 @@ extern "C" int ftf_create(const char* model, const char* signature_key, const ch
         return fail(nullptr, FTF_INVALID_ARGUMENT, "requirement failed: method name '" + std::string(method_name) +
                     "' does not match the signature's '" + r->signature.method_name + "'");
 
-    if ((e = cudaSetDevice(cfg.device)) != cudaSuccess) return fail(nullptr, FTF_INTERNAL, std::string("cudaSetDevice: ") + cudaGetErrorString(e));
-    ftf_runner* raw = r.release();
-    auto bail = [&](int code, const std::string& msg) { destroy_runner(raw); return fail(nullptr, code, msg); };
+    ftf_runner* raw = r.get();
+    auto bail = [&](int code, const std::string& msg) { return fail(nullptr, code, msg); };
     for (auto& s : raw->slots) {
         s.h_in.host = true;
         if ((e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking)) != cudaSuccess ||
@@ -451,8 +457,26 @@ extern "C" int ftf_create(const char* model, const char* signature_key, const ch
         ftf_tensor dummy{};
         fix_geometry(raw, dummy, false);
     }
-    *out = raw;
+    *out = r.release();
     return FTF_OK;
+}
+
+// No exception may cross the C boundary: a malformed model file that drives a container past its limits (std::length_error,
+// std::bad_alloc) becomes a status like every other failure, and the half-built runner is released.
+extern "C" int ftf_create(const char* model, const char* signature_key, const char* method_name,
+                          const ftf_config* cfg_in, ftf_runner** out) {
+    try {
+        return create_runner(model, signature_key, method_name, cfg_in, out);
+    } catch (const std::bad_alloc&) {
+        if (out) *out = nullptr;
+        return fail(nullptr, FTF_RESOURCE_EXHAUSTED, "ftf_create: out of host memory");
+    } catch (const std::exception& ex) {
+        if (out) *out = nullptr;
+        return fail(nullptr, FTF_INVALID_ARGUMENT, std::string("ftf_create: malformed model (") + ex.what() + ")");
+    } catch (...) {
+        if (out) *out = nullptr;
+        return fail(nullptr, FTF_INTERNAL, "ftf_create: unexpected failure");
+    }
 }
 
 extern "C" int ftf_destroy(ftf_runner* r) {
@@ -547,6 +571,8 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
             if (out_keys[i] && r->outs[j].key == out_keys[i]) want[i] = (int)j;
         if (want[i] < 0) return fail(r, FTF_NOT_FOUND, std::string("no output named '") + (out_keys[i] ? out_keys[i] : "(null)") + "' in this signature");
     }
+    std::vector<int> want_unique;                     // only the fetched outputs travel back (Session.runner().fetch)
+    for (int j : want) if (std::find(want_unique.begin(), want_unique.end(), j) == want_unique.end()) want_unique.push_back(j);
     r->run_out.resize(r->outs.size());
     r->run_dims.resize(r->outs.size());
     for (size_t j = 0; j < r->outs.size(); ++j) {
@@ -610,7 +636,7 @@ extern "C" int ftf_run(ftf_runner* r, int32_t n_in, const char* const* in_keys, 
         }
         std::vector<void*> dst(r->outs.size());
         for (size_t j = 0; j < dst.size(); ++j) dst[j] = (uint8_t*)r->run_out[j].p + (size_t)c0 * r->outs[j].rec_bytes;
-        rc = enqueue(r, s, cn, src, dst.data());
+        rc = enqueue(r, s, cn, src, dst.data(), want_unique);
         if (rc) { if (rc == FTF_INTERNAL) r->dead = true; return rc; }
     }
     // join the slot streams on slot 0's stream and stamp the end
@@ -702,7 +728,7 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
                 rc = sl.d_out[j].ensure((size_t)cap * r->outs[j].rec_bytes, &r->err);
                 if (!rc) rc = sl.h_out[j].ensure((size_t)cap * r->outs[j].rec_bytes, &r->err);
             }
-            if (!rc && is_label_kind(r->kind)) rc = sl.d_img.ensure((size_t)cap * kInceptionSide * kInceptionSide * 3 * 2, &r->err);
+            if (!rc && r->kind == Kind::kNormalizeLabel) rc = sl.d_img.ensure((size_t)cap * kInceptionSide * kInceptionSide * 3 * 2, &r->err);
             if (rc) { r->open_slot = -1; return rc; }
         }
     }
@@ -761,7 +787,8 @@ extern "C" int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor
     if (rc) return rc;
     if (!n_ready || cap < 0 || (cap && (!tags || !outs))) return fail(r, FTF_INVALID_ARGUMENT, "poll: null output arrays");
     *n_ready = 0;
-    int poll_rc = FTF_OK;
+    r->poll_status.clear();
+    r->poll_error.clear();
     const size_t no = r->outs.size();
     // a batch also closes max_delay_us after its first record (and at once when the caller blocks on it)
     if (r->open_slot >= 0 && r->slots[r->open_slot].n > 0) {
@@ -779,9 +806,25 @@ extern "C" int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor
         cudaError_t e = may_block ? cudaEventSynchronize(s.done) : cudaEventQuery(s.done);
         if (e == cudaErrorNotReady) { cudaGetLastError(); break; }
         if (e != cudaSuccess) { r->dead = true; return cuda_fail(e, "poll", &r->err); }
-        // a batch of JPEG records: a corrupt entropy-coded segment is only known now; the batch's results are still
-        // handed out (the damaged image decodes as far as libjpeg would have got) and the call reports the failure
-        if (s.emitted == 0 && s.jpeg_n > 0) { const int frc = files_status(r, s); if (frc && !poll_rc) poll_rc = frc; }
+        // a batch of JPEG records: a corrupt entropy-coded segment is only known now.  It fails that record alone -- the
+        // reference fails only the offending record's map() -- so the batch's results are all handed out (the damaged
+        // image decodes as far as libjpeg would have got) and ftf_poll_status() says which records are bad.
+        if (s.emitted == 0) {
+            s.rec_status.clear();
+            if (s.jpeg_n > 0 && files_status(r, s, &s.rec_status) != FTF_OK) r->poll_error = r->err;
+            // outputs selected after this batch was launched were not downloaded with it: fetch them now
+            bool late = false;
+            for (int j : r->poll_sel)
+                if (!(s.downloaded & (1u << j))) {
+                    if ((rc = s.h_out[j].ensure((size_t)s.n * r->outs[j].rec_bytes, &r->err))) return rc;
+                    e = cudaMemcpyAsync(s.h_out[j].p, s.d_out[j].p, (size_t)s.n * r->outs[j].rec_bytes, cudaMemcpyDeviceToHost, s.stream);
+                    if (e != cudaSuccess) { r->dead = true; return cuda_fail(e, "poll (late download)", &r->err); }
+                    r->stats.d2h_bytes += (uint64_t)s.n * r->outs[j].rec_bytes;
+                    s.downloaded |= 1u << j;
+                    late = true;
+                }
+            if (late && (e = cudaStreamSynchronize(s.stream)) != cudaSuccess) { r->dead = true; return cuda_fail(e, "poll (late download)", &r->err); }
+        }
         may_block = false;
         const auto now = std::chrono::steady_clock::now();
         while (s.emitted < s.n && *n_ready < cap) {
@@ -796,13 +839,26 @@ extern "C" int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor
                 t.data = (uint8_t*)s.h_out[j].p + (size_t)i * r->outs[j].rec_bytes;
                 t.nbytes = (int64_t)r->outs[j].rec_bytes;
             }
+            r->poll_status.push_back((size_t)i < s.rec_status.size() ? s.rec_status[(size_t)i] : FTF_OK);
             r->latencies_us.push_back(std::chrono::duration<double, std::micro>(now - s.t_submit[i]).count());
             *n_ready += 1;
         }
         if (s.emitted == s.n) { r->in_flight.pop_front(); s.busy = false; }
     }
     if (r->latencies_us.size() > (1u << 20)) r->latencies_us.erase(r->latencies_us.begin(), r->latencies_us.begin() + (1u << 19));
-    return poll_rc;
+    return FTF_OK;
+}
+
+extern "C" int ftf_poll_status(ftf_runner* r, int32_t* status, int32_t cap, const char** message) {
+    if (!r) return fail(nullptr, FTF_INVALID_ARGUMENT, "a session must be provided");
+    if (cap < 0 || (cap && !status)) return fail(r, FTF_INVALID_ARGUMENT, "poll_status: null status array");
+    int first = FTF_OK;
+    for (size_t i = 0; i < r->poll_status.size(); ++i) {
+        if ((int32_t)i < cap) status[i] = r->poll_status[i];
+        if (r->poll_status[i] != FTF_OK && first == FTF_OK) first = r->poll_status[i];
+    }
+    if (message) *message = first != FTF_OK ? r->poll_error.c_str() : "";
+    return first;
 }
 
 extern "C" int ftf_poll_select(ftf_runner* r, int32_t n_keys, const char* const* keys) {
@@ -864,21 +920,16 @@ extern "C" int ftf_label_dev(ftf_runner* r, const void* images, int32_t in_dtype
     if (n < 0 || n > r->net->max_batch()) return fail(r, FTF_INVALID_ARGUMENT, "label_dev: batch exceeds the runner's max_batch");
     if (n == 0) return FTF_OK;
     Slot& s = r->slots[0];
-    const size_t img_elems = (size_t)kInceptionSide * kInceptionSide * 3;
     const void* img = images;
     const uint64_t before = launches_so_far();
-    if (in_dtype == FTF_FLOAT) {
-        if ((rc = s.d_in.ensure((size_t)n * img_elems * 2, &r->err))) return rc;
-        if ((rc = launch_cast_f32_bf16((const float*)images, s.d_in.p, (int64_t)n * img_elems, r->net_stream, &r->err))) return rc;
-        img = s.d_in.p;
-    } else if (in_dtype != FTF_BFLOAT16) return fail(r, FTF_INVALID_ARGUMENT, "label_dev: images must be FLOAT or BFLOAT16");
+    if (in_dtype != FTF_FLOAT && in_dtype != FTF_BFLOAT16) return fail(r, FTF_INVALID_ARGUMENT, "label_dev: images must be FLOAT or BFLOAT16");
     float* lg = logits;
     if (!lg) {
         if (s.d_out.size() < 2) s.d_out.resize(2);
         if ((rc = s.d_out[1].ensure((size_t)n * r->cfg.num_classes * 4, &r->err))) return rc;
         lg = (float*)s.d_out[1].p;
     }
-    if ((rc = r->net->forward(img, n, lg, r->net_stream, &r->err))) { if (rc == FTF_INTERNAL) r->dead = true; return rc; }
+    if ((rc = r->net->forward(img, in_dtype, n, lg, r->net_stream, &r->err))) { if (rc == FTF_INTERNAL) r->dead = true; return rc; }
     if (probs || (idx && score))
         rc = launch_softmax_topk(lg, n, r->cfg.num_classes, r->cfg.num_classes, (idx && score) ? r->cfg.top_k : 0, 1, probs, idx, score,
                                  r->net_stream, &r->err);
@@ -901,9 +952,9 @@ extern "C" int ftf_conv2d_bf16_dev(const void* in, int32_t n, int32_t h, int32_t
     sg.out = out; sg.ld = out_ld; sg.coff = out_off; sg.col_begin = 0;
     sg.flags = (bias ? kSegBias : 0) | (relu ? kSegRelu : 0) | (out_dtype == FTF_FLOAT ? kSegF32 : 0);
     ConvGeometry g{in, n, h, w, cin, in_ld, weights, bias, cout, kh, kw, stride, pad_h, pad_w};
-    ConvPlan plan;
-    int rc = conv_tc_plan(g, &sg, 1, device_sm_count(dev), &plan, &err);
-    if (!rc) rc = conv_tc_launch(plan, n, (cudaStream_t)stream, &err);
+    const ConvPlan* plan = nullptr;
+    int rc = conv_tc_plan_cached(g, &sg, 1, device_sm_count(dev), dev, &plan, &err);
+    if (!rc) rc = conv_tc_launch(*plan, n, (cudaStream_t)stream, &err);
     if (rc) set_thread_error(err);
     return rc;
 }
@@ -951,9 +1002,9 @@ extern "C" int ftf_pool_branch_bf16_dev(const void* in, int32_t n, int32_t h, in
     ConvSegment sg{};
     sg.out = pre; sg.ld = cout; sg.coff = 0; sg.col_begin = 0; sg.flags = kSegF32;
     ConvGeometry g{in, n, h, w, cin, in_ld, weights, nullptr, cout, 1, 1, 1, 0, 0};
-    ConvPlan plan;
-    int rc = conv_tc_plan(g, &sg, 1, device_sm_count(dev), &plan, &err);
-    if (!rc) rc = conv_tc_launch(plan, n, s, &err);
+    const ConvPlan* plan = nullptr;
+    int rc = conv_tc_plan_cached(g, &sg, 1, device_sm_count(dev), dev, &plan, &err);
+    if (!rc) rc = conv_tc_launch(*plan, n, s, &err);
     if (!rc) rc = launch_avgpool3x3_bias_relu(pre, bias, out, n, h, w, cout, out_ld, out_off, s, &err);
     cudaFreeAsync(pre, s);
     if (rc) set_thread_error(err);

@@ -44,6 +44,8 @@ struct Slot {
     std::vector<uint64_t> tags;
     std::vector<std::chrono::steady_clock::time_point> t_submit;
     int64_t emitted = 0;
+    uint32_t downloaded = 0;           // bit j: output j of the batch in flight was copied to h_out[j]
+    std::vector<int32_t> rec_status;   // per record of a finished batch of JPEG files: FTF_OK or what was wrong with the file
     // records that arrive as JPEG files (the reference's ImageFileTensor): decoder state of this slot (it stages the
     // files of the open micro-batch as they arrive), and the geometry of the decoded images sitting in d_in (jpeg_n > 0)
     ftf_jpeg_batch* jpeg = nullptr;
@@ -91,6 +93,8 @@ struct ftf_runner {
     std::deque<int> in_flight;         // launched slots, oldest first
     std::vector<std::vector<int64_t>> poll_dims;
     std::vector<int> poll_sel{0};      // outputs handed out per record by ftf_poll
+    std::vector<int32_t> poll_status;  // status of each record the last ftf_poll handed out (ftf_poll_status)
+    std::string poll_error;            // message of the first bad record among them
     std::vector<double> latencies_us;
 
     ftf_stats stats{};

@@ -298,13 +298,13 @@ static int load_bundle(const std::string& dir, SavedModelLite* m, std::string* e
     size_t fp = idx.size() - 48;
     uint64_t mo, ms, io, is;
     if (!varint(&fp, &mo) || !varint(&fp, &ms) || !varint(&fp, &io) || !varint(&fp, &is) ||
-        io + is + 5 > idx.size()) {
+        is > idx.size() - 5 || io > idx.size() - 5 - is) {          // no sums: offsets near 2^64 must not wrap past the check
         *err = ipath + ": corrupt table footer";
         return FTF_INVALID_ARGUMENT;
     }
     // Walks one block's entries (prefix-compressed keys; restart array at the tail).
     auto walk = [&](uint64_t off, uint64_t size, auto&& fn) -> bool {
-        if (off + size + 5 > idx.size() || size < 4) return false;
+        if (size < 4 || size > idx.size() - 5 || off > idx.size() - 5 - size) return false;      // idx.size() >= 48; no wrapping sums
         if (idx[off + size] != 0) return false;                              // compressed blocks unsupported
         uint32_t stored;
         memcpy(&stored, &idx[off + size + 1], 4);
@@ -318,7 +318,7 @@ static int load_bundle(const std::string& dir, SavedModelLite* m, std::string* e
         while (pos < limit) {
             uint64_t shared, fresh, vlen;
             if (!varint(&pos, &shared) || !varint(&pos, &fresh) || !varint(&pos, &vlen)) return false;
-            if (shared > key.size() || pos + fresh + vlen > limit) return false;
+            if (shared > key.size() || fresh > limit - pos || vlen > limit - pos - fresh) return false;
             key.resize(shared);
             key.append((const char*)&idx[pos], fresh);
             pos += fresh;
@@ -433,8 +433,8 @@ int SavedModelLite::variable_f32(const std::string& name, float* out, std::strin
     const BundleEntry& e = it->second;
     int64_t elems = 1;
     for (int64_t d : e.dims) elems *= d;
-    if (e.dtype != FTF_FLOAT || elems != 1 || e.size != 4 || e.offset < 0 ||
-        (size_t)(e.offset + e.size) > variable_data.size()) {
+    if (e.dtype != FTF_FLOAT || elems != 1 || e.size != 4 || e.offset < 0 || variable_data.size() < 4 ||
+        (uint64_t)e.offset > (uint64_t)variable_data.size() - 4) {
         *err = "variable '" + name + "' is not a readable float scalar";
         return FTF_INVALID_ARGUMENT;
     }

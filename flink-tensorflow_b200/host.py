@@ -291,13 +291,24 @@ class Runner:
         _check(self._lib.ftf_submit(self._h, tag, C.byref(t)), self._h)
 
     def poll(self, block=False, cap=256):
+        """[(tag, TensorValue or [TensorValue])] of the records that are ready, in submission order.  A record that failed
+        on its own (a JPEG file found corrupt on the device) comes back as (tag, exception): it fails alone, like one
+        map() call of the reference, and the records polled with it keep their results."""
         nsel = getattr(self, "_nsel", 1)
         tags = (C.c_uint64 * cap)()
         outs = (FtfTensor * (cap * nsel))()
         n = C.c_int32()
         _check(self._lib.ftf_poll(self._h, 1 if block else 0, tags, outs, cap, C.byref(n)), self._h)
+        status = (C.c_int32 * max(1, n.value))()
+        msg = C.c_char_p()
+        any_bad = self._lib.ftf_poll_status(self._h, status, n.value, C.byref(msg)) != _abi.OK
         res = []
         for i in range(n.value):
+            if any_bad and status[i] != _abi.OK:
+                res.append((tags[i], _ERRORS.get(status[i], RuntimeError)(
+                    f"record {tags[i]}: DecodeJpeg: invalid JPEG data (first bad record of this poll: "
+                    f"{(msg.value or b'').decode('utf-8', 'replace')}) [status {status[i]}]")))
+                continue
             vals = []
             for q in range(nsel):
                 o = outs[i * nsel + q]

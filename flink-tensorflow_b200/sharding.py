@@ -3,10 +3,9 @@
 One process (or Flink subtask) per GPU.  Records are dealt round-robin -- Flink's rebalance partitioner, which is what
 sits in front of a parallel mapWithModel (FT/streaming/package.scala:23-34) -- subtask i serves GPU i % n_gpus, weights are
 replicated.  torch.distributed is used only around the timed region: a barrier before and after, and a MAX reduction of the
-per-rank device time.  Nothing in this module touches CUDA, so it is testable with the gloo backend on CPU.
+per-rank device time.  Nothing in this module touches CUDA, so it is testable with the gloo backend on CPU.  torch is
+imported only inside the two reductions (bench.py and the gloo test call them); the partitioning helpers are plain Python.
 """
-import torch
-import torch.distributed as dist
 
 
 def shard_indices(n_records, rank, world):
@@ -38,6 +37,8 @@ def merge_sharded(parts, n_records):
 
 def max_over_ranks(value, device="cpu"):
     """The slowest rank's time: what a multi-GPU step takes."""
+    import torch
+    import torch.distributed as dist
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
         return float(value)
     t = torch.tensor([float(value)], dtype=torch.float64, device=device)
@@ -47,6 +48,7 @@ def max_over_ranks(value, device="cpu"):
 
 def aggregate_throughput(units_per_rank, ms_per_step_this_rank, device="cpu"):
     """Whole-job throughput: every rank's units per step over the slowest rank's step time."""
+    import torch.distributed as dist
     world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
     ms = max_over_ranks(ms_per_step_this_rank, device)
     return units_per_rank * world / (ms / 1e3), ms

@@ -114,6 +114,13 @@ int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* record);
 int ftf_poll(ftf_runner* r, int32_t block, uint64_t* tags, ftf_tensor* outs, int32_t cap,
              int32_t* n_ready);
 int ftf_flush(ftf_runner* r);
+/* Per-record outcome of the records the LAST ftf_poll handed out, in the same order: FTF_OK, or FTF_INVALID_ARGUMENT for
+ * a record whose JPEG file turned out to be corrupt once the device decoded it ("Invalid JPEG data" in TF's DecodeJpeg).
+ * ftf_poll itself returns FTF_OK in that case and still hands out every record of the batch: a bad record fails alone,
+ * as the reference's per-record map() does (EX/inception/inception.scala:39-46), and its neighbours keep their results.
+ * status may hold fewer than n_ready entries (cap); returns the first non-OK status (FTF_OK if none) and, through
+ * *message (may be NULL), the text describing it (valid until the next call on this runner). */
+int ftf_poll_status(ftf_runner* r, int32_t* status, int32_t cap, const char** message);
 /* Which outputs ftf_poll hands out per record (default: the signature's "outputs").  With n_keys > 1 the
  * caller's outs array holds cap * n_keys entries and record i's tensors sit at outs[i*n_keys + j].  Label
  * runners also expose "logits", "top_k_indices", "top_k_scores" (toTextLabels, InceptionModel.scala:81-89). */
@@ -206,7 +213,8 @@ int ftf_pool_branch_bf16_dev(const void* in, int32_t n, int32_t h, int32_t w, in
  * HBM at open() and treats later allocations as faults.  Same arguments and result as ftf_pool_branch_bf16_dev; the fp32
  * scratch is a fixed FTF_POOL_BRANCH_STATIC_MAX_BYTES array inside the library (resident on every GPU that loads it
  * until the process exits).  n*h*w*cout*4 beyond that size is refused with FTF_RESOURCE_EXHAUSTED.  The first call on a
- * device also looks up the array's device address; make that call before starting any stream capture.  All calls on a
+ * device also looks up the array's device address; make that call before starting any stream capture.  Planning is
+ * host work only (the FTF_CONV_TUNE switch that lets other planners time kernels on the device is ignored).  All calls on a
  * device share the array: calls whose GPU work may overlap (other streams, other threads) race and must be ordered by
  * the caller.  Nothing in it needs clearing between calls. */
 #define FTF_POOL_BRANCH_STATIC_MAX_BYTES (8ll << 20)

@@ -129,6 +129,28 @@ def test_conv_variants_agree(dev, monkeypatch):
         assert diffs[("wm", "1")] <= 1e-5, diffs
 
 
+@pytest.mark.parametrize("shape", CONV_SHAPES)
+def test_pixel_major_and_weight_major_give_the_same_bits(dev, monkeypatch, shape):
+    """Every kernel family walks K in the same order and the tensor core's fp32 accumulation does not depend on which
+    operand sits on the M side: whichever family the plan-time timing picks on a given GPU, a record's result is the same.
+    (This is what lets subtasks on different GPUs, which time their candidates independently, agree bit for bit.)"""
+    import torch
+    n, h, w, cin, cout, kh, kw, s, ph, pw = shape
+    g = torch.Generator(device="cuda").manual_seed(sum(shape))
+    x = torch.randn((n, h, w, cin), device="cuda", generator=g).to(torch.bfloat16)
+    wt = (torch.randn((cout, kh, kw, cin), device="cuda", generator=g) * (2.0 / (kh * kw * cin)) ** 0.5).to(torch.bfloat16)
+    b = torch.rand(cout, device="cuda", generator=g) * 0.2 - 0.1
+    outs = {}
+    monkeypatch.setenv("FTF_CONV_TUNE", "0")
+    for kind in ("pm", "wm"):
+        monkeypatch.setenv("FTF_CONV_KIND", kind)
+        try:
+            outs[kind] = dev.conv2d_bf16(x, wt, b, s, (ph, pw), out_dtype=torch.float32).clone()
+        except ValueError:
+            pytest.skip(f"no {kind} plan for this shape")
+    assert torch.equal(outs["pm"], outs["wm"]), float((outs["pm"] - outs["wm"]).abs().max())
+
+
 def test_pool_kernels_match_oracle(dev, oracle):
     """K4 max pool, K5 pool branch, K6 global average pool on bf16 tensors."""
     import torch
@@ -238,11 +260,11 @@ def test_whole_network_on_one_kernel_family(ftf, oracle, monkeypatch, kind):
     assert np.array_equal(res["top_k_indices"].to_array(), wi)
 
 
-def test_two_label_runners_share_one_gpu(ftf, monkeypatch):
+def test_two_label_runners_share_one_gpu(ftf):
     """Two Flink subtasks on one GPU: two runners created and driven concurrently from two threads give the bits a single
-    runner gives (model-chosen kernels, so that both pick the same ones whatever the timing noise)."""
+    runner gives.  Kernel choices are timed once per process and layer (under a lock) and taken over by every later runner,
+    so all three runners here run the same kernels whatever the timing noise."""
     import threading
-    monkeypatch.setenv("FTF_CONV_TUNE", "0")
     x = np.random.default_rng(11).standard_normal((4, 299, 299, 3)).astype(np.float32)
     cfg = ftf.default_config(max_batch=4, top_k=5, num_classes=1000, seed=2024)
     ref = ftf.Runner("builtin:inception_v3", None, None, cfg)

@@ -235,6 +235,79 @@ def test_file_records_through_submit_poll(ftf, oracle):
     r.close()
 
 
+def test_one_corrupt_file_fails_alone_in_its_micro_batch(ftf, oracle):
+    """A record whose file turns out corrupt on the device fails by itself (the reference fails that record's map() call
+    only); the records batched and polled with it keep their results, in order."""
+    rng = np.random.default_rng(31)
+    files = [_jpeg(_photo(rng, 96, 128), quality=80, optimize=True) for _ in range(6)]
+    i = files[2].index(b"\xff\xda")
+    start = i + 2 + int.from_bytes(files[2][i + 2:i + 4], "big")
+    files[2] = files[2][:start + 50] + b"\xfe" * 200 + files[2][start + 250:]     # no all-ones code in an optimised table
+    cfg = ftf.default_config(max_batch=4, max_delay_us=500, out_h=32, out_w=24, mean=117.0, scale=1.0)
+    r = ftf.Runner("builtin:image_normalization", None, None, cfg)
+    try:
+        for k, f in enumerate(files):
+            r.submit(70 + k, ftf.bytes_to_tensor(f))
+        r.flush()
+        res = []
+        while len(res) < len(files):
+            res += r.poll(block=True)                     # must not raise: the bad record is an entry, not a failed call
+        assert [t for t, _ in res] == list(range(70, 76))
+        for k, (_, tv) in enumerate(res):
+            if k == 2:
+                assert isinstance(tv, ValueError) and "invalid JPEG data" in str(tv)
+                continue
+            want = oracle.resize_bilinear_norm_u8(oracle.jpeg_decode(files[k])[None], 32, 24, 117.0, 1.0)[0]
+            assert np.array_equal(_bits(tv.to_array()), _bits(want)), k
+        # the C-level view of the same thing: ftf_poll returns OK, ftf_poll_status names the record
+        import ctypes as C
+        lib = ftf._abi.load_library()
+        r.submit(1, ftf.bytes_to_tensor(files[2]))
+        r.submit(2, ftf.bytes_to_tensor(files[0]))
+        r.flush()
+        from flink_tensorflow_b200.host import FtfTensor
+        tags, outs, n = (C.c_uint64 * 8)(), (FtfTensor * 8)(), C.c_int32()
+        assert lib.ftf_poll(r.handle, 1, tags, outs, 8, C.byref(n)) == 0 and n.value == 2
+        st, msg = (C.c_int32 * 8)(), C.c_char_p()
+        assert lib.ftf_poll_status(r.handle, st, 8, C.byref(msg)) == ftf._abi.INVALID_ARGUMENT
+        assert list(st[:2]) == [ftf._abi.INVALID_ARGUMENT, 0] and b"image 0" in msg.value
+    finally:
+        r.close()
+
+
+def test_forged_giant_header_is_refused_before_anything_is_sized(dev, cases):
+    """TF refuses frames of 2^29 or more output bytes; a 65535x65535 header must not become a multi-gigabyte allocation."""
+    f = bytearray(cases["444_q98"][0])
+    i = f.index(b"\xff\xc0")
+    f[i + 5:i + 9] = b"\xff\xff\xff\xff"                  # height, width
+    b = dev.JpegBatch()
+    with pytest.raises(ValueError, match="too large"):
+        b.load([bytes(f)])
+    b.close()
+
+
+def test_refused_file_leaves_the_open_micro_batch_as_it_was(ftf, oracle, cases):
+    """A file that ends inside its scan is refused at submit (try_recover_truncated is false in the reference's graph) and
+    joins no batch; what it had reserved in the open batch is given back, so its neighbours decode and resize as one
+    uniform batch and come back in order."""
+    good = cases["420_48x64_q75"][0]
+    cfg = ftf.default_config(max_batch=8, max_delay_us=500, out_h=20, out_w=28, mean=117.0, scale=1.0)
+    r = ftf.Runner("builtin:image_normalization", None, None, cfg)
+    try:
+        r.submit(1, ftf.bytes_to_tensor(good))
+        with pytest.raises(ValueError, match="ends inside the scan"):
+            r.submit(2, ftf.bytes_to_tensor(good[: len(good) * 2 // 3]))
+        r.submit(3, ftf.bytes_to_tensor(good))
+        r.flush()
+        res = r.poll(block=True)
+        assert [t for t, _ in res] == [1, 3]
+        want = oracle.resize_bilinear_norm_u8(cases["420_48x64_q75"][1][None], 20, 28, 117.0, 1.0)[0]
+        for _, tv in res:
+            assert np.array_equal(_bits(tv.to_array()), _bits(want))
+    finally:
+        r.close()
+
+
 def test_files_and_decoded_pixels_label_alike(ftf, oracle):
     """normalize_label fed JPEG files gives exactly what it gives when fed the oracle-decoded pixels of those files."""
     rng = np.random.default_rng(29)
