@@ -250,7 +250,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
     uint64_t* tmem_empty = tmem_full + kAccStages;
     uint32_t* tmem_slot = (uint32_t*)(tmem_empty + kAccStages);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // The warp index comes out of a shuffle so that the compiler KNOWS it is warp-uniform: the role loops below (TMA
+    // producer, MMA issuer) then live entirely on the uniform datapath -- descriptors in uniform registers, stepped by
+    // UIADD3, UTCHMMA / UTMALDG issued back to back -- instead of being carried in vector registers and moved over with
+    // an ELECT + five R2UR + VOTEU sequence in front of every single tcgen05.mma (245 R2UR in the halo kernel before, 32
+    // after), which made the issuing thread, not the tensor pipe, the limit of every tile narrower than 256 columns.
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int k_blocks = p.KH * p.KW * p.cin_chunks;
     const int rank = kPair ? (int)ptx::cluster_ctarank() : 0;
     // work items: (tile of 128 pixels, or pair of tiles) x n_tile, walked by CTA (or cluster) index
@@ -409,7 +414,12 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
     uint64_t* tmem_empty = tmem_full + kAccStages;
     uint32_t* tmem_slot = (uint32_t*)(tmem_empty + kAccStages);
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // The warp index comes out of a shuffle so that the compiler KNOWS it is warp-uniform: the role loops below (TMA
+    // producer, MMA issuer) then live entirely on the uniform datapath -- descriptors in uniform registers, stepped by
+    // UIADD3, UTCHMMA / UTMALDG issued back to back -- instead of being carried in vector registers and moved over with
+    // an ELECT + five R2UR + VOTEU sequence in front of every single tcgen05.mma (245 R2UR in the halo kernel before, 32
+    // after), which made the issuing thread, not the tensor pipe, the limit of every tile narrower than 256 columns.
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int taps = p.KH * p.KW;
     const int T = p.S * kBlockM;
     const int q_tiles = (int)((p.Q + T - 1) / T);

@@ -146,7 +146,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
 
     __shared__ int pix_tab[2 * kMaxTilePixels];
     __shared__ __align__(16) uint16_t stage_t[kEpiWarps * 32 * kStageRow];   // per-warp 32 pixel x 32 channel transposition tiles                // halo mode: tile column -> output pixel index or -1 (double buffered)
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // The warp index comes out of a shuffle so that the compiler KNOWS it is warp-uniform: the role loops below (TMA
+    // producer, MMA issuer) then live entirely on the uniform datapath -- descriptors in uniform registers, stepped by
+    // UIADD3, UTCHMMA / UTMALDG issued back to back -- instead of being carried in vector registers and moved over with
+    // an ELECT + five R2UR + VOTEU sequence in front of every single tcgen05.mma (245 R2UR in the halo kernel before, 32
+    // after), which made the issuing thread, not the tensor pipe, the limit of every tile narrower than 256 columns.
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int taps = p.KH * p.KW;
     const int T = p.S * p.np;                                  // (virtual) pixels per CTA tile
     const long long span = kHalo ? p.Q : p.M;

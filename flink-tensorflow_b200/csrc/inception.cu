@@ -14,6 +14,7 @@
 #include "inception.h"
 #include "conv_tc.h"
 #include "pools.h"
+#include "f32_path.h"
 #include "ptx.cuh"
 #include <cuda_bf16.h>
 #include <math.h>
@@ -172,14 +173,14 @@ int launch_cast_f32_bf16(const float* in, void* out, int64_t n, cudaStream_t s, 
 // network
 // ------------------------------------------------------------------------------------------------
 struct Act {
-    __nv_bfloat16* p = nullptr;
+    void* p = nullptr;                   // bf16 (tensor-core mode) or fp32 (precision mode) NHWC
     int h = 0, w = 0, c = 0;
 };
 
 constexpr int kLanes = 4;                // streams an Inception block's independent branches are spread over
 
 struct Op {
-    enum Type { kStem, kConv, kMaxPool, kAvgPoolBiasRelu, kGap, kFork, kJoin } type;
+    enum Type { kStem, kConv, kMaxPool, kAvgPoolBiasRelu, kGap, kFork, kJoin, kConvF32 } type;
     int lane = 0;                        // stream the op runs on (0 = the caller's stream)
     int lanes = 0;                       // kFork/kJoin: bit mask of the lanes 1..3 that branch off / come back
     int plan = -1;                       // kConv
@@ -190,8 +191,16 @@ struct Op {
     std::string tag;                     // layer name(s) for the FTF_TIMELINE dump
 };
 
+// one convolution of the fp32 mode: geometry + where its column ranges go
+struct ConvF32 {
+    ConvGeometry g;
+    std::vector<ConvSegment> segs;
+};
+
 struct InceptionV3::Impl {
     int device = 0, sms = 148, max_batch = 0, classes = 0;
+    bool f32 = false;                     // compute_dtype FTF_FLOAT: fp32 activations and weights, CUDA-core kernels (f32_path.cu)
+    std::vector<ConvF32> convs_f32;
     uint64_t seed = 0;
     std::vector<void*> allocs;
     std::vector<ConvPlan> plans;
@@ -241,7 +250,7 @@ struct InceptionV3::Impl {
     }
     Act act(int h, int w, int c) {
         Act a; a.h = h; a.w = w; a.c = c;
-        a.p = (__nv_bfloat16*)dev_alloc((size_t)max_batch * h * w * c * 2, true);
+        a.p = dev_alloc((size_t)max_batch * h * w * c * (f32 ? 4 : 2), true);
         return a;
     }
     struct Branch { std::string name; int cout; Act* dst; int coff; bool pool; };
@@ -251,7 +260,8 @@ struct InceptionV3::Impl {
         if (rc) return;
         int total = 0;
         for (auto& b : br) total += b.cout;
-        std::vector<uint16_t> w16((size_t)total * kh * kw * in.c);
+        std::vector<uint16_t> w16(f32 ? 0 : (size_t)total * kh * kw * in.c);
+        std::vector<float> w32(f32 ? (size_t)total * kh * kw * in.c : 0);
         std::vector<float> bias(total);
         std::vector<ConvSegment> segs;
         const int OH = (in.h + 2 * ph - kh) / s + 1, OW = (in.w + 2 * pw - kw) / s + 1;
@@ -260,7 +270,8 @@ struct InceptionV3::Impl {
             std::vector<float> w, bb;
             conv_weights(seed, b.name, b.cout, kh, kw, in.c, &w, &bb);
             const size_t per = (size_t)kh * kw * in.c;
-            for (size_t i = 0; i < w.size(); ++i) w16[(size_t)col * per + i] = bf16_bits(w[i]);
+            if (f32) memcpy(&w32[(size_t)col * per], w.data(), w.size() * 4);         // the oracle's fp32 weights, unrounded
+            else for (size_t i = 0; i < w.size(); ++i) w16[(size_t)col * per + i] = bf16_bits(w[i]);
             for (int o = 0; o < b.cout; ++o) bias[col + o] = bb[o];
             ConvSegment sg{};
             sg.col_begin = col;
@@ -272,17 +283,24 @@ struct InceptionV3::Impl {
                 sg.out = scratch; sg.ld = b.cout; sg.coff = 0; sg.flags = kSegF32;
                 pending_pool.push_back({scratch, dbias, b.dst, b.coff, b.cout, OH, OW});
             } else {
-                sg.out = b.dst->p; sg.ld = b.dst->c; sg.coff = b.coff; sg.flags = kSegBias | kSegRelu;
+                sg.out = b.dst->p; sg.ld = b.dst->c; sg.coff = b.coff; sg.flags = kSegBias | kSegRelu | (f32 ? kSegF32 : 0);
             }
             segs.push_back(sg);
             col += b.cout;
         }
-        void* dw = dev_alloc(w16.size() * 2, false);
+        void* dw = dev_alloc(f32 ? w32.size() * 4 : w16.size() * 2, false);
         float* db = (float*)dev_alloc((size_t)total * 4, false);
         if (rc) return;
-        cudaMemcpy(dw, w16.data(), w16.size() * 2, cudaMemcpyHostToDevice);
+        if (f32) cudaMemcpy(dw, w32.data(), w32.size() * 4, cudaMemcpyHostToDevice);
+        else cudaMemcpy(dw, w16.data(), w16.size() * 2, cudaMemcpyHostToDevice);
         cudaMemcpy(db, bias.data(), (size_t)total * 4, cudaMemcpyHostToDevice);
         ConvGeometry g{in.p, max_batch, in.h, in.w, in.c, in.c, dw, db, total, kh, kw, s, ph, pw};
+        if (f32) {
+            convs_f32.push_back(ConvF32{g, segs});
+            Op op{}; op.type = Op::kConvF32; op.lane = cur_lane; op.plan = (int)convs_f32.size() - 1; op.tag = br[0].name;
+            ops.push_back(op);
+            return;
+        }
         ConvPlan plan;
         rc = conv_tc_plan(g, segs.data(), (int)segs.size(), share(), &plan, err, kPlanTune);
         if (rc) return;
@@ -430,9 +448,13 @@ struct InceptionV3::Impl {
                 stem.b[o] = b[o];
             }
         }
-        Act a1 = act(149, 149, 32);
-        { Op o{}; o.type = Op::kStem; o.in = image.p; o.out = a1.p; o.H = 299; o.W = 299; o.OH = 149; o.OW = 149; ops.push_back(o); }
-        named["Conv2d_1a_3x3"] = a1;
+        Act a1;
+        if (f32) a1 = conv("Conv2d_1a_3x3", image, 32, 3, 3, 2, 0, 0);        // the generic fp32 kernel takes any channel count
+        else {
+            a1 = act(149, 149, 32);
+            Op o{}; o.type = Op::kStem; o.in = image.p; o.out = a1.p; o.H = 299; o.W = 299; o.OH = 149; o.OW = 149; ops.push_back(o);
+            named["Conv2d_1a_3x3"] = a1;
+        }
         Act a2 = conv("Conv2d_2a_3x3", a1, 32, 3, 3, 1, 0, 0);
         Act a3 = conv("Conv2d_2b_3x3", a2, 64, 3, 3, 1, 1, 1);
         Act p1 = act(73, 73, 64);
@@ -461,6 +483,22 @@ struct InceptionV3::Impl {
         if (rc) return;
         const int cols = (classes + 15) / 16 * 16;
         logits = (float*)dev_alloc((size_t)max_batch * cols * 4, true);
+        if (f32) {
+            std::vector<float> w32((size_t)cols * x.c, 0.0f);
+            const Stream sw(seed + 90, "fc", 0);
+            float* wp = w32.data();
+            fill_parallel((int64_t)classes * x.c, [&](int64_t lo, int64_t hi) { for (int64_t i = lo; i < hi; ++i) wp[i] = (float)(sw.normal((uint64_t)i) * 0.05); });
+            void* dw = dev_alloc(w32.size() * 4, false);
+            float* db = (float*)dev_alloc((size_t)cols * 4, true);              // fc bias = 0
+            if (rc) return;
+            cudaMemcpy(dw, w32.data(), w32.size() * 4, cudaMemcpyHostToDevice);
+            ConvSegment sg{}; sg.out = logits; sg.ld = cols; sg.coff = 0; sg.col_begin = 0; sg.flags = kSegBias | kSegF32;
+            convs_f32.push_back(ConvF32{ConvGeometry{gap.p, max_batch, 1, 1, x.c, x.c, dw, db, cols, 1, 1, 1, 0, 0}, {sg}});
+            Op op{}; op.type = Op::kConvF32; op.plan = (int)convs_f32.size() - 1; op.tag = "fc";
+            ops.push_back(op);
+            logits_ld = cols;
+            return;
+        }
         std::vector<uint16_t> w16((size_t)cols * x.c, 0);
         std::vector<float> bias(cols, 0.0f);
         {
@@ -491,9 +529,9 @@ InceptionV3::~InceptionV3() { delete impl_; }
 
 int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batch, int compute_dtype,
                         std::unique_ptr<InceptionV3>* out, std::string* err) {
-    if (compute_dtype != FTF_BFLOAT16) {
-        if (err) *err = "builtin:inception_v3 computes in bf16 (fp32 accumulate); compute_dtype FLOAT is not built";
-        return FTF_UNIMPLEMENTED;
+    if (compute_dtype != FTF_BFLOAT16 && compute_dtype != FTF_FLOAT) {
+        if (err) *err = "builtin:inception_v3: compute_dtype must be FTF_BFLOAT16 (tensor cores, fp32 accumulate) or FTF_FLOAT (fp32 throughout)";
+        return FTF_INVALID_ARGUMENT;
     }
     if (max_batch <= 0 || max_batch > 1024 || num_classes <= 0 || num_classes > 65536) {
         if (err) *err = "inception_v3: max_batch must be in [1,1024] and num_classes in [1,65536]";
@@ -504,6 +542,7 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
     net->impl_ = new Impl();
     Impl& m = *net->impl_;
     m.device = device; m.sms = device_sm_count(device); m.max_batch = max_batch; m.classes = num_classes; m.seed = seed; m.err = err;
+    m.f32 = compute_dtype == FTF_FLOAT;
     m.build();
     if (m.rc) return m.rc;
     if (const char* tl = getenv("FTF_TIMELINE")) {         // diagnostics only: kernels stamp their start/end times
@@ -558,18 +597,27 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
             if (rc) return rc;
             break;
         }
+        case Op::kConvF32: {
+            const ConvF32& c = m.convs_f32[op.plan];
+            const int rc = f32::launch_conv(c.g, c.segs.data(), (int)c.segs.size(), nb, st, err);
+            if (rc) return rc;
+            break;
+        }
         case Op::kMaxPool: {
-            const int rc = launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
+            const int rc = m.f32 ? f32::launch_maxpool3x3s2((const float*)op.in, (float*)op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err)
+                                 : launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
             if (rc) return rc;
             break;
         }
         case Op::kAvgPoolBiasRelu: {
-            const int rc = launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
+            const int rc = m.f32 ? f32::launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, (float*)op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err)
+                                 : launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
             if (rc) return rc;
             break;
         }
         case Op::kGap: {
-            const int rc = launch_global_avgpool(op.in, op.out, nb, op.H * op.W, op.C, st, err, tl);
+            const int rc = m.f32 ? f32::launch_global_avgpool((const float*)op.in, (float*)op.out, nb, op.H * op.W, op.C, st, err)
+                                 : launch_global_avgpool(op.in, op.out, nb, op.H * op.W, op.C, st, err, tl);
             if (rc) return rc;
             break;
         }
@@ -616,6 +664,17 @@ int InceptionV3::forward(const void* images, int in_dtype, int64_t n, float* log
     if (in_dtype != FTF_FLOAT && in_dtype != FTF_BFLOAT16) { if (err) *err = "inception_v3: images must be FLOAT or BFLOAT16"; return FTF_INVALID_ARGUMENT; }
     if (n == 0) return FTF_OK;
     const int nb = (int)n;
+    if (m.f32) {
+        // precision mode: fp32 images only; they are copied into the network's own input tensor (its convolutions were
+        // planned on fixed buffers) and the ops run as plain stream launches
+        if (in_dtype != FTF_FLOAT) { if (err) *err = "inception_v3 (compute_dtype FLOAT) takes FLOAT images"; return FTF_INVALID_ARGUMENT; }
+        FTF_CUDA(cudaMemcpyAsync(m.image.p, images, (size_t)n * 299 * 299 * 3 * 4, cudaMemcpyDeviceToDevice, s), err);
+        const int rc = run_ops(m, nb, s, err, m.image.p, FTF_FLOAT, 0, m.ops.size());
+        if (rc) return rc;
+        FTF_CUDA(cudaMemcpy2DAsync(logits, (size_t)m.classes * 4, m.logits, (size_t)m.logits_ld * 4, (size_t)m.classes * 4, (size_t)n,
+                                   cudaMemcpyDeviceToDevice, s), err);
+        return FTF_OK;
+    }
     // The stem convolution reads the caller's images in place and is launched on its own, in front of the graph: a graph
     // fixes its kernels' pointers, and copying every batch (34 MB in, 34 MB out) into a fixed buffer first cost about 1 %
     // of the step.
@@ -684,6 +743,7 @@ int InceptionV3::activation(const std::string& name, int64_t n, float* host_out,
     dims[0] = (int)n; dims[1] = a.h; dims[2] = a.w; dims[3] = a.c;
     if (!host_out) return FTF_OK;
     if (elems > cap) { if (err) *err = "activation buffer too small"; return FTF_OUT_OF_RANGE; }
+    if (m.f32) { FTF_CUDA(cudaMemcpy(host_out, a.p, (size_t)elems * 4, cudaMemcpyDeviceToHost), err); return FTF_OK; }
     std::vector<uint16_t> tmp((size_t)elems);
     FTF_CUDA(cudaMemcpy(tmp.data(), a.p, (size_t)elems * 2, cudaMemcpyDeviceToHost), err);
     for (int64_t i = 0; i < elems; ++i) {

@@ -216,10 +216,12 @@ int enqueue(ftf_runner* r, Slot& s, int64_t n, const void* h_src, void* const* h
         const void* img = s.d_in.p;        // fp32 records: the first convolution reads them where they were uploaded
         int img_dtype = FTF_FLOAT;
         if (r->kind == Kind::kNormalizeLabel) {
-            // bf16 image batch, per slot so that the next batch's normalisation can overlap this one's network
-            if ((rc = s.d_img.ensure((size_t)n * img_elems * 2, err))) return rc;
-            if ((rc = normalise(kInceptionSide, kInceptionSide, s.d_img.p, FTF_BFLOAT16))) break;
-            img = s.d_img.p; img_dtype = FTF_BFLOAT16;
+            // normalised image batch (bf16, or fp32 for a compute_dtype FLOAT network), per slot so that the next batch's
+            // normalisation can overlap this one's network
+            img_dtype = r->cfg.compute_dtype == FTF_FLOAT ? FTF_FLOAT : FTF_BFLOAT16;
+            if ((rc = s.d_img.ensure((size_t)n * img_elems * (img_dtype == FTF_FLOAT ? 4 : 2), err))) return rc;
+            if ((rc = normalise(kInceptionSide, kInceptionSide, s.d_img.p, img_dtype))) break;
+            img = s.d_img.p;
         }
         FTF_CUDA(cudaEventRecord(s.done, s.stream), err);
         FTF_CUDA(cudaStreamWaitEvent(r->net_stream, s.done, 0), err);
@@ -728,7 +730,8 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
                 rc = sl.d_out[j].ensure((size_t)cap * r->outs[j].rec_bytes, &r->err);
                 if (!rc) rc = sl.h_out[j].ensure((size_t)cap * r->outs[j].rec_bytes, &r->err);
             }
-            if (!rc && r->kind == Kind::kNormalizeLabel) rc = sl.d_img.ensure((size_t)cap * kInceptionSide * kInceptionSide * 3 * 2, &r->err);
+            if (!rc && r->kind == Kind::kNormalizeLabel)
+                rc = sl.d_img.ensure((size_t)cap * kInceptionSide * kInceptionSide * 3 * (r->cfg.compute_dtype == FTF_FLOAT ? 4 : 2), &r->err);
             if (rc) { r->open_slot = -1; return rc; }
         }
     }

@@ -336,3 +336,44 @@ def test_normalize_label_chain(ftf, oracle):
     assert np.abs(res["logits"].to_array() - want).max() <= 1e-2 * np.abs(want).max()
     assert np.array_equal(res["top_k_indices"].to_array(), oracle.top_labels(oracle.softmax_rows(want), 1000, 5)[0])
     r.close()
+
+
+def test_fp32_compute_mode_matches_the_fp32_oracle(ftf, oracle):
+    """compute_dtype = FTF_FLOAT (north_star: logits within 1e-4 in fp32): fp32 activations, weights and accumulation --
+    the precision the reference's Session.run computes in (InceptionModel.scala:58-67).  Checked against the fp32 oracle
+    (mode 0) and the committed torchvision logits, layer taps included."""
+    import oracle.inception as oi
+    g = np.load(os.path.join(HERE, "golden", "inception_v3.npz"))
+    x = np.random.default_rng(int(g["image_seed"])).standard_normal((2, 299, 299, 3)).astype(np.float32)
+    cfg = ftf.default_config(max_batch=2, top_k=5, num_classes=1000, seed=int(g["seed"]), compute_dtype=ftf.DataType.FLOAT)
+    r = ftf.Runner("builtin:inception_v3", None, None, cfg)
+    try:
+        res = r.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits", "top_k_indices", "outputs"])
+        logits = res["logits"].to_array()
+        net = oi.Net(1000, int(g["seed"]), mode=0)
+        want = net.forward(x)
+        assert np.abs(logits - want).max() <= 1e-4 * np.abs(want).max(), np.abs(logits - want).max() / np.abs(want).max()
+        tv = g["logits_torchvision"]
+        assert np.abs(logits - tv).max() <= 1e-4 * np.abs(tv).max()
+        assert np.array_equal(res["top_k_indices"].to_array(), np.argsort(-want, axis=1, kind="stable")[:, :5])
+        assert np.allclose(res["outputs"].to_array(), oracle.softmax_rows(logits), rtol=1e-5, atol=1e-12)
+        for name in ("Conv2d_1a_3x3", "Conv2d_4a_3x3", "Mixed_5b", "Mixed_6a", "Mixed_6e", "Mixed_7c", "gap"):
+            _, tap = net.forward(x, tap=name)
+            got = _activation(ftf, r, name, 2)
+            assert got.shape == tap.shape and np.abs(got - tap).max() <= 1e-4 * (np.abs(tap).max() + 1e-6), name
+        # a bf16 image batch has no meaning for this network
+        with pytest.raises(ValueError):
+            ftf.Runner("builtin:inception_v3", None, None, ftf.default_config(max_batch=1, compute_dtype=ftf.DataType.INT32))
+    finally:
+        r.close()
+    # the chained runner normalises to fp32 in this mode
+    cfg2 = ftf.default_config(max_batch=1, top_k=5, out_h=299, out_w=299, mean=128.0, scale=128.0, seed=2024, compute_dtype=ftf.DataType.FLOAT)
+    r2 = ftf.Runner("builtin:normalize_label", None, None, cfg2)
+    try:
+        img = np.random.default_rng(9).integers(0, 256, (1, 480, 640, 3), dtype=np.uint8)
+        got = r2.run({"inputs": ftf.TensorValue.from_array(img)}, ["logits"])["logits"].to_array()
+        norm = oracle.resize_bilinear_norm_u8(img, 299, 299, 128.0, 128.0, threads=8)
+        want = oi.Net(1000, 2024, mode=0).forward(norm)
+        assert np.abs(got - want).max() <= 1e-4 * np.abs(want).max()
+    finally:
+        r2.close()
