@@ -154,8 +154,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int taps = p.KH * p.KW;
     const int T = p.S * p.np;                                  // (virtual) pixels per CTA tile
-    const long long span = kHalo ? p.Q : p.M;
-    const int p_tiles = (int)((span + T - 1) / T);
+    // 32-bit index arithmetic throughout (the plan refuses layers of 2^31 pixels): a 64-bit division is a subroutine call, and
+    // with calls in the kernel the compiler keeps the role loops off the uniform datapath
+    const uint32_t span = (uint32_t)(kHalo ? p.Q : p.M);
+    const int p_tiles = (int)((span + (uint32_t)T - 1u) / (uint32_t)T);
     const int total_tiles = p_tiles * p.m_tiles;
     const int acc_cols = p.S * p.np;
     const int n_a = kHalo ? 2 : p.stages;
@@ -186,10 +188,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
         int as = 0, aph = 0, bs = 0, bph = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int p_tile = tile / p.m_tiles, m_tile = tile - p_tile * p.m_tiles;
-            const long long x0 = (long long)p_tile * T;                    // first (virtual) pixel of the tile
+            const uint32_t x0 = (uint32_t)p_tile * (uint32_t)T;            // first (virtual) pixel of the tile
             if (!kHalo) {
-                const int img = (int)(x0 / (p.OH * p.OW));
-                const int rem = (int)(x0 - (long long)img * (p.OH * p.OW));
+                const int img = (int)(x0 / (uint32_t)(p.OH * p.OW));
+                const int rem = (int)(x0 - (uint32_t)img * (uint32_t)(p.OH * p.OW));
                 const int oh = rem / p.OW, ow = rem - oh * p.OW;
                 const int base_w = ow * p.stride - p.pad_w, base_h = oh * p.stride - p.pad_h;
                 for (int chunk = 0; chunk < p.cin_chunks; ++chunk) {          // K order: chunk outer, tap inner (as in halo mode)
@@ -209,11 +211,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                     uint8_t* dst = win_base + (size_t)as * p.p_stage_bytes;
                     ptx::mbar_expect_tx_elect(&bars->a_full[as], (uint32_t)p.p_stage_bytes);
                     for (int i = 0; i < p.p_loads; ++i) {                  // the window, kHaloLoadRows padded pixels per load
-                        const long long q = x0 + (long long)i * kHaloLoadRows;
-                        const int wp = (int)(q % p.Wp);
-                        const long long t = q / p.Wp;
-                        const int hp = (int)(t % p.Hp);
-                        const int img = (int)(t / p.Hp);
+                        const uint32_t q = x0 + (uint32_t)i * kHaloLoadRows;
+                        const int wp = (int)(q % (uint32_t)p.Wp);
+                        const uint32_t t = q / (uint32_t)p.Wp;
+                        const int hp = (int)(t % (uint32_t)p.Hp);
+                        const int img = (int)(t / (uint32_t)p.Hp);
                         ptx::tma_load_im2col_elect(dst + (size_t)i * kHaloLoadRows * rb, &tm_p, &bars->a_full[as], chunk * p.kc, wp - p.pad_w,
                                         hp - p.pad_h, img, 0, 0, false);
                     }
@@ -315,16 +317,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             ++n_done;
             const int p_tile = tile / p.m_tiles, m_tile = tile - p_tile * p.m_tiles;
-            const long long tile_x0 = (long long)p_tile * T;
+            const uint32_t tile_x0 = (uint32_t)p_tile * (uint32_t)T;
             if (kHalo) {
                 int* tab = pix_tab + tbuf * kMaxTilePixels;
                 for (int j = et; j < T; j += kEpiWarps * 32) {
-                    const long long q = tile_x0 + j;
-                    const int wp = (int)(q % p.Wp);
-                    const long long t = q / p.Wp;
-                    const int hp = (int)(t % p.Hp);
-                    const bool ok = q < p.Q && wp < p.OW && hp < p.OH;
-                    tab[j] = ok ? (int)(((t / p.Hp) * p.OH + hp) * p.OW + wp) : -1;
+                    const uint32_t q = tile_x0 + (uint32_t)j;
+                    const int wp = (int)(q % (uint32_t)p.Wp);
+                    const uint32_t t = q / (uint32_t)p.Wp;
+                    const int hp = (int)(t % (uint32_t)p.Hp);
+                    const bool ok = q < span && wp < p.OW && hp < p.OH;
+                    tab[j] = ok ? (int)(((t / (uint32_t)p.Hp) * (uint32_t)p.OH + (uint32_t)hp) * (uint32_t)p.OW + (uint32_t)wp) : -1;
                 }
                 asm volatile("bar.sync 1, %0;" ::"n"(kEpiWarps * 32) : "memory");   // table complete (and the other buffer free)
             }
@@ -359,11 +361,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                 uint16_t* stg = stage_t + (warp - 4) * 32 * kStageRow;
                 for (int s = 0; s < p.S; ++s) {
                     const int j0 = s * p.np + half * hcols;
-                    const long long x0 = tile_x0 + j0;
+                    const uint32_t x0 = tile_x0 + (uint32_t)j0;
                     const int* tab = pix_tab + tbuf * kMaxTilePixels + j0;
                     const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + j0) + ((uint32_t)(e * 32) << 16);
                     for (int col = 0; col < hcols; col += 32) {
-                        if (x0 + col >= span) break;                                   // warp-uniform
+                        if (x0 + (uint32_t)col >= span) break;                                   // warp-uniform
                         uint32_t v[32];
                         ptx::tmem_ld_32x32(t_row + (uint32_t)col, v);
                         ptx::tmem_ld_wait();
@@ -377,7 +379,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
                         long long m;                                                   // the output pixel this lane now owns
                         bool ok;
                         if (kHalo) { const int t = tab[col + lane]; ok = t >= 0; m = t; }
-                        else { m = x0 + col + lane; ok = m < span; }
+                        else { m = (long long)(x0 + (uint32_t)(col + lane)); ok = x0 + (uint32_t)(col + lane) < span; }
                         if (ok) {
                             const uint4* r = reinterpret_cast<const uint4*>(stg + lane * kStageRow);
                             uint4* dst = reinterpret_cast<uint4*>(warp_base + m * step);
@@ -390,16 +392,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
             } else if (warp_has_work) {
                 for (int s = 0; s < p.S; ++s) {
                     const int j0 = s * p.np + half * hcols;                            // first column of this warp in the tile
-                    const long long x0 = tile_x0 + j0;
-                    char* ptr = out_base + x0 * step;                                  // im2col mode: pixels are consecutive
+                    const uint32_t x0 = tile_x0 + (uint32_t)j0;
+                    char* ptr = out_base + (long long)x0 * step;                                  // im2col mode: pixels are consecutive
                     const int* tab = pix_tab + tbuf * kMaxTilePixels + j0;
                     const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + j0) + ((uint32_t)(e * 32) << 16);
                     for (int col = 0; col < hcols; col += 16) {
-                        if (x0 + col >= span) break;                                   // warp-uniform
+                        if (x0 + (uint32_t)col >= span) break;                                   // warp-uniform
                         uint32_t v[16];
                         tmem_ld_x16(t_row + (uint32_t)col, v);
                         ptx::tmem_ld_wait();
-                        const long long left = span - (x0 + col);
+                        const long long left = (long long)span - (long long)(x0 + (uint32_t)col);
 #pragma unroll
                         for (int j = 0; j < 16; ++j) {
                             float f = __uint_as_float(v[j]) + bias;
@@ -451,6 +453,9 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     if (((uintptr_t)g.in | (uintptr_t)g.weights) & 15) return bad("unaligned tensor base");
     const int OH = (g.H + 2 * g.pad_h - g.KH) / g.stride + 1, OW = (g.W + 2 * g.pad_w - g.KW) / g.stride + 1;
     if (OH <= 0 || OW <= 0) return bad("empty output");
+    // the kernel indexes (virtual) pixels with 32 bits
+    if ((long long)g.n_max * (g.H + 2 * g.pad_h) * (g.W + 2 * g.pad_w) >= (1ll << 31) - 65536 || (long long)g.n_max * OH * OW >= (1ll << 31) - 65536)
+        return bad("layer too large (2^31 pixels)");
     for (int i = 0; i < n_seg; ++i)
         if (segs[i].col_begin % 16 || (i && segs[i].col_begin <= segs[i - 1].col_begin))
             return bad("segment alignment / order");
