@@ -50,6 +50,20 @@ static float time_candidate(const ConvPlan& cand, int n, cudaStream_t s, cudaEve
 
 int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
                  std::string* err, int mode) {
+    ConvPlanSet set;
+    const int rc = conv_tc_plan_set(g, segs, n_seg, sm_count, &set, err, mode);
+    if (rc) return rc;
+    *plan = set.cands[set.chosen];
+    return FTF_OK;
+}
+
+void conv_tc_choice_put(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, int variant) {
+    std::lock_guard<std::mutex> lock(g_tune_mu);
+    g_choice[choice_key(g, segs, n_seg, sm_count)] = variant;
+}
+
+int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlanSet* set,
+                     std::string* err, int mode) {
     // FTF_CONV_KIND=pm|wm forces one kernel (tests and profiling); FTF_CONV_TUNE=0/1 overrides the caller's choice --
     // except for callers that promise to do no device work while planning (kPlanModelOnly: the per-call entry points)
     const char* force = getenv("FTF_CONV_KIND");
@@ -57,8 +71,9 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
     const bool halo_only = getenv("FTF_CONV_HALO_ONLY") != nullptr;     // profiling: drop the im2col candidate where a halo one exists
     bool tune = mode == kPlanTune;
     if (tenv && mode != kPlanModelOnly) tune = tenv[0] == '1';
-    ConvPlan cands[5];
-    int cand_variant[5];
+    ConvPlan* cands = set->cands;
+    int* cand_variant = set->variant;
+    bool eligible[5];                    // a candidate of the isolated timing (the CTA pair only on many-wave layers)
     int n_cand = 0;
     std::string first_err;
     // candidates: pixel-major (im2col / halo window / CTA pair), weight-major (im2col / halo window)
@@ -76,7 +91,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         if (force) {   // FTF_CONV_KIND: "pm" = one-CTA pixel-major, "pm2" = CTA-pair pixel-major, "wm" = weight-major
             const bool want_pair = force[0] == 'p' && force[2] == '2';
             if ((force[0] == 'p') != (v.kind == 0) || (v.kind == 0 && want_pair != v.pair)) continue;
-        } else if (v.pair && no_pair) continue;
+        }
         ConvPlan& c = cands[n_cand];
         c.kind = v.kind;
         std::string e;
@@ -88,6 +103,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         if (v.halo && !is_halo) continue;                      // same plan as the no-halo candidate
         if (v.pair && !c.pm.p.pair) continue;
         cand_variant[n_cand] = vi;
+        eligible[n_cand] = force || !(v.pair && no_pair);
         ++n_cand;
     }
     if (n_cand == 0) { if (err) *err = first_err; return FTF_INVALID_ARGUMENT; }
@@ -95,13 +111,14 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         int w = 0;
         for (int i = 0; i < n_cand; ++i) {
             const bool hm = cands[i].kind ? cands[i].wm.p.halo_mode != 0 : cands[i].pm.p.halo_mode != 0;
-            if (hm) { cand_variant[w] = cand_variant[i]; cands[w++] = cands[i]; }
+            if (hm) { cand_variant[w] = cand_variant[i]; eligible[w] = eligible[i]; cands[w++] = cands[i]; }
         }
         if (w > 0) n_cand = w;
     }
-    int best = 0;
-    for (int i = 1; i < n_cand; ++i)
-        if (cands[i].est_cycles < cands[best].est_cycles) best = i;
+    int best = -1;
+    for (int i = 0; i < n_cand; ++i)
+        if (eligible[i] && (best < 0 || cands[i].est_cycles < cands[best].est_cycles)) best = i;
+    if (best < 0) best = 0;
     // A choice another runner of this process already timed for the same layer is taken as it is.  Timing itself runs
     // under a process-wide lock: two task threads that open their models at the same moment would otherwise disturb each
     // other's measurements and could settle on different kernels.
@@ -135,7 +152,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
             float best_t = time_candidate(cands[model], g.n_max, s, e0, e1);
             if (verbose) describe(model, best_t);
             for (int i = 0; i < n_cand; ++i) {
-                if (i == model) continue;
+                if (i == model || !eligible[i]) continue;
                 const float t = time_candidate(cands[i], g.n_max, s, e0, e1);
                 if (verbose) describe(i, t);
                 if (t >= 0 && (best_t < 0 || t < 0.92f * best_t)) { best_t = t; best = i; }
@@ -147,7 +164,11 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
         cudaGetLastError();
         if (cacheable) g_choice[key] = cand_variant[best];
     }
-    *plan = cands[best];
+    set->n = n_cand;
+    set->chosen = best;
+    set->from_cache = cached;
+    set->cacheable = cacheable;
+    const ConvPlan* plan = &cands[best];
     if (getenv("FTF_CONV_VERBOSE")) {
         const bool hm = plan->kind ? plan->wm.p.halo_mode : plan->pm.p.halo_mode;
         fprintf(stderr, "conv %dx%d s%d Cin %d Cout %d HxW %dx%d -> %s%s kc %d (%d candidates, %s)\n", g.KH, g.KW, g.stride, g.Cin, g.Cout, g.H, g.W,

@@ -34,6 +34,20 @@ enum {
 // accumulates K in the same order (channel chunk, filter tap, 16-element step).
 int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
                  std::string* err, int mode = kPlanModel);
+// Every candidate kernel of a layer and which one the planning chose; the network keeps the set so that it can re-time the
+// alternatives inside the whole forward pass (InceptionV3's in-situ refinement), where sibling branches share the SMs and the
+// L2 -> SM bandwidth, which the isolated timing of conv_tc_plan cannot see.
+struct ConvPlanSet {
+    ConvPlan cands[5];
+    int variant[5];           // which of the five kernel variants cands[i] is (the value remembered per process)
+    int n = 0, chosen = 0;
+    bool from_cache = false;  // the choice was taken over from an earlier runner of this process
+    bool cacheable = false;   // the choice is one that gets remembered (timed, no FTF_CONV_KIND override, several candidates)
+};
+int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlanSet* set,
+                     std::string* err, int mode = kPlanModel);
+// Remembers `variant` as this process's choice for the layer (what later runners take over).
+void conv_tc_choice_put(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, int variant);
 // The same for the per-call entry points (ftf_conv2d_bf16_dev, ftf_pool_branch_bf16*_dev): a call that repeats an earlier one
 // of this thread -- same device, buffers, geometry and mode -- gets that call's plan back (no tensor-map encoding).
 // *plan stays valid until the thread's 256-entry table is cleared by a later call.

@@ -195,13 +195,18 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full[3], empty[3];
     __shared__ uint4 rows_all[(kBS / 32) * 8];          // per warp: the row terms of its current band
-    uint4* rows_sm = rows_all + (threadIdx.x >> 5) * 8;
+    // The warp index comes out of a shuffle so that the compiler knows it -- and everything derived from it: the warp's first
+    // column, its number of column groups, the switch below -- to be warp-uniform.  Otherwise the whole band loop counts as a
+    // possibly divergent region: kernel parameters, shared-memory row offsets and the global-memory descriptor are then kept
+    // in vector registers and moved to uniform ones (R2UR) in front of every load and store that wants them there.
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
+    uint4* rows_sm = rows_all + warp * 8;
     if (threadIdx.x == 0) {
         for (int s = 0; s < 3; ++s) { ptx::mbar_init(&full[s], 1); ptx::mbar_init(&empty[s], kBS / 32); }
         ptx::fence_mbar_init();
     }
     __syncthreads();
-    if (threadIdx.x < 32) {                                     // the first bands, one per stage
+    if (warp == 0) {                                            // the first bands, one per stage
         for (int s = 0; s < p.stages; ++s) {
             const long long blk = (long long)blockIdx.x + (long long)s * gridDim.x;
             if (blk >= total_bands) break;
@@ -214,7 +219,7 @@ resize_norm_band_tma(const __grid_constant__ CUtensorMap tmap, OutT* __restrict_
         }
     }
     const uint32_t smem_a = ptx::smem_u32(smem);             // 32-bit shared-window addresses: no generic-pointer arithmetic
-    const int warp_c0 = (int)(threadIdx.x & ~31u);            // first column of this warp
+    const int warp_c0 = warp * 32;                            // first column of this warp
     const int ow3 = p.out_w * 3;
     const int nj = warp_c0 < ow3 ? min(kCols, (ow3 - warp_c0 + kBS - 1) / kBS) : 0;   // columns with at least one live lane in this warp
     // a warp whose last column group is cut by the end of the row stores under a predicate; every other warp runs code
