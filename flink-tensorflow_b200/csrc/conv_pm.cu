@@ -580,7 +580,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 }  // namespace
 
 int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan, std::string* err,
-         double* est_cycles, bool may_use_halo, bool pair) {
+         double* est_cycles, bool may_use_halo, bool pair, bool wide_halo) {
     auto bad = [&](const std::string& m) { if (err) *err = "conv_pm plan: " + m; return FTF_INVALID_ARGUMENT; };
     if (n_seg < 1 || n_seg > kConvMaxSegments) return bad("segment count");
     if (g.Cin % 8 || g.in_ld % 8 || g.Cout % 16) return bad("Cin and the input row stride must be multiples of 8, Cout of 16");
@@ -643,7 +643,9 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             if (force_nt && nt != force_nt) continue;
             const int tiles_n = (g.Cout + bn - 1) / bn;
             const long long b_bytes = (long long)bn * rb;
-            if (!pair) {   // one im2col load per tap.  Every operand byte is written to shared memory once and read once: 64 + N/2 cycles per MMA
+            if (wide_halo) {
+                // only the wide halo shapes below are candidates
+            } else if (!pair) {   // one im2col load per tap.  Every operand byte is written to shared memory once and read once: 64 + N/2 cycles per MMA
                 const long long tiles = (long long)p.m_tiles * tiles_n, waves = (tiles + sm_count - 1) / sm_count;
                 const double cyc = (double)taps * total_ksteps * (64.0 + bn / 2.0), bytes = (double)taps * chunks * (a_tile + b_bytes) * real_frac;
                 const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
@@ -669,7 +671,12 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             if (!(allow_halo && g.stride == 1 && taps > 1) || Q >= (1ll << 31) - 4096) continue;
             for (int S = 1; S <= 4; S *= 2) {
                 if (force_S && S != force_S) continue;
-                if (2 * S * bn > kTmemCols) continue;                  // keep two accumulator sets: epilogue overlaps the next tile
+                // Two accumulator sets let the epilogue of one tile overlap the MMAs of the next.  The "wide" halo candidate
+                // gives that up for twice the sub-tiles per weight tile (one set of S * bn <= 512 columns): half the weight
+                // bytes pulled from L2 per pixel, which is what counts where sibling layers saturate the L2 -> SM path and a
+                // CTA only has a tile or two to work on anyway.
+                const bool one_set = 2 * S * bn > kTmemCols;
+                if (S * bn > kTmemCols || one_set != wide_halo) continue;
                 const int T = S * kBlockM;
                 const int loads = (T + halo + kHaloLoadRows - 1) / kHaloLoadRows;
                 const long long a_bytes = (long long)loads * kHaloLoadRows * rb;
@@ -679,7 +686,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                 const double cyc = (double)total_ksteps * taps * S * 128.0;
                 const double bytes = chunks * (a_bytes + (double)taps * b_bytes) * real_frac;
                 const double t = waves * ((cyc > bytes / kFill ? cyc : bytes / kFill) + kFixed);
-                if (t < best) {
+                if (best < 0 || t < best) {
                     best = t;
                     p.halo_mode = 1; p.Hp = Hp; p.Wp = Wp; p.Q = Q; p.S = S; p.block_n = bn; p.n_tiles = tiles_n; p.kc = kc; p.cin_chunks = chunks;
                     p.a_loads = loads; p.a_stage_bytes = (int)a_bytes;
@@ -692,11 +699,12 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
                     p.b_group = grp; p.b_stage_bytes = (int)(grp * b_bytes);
                     p.b_stages = (int)(room / p.b_stage_bytes > kMaxStages ? kMaxStages : room / p.b_stage_bytes);
                     if (p.b_stages < 2) { p.b_group = 1; p.b_stage_bytes = (int)b_bytes; p.b_stages = (int)(room / b_bytes > kMaxStages ? kMaxStages : room / b_bytes); }
-                    p.acc_stages = 2;
+                    p.acc_stages = one_set ? 1 : 2;
                 }
             }
         }
     }
+    if (best < 0) return bad(wide_halo ? "no wide halo shape for this layer" : "no tile shape fits");
     p.ksteps_last = (g.Cin - p.kc * (p.cin_chunks - 1) + 15) / 16;
     p.wide_stores = 1;
     for (int i = 0; i < n_seg; ++i) {

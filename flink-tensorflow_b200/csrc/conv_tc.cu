@@ -73,12 +73,13 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
     if (tenv && mode != kPlanModelOnly) tune = tenv[0] == '1';
     ConvPlan* cands = set->cands;
     int* cand_variant = set->variant;
-    bool eligible[5];                    // a candidate of the isolated timing (the CTA pair only on many-wave layers)
+    bool eligible[kConvVariants];                    // a candidate of the isolated timing (the CTA pair only on many-wave layers)
     int n_cand = 0;
     std::string first_err;
     // candidates: pixel-major (im2col / halo window / CTA pair), weight-major (im2col / halo window)
-    struct Variant { int kind; bool halo, pair; };
-    static const Variant kVariants[] = {{0, false, false}, {0, true, false}, {0, false, true}, {1, false, false}, {1, true, false}};
+    struct Variant { int kind; bool halo, pair, wide; };
+    static const Variant kVariants[kConvVariants] = {{0, false, false, false}, {0, true, false, false}, {0, false, true, false},
+                                                     {1, false, false, false}, {1, true, false, false}, {0, true, false, true}};
     // The CTA-pair kernel halves the weight bytes each SM pulls from L2.  That pays on layers of many waves, which are bound by
     // L2 -> SM operand fill (Conv2d_4a: 155 -> 137 us); single-wave layers are bound by the K-block cadence of the issuing
     // warp and a pair only halves the number of workers.  So it is a candidate from four tiles per SM on (FTF_CONV_PAIR=0/1
@@ -86,21 +87,24 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
     const long long m_tiles = ((long long)g.n_max * ((g.H + 2 * g.pad_h - g.KH) / g.stride + 1) * ((g.W + 2 * g.pad_w - g.KW) / g.stride + 1) + 127) / 128;
     const char* pair_env = getenv("FTF_CONV_PAIR");
     const bool no_pair = pair_env ? pair_env[0] != '1' : m_tiles < 4ll * sm_count;
-    for (int vi = 0; vi < 5; ++vi) {
+    for (int vi = 0; vi < kConvVariants; ++vi) {
         const Variant& v = kVariants[vi];
-        if (force) {   // FTF_CONV_KIND: "pm" = one-CTA pixel-major, "pm2" = CTA-pair pixel-major, "wm" = weight-major
-            const bool want_pair = force[0] == 'p' && force[2] == '2';
+        if (force) {   // FTF_CONV_KIND: "pm" = one-CTA pixel-major, "pm2" = CTA-pair pixel-major, "pmw" = wide halo (falls back to
+                       // the other one-CTA pixel-major shapes where a layer has no wide one), "wm" = weight-major
+            const bool want_pair = force[0] == 'p' && force[2] == '2', want_wide = force[0] == 'p' && force[2] == 'w';
             if ((force[0] == 'p') != (v.kind == 0) || (v.kind == 0 && want_pair != v.pair)) continue;
+            if (v.wide && !want_wide) continue;
         }
         ConvPlan& c = cands[n_cand];
         c.kind = v.kind;
         std::string e;
         const int rc = v.kind ? wm::plan(g, segs, n_seg, sm_count, &c.wm, &e, &c.est_cycles, v.halo)
-                              : pm::plan(g, segs, n_seg, sm_count, &c.pm, &e, &c.est_cycles, v.halo, v.pair);
+                              : pm::plan(g, segs, n_seg, sm_count, &c.pm, &e, &c.est_cycles, v.halo, v.pair, v.wide);
         if (rc == FTF_INTERNAL) { if (err) *err = e; return rc; }   // a CUDA/driver failure, not "this variant does not apply"
         if (rc) { if (first_err.empty()) first_err = e; continue; }
         const bool is_halo = v.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
         if (v.halo && !is_halo) continue;                      // same plan as the no-halo candidate
+        if (v.wide && c.pm.p.acc_stages != 1) continue;        // no wide shape exists for this layer
         if (v.pair && !c.pm.p.pair) continue;
         cand_variant[n_cand] = vi;
         eligible[n_cand] = force || !(v.pair && no_pair);
@@ -119,6 +123,8 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
     for (int i = 0; i < n_cand; ++i)
         if (eligible[i] && (best < 0 || cands[i].est_cycles < cands[best].est_cycles)) best = i;
     if (best < 0) best = 0;
+    if (force && force[0] == 'p' && force[2] == 'w')
+        for (int i = 0; i < n_cand; ++i) if (cand_variant[i] == 5) best = i;
     // A choice another runner of this process already timed for the same layer is taken as it is.  Timing itself runs
     // under a process-wide lock: two task threads that open their models at the same moment would otherwise disturb each
     // other's measurements and could settle on different kernels.
@@ -146,7 +152,8 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
             auto describe = [&](int i, float t) {
                 const ConvPlan& c = cands[i];
                 const bool hm = c.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
-                fprintf(stderr, "   candidate %s%s kc %d: %.1f us (model %.0f cycles)%s\n", c.kind ? "wm" : (c.pm.p.pair ? "pm pair" : "pm"), hm ? " halo" : "",
+                fprintf(stderr, "   candidate %s%s%s kc %d: %.1f us (model %.0f cycles)%s\n", c.kind ? "wm" : (c.pm.p.pair ? "pm pair" : "pm"), hm ? " halo" : "",
+                        (!c.kind && hm && c.pm.p.acc_stages == 1) ? " wide" : "",
                         c.kind ? c.wm.p.kc : c.pm.p.kc, t * 1e3f, c.est_cycles, i == model ? "  <- model" : "");
             };
             float best_t = time_candidate(cands[model], g.n_max, s, e0, e1);

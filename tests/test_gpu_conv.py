@@ -111,10 +111,10 @@ def test_conv_variants_agree(dev, monkeypatch):
         wt = _to_bf16_cuda(rng.standard_normal((cout, kh, kw, cin)) * np.sqrt(2.0 / (kh * kw * cin)))
         b = torch.from_numpy(rng.uniform(-0.1, 0.1, cout).astype(np.float32)).cuda()
         outs = {}
-        for kind in ("pm", "wm", "pm2"):
+        for kind in ("pm", "wm", "pm2", "pmw"):
             for no_halo in ("1", "0"):
-                if kind == "pm2" and no_halo == "0":
-                    continue                                   # the CTA-pair kernel has no halo variant
+                if kind in ("pm2", "pmw") and no_halo == ("0" if kind == "pm2" else "1"):
+                    continue                                   # the CTA-pair kernel has no halo variant, the wide one is nothing else
                 monkeypatch.setenv("FTF_CONV_KIND", kind)
                 monkeypatch.setenv("FTF_NO_HALO", no_halo)
                 monkeypatch.setenv("FTF_CONV_TUNE", "0")
@@ -126,6 +126,7 @@ def test_conv_variants_agree(dev, monkeypatch):
         assert torch.equal(outs[("pm", "0")], outs[("pm", "1")]), diffs
         assert torch.equal(outs[("wm", "0")], outs[("wm", "1")]), diffs
         assert torch.equal(outs[("pm2", "1")], outs[("pm", "1")]), diffs      # cta_group::2: same K order, same bits
+        assert torch.equal(outs[("pmw", "0")], outs[("pm", "1")]), diffs      # halo window with one wide accumulator set
         assert diffs[("wm", "1")] <= 1e-5, diffs
 
 
@@ -239,7 +240,7 @@ def test_inception_logits_and_top5(ftf, oracle, label_runner):
     assert np.array_equal(res["top_k_scores"].to_array(), np.take_along_axis(p, res["top_k_indices"].to_array(), 1))
 
 
-@pytest.mark.parametrize("kind", ["pm", "pm2", "wm"])
+@pytest.mark.parametrize("kind", ["pm", "pm2", "pmw", "wm"])
 def test_whole_network_on_one_kernel_family(ftf, oracle, monkeypatch, kind):
     """The network built from ONE kernel family (one-CTA pixel-major, CTA-pair pixel-major, weight-major), so that every
     layer shape -- the multi-segment fused 1x1 groups and the fp32 pool-branch segments included -- runs through that
