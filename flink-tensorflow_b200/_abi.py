@@ -76,6 +76,7 @@ SYMBOLS = {
     "ftf_pool_branch_bf16_static_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_void_p,
                                                   C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p]),
     "ftf_global_avgpool_bf16_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
+    "ftf_label_export_weights": (C.c_int, [C.c_void_p, C.c_char_p]),
     "ftf_debug_conv_profile": (C.c_int, [C.POINTER(C.c_uint64), C.c_int32]),
     "ftf_debug_activation": (C.c_int, [C.c_void_p, C.c_char_p, C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int32)]),
     "ftf_label_dev": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p,

@@ -12,6 +12,7 @@
 // that read the block input are one GEMM whose column ranges ("segments") go to different tensors; the pool
 // branch is conv1x1 -> fp32 scratch -> (avgpool3x3 + bias + ReLU) since pool and 1x1 conv commute.
 #include "inception.h"
+#include "wire.h"
 #include "conv_tc.h"
 #include "pools.h"
 #include "f32_path.h"
@@ -200,6 +201,41 @@ struct ConvF32 {
 
 struct InceptionV3::Impl {
     int device = 0, sms = 148, max_batch = 0, classes = 0;
+    // Trained weights (ftf_create("inception_v3:<dir>")): a TensorBundle holding "<layer>/weights" fp32 [Cout,KH,KW,Cin] with
+    // the BatchNorm already folded in, "<layer>/biases" fp32 [Cout], "fc/weights" [classes,2048] and "fc/biases" [classes].
+    // Empty: the seeded random-init recipe of the oracle.
+    std::unique_ptr<SavedModelLite> bundle;
+    bool weights_dir_loaded = false;
+    struct LayerSpec { std::string name; int cout, kh, kw, cin; };
+    std::vector<LayerSpec> layer_specs;   // every convolution in build order (what ftf_label_export_weights writes)
+    int layer_weights(const std::string& name, int cout, int kh, int kw, int cin, std::vector<float>* w, std::vector<float>* b) {
+        layer_specs.push_back({name, cout, kh, kw, cin});
+        if (!bundle) { conv_weights(seed, name, cout, kh, kw, cin, w, b); return FTF_OK; }
+        const float *pw = nullptr, *pb = nullptr;
+        int r = bundle->tensor_f32(name + "/weights", {cout, kh, kw, cin}, &pw, err);
+        if (!r) r = bundle->tensor_f32(name + "/biases", {cout}, &pb, err);
+        if (r) return r;
+        w->assign(pw, pw + (size_t)cout * kh * kw * cin);
+        b->assign(pb, pb + cout);
+        return FTF_OK;
+    }
+    int fc_weights(int cin, std::vector<float>* w, std::vector<float>* b) {       // [classes][cin], [classes]
+        if (bundle) {
+            const float *pw = nullptr, *pb = nullptr;
+            int r = bundle->tensor_f32("fc/weights", {classes, cin}, &pw, err);
+            if (!r) r = bundle->tensor_f32("fc/biases", {classes}, &pb, err);
+            if (r) return r;
+            w->assign(pw, pw + (size_t)classes * cin);
+            b->assign(pb, pb + classes);
+            return FTF_OK;
+        }
+        w->resize((size_t)classes * cin);
+        b->assign(classes, 0.0f);
+        const Stream sw(seed + 90, "fc", 0);      // salted fc stream: well-separated top logits for the default seed (see the oracle)
+        float* wp = w->data();
+        fill_parallel((int64_t)classes * cin, [&](int64_t lo, int64_t hi) { for (int64_t i = lo; i < hi; ++i) wp[i] = (float)(sw.normal((uint64_t)i) * 0.05); });
+        return FTF_OK;
+    }
     bool f32 = false;                     // compute_dtype FTF_FLOAT: fp32 activations and weights, CUDA-core kernels (f32_path.cu)
     std::vector<ConvF32> convs_f32;
     uint64_t seed = 0;
@@ -271,7 +307,7 @@ struct InceptionV3::Impl {
         int col = 0;
         for (auto& b : br) {
             std::vector<float> w, bb;
-            conv_weights(seed, b.name, b.cout, kh, kw, in.c, &w, &bb);
+            if ((rc = layer_weights(b.name, b.cout, kh, kw, in.c, &w, &bb))) return;
             const size_t per = (size_t)kh * kw * in.c;
             if (f32) memcpy(&w32[(size_t)col * per], w.data(), w.size() * 4);         // the oracle's fp32 weights, unrounded
             else for (size_t i = 0; i < w.size(); ++i) w16[(size_t)col * per + i] = bf16_bits(w[i]);
@@ -448,8 +484,8 @@ struct InceptionV3::Impl {
         // stem layer 1: direct kernel
         {
             std::vector<float> w, b;
-            conv_weights(seed, "Conv2d_1a_3x3", 32, 3, 3, 3, &w, &b);
-            for (int o = 0; o < 32; ++o) {
+            if (!f32) { if ((rc = layer_weights("Conv2d_1a_3x3", 32, 3, 3, 3, &w, &b))) return; }
+            for (int o = 0; o < 32 && !f32; ++o) {
                 for (int k = 0; k < 27; ++k) stem.w[k][o] = bf16_value(w[(size_t)o * 27 + k]);
                 stem.b[o] = b[o];
             }
@@ -489,15 +525,16 @@ struct InceptionV3::Impl {
         if (rc) return;
         const int cols = (classes + 15) / 16 * 16;
         logits = (float*)dev_alloc((size_t)max_batch * cols * 4, true);
+        std::vector<float> fw, fb;
+        if ((rc = fc_weights(x.c, &fw, &fb))) return;
         if (f32) {
             std::vector<float> w32((size_t)cols * x.c, 0.0f);
-            const Stream sw(seed + 90, "fc", 0);
-            float* wp = w32.data();
-            fill_parallel((int64_t)classes * x.c, [&](int64_t lo, int64_t hi) { for (int64_t i = lo; i < hi; ++i) wp[i] = (float)(sw.normal((uint64_t)i) * 0.05); });
+            memcpy(w32.data(), fw.data(), fw.size() * 4);                       // rows [classes, cols) stay zero
             void* dw = dev_alloc(w32.size() * 4, false);
-            float* db = (float*)dev_alloc((size_t)cols * 4, true);              // fc bias = 0
+            float* db = (float*)dev_alloc((size_t)cols * 4, true);
             if (rc) return;
             cudaMemcpy(dw, w32.data(), w32.size() * 4, cudaMemcpyHostToDevice);
+            cudaMemcpy(db, fb.data(), fb.size() * 4, cudaMemcpyHostToDevice);
             ConvSegment sg{}; sg.out = logits; sg.ld = cols; sg.coff = 0; sg.col_begin = 0; sg.flags = kSegBias | kSegF32;
             convs_f32.push_back(ConvF32{ConvGeometry{gap.p, max_batch, 1, 1, x.c, x.c, dw, db, cols, 1, 1, 1, 0, 0}, {sg}});
             Op op{}; op.type = Op::kConvF32; op.plan = (int)convs_f32.size() - 1; op.tag = "fc";
@@ -508,10 +545,10 @@ struct InceptionV3::Impl {
         std::vector<uint16_t> w16((size_t)cols * x.c, 0);
         std::vector<float> bias(cols, 0.0f);
         {
-            const Stream sw(seed + 90, "fc", 0);      // salted fc stream: well-separated top logits for the default seed (see the oracle)
             uint16_t* wp = w16.data();
-            const int64_t n = (int64_t)classes * x.c;
-            fill_parallel(n, [&](int64_t lo, int64_t hi) { for (int64_t i = lo; i < hi; ++i) wp[i] = bf16_bits((float)(sw.normal((uint64_t)i) * 0.05)); });
+            const float* src = fw.data();
+            fill_parallel((int64_t)classes * x.c, [&](int64_t lo, int64_t hi) { for (int64_t i = lo; i < hi; ++i) wp[i] = bf16_bits(src[i]); });
+            memcpy(bias.data(), fb.data(), fb.size() * 4);
         }
         void* dw = dev_alloc(w16.size() * 2, false);
         float* db = (float*)dev_alloc((size_t)cols * 4, false);
@@ -624,7 +661,7 @@ int InceptionV3::Impl::refine(std::string* e) {
 InceptionV3::~InceptionV3() { delete impl_; }
 
 int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batch, int compute_dtype,
-                        std::unique_ptr<InceptionV3>* out, std::string* err) {
+                        std::unique_ptr<InceptionV3>* out, std::string* err, const char* weights_dir) {
     if (compute_dtype != FTF_BFLOAT16 && compute_dtype != FTF_FLOAT) {
         if (err) *err = "builtin:inception_v3: compute_dtype must be FTF_BFLOAT16 (tensor cores, fp32 accumulate) or FTF_FLOAT (fp32 throughout)";
         return FTF_INVALID_ARGUMENT;
@@ -639,6 +676,12 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
     Impl& m = *net->impl_;
     m.device = device; m.sms = device_sm_count(device); m.max_batch = max_batch; m.classes = num_classes; m.seed = seed; m.err = err;
     m.f32 = compute_dtype == FTF_FLOAT;
+    if (weights_dir && weights_dir[0]) {
+        m.bundle.reset(new SavedModelLite());
+        const int rc = m.bundle->load_variables_only(weights_dir, err);
+        if (rc) return rc;
+        m.weights_dir_loaded = true;
+    }
     {
         // one label model is built at a time per process: the timing runs of two builds would disturb each other, and the
         // second build takes over the first one's kernel choices anyway
@@ -658,6 +701,7 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
     // is refused (and breaks the capture) while another runner's thread is recording its CUDA graph on this GPU
     FTF_CUDA(cudaStreamSynchronize(cudaStreamLegacy), err);
     m.err = nullptr;
+    m.bundle.reset();                     // the host copy of a weight file is not needed once everything is in HBM
     net->classes_ = num_classes; net->max_batch_ = max_batch;
     *out = std::move(net);
     return FTF_OK;
@@ -836,6 +880,29 @@ int InceptionV3::forward(const void* images, int in_dtype, int64_t n, float* log
     FTF_CUDA(cudaMemcpy2DAsync(logits, (size_t)m.classes * 4, m.logits, (size_t)m.logits_ld * 4, (size_t)m.classes * 4, (size_t)n,
                                cudaMemcpyDeviceToDevice, s), err);
     return FTF_OK;
+}
+
+int InceptionV3::export_weights(const std::string& dir, std::string* err) {
+    Impl& m = *impl_;
+    if (m.weights_dir_loaded) { if (err) *err = "export_weights: this network was loaded from a weight file; copy that file instead"; return FTF_FAILED_PRECONDITION; }
+    TensorBundleWriter wr;
+    int rc = wr.open(dir, err);
+    std::vector<float> w, b;
+    for (size_t i = 0; i < m.layer_specs.size() && !rc; ++i) {
+        const auto& L = m.layer_specs[i];
+        conv_weights(m.seed, L.name, L.cout, L.kh, L.kw, L.cin, &w, &b);
+        rc = wr.add_f32(L.name + "/weights", {L.cout, L.kh, L.kw, L.cin}, w.data(), err);
+        if (!rc) rc = wr.add_f32(L.name + "/biases", {L.cout}, b.data(), err);
+    }
+    if (!rc) {
+        std::string* saved = m.err; m.err = err;
+        rc = m.fc_weights(2048, &w, &b);
+        m.err = saved;
+    }
+    if (!rc) rc = wr.add_f32("fc/weights", {m.classes, 2048}, w.data(), err);
+    if (!rc) rc = wr.add_f32("fc/biases", {m.classes}, b.data(), err);
+    if (!rc) rc = wr.finish(err);
+    return rc;
 }
 
 int InceptionV3::activation(const std::string& name, int64_t n, float* host_out, int64_t cap, int dims[4], std::string* err) {

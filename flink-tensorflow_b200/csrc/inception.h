@@ -17,8 +17,12 @@ public:
     ~InceptionV3();
     // Builds the network for up to max_batch images: generates the weights (seeded), uploads them,
     // allocates the activation arena.  compute_dtype: FTF_BFLOAT16 (tcgen05 path).
+    // weights_dir (optional): a TensorBundle directory with trained, BatchNorm-folded weights ("<layer>/weights" fp32
+    // [Cout,KH,KW,Cin], "<layer>/biases", "fc/weights" [classes,2048], "fc/biases"); the seed is then unused.
     static int create(int device, int num_classes, uint64_t seed, int max_batch, int compute_dtype,
-                      std::unique_ptr<InceptionV3>* out, std::string* err);
+                      std::unique_ptr<InceptionV3>* out, std::string* err, const char* weights_dir = nullptr);
+    // Writes this (seeded) network's weights as such a directory: the template of the layout and the test of the reader.
+    int export_weights(const std::string& dir, std::string* err);
     // images: [n,299,299,3] NHWC in HBM, bf16 or fp32 (in_dtype FTF_BFLOAT16 / FTF_FLOAT; fp32 values are rounded to bf16 as
     // the first convolution loads them); logits: [n,classes] f32.  Enqueues on s.
     int forward(const void* images, int in_dtype, int64_t n, float* logits, cudaStream_t s, std::string* err);

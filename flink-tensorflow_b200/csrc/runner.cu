@@ -402,7 +402,7 @@ static int create_runner(const char* model, const char* signature_key, const cha
     r->cfg = cfg;
     r->device = cfg.device;
     const std::string m(model);
-    std::string err;
+    std::string err, weights_dir;
     int rc = FTF_OK;
     if (m == "builtin:image_normalization") {
         r->kind = Kind::kNormalize; r->in_key = "inputs";
@@ -413,6 +413,12 @@ static int create_runner(const char* model, const char* signature_key, const cha
     } else if (m == "builtin:normalize_label") {
         r->kind = Kind::kNormalizeLabel; r->in_key = "inputs";
         r->signature.method_name = "inception/label";
+    } else if (m.rfind("inception_v3:", 0) == 0 || m.rfind("normalize_label:", 0) == 0) {
+        // the label model with TRAINED weights from a directory (where InceptionModel.scala:51-55 loads its frozen graph
+        // file): "<kind>:<dir>", dir/variables/* a TensorBundle of BatchNorm-folded fp32 tensors (csrc/inception.h)
+        r->kind = m[0] == 'i' ? Kind::kLabel : Kind::kNormalizeLabel; r->in_key = "inputs";
+        r->signature.method_name = "inception/label";
+        weights_dir = m.substr(m.find(':') + 1);
     } else {
         r->kind = Kind::kAffine;
         if (!signature_key) return fail(nullptr, FTF_INVALID_ARGUMENT, "a signatureDef must be provided");
@@ -452,7 +458,8 @@ static int create_runner(const char* model, const char* signature_key, const cha
         if ((e = cudaStreamCreateWithFlags(&raw->net_stream, cudaStreamNonBlocking)) != cudaSuccess ||
             (e = cudaEventCreateWithFlags(&raw->net_done, cudaEventDisableTiming)) != cudaSuccess)
             return bail(FTF_INTERNAL, std::string("stream/event creation: ") + cudaGetErrorString(e));
-        rc = InceptionV3::create(cfg.device, cfg.num_classes, cfg.seed, cfg.max_batch, cfg.compute_dtype, &raw->net, &err);
+        rc = InceptionV3::create(cfg.device, cfg.num_classes, cfg.seed, cfg.max_batch, cfg.compute_dtype, &raw->net, &err,
+                                 weights_dir.empty() ? nullptr : weights_dir.c_str());
         if (rc) return bail(rc, err);
     }
     if (raw->kind == Kind::kAffine) {
@@ -960,6 +967,11 @@ extern "C" int ftf_conv2d_bf16_dev(const void* in, int32_t n, int32_t h, int32_t
     if (!rc) rc = conv_tc_launch(*plan, n, (cudaStream_t)stream, &err);
     if (rc) set_thread_error(err);
     return rc;
+}
+
+extern "C" int ftf_label_export_weights(ftf_runner* r, const char* dir) {
+    if (!r || !is_label_kind(r->kind) || !dir) return fail(r, FTF_INVALID_ARGUMENT, "label_export_weights needs a label runner and a directory");
+    return r->net->export_weights(dir, &r->err);
 }
 
 extern "C" int ftf_debug_activation(ftf_runner* r, const char* name, int64_t n, float* host_out, int64_t cap, int32_t* dims4) {

@@ -10,8 +10,10 @@
 //   FT/types/TensorName.scala:14-19                            "op:idx"
 #include "wire.h"
 #include "common.h"
+#include <errno.h>
 #include <stdio.h>
 #include <stdlib.h>
+#include <sys/stat.h>
 #include <algorithm>
 
 namespace ftf {
@@ -425,6 +427,124 @@ int SavedModelLite::load(const std::string& dir, const std::vector<std::string>&
         return FTF_NOT_FOUND;
     }
     return load_bundle(dir, this, err);
+}
+
+int SavedModelLite::load_variables_only(const std::string& dir, std::string* err) {
+    variables.clear(); variable_data.clear();
+    const int rc = load_bundle(dir, this, err);
+    if (rc) return rc;
+    if (variables.empty()) { *err = dir + "/variables/variables.index: not found or empty"; return FTF_NOT_FOUND; }
+    return FTF_OK;
+}
+
+int SavedModelLite::tensor_f32(const std::string& name, const std::vector<int64_t>& want_dims, const float** out, std::string* err) const {
+    auto it = variables.find(name);
+    if (it == variables.end()) { *err = "tensor '" + name + "' is not in the bundle"; return FTF_NOT_FOUND; }
+    const BundleEntry& e = it->second;
+    int64_t elems = 1;
+    for (int64_t d : want_dims) elems *= d;
+    if (e.dtype != FTF_FLOAT || e.dims != want_dims) {
+        std::string have = "[", want = "[";
+        for (int64_t d : e.dims) have += std::to_string(d) + ",";
+        for (int64_t d : want_dims) want += std::to_string(d) + ",";
+        *err = "tensor '" + name + "': expected FLOAT " + want + "], the bundle holds dtype " + std::to_string(e.dtype) + " " + have + "]";
+        return FTF_INVALID_ARGUMENT;
+    }
+    if (e.size != elems * 4 || e.offset < 0 || (uint64_t)e.size > variable_data.size() || (uint64_t)e.offset > variable_data.size() - (uint64_t)e.size) {
+        *err = "tensor '" + name + "': entry does not fit the data file";
+        return FTF_INVALID_ARGUMENT;
+    }
+    if (crc32c_mask(crc32c(variable_data.data() + e.offset, (size_t)e.size)) != e.crc32c) {
+        *err = "tensor '" + name + "': crc32c mismatch (corrupt variables.data file)";
+        return FTF_INVALID_ARGUMENT;
+    }
+    if (e.offset % 4) { *err = "tensor '" + name + "': unaligned offset"; return FTF_INVALID_ARGUMENT; }
+    *out = reinterpret_cast<const float*>(variable_data.data() + e.offset);
+    return FTF_OK;
+}
+
+// ---- TensorBundle writer (fp32 tensors, one shard): the inverse of load_bundle --------------------------------------------
+static void put_varint(std::string* o, uint64_t v) {
+    while (v >= 0x80) { o->push_back((char)(v | 0x80)); v >>= 7; }
+    o->push_back((char)v);
+}
+static void put_u32(std::string* o, uint32_t v) { o->append((const char*)&v, 4); }
+// one table block: entries (no key sharing, every entry a restart point) + restart array + trailer; returns its handle
+static void put_block(std::string* file, const std::vector<std::pair<std::string, std::string>>& kv, uint64_t* off, uint64_t* size) {
+    std::string b;
+    std::vector<uint32_t> restarts;
+    for (auto& e : kv) {
+        restarts.push_back((uint32_t)b.size());
+        put_varint(&b, 0); put_varint(&b, e.first.size()); put_varint(&b, e.second.size());
+        b += e.first; b += e.second;
+    }
+    if (restarts.empty()) restarts.push_back(0);
+    for (uint32_t r : restarts) put_u32(&b, r);
+    put_u32(&b, (uint32_t)restarts.size());
+    *off = file->size(); *size = b.size();
+    b.push_back((char)0);                                                       // block type: uncompressed
+    const uint32_t crc = crc32c_mask(crc32c((const uint8_t*)b.data(), b.size()));
+    *file += b;
+    put_u32(file, crc);
+}
+
+int TensorBundleWriter::open(const std::string& dir_, std::string* err) {
+    dir = dir_;
+    const std::string cmd_dir = dir + "/variables";
+    if (mkdir(dir.c_str(), 0777) != 0 && errno != EEXIST) { *err = "cannot create " + dir; return FTF_INVALID_ARGUMENT; }
+    if (mkdir(cmd_dir.c_str(), 0777) != 0 && errno != EEXIST) { *err = "cannot create " + cmd_dir; return FTF_INVALID_ARGUMENT; }
+    data = fopen((cmd_dir + "/variables.data-00000-of-00001").c_str(), "wb");
+    if (!data) { *err = "cannot write " + cmd_dir + "/variables.data-00000-of-00001"; return FTF_INVALID_ARGUMENT; }
+    offset = 0;
+    entries.clear();
+    return FTF_OK;
+}
+int TensorBundleWriter::add_f32(const std::string& name, const std::vector<int64_t>& dims, const float* v, std::string* err) {
+    size_t elems = 1;
+    for (int64_t d : dims) elems *= (size_t)d;
+    if (!data || name.empty() || entries.count(name)) { *err = "bundle writer: bad or duplicate tensor name '" + name + "'"; return FTF_INVALID_ARGUMENT; }
+    if (fwrite(v, 4, elems, data) != elems) { *err = "bundle writer: short write"; return FTF_INTERNAL; }
+    BundleEntry e;
+    e.dtype = FTF_FLOAT; e.dims = dims; e.offset = offset; e.size = (int64_t)elems * 4;
+    e.crc32c = crc32c_mask(crc32c((const uint8_t*)v, elems * 4));
+    entries[name] = e;
+    offset += e.size;
+    return FTF_OK;
+}
+int TensorBundleWriter::finish(std::string* err) {
+    if (!data) { *err = "bundle writer: not open"; return FTF_FAILED_PRECONDITION; }
+    const bool ok = fclose(data) == 0;
+    data = nullptr;
+    if (!ok) { *err = "bundle writer: close failed"; return FTF_INTERNAL; }
+    std::vector<std::pair<std::string, std::string>> kv;
+    kv.emplace_back(std::string(), std::string("\x08\x01\x1a\x02\x08\x01", 6));    // BundleHeaderProto{num_shards 1, version{producer 1}}
+    for (auto& it : entries) {                                                  // std::map: keys in bytewise order, as the table wants
+        const BundleEntry& e = it.second;
+        std::string shape, pb;
+        for (int64_t d : e.dims) { std::string dim; dim.push_back((char)0x08); put_varint(&dim, (uint64_t)d); shape.push_back((char)0x12); put_varint(&shape, dim.size()); shape += dim; }
+        pb.push_back((char)0x08); put_varint(&pb, (uint64_t)e.dtype);
+        pb.push_back((char)0x12); put_varint(&pb, shape.size()); pb += shape;
+        pb.push_back((char)0x20); put_varint(&pb, (uint64_t)e.offset);
+        pb.push_back((char)0x28); put_varint(&pb, (uint64_t)e.size);
+        pb.push_back((char)0x35); put_u32(&pb, e.crc32c);
+        kv.emplace_back(it.first, pb);
+    }
+    std::string file;
+    uint64_t d_off, d_size, m_off, m_size, i_off, i_size;
+    put_block(&file, kv, &d_off, &d_size);
+    put_block(&file, {}, &m_off, &m_size);                                      // metaindex: empty
+    std::string handle;
+    put_varint(&handle, d_off); put_varint(&handle, d_size);
+    put_block(&file, {{kv.back().first, handle}}, &i_off, &i_size);             // index: one data block
+    std::string footer;
+    put_varint(&footer, m_off); put_varint(&footer, m_size); put_varint(&footer, i_off); put_varint(&footer, i_size);
+    footer.resize(40, (char)0);
+    static const uint8_t magic[8] = {0x57, 0xfb, 0x80, 0x8b, 0x24, 0x75, 0x47, 0xdb};
+    footer.append((const char*)magic, 8);
+    file += footer;
+    FILE* f = fopen((dir + "/variables/variables.index").c_str(), "wb");
+    if (!f || fwrite(file.data(), 1, file.size(), f) != file.size() || fclose(f) != 0) { *err = "cannot write " + dir + "/variables/variables.index"; return FTF_INTERNAL; }
+    return FTF_OK;
 }
 
 int SavedModelLite::variable_f32(const std::string& name, float* out, std::string* err) const {

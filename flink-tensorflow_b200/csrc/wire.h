@@ -1,6 +1,7 @@
 // wire.h -- protobuf wire-format cursor and the host-side record codecs of the path.
 #pragma once
 #include <stdint.h>
+#include <stdio.h>
 #include <string.h>
 #include <map>
 #include <string>
@@ -74,6 +75,23 @@ struct SavedModelLite {
     int load(const std::string& dir, const std::vector<std::string>& want_tags, std::string* err);
     // float scalar variable by name (checks dtype, size and the masked crc32c of the bundle entry)
     int variable_f32(const std::string& name, float* out, std::string* err) const;
+    // Only dir/variables/* (a TensorBundle without a saved_model.pb): the container of a label model's trained weights.
+    int load_variables_only(const std::string& dir, std::string* err);
+    // A whole fp32 tensor by name: shape and crc32c checked, *out points into variable_data.
+    int tensor_f32(const std::string& name, const std::vector<int64_t>& want_dims, const float** out, std::string* err) const;
+};
+
+// Writes dir/variables/variables.{index,data-00000-of-00001} (fp32 tensors, one shard) in the TensorBundle format that
+// load() reads -- and that TensorFlow's tf.train.load_checkpoint / SavedModel loader read.
+struct TensorBundleWriter {
+    std::string dir;
+    FILE* data = nullptr;
+    int64_t offset = 0;
+    std::map<std::string, BundleEntry> entries;
+    int open(const std::string& dir, std::string* err);
+    int add_f32(const std::string& name, const std::vector<int64_t>& dims, const float* v, std::string* err);
+    int finish(std::string* err);
+    ~TensorBundleWriter() { if (data) fclose(data); }
 };
 
 // y = a*x + b recovered from the graph behind one signature output.

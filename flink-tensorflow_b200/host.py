@@ -320,6 +320,9 @@ class Runner:
     def flush(self):
         _check(self._lib.ftf_flush(self._h), self._h)
 
+    def export_weights(self, directory):
+        _check(self._lib.ftf_label_export_weights(self._h, str(directory).encode()), self._h)
+
     def stats(self):
         s = FtfStats()
         _check(self._lib.ftf_stats_get(self._h, C.byref(s)))
@@ -458,8 +461,18 @@ class InceptionModel(GenericModel):
     """EX/inception/InceptionModel.scala:47-90; `labels` is the label file's lines."""
     kind = "builtin:inception_v3"
 
-    def __init__(self, labels=None, **config):
+    def __init__(self, labels=None, model_dir=None, **config):
+        """labels: the label file's lines.  model_dir: a directory with trained weights (variables/*, see include/ftf.h)
+        and, optionally, labels.txt -- read like imagenet_comp_graph_label_strings.txt (InceptionModel.scala:54-55,
+        GraphUtils.readAllLines) when `labels` is not given.  Without model_dir: seeded random-init weights."""
         super().__init__(**config)
+        if model_dir is not None:
+            import os
+            self.kind = "inception_v3:" + str(model_dir)
+            lf = os.path.join(str(model_dir), "labels.txt")
+            if labels is None and os.path.exists(lf):
+                with open(lf, encoding="utf-8") as f:
+                    labels = [line.rstrip("\n") for line in f]
         self.labels = labels
 
     @property

@@ -83,7 +83,13 @@ void ftf_default_config(ftf_config* cfg);
  *        variables/variables.{index,data-00000-of-00001}), or "builtin:image_normalization"
  *        (EX/inception/ImageNormalization.scala:40-85), or "builtin:inception_v3"
  *        (stands where EX/inception/InceptionModel.scala:47-67 loads its frozen graph), or
- *        "builtin:normalize_label" (both chained on the device).
+ *        "builtin:normalize_label" (both chained on the device) -- these two with seeded random-init weights -- or
+ *        "inception_v3:<dir>" / "normalize_label:<dir>": the same network with TRAINED weights read from <dir>, where
+ *        InceptionModel.scala:51-55 reads its frozen graph file.  <dir>/variables/ is a TensorBundle (the format of
+ *        models/half_plus_two/variables) of fp32 tensors with BatchNorm folded in: "<layer>/weights" [Cout,KH,KW,Cin],
+ *        "<layer>/biases" [Cout] for every convolution (torchvision's layer names: "Conv2d_1a_3x3", "Mixed_5b.branch1x1",
+ *        ...), "fc/weights" [classes,2048], "fc/biases" [classes]; shapes and crc32c are checked, a missing or
+ *        misshapen tensor is NOT_FOUND / INVALID_ARGUMENT.  ftf_label_export_weights writes such a directory.
  * signature_key: SignatureDef key for a SavedModel ("regress_x_to_y", "serving_default", ...;
  *        TensorFlowModel.signatureDef, TensorFlowModel.scala:19-26); NULL for builtins.
  * method_name: if non-NULL it must equal the SignatureDef's method name, else INVALID_ARGUMENT
@@ -260,6 +266,9 @@ int ftf_jpeg_batch_status(ftf_jpeg_batch* b, int32_t* per_image, int32_t n);
  * logits/probs/idx/score may be NULL. */
 int ftf_label_dev(ftf_runner* r, const void* images, int32_t in_dtype, int64_t n, float* logits,
                   float* probs, int32_t* idx, float* score);
+/* Writes the weights of a seeded label runner as the weight directory "inception_v3:<dir>" reads (the template of that
+ * layout; stands where the reference's users download tensorflow_inception_graph.pb, models/README.md:5). */
+int ftf_label_export_weights(ftf_runner* r, const char* dir);
 /* Diagnostic (no reference counterpart; TF-Java would fetch an intermediate tensor by name): copies a named
  * activation of a label runner's last forward to host fp32 [n,h,w,c].  Names are torchvision's layer/block names
  * ("Conv2d_2a_3x3", "Mixed_5b", "pool1", "gap", ...).  host_out NULL: dims only. */

@@ -230,3 +230,60 @@ def test_outputs_selected_after_launch_are_still_delivered(ftf, net64):
         got += net64.poll(block=True)
     assert np.array_equal(_bits(np.stack([v[0].to_array() for _, v in got])), _bits(want["outputs"].to_array()))
     assert np.array_equal(_bits(np.stack([v[1].to_array() for _, v in got])), _bits(want["top_k_scores"].to_array()))
+
+
+def test_trained_weights_are_read_from_a_weight_directory(ftf, tmp_path):
+    """ftf_create("inception_v3:<dir>"): the label model with weights from a TensorBundle directory (where the reference
+    loads its frozen graph file, InceptionModel.scala:51-55).  A seeded runner exports its weights; a runner created from
+    that directory with ANOTHER seed returns the same bits (the file decides, not the seed); labels.txt is picked up; a
+    damaged data file, a missing tensor and a misshapen tensor are refused."""
+    import os
+    import shutil
+    d = str(tmp_path / "inception_v3_weights")
+    x = _images(21, 3)
+    cfg = ftf.default_config(max_batch=4, top_k=5, num_classes=1000, seed=77)
+    a = ftf.Runner("builtin:inception_v3", None, None, cfg)
+    try:
+        want = a.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits", "top_k_indices"])
+        a.export_weights(d)
+    finally:
+        a.close()
+    assert os.path.getsize(os.path.join(d, "variables", "variables.data-00000-of-00001")) > 90e6      # 23.8 M fp32 parameters
+    # the exported directory is a TensorBundle in the half_plus_two layout's format: the index carries the bundle magic
+    idx = open(os.path.join(d, "variables", "variables.index"), "rb").read()
+    assert idx[-8:] == bytes([0x57, 0xfb, 0x80, 0x8b, 0x24, 0x75, 0x47, 0xdb]) and b"Mixed_7c.branch_pool/weights" in idx and b"fc/biases" in idx
+    with open(os.path.join(d, "labels.txt"), "w") as f:
+        f.write("\n".join(f"label {i}" for i in range(1000)) + "\n")
+    m = ftf.InceptionModel(model_dir=d, max_batch=4, top_k=5, num_classes=1000, seed=12345)
+    m.open()
+    try:
+        assert m.labels[7] == "label 7" and len(m.labels) == 1000
+        got = m.session.run({"inputs": ftf.TensorValue.from_array(x)}, ["logits", "top_k_indices"])
+        assert np.array_equal(_bits(got["logits"].to_array()), _bits(want["logits"].to_array()))
+        assert np.array_equal(got["top_k_indices"].to_array(), want["top_k_indices"].to_array())
+        with pytest.raises(RuntimeError, match="loaded from a weight file"):
+            m.session.export_weights(str(tmp_path / "again"))
+    finally:
+        m.close()
+    # the fp32 mode reads the same file
+    r32 = ftf.Runner("inception_v3:" + d, None, None, ftf.default_config(max_batch=1, top_k=5, compute_dtype=ftf.DataType.FLOAT))
+    try:
+        l32 = r32.run({"inputs": ftf.TensorValue.from_array(x[:1])}, ["logits"])["logits"].to_array()
+        assert np.abs(l32 - want["logits"].to_array()[:1]).max() <= 1e-2 * np.abs(l32).max()
+    finally:
+        r32.close()
+    # one flipped byte in the data file: the crc32c of that tensor no longer matches
+    bad = str(tmp_path / "bad")
+    shutil.copytree(d, bad)
+    p = os.path.join(bad, "variables", "variables.data-00000-of-00001")
+    with open(p, "r+b") as f:
+        f.seek(1 << 20)
+        b = f.read(1)
+        f.seek(1 << 20)
+        f.write(bytes([b[0] ^ 0x40]))
+    with pytest.raises(ValueError, match="crc32c mismatch"):
+        ftf.Runner("inception_v3:" + bad, None, None, cfg)
+    with pytest.raises(KeyError):
+        ftf.Runner("inception_v3:" + str(tmp_path / "nothing_here"), None, None, cfg)
+    with pytest.raises(ValueError, match="expected FLOAT"):                                            # 1001 classes: fc has the wrong shape
+        ftf.Runner("inception_v3:" + d, None, None, ftf.default_config(max_batch=1, num_classes=1001))
