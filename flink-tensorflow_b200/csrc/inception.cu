@@ -152,6 +152,115 @@ stem_conv3x3s2(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, int 
     ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Conv2d_1a_3x3 on the tensor cores.  K = 27 (padded to 32) is below what TMA im2col can express -- three channels are six
+// bytes, no 16-byte box -- so the A operand is built by the threads: thread t of a 128-thread CTA gathers the 3 x 9 input
+// values of output pixel t (each filter row is nine contiguous elements of the NHWC image), rounds fp32 records to bf16 as
+// it goes, and writes the pixel's 64-byte K row into shared memory in the 64-byte-swizzled K-major layout tcgen05 reads
+// (16-byte chunk j of row r lands at chunk j ^ ((r >> 1) & 3): the pattern TMA's SWIZZLE_64B writes).  The 32 x 32 weight
+// tile gets the same layout.  Two tcgen05.mma (M = 128, N = 32, K = 16) fill a 32-column TMEM accumulator; every thread
+// then reads back its own row (tcgen05.ld), adds the bias, applies ReLU and stores its pixel's 32 channels as 64 bytes.
+// The direct-FMA kernel this replaces (864 FMAs per pixel) was bound by the CUDA cores at twice the layer's HBM time.
+// ------------------------------------------------------------------------------------------------
+struct StemTcParams {
+    float bias[32];
+};
+__device__ __forceinline__ uint32_t stem_pack(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float stem_raw(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+__device__ __forceinline__ float stem_raw(const float* p) { return __ldg(p); }
+template <typename TIn>
+__global__ void __launch_bounds__(128)
+stem_conv_tc(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ w32 /* [32 cout][32 k] */,
+             int n, int H, int W, int OH, int OW, const __grid_constant__ StemTcParams prm, unsigned long long* tl) {
+    __shared__ __align__(1024) uint8_t a_s[128 * 64];
+    __shared__ __align__(1024) uint8_t b_s[32 * 64];
+    __shared__ __align__(8) uint64_t done_bar;
+    __shared__ uint32_t tmem_slot;
+    ptx::tl_stamp_min(tl);
+    const int t = (int)threadIdx.x;
+    const int warp = __shfl_sync(0xffffffffu, t >> 5, 0);
+    if (warp == 0) ptx::tmem_alloc<32>(&tmem_slot);
+    if (t == 32) { ptx::mbar_init(&done_bar, 1); ptx::fence_mbar_init(); }
+    // the weight tile: thread o < 32 writes row o (64 bytes = four swizzled 16-byte chunks)
+    if (t < 32) {
+        const uint4* src = reinterpret_cast<const uint4*>(w32 + (size_t)t * 32);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(b_s + t * 64 + ((j ^ ((t >> 1) & 3)) << 4)) = __ldg(src + j);
+    }
+    ptx::pdl_launch_dependents();
+    ptx::pdl_wait();
+    ptx::tl_stamp_min(tl ? tl + 2 : nullptr);
+    const long long total = (long long)n * OH * OW;
+    const long long pix = (long long)blockIdx.x * 128 + t;
+    const bool live = pix < total;
+    {
+        uint32_t kw[16];                       // 32 bf16: k = ky*9 + kx*3 + c for k < 27, zeros behind
+#pragma unroll
+        for (int i = 0; i < 16; ++i) kw[i] = 0u;
+        if (live) {
+            const int img = (int)(pix / (OH * OW));
+            const int rem = (int)(pix - (long long)img * OH * OW);
+            const int oy = rem / OW, ox = rem - oy * OW;
+            const TIn* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
+            float v[28];
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                for (int i = 0; i < 9; ++i) v[ky * 9 + i] = stem_raw(base + (size_t)ky * W * 3 + i);
+            v[27] = 0.0f;
+#pragma unroll
+            for (int i = 0; i < 14; ++i) kw[i] = stem_pack(v[2 * i], v[2 * i + 1]);      // RNE to bf16, as a cast pass would
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            *reinterpret_cast<uint4*>(a_s + t * 64 + ((j ^ ((t >> 1) & 3)) << 4)) = make_uint4(kw[4 * j], kw[4 * j + 1], kw[4 * j + 2], kw[4 * j + 3]);
+    }
+    ptx::fence_proxy_async();                  // the tensor core reads shared memory through the async proxy
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = tmem_slot;
+    if (warp == 0) {
+        // K-major, 64-byte rows, 8-row groups 512 bytes apart, SWIZZLE_64B; K step 1 starts 32 bytes into the row
+        const uint32_t hi = (uint32_t)(512 >> 4) | (1u << 14) | (4u << 29);
+        const uint32_t a_lo = ((ptx::smem_u32(a_s) & 0x3FFFF) >> 4) | (1u << 16), b_lo = ((ptx::smem_u32(b_s) & 0x3FFFF) >> 4) | (1u << 16);
+        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            uint64_t da, db;
+            asm("mov.b64 %0, {%1, %2};" : "=l"(da) : "r"(a_lo + 2u * k), "r"(hi));
+            asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + 2u * k), "r"(hi));
+            ptx::umma_bf16_elect(tmem_base, da, db, idesc, k ? 1u : 0u);
+        }
+        ptx::umma_commit_elect(&done_bar);
+    }
+    ptx::mbar_wait(&done_bar, 0);
+    ptx::tc_fence_after();
+    uint32_t acc[32];
+    ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
+    ptx::tmem_ld_wait();
+    if (live) {
+        uint4* op = reinterpret_cast<uint4*>(out + (size_t)pix * 32);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint32_t r[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int o = q * 8 + j * 2;
+                r[j] = stem_pack(fmaxf(__uint_as_float(acc[o]) + prm.bias[o], 0.0f), fmaxf(__uint_as_float(acc[o + 1]) + prm.bias[o + 1], 0.0f));
+            }
+            op[q] = make_uint4(r[0], r[1], r[2], r[3]);
+        }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (warp == 0) ptx::tmem_dealloc<32>(tmem_base);
+    ptx::tl_stamp_max(tl ? tl + 1 : nullptr);
+}
+
 __global__ void __launch_bounds__(256) cast_f32_bf16(const float* __restrict__ in, __nv_bfloat16* __restrict__ out, int64_t n) {
     const int64_t stride = (int64_t)gridDim.x * 256;
     for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += stride) out[i] = __float2bfloat16_rn(__ldg(in + i));
@@ -246,6 +355,8 @@ struct InceptionV3::Impl {
     std::vector<Op> ops;
     std::map<std::string, Act> named;     // activations by layer / block name (test hook)
     StemWeights stem;
+    StemTcParams stem_tc;                 // bias of the tensor-core stem kernel
+    __nv_bfloat16* stem_w32 = nullptr;    // its weights, bf16 [32 cout][32 k] (k = ky*9 + kx*3 + c, zeros from 27 on)
     Act image;                            // [max_batch,299,299,3] staging of the caller's images
     float* logits = nullptr;              // [max_batch, classes] fp32
     std::string* err = nullptr;
@@ -488,6 +599,15 @@ struct InceptionV3::Impl {
             for (int o = 0; o < 32 && !f32; ++o) {
                 for (int k = 0; k < 27; ++k) stem.w[k][o] = bf16_value(w[(size_t)o * 27 + k]);
                 stem.b[o] = b[o];
+                stem_tc.bias[o] = b[o];
+            }
+            if (!f32) {
+                std::vector<uint16_t> w32(32 * 32, 0);
+                for (int o = 0; o < 32; ++o)
+                    for (int k = 0; k < 27; ++k) w32[(size_t)o * 32 + k] = bf16_bits(w[(size_t)o * 27 + k]);
+                stem_w32 = (__nv_bfloat16*)dev_alloc(w32.size() * 2, false);
+                if (rc) return;
+                cudaMemcpy(stem_w32, w32.data(), w32.size() * 2, cudaMemcpyHostToDevice);
             }
         }
         Act a1;
@@ -731,6 +851,17 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
             break;
         case Op::kStem: {
             const long long pix = (long long)nb * op.OH * op.OW;
+            static const bool direct = getenv("FTF_STEM_DIRECT") != nullptr;      // measurement switch: the CUDA-core kernel
+            if (!direct) {
+                if (image_dtype == FTF_FLOAT)
+                    FTF_CUDA(launch_pdl(stem_conv_tc<float>, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const float*)image,
+                                        (__nv_bfloat16*)op.out, (const __nv_bfloat16*)m.stem_w32, nb, op.H, op.W, op.OH, op.OW, m.stem_tc, tl), err);
+                else
+                    FTF_CUDA(launch_pdl(stem_conv_tc<__nv_bfloat16>, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const __nv_bfloat16*)image,
+                                        (__nv_bfloat16*)op.out, (const __nv_bfloat16*)m.stem_w32, nb, op.H, op.W, op.OH, op.OW, m.stem_tc, tl), err);
+                count_launch();
+                break;
+            }
             if (image_dtype == FTF_FLOAT)
                 FTF_CUDA(launch_pdl(stem_conv3x3s2<float>, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const float*)image,
                                     (__nv_bfloat16*)op.out, nb, op.H, op.W, op.OH, op.OW, m.stem, tl), err);
