@@ -172,7 +172,7 @@ __device__ __forceinline__ uint32_t stem_pack(float a, float b) {
 __device__ __forceinline__ float stem_raw(const __nv_bfloat16* p) { return __bfloat162float(*p); }
 __device__ __forceinline__ float stem_raw(const float* p) { return __ldg(p); }
 template <typename TIn>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 8)
 stem_conv_tc(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ w32 /* [32 cout][32 k] */,
              int n, int H, int W, int OH, int OW, const __grid_constant__ StemTcParams prm, unsigned long long* tl) {
     __shared__ __align__(1024) uint8_t a_s[128 * 64];
@@ -194,65 +194,76 @@ stem_conv_tc(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, const 
     ptx::pdl_wait();
     ptx::tl_stamp_min(tl ? tl + 2 : nullptr);
     const long long total = (long long)n * OH * OW;
-    const long long pix = (long long)blockIdx.x * 128 + t;
-    const bool live = pix < total;
-    {
-        uint32_t kw[16];                       // 32 bf16: k = ky*9 + kx*3 + c for k < 27, zeros behind
-#pragma unroll
-        for (int i = 0; i < 16; ++i) kw[i] = 0u;
-        if (live) {
-            const int img = (int)(pix / (OH * OW));
-            const int rem = (int)(pix - (long long)img * OH * OW);
-            const int oy = rem / OW, ox = rem - oy * OW;
-            const TIn* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
-            float v[28];
-#pragma unroll
-            for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-                for (int i = 0; i < 9; ++i) v[ky * 9 + i] = stem_raw(base + (size_t)ky * W * 3 + i);
-            v[27] = 0.0f;
-#pragma unroll
-            for (int i = 0; i < 14; ++i) kw[i] = stem_pack(v[2 * i], v[2 * i + 1]);      // RNE to bf16, as a cast pass would
-        }
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-            *reinterpret_cast<uint4*>(a_s + t * 64 + ((j ^ ((t >> 1) & 3)) << 4)) = make_uint4(kw[4 * j], kw[4 * j + 1], kw[4 * j + 2], kw[4 * j + 3]);
-    }
-    ptx::fence_proxy_async();                  // the tensor core reads shared memory through the async proxy
+    const long long tiles = (total + 127) / 128;
     ptx::tc_fence_before();
-    __syncthreads();
+    __syncthreads();                           // TMEM address, barrier and weight tile are in place
     ptx::tc_fence_after();
     const uint32_t tmem_base = tmem_slot;
-    if (warp == 0) {
-        // K-major, 64-byte rows, 8-row groups 512 bytes apart, SWIZZLE_64B; K step 1 starts 32 bytes into the row
-        const uint32_t hi = (uint32_t)(512 >> 4) | (1u << 14) | (4u << 29);
-        const uint32_t a_lo = ((ptx::smem_u32(a_s) & 0x3FFFF) >> 4) | (1u << 16), b_lo = ((ptx::smem_u32(b_s) & 0x3FFFF) >> 4) | (1u << 16);
-        const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    // K-major, 64-byte rows, 8-row groups 512 bytes apart, SWIZZLE_64B; K step 1 starts 32 bytes into the row
+    const uint32_t hi = (uint32_t)(512 >> 4) | (1u << 14) | (4u << 29);
+    const uint32_t a_lo = ((ptx::smem_u32(a_s) & 0x3FFFF) >> 4) | (1u << 16), b_lo = ((ptx::smem_u32(b_s) & 0x3FFFF) >> 4) | (1u << 16);
+    const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(32 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    uint32_t parity = 0;
+    // Persistent: TMEM is allocated once per CTA (allocations on an SM are serialised; one per 128-pixel tile made them
+    // the kernel's critical path) and the CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...; eight CTAs per SM
+    // overlap one another's gather, MMA and store phases.
+    for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const long long pix = tile * 128 + t;
+        const bool live = pix < total;
+        {
+            uint32_t kw[16];                       // 32 bf16: k = ky*9 + kx*3 + c for k < 27, zeros behind
 #pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            uint64_t da, db;
-            asm("mov.b64 %0, {%1, %2};" : "=l"(da) : "r"(a_lo + 2u * k), "r"(hi));
-            asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + 2u * k), "r"(hi));
-            ptx::umma_bf16_elect(tmem_base, da, db, idesc, k ? 1u : 0u);
-        }
-        ptx::umma_commit_elect(&done_bar);
-    }
-    ptx::mbar_wait(&done_bar, 0);
-    ptx::tc_fence_after();
-    uint32_t acc[32];
-    ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
-    ptx::tmem_ld_wait();
-    if (live) {
-        uint4* op = reinterpret_cast<uint4*>(out + (size_t)pix * 32);
+            for (int i = 0; i < 16; ++i) kw[i] = 0u;
+            if (live) {
+                const int img = (int)(pix / (OH * OW));
+                const int rem = (int)(pix - (long long)img * OH * OW);
+                const int oy = rem / OW, ox = rem - oy * OW;
+                const TIn* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
+                float v[28];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            uint32_t r[4];
+                for (int ky = 0; ky < 3; ++ky)
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const int o = q * 8 + j * 2;
-                r[j] = stem_pack(fmaxf(__uint_as_float(acc[o]) + prm.bias[o], 0.0f), fmaxf(__uint_as_float(acc[o + 1]) + prm.bias[o + 1], 0.0f));
+                    for (int i = 0; i < 9; ++i) v[ky * 9 + i] = stem_raw(base + (size_t)ky * W * 3 + i);
+                v[27] = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 14; ++i) kw[i] = stem_pack(v[2 * i], v[2 * i + 1]);      // RNE to bf16, as a cast pass would
             }
-            op[q] = make_uint4(r[0], r[1], r[2], r[3]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                *reinterpret_cast<uint4*>(a_s + t * 64 + ((j ^ ((t >> 1) & 3)) << 4)) = make_uint4(kw[4 * j], kw[4 * j + 1], kw[4 * j + 2], kw[4 * j + 3]);
+        }
+        ptx::fence_proxy_async();                  // the tensor core reads shared memory through the async proxy
+        ptx::tc_fence_before();
+        __syncthreads();                           // (also: every thread has read the previous tile's accumulator)
+        ptx::tc_fence_after();
+        if (warp == 0) {
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                uint64_t da, db;
+                asm("mov.b64 %0, {%1, %2};" : "=l"(da) : "r"(a_lo + 2u * k), "r"(hi));
+                asm("mov.b64 %0, {%1, %2};" : "=l"(db) : "r"(b_lo + 2u * k), "r"(hi));
+                ptx::umma_bf16_elect(tmem_base, da, db, idesc, k ? 1u : 0u);
+            }
+            ptx::umma_commit_elect(&done_bar);
+        }
+        ptx::mbar_wait(&done_bar, parity);         // the MMAs have read a_s and written the accumulator
+        parity ^= 1u;
+        ptx::tc_fence_after();
+        uint32_t acc[32];
+        ptx::tmem_ld_32x32(tmem_base + ((uint32_t)(warp * 32) << 16), acc);
+        ptx::tmem_ld_wait();
+        if (live) {
+            uint4* op = reinterpret_cast<uint4*>(out + (size_t)pix * 32);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t r[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const int o = q * 8 + j * 2;
+                    r[j] = stem_pack(fmaxf(__uint_as_float(acc[o]) + prm.bias[o], 0.0f), fmaxf(__uint_as_float(acc[o + 1]) + prm.bias[o + 1], 0.0f));
+                }
+                op[q] = make_uint4(r[0], r[1], r[2], r[3]);
+            }
         }
     }
     ptx::tc_fence_before();
@@ -853,11 +864,13 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
             const long long pix = (long long)nb * op.OH * op.OW;
             static const bool direct = getenv("FTF_STEM_DIRECT") != nullptr;      // measurement switch: the CUDA-core kernel
             if (!direct) {
+                const long long tiles = (pix + 127) / 128, cap = (long long)m.sms * 8;
+                const unsigned grid = (unsigned)(tiles < cap ? tiles : cap);
                 if (image_dtype == FTF_FLOAT)
-                    FTF_CUDA(launch_pdl(stem_conv_tc<float>, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const float*)image,
+                    FTF_CUDA(launch_pdl(stem_conv_tc<float>, dim3(grid), dim3(128), 0, st, (const float*)image,
                                         (__nv_bfloat16*)op.out, (const __nv_bfloat16*)m.stem_w32, nb, op.H, op.W, op.OH, op.OW, m.stem_tc, tl), err);
                 else
-                    FTF_CUDA(launch_pdl(stem_conv_tc<__nv_bfloat16>, dim3((unsigned)((pix + 127) / 128)), dim3(128), 0, st, (const __nv_bfloat16*)image,
+                    FTF_CUDA(launch_pdl(stem_conv_tc<__nv_bfloat16>, dim3(grid), dim3(128), 0, st, (const __nv_bfloat16*)image,
                                         (__nv_bfloat16*)op.out, (const __nv_bfloat16*)m.stem_w32, nb, op.H, op.W, op.OH, op.OW, m.stem_tc, tl), err);
                 count_launch();
                 break;
