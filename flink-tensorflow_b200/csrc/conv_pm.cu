@@ -553,7 +553,11 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
             const int q_tile = tile / p.n_tiles, n_tile = tile - q_tile * p.n_tiles;
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
+            // a tile of at most 32 columns cannot be split between the two warps of a lane quarter by columns (TMEM is read 32
+            // columns at a time): they take alternate sub-tiles instead, so that all eight epilogue warps work on it
+            const bool by_subtile = min(p.block_n, p.N_total - n_tile * p.block_n) <= 32 && p.S > 1;
             for (int s = 0; s < p.S; ++s) {
+                if (by_subtile && (s & 1) != half) continue;
                 const uint32_t q = (uint32_t)q_tile * (uint32_t)T + (uint32_t)(s * kBlockM + row);      // < 2^31 by plan
                 const int wp = (int)(q % (uint32_t)p.Wp);
                 const uint32_t t = q / (uint32_t)p.Wp;
@@ -562,7 +566,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
                 const bool row_ok = (long long)q < p.Q && wp < p.OW && hp < p.OH;
                 const long long m = (img * p.OH + hp) * p.OW + wp;
                 const uint32_t t_row = tmem_base + (uint32_t)(acc * acc_cols + s * p.block_n) + ((uint32_t)(e * 32) << 16);
-                epilogue_row(p, bias, t_row, n_tile, m, row_ok, half);
+                epilogue_row(p, bias, t_row, n_tile, m, row_ok, by_subtile ? 0 : half);
             }
             ptx::tc_fence_before();
             __syncwarp();
