@@ -2,6 +2,7 @@
 #include "conv_tc.h"
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -22,6 +23,51 @@ struct ChoiceKey {
 };
 std::mutex g_tune_mu;                   // guards g_choice and serialises the timing runs
 std::map<ChoiceKey, int> g_choice;      // -> index into kVariants
+
+// FTF_CONV_PLAN_FILE=<path>: the remembered choices also live in a text file, one "key numbers = variant" line per layer.
+// A process that finds a layer there takes the choice without timing anything; a process that times a layer appends its
+// choice.  This carries a tuned plan from one process to the next: a service restart skips the timing runs, every rank of
+// a job can be handed rank 0's file, and a profiler run (whose overhead would disturb the timing) replays exactly the plan
+// the unprofiled run chose.  Later lines win.
+const char* plan_file() {
+    static const char* path = getenv("FTF_CONV_PLAN_FILE");
+    return (path && path[0]) ? path : nullptr;
+}
+void load_plan_file_locked() {
+    static bool loaded = false;
+    if (loaded || !plan_file()) return;
+    loaded = true;
+    FILE* f = fopen(plan_file(), "r");
+    if (!f) return;
+    char line[1024];
+    while (fgets(line, sizeof line, f)) {
+        ChoiceKey k;
+        char* p = line;
+        bool ok = false;
+        int variant = -1;
+        for (;;) {
+            while (*p == ' ') ++p;
+            if (*p == '=') { variant = atoi(p + 1); ok = true; break; }
+            char* end = nullptr;
+            const long long v = strtoll(p, &end, 10);
+            if (end == p) break;
+            k.v.push_back(v);
+            p = end;
+        }
+        if (ok && variant >= 0 && variant < kConvVariants && !k.v.empty()) g_choice[k] = variant;
+    }
+    fclose(f);
+}
+void append_plan_file_locked(const ChoiceKey& k, int variant) {
+    if (!plan_file()) return;
+    std::string line;
+    for (long long v : k.v) line += std::to_string(v) + " ";
+    line += "= " + std::to_string(variant) + "\n";
+    FILE* f = fopen(plan_file(), "a");
+    if (!f) return;
+    fwrite(line.data(), 1, line.size(), f);      // one short write in append mode: lines of concurrent processes do not interleave
+    fclose(f);
+}
 
 ChoiceKey choice_key(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count) {
     ChoiceKey k;
@@ -59,7 +105,12 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
 
 void conv_tc_choice_put(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, int variant) {
     std::lock_guard<std::mutex> lock(g_tune_mu);
-    g_choice[choice_key(g, segs, n_seg, sm_count)] = variant;
+    load_plan_file_locked();
+    const ChoiceKey k = choice_key(g, segs, n_seg, sm_count);
+    auto it = g_choice.find(k);
+    if (it != g_choice.end() && it->second == variant) return;
+    g_choice[k] = variant;
+    append_plan_file_locked(k, variant);
 }
 
 int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlanSet* set,
@@ -135,6 +186,7 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
     if (cacheable) {
         key = choice_key(g, segs, n_seg, sm_count);
         tune_lock.lock();
+        load_plan_file_locked();
         auto it = g_choice.find(key);
         if (it != g_choice.end())
             for (int i = 0; i < n_cand; ++i)
@@ -169,7 +221,7 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
         if (e1) cudaEventDestroy(e1);
         if (s) cudaStreamDestroy(s);
         cudaGetLastError();
-        if (cacheable) g_choice[key] = cand_variant[best];
+        if (cacheable) { g_choice[key] = cand_variant[best]; append_plan_file_locked(key, cand_variant[best]); }
     }
     set->n = n_cand;
     set->chosen = best;
@@ -179,7 +231,7 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
     if (getenv("FTF_CONV_VERBOSE")) {
         const bool hm = plan->kind ? plan->wm.p.halo_mode : plan->pm.p.halo_mode;
         fprintf(stderr, "conv %dx%d s%d Cin %d Cout %d HxW %dx%d -> %s%s kc %d (%d candidates, %s)\n", g.KH, g.KW, g.stride, g.Cin, g.Cout, g.H, g.W,
-                plan->kind ? "weight-major" : (plan->pm.p.pair ? "pixel-major pair" : "pixel-major"), hm ? " halo" : "", plan->kind ? plan->wm.p.kc : plan->pm.p.kc, n_cand, cached ? "choice of an earlier runner" : (tune ? "timed" : "model"));
+                plan->kind ? "weight-major" : (plan->pm.p.pair ? "pixel-major pair" : "pixel-major"), hm ? " halo" : "", plan->kind ? plan->wm.p.kc : plan->pm.p.kc, n_cand, cached ? "choice of an earlier runner" : ((tune && n_cand > 1) ? "timed" : "model"));
     }
     return FTF_OK;
 }

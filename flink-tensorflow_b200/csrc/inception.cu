@@ -699,6 +699,8 @@ struct InceptionV3::Impl {
         logits_ld = cols;
     }
     int logits_ld = 0;
+    // CTAs per SM of a pooling kernel on a branch stream (beside convolutions): see pools.cu.  FTF_BRANCH_POOL_CTAS overrides (measurement).
+    int branch_pool_ctas = getenv("FTF_BRANCH_POOL_CTAS") ? atoi(getenv("FTF_BRANCH_POOL_CTAS")) : 1;
     int refine(std::string* e);
 };
 
@@ -897,13 +899,13 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
         }
         case Op::kMaxPool: {
             const int rc = m.f32 ? f32::launch_maxpool3x3s2((const float*)op.in, (float*)op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err)
-                                 : launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
+                                 : launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl, op.lane ? m.branch_pool_ctas : 16);
             if (rc) return rc;
             break;
         }
         case Op::kAvgPoolBiasRelu: {
             const int rc = m.f32 ? f32::launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, (float*)op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err)
-                                 : launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl);
+                                 : launch_avgpool3x3_bias_relu((const float*)op.in, op.bias, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl, op.lane ? m.branch_pool_ctas : 16);
             if (rc) return rc;
             break;
         }

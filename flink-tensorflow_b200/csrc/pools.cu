@@ -112,20 +112,24 @@ global_avgpool(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__
 
 }  // namespace
 
-static long long grid_cap(cudaStream_t) {
+// ctas_per_sm: 16 fills an otherwise idle GPU; a pooling kernel that runs BESIDE tensor-core convolutions (the pool branch of
+// an Inception block, on its own stream) is launched with 1: a convolution CTA needs three quarters of an SM's registers, and
+// a pool kernel with thousands of small CTAs floods every SM a convolution has just left, so that the next convolution's CTAs
+// wait for the flood to drain (measured: 7-9 us per block boundary in the 17x17 blocks).
+static long long grid_cap(int ctas_per_sm) {
     int dev = 0;
     cudaGetDevice(&dev);
-    return (long long)device_sm_count(dev) * 16;
+    return (long long)device_sm_count(dev) * (ctas_per_sm > 0 ? ctas_per_sm : 16);
 }
 
 int launch_maxpool3x3s2(const void* in, void* out, int n, int H, int W, int C, int out_ld, int out_off, cudaStream_t s,
-                        std::string* err, unsigned long long* tl) {
+                        std::string* err, unsigned long long* tl, int ctas_per_sm) {
     if (n <= 0) return FTF_OK;
     if (H < 3 || W < 3 || C % 8 || out_ld % 8 || out_off % 8) { if (err) *err = "maxpool3x3s2: H,W >= 3 and C, out_ld, out_off multiples of 8"; return FTF_INVALID_ARGUMENT; }
     const int OH = (H - 3) / 2 + 1, OW = (W - 3) / 2 + 1;
     const long long total = (long long)n * OH * OW * (C / 8);
     if (total >= (1ll << 31)) { if (err) *err = "maxpool3x3s2: tensor too large"; return FTF_INVALID_ARGUMENT; }
-    const long long want = (total + 255) / 256, cap = grid_cap(s);
+    const long long want = (total + 255) / 256, cap = grid_cap(ctas_per_sm);
     FTF_CUDA(launch_pdl(maxpool3x3s2, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, H, W, C,
                         OH, OW, out_ld, out_off, tl), err);
     count_launch();
@@ -133,12 +137,12 @@ int launch_maxpool3x3s2(const void* in, void* out, int n, int H, int W, int C, i
 }
 
 int launch_avgpool3x3_bias_relu(const float* pre, const float* bias, void* out, int n, int H, int W, int C, int out_ld,
-                                int out_off, cudaStream_t s, std::string* err, unsigned long long* tl) {
+                                int out_off, cudaStream_t s, std::string* err, unsigned long long* tl, int ctas_per_sm) {
     if (n <= 0) return FTF_OK;
     if (C % 4 || out_ld % 4 || out_off % 4) { if (err) *err = "avgpool3x3: C, out_ld, out_off multiples of 4"; return FTF_INVALID_ARGUMENT; }
     const long long total = (long long)n * H * W * (C / 4);
     if (total >= (1ll << 31)) { if (err) *err = "avgpool3x3: tensor too large"; return FTF_INVALID_ARGUMENT; }
-    const long long want = (total + 255) / 256, cap = grid_cap(s);
+    const long long want = (total + 255) / 256, cap = grid_cap(ctas_per_sm);
     FTF_CUDA(launch_pdl(avgpool3x3_bias_relu, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, pre, bias, (__nv_bfloat16*)out, n, H, W, C,
                         out_ld, out_off, tl), err);
     count_launch();

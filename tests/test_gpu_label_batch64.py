@@ -287,3 +287,27 @@ def test_trained_weights_are_read_from_a_weight_directory(ftf, tmp_path):
         ftf.Runner("inception_v3:" + str(tmp_path / "nothing_here"), None, None, cfg)
     with pytest.raises(ValueError, match="expected FLOAT"):                                            # 1001 classes: fc has the wrong shape
         ftf.Runner("inception_v3:" + d, None, None, ftf.default_config(max_batch=1, num_classes=1001))
+
+
+def test_kernel_choices_travel_between_processes_through_the_plan_file(ftf, tmp_path):
+    """FTF_CONV_PLAN_FILE: the first process times its candidates and writes its choices, the second one reads them and
+    times nothing -- same kernels (a profiler run replays the plan of the plain run; every rank can be handed one file)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    plan = str(tmp_path / "plan.txt")
+    code = ("import sys, numpy as np; sys.path.insert(0, %r); import ftf_loader; ftf = ftf_loader.load();"
+            "r = ftf.Runner('builtin:inception_v3', None, None, ftf.default_config(max_batch=8, top_k=5, seed=2024));"
+            "x = np.random.default_rng(3).standard_normal((2, 299, 299, 3)).astype(np.float32);"
+            "print('DIGEST', r.run({'inputs': ftf.TensorValue.from_array(x)}, ['logits'])['logits'].to_array().tobytes().hex()[:64]); r.close()") % root
+    env = dict(os.environ, FTF_CONV_PLAN_FILE=plan, FTF_CONV_VERBOSE="1")
+    a = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert a.returncode == 0, a.stderr[-2000:]
+    assert ", timed)" in a.stderr and os.path.getsize(plan) > 0
+    n_lines = sum(1 for _ in open(plan))
+    b = subprocess.run([sys.executable, "-c", code], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=600)
+    assert b.returncode == 0, b.stderr[-2000:]
+    assert ", timed)" not in b.stderr and "choice of an earlier runner" in b.stderr and "refine:" not in b.stderr
+    assert sum(1 for _ in open(plan)) == n_lines                      # nothing new was learnt
+    assert a.stdout.split("DIGEST")[1].strip() == b.stdout.split("DIGEST")[1].strip()
