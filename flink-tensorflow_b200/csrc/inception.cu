@@ -516,6 +516,7 @@ struct InceptionV3::Impl {
         conv_multi(x, {{blk + ".branch1x1", 64, &out, 0, false}, {blk + ".branch5x5_1", 48, &t5, 0, false},
                        {blk + ".branch3x3dbl_1", 64, &t3, 0, false}, {blk + ".branch_pool", pf, &out, 224, true}}, 1, 1, 1, 0, 0);
         fork(0b0110);
+        if (pool_first) { cur_lane = 2; emit_pools(); }
         cur_lane = 0; conv_to(blk + ".branch5x5_2", t5, 64, 5, 5, 1, 2, 2, &out, 64);
         cur_lane = 1; Act u = conv(blk + ".branch3x3dbl_2", t3, 96, 3, 3, 1, 1, 1);
         conv_to(blk + ".branch3x3dbl_3", u, 96, 3, 3, 1, 1, 1, &out, 128);
@@ -543,6 +544,7 @@ struct InceptionV3::Impl {
         conv_multi(x, {{blk + ".branch1x1", 192, &out, 0, false}, {blk + ".branch7x7_1", c7, &t, 0, false},
                        {blk + ".branch7x7dbl_1", c7, &d, 0, false}, {blk + ".branch_pool", 192, &out, 576, true}}, 1, 1, 1, 0, 0);
         fork(0b0110);
+        if (pool_first) { cur_lane = 2; emit_pools(); }
         sm_share_den = 2;
         cur_lane = 0; Act u = conv(blk + ".branch7x7_2", t, c7, 1, 7, 1, 0, 3);
         conv_to(blk + ".branch7x7_3", u, 192, 7, 1, 1, 3, 0, &out, 192);
@@ -581,6 +583,7 @@ struct InceptionV3::Impl {
         conv_multi(x, {{blk + ".branch1x1", 320, &out, 0, false}, {blk + ".branch3x3_1", 384, &t, 0, false},
                        {blk + ".branch3x3dbl_1", 448, &d, 0, false}, {blk + ".branch_pool", 192, &out, 1856, true}}, 1, 1, 1, 0, 0);
         fork(0b1110);
+        if (pool_first) { cur_lane = 3; emit_pools(); }
         sm_share_den = 4;
         cur_lane = 0; conv_to(blk + ".branch3x3_2a", t, 384, 1, 3, 1, 0, 1, &out, 320);
         cur_lane = 1; conv_to(blk + ".branch3x3_2b", t, 384, 3, 1, 1, 1, 0, &out, 704);
@@ -700,7 +703,8 @@ struct InceptionV3::Impl {
     }
     int logits_ld = 0;
     // CTAs per SM of a pooling kernel on a branch stream (beside convolutions): see pools.cu.  FTF_BRANCH_POOL_CTAS overrides (measurement).
-    int branch_pool_ctas = getenv("FTF_BRANCH_POOL_CTAS") ? atoi(getenv("FTF_BRANCH_POOL_CTAS")) : 1;
+    int branch_pool_ctas = getenv("FTF_BRANCH_POOL_CTAS") ? atoi(getenv("FTF_BRANCH_POOL_CTAS")) : 16;
+    bool pool_first = getenv("FTF_POOL_FIRST") != nullptr;      // measurement switch: issue a block's pool kernel before its convolutions
     int refine(std::string* e);
 };
 

@@ -116,6 +116,16 @@ global_avgpool(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__
 // an Inception block, on its own stream) is launched with 1: a convolution CTA needs three quarters of an SM's registers, and
 // a pool kernel with thousands of small CTAs floods every SM a convolution has just left, so that the next convolution's CTAs
 // wait for the flood to drain (measured: 7-9 us per block boundary in the 17x17 blocks).
+// An SM's split between L1 and shared memory is fixed while any CTA runs on it.  A pooling kernel that asks for no shared
+// memory gets SMs configured for a large L1, and a convolution CTA (200 KB of shared memory) cannot start on such an SM until
+// every pool CTA has left it -- nor can a pool CTA join an SM a convolution has configured.  Measured in the Inception blocks:
+// the convolutions behind a pool kernel on a sibling stream started only when the pool kernel had finished, 7-15 us late per
+// block.  Asking for the maximum shared-memory carve-out gives both kinds of kernel the same configuration, so they share SMs.
+template <typename K>
+static void prefer_max_smem(K kernel) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaGetLastError();
+}
 static long long grid_cap(int ctas_per_sm) {
     int dev = 0;
     cudaGetDevice(&dev);
@@ -130,6 +140,7 @@ int launch_maxpool3x3s2(const void* in, void* out, int n, int H, int W, int C, i
     const long long total = (long long)n * OH * OW * (C / 8);
     if (total >= (1ll << 31)) { if (err) *err = "maxpool3x3s2: tensor too large"; return FTF_INVALID_ARGUMENT; }
     const long long want = (total + 255) / 256, cap = grid_cap(ctas_per_sm);
+    prefer_max_smem(maxpool3x3s2);
     FTF_CUDA(launch_pdl(maxpool3x3s2, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, (const __nv_bfloat16*)in, (__nv_bfloat16*)out, n, H, W, C,
                         OH, OW, out_ld, out_off, tl), err);
     count_launch();
@@ -143,6 +154,7 @@ int launch_avgpool3x3_bias_relu(const float* pre, const float* bias, void* out, 
     const long long total = (long long)n * H * W * (C / 4);
     if (total >= (1ll << 31)) { if (err) *err = "avgpool3x3: tensor too large"; return FTF_INVALID_ARGUMENT; }
     const long long want = (total + 255) / 256, cap = grid_cap(ctas_per_sm);
+    prefer_max_smem(avgpool3x3_bias_relu);
     FTF_CUDA(launch_pdl(avgpool3x3_bias_relu, dim3((unsigned)(want < cap ? want : cap)), dim3(256), 0, s, pre, bias, (__nv_bfloat16*)out, n, H, W, C,
                         out_ld, out_off, tl), err);
     count_launch();
