@@ -584,7 +584,7 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
 }  // namespace
 
 int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan, std::string* err,
-         double* est_cycles, bool may_use_halo, bool pair, bool wide_halo) {
+         double* est_cycles, bool may_use_halo, bool pair, bool wide_halo, int halo_S) {
     auto bad = [&](const std::string& m) { if (err) *err = "conv_pm plan: " + m; return FTF_INVALID_ARGUMENT; };
     if (n_seg < 1 || n_seg > kConvMaxSegments) return bad("segment count");
     if (g.Cin % 8 || g.in_ld % 8 || g.Cout % 16) return bad("Cin and the input row stride must be multiples of 8, Cout of 16");
@@ -626,7 +626,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     static const bool allow_kc32 = !(getenv("FTF_NO_KC32") && getenv("FTF_NO_KC32")[0] == '1');
     const double kFill = 36.0, kFixed = 2500.0;
     // experiment switches: force the number of N tiles / halo sub-tiles the shape search may pick
-    const int force_nt = getenv("FTF_PM_NT") ? atoi(getenv("FTF_PM_NT")) : 0, force_S = getenv("FTF_PM_S") ? atoi(getenv("FTF_PM_S")) : 0,
+    const int force_nt = getenv("FTF_PM_NT") ? atoi(getenv("FTF_PM_NT")) : 0, force_S = halo_S ? halo_S : (getenv("FTF_PM_S") ? atoi(getenv("FTF_PM_S")) : 0),
               force_grp = getenv("FTF_PM_BGROUP") ? atoi(getenv("FTF_PM_BGROUP")) : 0;
     const long long kSmem = 208 * 1024;
     double best = -1.0;
@@ -647,8 +647,8 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             if (force_nt && nt != force_nt) continue;
             const int tiles_n = (g.Cout + bn - 1) / bn;
             const long long b_bytes = (long long)bn * rb;
-            if (wide_halo) {
-                // only the wide halo shapes below are candidates
+            if (wide_halo || halo_S) {
+                // only the (wide / S-pinned) halo shapes below are candidates
             } else if (!pair) {   // one im2col load per tap.  Every operand byte is written to shared memory once and read once: 64 + N/2 cycles per MMA
                 const long long tiles = (long long)p.m_tiles * tiles_n, waves = (tiles + sm_count - 1) / sm_count;
                 const double cyc = (double)taps * total_ksteps * (64.0 + bn / 2.0), bytes = (double)taps * chunks * (a_tile + b_bytes) * real_frac;
@@ -708,7 +708,7 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
             }
         }
     }
-    if (best < 0) return bad(wide_halo ? "no wide halo shape for this layer" : "no tile shape fits");
+    if (best < 0) return bad(wide_halo || halo_S ? "no such halo shape for this layer" : "no tile shape fits");
     p.ksteps_last = (g.Cin - p.kc * (p.cin_chunks - 1) + 15) / 16;
     p.wide_stores = 1;
     for (int i = 0; i < n_seg; ++i) {

@@ -50,7 +50,7 @@ struct ConvPlan {
 // Encodes the tensor maps and tile shapes for one convolution (called once, at network build).
 // *est_cycles: modelled cycles of the whole layer on sm_count SMs (for choosing between the two kernels).
 int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
-         std::string* err, double* est_cycles, bool may_use_halo = true, bool pair = false, bool wide_halo = false);
+         std::string* err, double* est_cycles, bool may_use_halo = true, bool pair = false, bool wide_halo = false, int halo_S = 0);
 // Enqueues the convolution for the first n images.
 int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
 // Diagnostic: copies (and optionally clears) the 16 pipeline cycle counters the kernels accumulate when the

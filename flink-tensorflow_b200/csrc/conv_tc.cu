@@ -128,9 +128,12 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
     int n_cand = 0;
     std::string first_err;
     // candidates: pixel-major (im2col / halo window / CTA pair), weight-major (im2col / halo window)
-    struct Variant { int kind; bool halo, pair, wide; };
-    static const Variant kVariants[kConvVariants] = {{0, false, false, false}, {0, true, false, false}, {0, false, true, false},
-                                                     {1, false, false, false}, {1, true, false, false}, {0, true, false, true}};
+    struct Variant { int kind; bool halo, pair, wide; int S; };
+    // 1: the halo shape the cost model likes best; 6-8: the halo window with 1, 2, 4 sub-tiles per CTA tile pinned -- the model
+    // cannot see how a layer's tile count falls on the SMs it gets (190 tiles on 148 SMs is two rounds, 380 is 2.6), the timing can
+    static const Variant kVariants[kConvVariants] = {{0, false, false, false, 0}, {0, true, false, false, 0}, {0, false, true, false, 0},
+                                                     {1, false, false, false, 0}, {1, true, false, false, 0}, {0, true, false, true, 0},
+                                                     {0, true, false, false, 1}, {0, true, false, false, 2}, {0, true, false, false, 4}};
     // The CTA-pair kernel halves the weight bytes each SM pulls from L2.  That pays on layers of many waves, which are bound by
     // L2 -> SM operand fill (Conv2d_4a: 155 -> 137 us); single-wave layers are bound by the K-block cadence of the issuing
     // warp and a pair only halves the number of workers.  So it is a candidate from four tiles per SM on (FTF_CONV_PAIR=0/1
@@ -150,12 +153,18 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
         c.kind = v.kind;
         std::string e;
         const int rc = v.kind ? wm::plan(g, segs, n_seg, sm_count, &c.wm, &e, &c.est_cycles, v.halo)
-                              : pm::plan(g, segs, n_seg, sm_count, &c.pm, &e, &c.est_cycles, v.halo, v.pair, v.wide);
+                              : pm::plan(g, segs, n_seg, sm_count, &c.pm, &e, &c.est_cycles, v.halo, v.pair, v.wide, v.S);
         if (rc == FTF_INTERNAL) { if (err) *err = e; return rc; }   // a CUDA/driver failure, not "this variant does not apply"
         if (rc) { if (first_err.empty()) first_err = e; continue; }
         const bool is_halo = v.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
         if (v.halo && !is_halo) continue;                      // same plan as the no-halo candidate
         if (v.wide && c.pm.p.acc_stages != 1) continue;        // no wide shape exists for this layer
+        if (v.S) {                                             // the same shape as the model's halo candidate: once is enough
+            bool dup = false;
+            for (int k = 0; k < n_cand; ++k)
+                if (cand_variant[k] == 1 && cands[k].pm.p.S == c.pm.p.S && cands[k].pm.p.block_n == c.pm.p.block_n && cands[k].pm.p.kc == c.pm.p.kc) dup = true;
+            if (dup || force) continue;
+        }
         if (v.pair && !c.pm.p.pair) continue;
         cand_variant[n_cand] = vi;
         eligible[n_cand] = force || !(v.pair && no_pair);
@@ -204,8 +213,8 @@ int conv_tc_plan_set(const ConvGeometry& g, const ConvSegment* segs, int n_seg, 
             auto describe = [&](int i, float t) {
                 const ConvPlan& c = cands[i];
                 const bool hm = c.kind ? c.wm.p.halo_mode != 0 : c.pm.p.halo_mode != 0;
-                fprintf(stderr, "   candidate %s%s%s kc %d: %.1f us (model %.0f cycles)%s\n", c.kind ? "wm" : (c.pm.p.pair ? "pm pair" : "pm"), hm ? " halo" : "",
-                        (!c.kind && hm && c.pm.p.acc_stages == 1) ? " wide" : "",
+                fprintf(stderr, "   candidate %s%s%s S%d kc %d: %.1f us (model %.0f cycles)%s\n", c.kind ? "wm" : (c.pm.p.pair ? "pm pair" : "pm"), hm ? " halo" : "",
+                        (!c.kind && hm && c.pm.p.acc_stages == 1) ? " wide" : "", c.kind ? c.wm.p.S : c.pm.p.S,
                         c.kind ? c.wm.p.kc : c.pm.p.kc, t * 1e3f, c.est_cycles, i == model ? "  <- model" : "");
             };
             float best_t = time_candidate(cands[model], g.n_max, s, e0, e1);

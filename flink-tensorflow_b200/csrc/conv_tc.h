@@ -37,7 +37,7 @@ int conv_tc_plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int 
 // Every candidate kernel of a layer and which one the planning chose; the network keeps the set so that it can re-time the
 // alternatives inside the whole forward pass (InceptionV3's in-situ refinement), where sibling branches share the SMs and the
 // L2 -> SM bandwidth, which the isolated timing of conv_tc_plan cannot see.
-constexpr int kConvVariants = 6;     // pm im2col, pm halo, pm pair, wm im2col, wm halo, pm halo with one wide accumulator set
+constexpr int kConvVariants = 9;     // pm im2col, pm halo, pm pair, wm im2col, wm halo, pm halo with one wide accumulator set, pm halo with S = 1 / 2 / 4 pinned
 struct ConvPlanSet {
     ConvPlan cands[kConvVariants];
     int variant[kConvVariants];   // which of the kernel variants cands[i] is (the value remembered per process)
