@@ -44,15 +44,21 @@ int launch_softmax_topk(const float* x, int64_t m, int n, int n_labels, int k, i
 
 // Launch with programmatic dependent launch allowed (see ptx::pdl_wait): inside a stream or a captured graph the next
 // kernel's prologue overlaps this kernel's tail.
+// Priority of the kernels the calling thread launches from here on (0: the stream's own).  The block scheduler hands pending
+// CTAs of a higher-priority grid to a freed SM first, whichever grid was launched earlier: InceptionV3 gives its convolutions
+// a higher priority than the pooling kernel of the sibling branch (see run_ops).  Also recorded into captured graph nodes.
+inline int& launch_priority() { static thread_local int p = 0; return p; }
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl_cluster(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, int cluster, Args&&... args) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
-    cudaLaunchAttribute at[2];
+    cudaLaunchAttribute at[3];
     static const bool off = getenv("FTF_NO_PDL") != nullptr;      // A/B switch for measurements
     int n = 0;
     if (!off) { at[n].id = cudaLaunchAttributeProgrammaticStreamSerialization; at[n].val.programmaticStreamSerializationAllowed = 1; ++n; }
     if (cluster > 1) { at[n].id = cudaLaunchAttributeClusterDimension; at[n].val.clusterDim.x = (unsigned)cluster; at[n].val.clusterDim.y = 1; at[n].val.clusterDim.z = 1; ++n; }
+    if (launch_priority() != 0) { at[n].id = cudaLaunchAttributePriority; at[n].val.priority = launch_priority(); ++n; }
     cfg.attrs = at; cfg.numAttrs = (unsigned)n;
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }

@@ -286,7 +286,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         long long t_wait = 0;
         const long long t_begin = prof ? clock64() : 0;
         for (int item = worker; item < total_items; item += n_workers) {
-            const int m_grp = item / p.n_tiles, n_tile = item - m_grp * p.n_tiles;
+            const int item_ = p.reverse ? total_items - 1 - item : item;
+            const int m_grp = item_ / p.n_tiles, n_tile = item_ - m_grp * p.n_tiles;
             // an odd tile count leaves the last pair's second CTA without pixels: it reloads the last tile, stores nothing
             const int m_tile = kPair ? min(2 * m_grp + rank, p.m_tiles - 1) : m_grp;
             const int m0 = m_tile * kBlockM;
@@ -361,7 +362,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
         const long long t_begin = prof ? clock64() : 0;
         for (int item = worker; item < total_items; item += n_workers) {
             ++n_tiles_done;
-            const int m_grp = item / p.n_tiles, n_tile = item - m_grp * p.n_tiles;
+            const int item_ = p.reverse ? total_items - 1 - item : item;
+            const int m_grp = item_ / p.n_tiles, n_tile = item_ - m_grp * p.n_tiles;
             const int m_tile = kPair ? 2 * m_grp + rank : m_grp;
             const long long m = (long long)m_tile * kBlockM + row;
             const bool row_ok = m < p.M;                               // also false for the surplus CTA of an odd last pair
@@ -452,7 +454,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         long long t_wait = 0;
         const long long t_begin = prof ? clock64() : 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const int q_tile = tile / p.n_tiles, n_tile = tile - q_tile * p.n_tiles;
+            const int tile_ = p.reverse ? total_tiles - 1 - tile : tile;
+            const int q_tile = tile_ / p.n_tiles, n_tile = tile_ - q_tile * p.n_tiles;
             // first padded pixel of the window, decoded once per tile (32-bit: the plan keeps Q below 2^31); the loads then
             // step through the padded image incrementally instead of dividing per load
             const uint32_t q0 = (uint32_t)q_tile * (uint32_t)T;
@@ -550,7 +553,8 @@ conv_halo_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant
         const long long t_begin = prof ? clock64() : 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             ++n_tiles_done;
-            const int q_tile = tile / p.n_tiles, n_tile = tile - q_tile * p.n_tiles;
+            const int tile_ = p.reverse ? total_tiles - 1 - tile : tile;
+            const int q_tile = tile_ / p.n_tiles, n_tile = tile_ - q_tile * p.n_tiles;
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
             // a tile of at most 32 columns cannot be split between the two warps of a lane quarter by columns (TMEM is read 32
@@ -775,9 +779,10 @@ int profile_read(unsigned long long* out16, int reset) {
     return FTF_OK;
 }
 
-int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl) {
+int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl, int reverse) {
     ConvParams p = plan.p;
     p.tl = tl;
+    p.reverse = reverse;
     p.M = n * p.OH * p.OW;
     if (p.M <= 0) return FTF_OK;
     p.m_tiles = (p.M + kBlockM - 1) / kBlockM;

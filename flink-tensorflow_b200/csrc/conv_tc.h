@@ -55,7 +55,7 @@ void conv_tc_choice_put(const ConvGeometry& g, const ConvSegment* segs, int n_se
 int conv_tc_plan_cached(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, int device, const ConvPlan** plan,
                         std::string* err, int mode = kPlanModel);
 // Enqueues the convolution for the first n images.
-int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
+int conv_tc_launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr, int reverse = 0);
 // Diagnostic cycle counters of both kernels, summed (see conv_pm.h).
 int conv_tc_profile_read(unsigned long long* out16, int reset);
 

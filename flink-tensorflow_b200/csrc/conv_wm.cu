@@ -187,7 +187,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
         const long long t_begin = profiling ? clock64() : 0;
         int as = 0, aph = 0, bs = 0, bph = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const int p_tile = tile / p.m_tiles, m_tile = tile - p_tile * p.m_tiles;
+            const int tile_ = p.reverse ? total_tiles - 1 - tile : tile;
+            const int p_tile = tile_ / p.m_tiles, m_tile = tile_ - p_tile * p.m_tiles;
             const uint32_t x0 = (uint32_t)p_tile * (uint32_t)T;            // first (virtual) pixel of the tile
             if (!kHalo) {
                 const int img = (int)(x0 / (uint32_t)(p.OH * p.OW));
@@ -316,7 +317,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_p, const __grid_constant__
         int acc = 0, acc_phase = 0, tbuf = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             ++n_done;
-            const int p_tile = tile / p.m_tiles, m_tile = tile - p_tile * p.m_tiles;
+            const int tile_ = p.reverse ? total_tiles - 1 - tile : tile;
+            const int p_tile = tile_ / p.m_tiles, m_tile = tile_ - p_tile * p.m_tiles;
             const uint32_t tile_x0 = (uint32_t)p_tile * (uint32_t)T;
             if (kHalo) {
                 int* tab = pix_tab + tbuf * kMaxTilePixels;
@@ -595,9 +597,10 @@ int profile_read(unsigned long long* out16, int reset) {
     return FTF_OK;
 }
 
-int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl) {
+int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl, int reverse) {
     ConvParams p = plan.p;
     p.tl = tl;
+    p.reverse = reverse;
     p.M = (long long)n * p.OH * p.OW;
     p.Q = (long long)n * p.Hp * p.Wp;
     if (p.M <= 0) return FTF_OK;

@@ -31,6 +31,8 @@ struct ConvParams {
     int w_group;                // halo mode: filter taps whose weight tiles share one stage
     int acc_stages;             // 1 or 2 TMEM accumulator sets of S * np columns
     int ksteps_last;            // K=16 steps holding real channels in the LAST channel chunk (the all-zero rest is skipped)
+    int reverse;                // 1: walk the tiles from the last image to the first (see InceptionV3: the consumer of a tensor larger than L2's share
+                                // walks it in the opposite direction of its producer, so that it starts on what is still cached)
     unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
     unsigned long long* tl;     // timeline stamps of this launch (FTF_TIMELINE), else NULL
 };
@@ -50,7 +52,7 @@ struct ConvPlan {
 int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count, ConvPlan* plan,
          std::string* err, double* est_cycles, bool may_use_halo = true);
 // Enqueues the convolution for the first n images.
-int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr);
+int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsigned long long* tl = nullptr, int reverse = 0);
 // Diagnostic: copies (and optionally clears) the 16 pipeline cycle counters the kernels accumulate when the
 // environment has FTF_CONV_PROFILE=1: [0] CTAs, [1] producer cycles, [2] producer waiting for free stages,
 // [3] MMA-issuer cycles, [4] waiting for operands, [5] waiting for a drained accumulator, [6] epilogue cycles,

@@ -299,6 +299,11 @@ struct Act {
     int h = 0, w = 0, c = 0;
 };
 
+// Images per group of the layers ahead of Mixed_5b (Impl::split_early_layers); 0: whole batch, layer by layer.  Measured at
+// batch 64: groups of 16 make the two max pools 34 us faster (their input is still in L2) and the four convolutions 60 us
+// slower (each launch pays its pipeline fill and its tail again, and 630 tiles fall worse on 148 SMs than 2521), groups of 32
+// come out even: off, and kept as a switch (FTF_EARLY_GROUP=<images>).
+constexpr int kEarlyGroup = 0;
 constexpr int kLanes = 4;                // streams an Inception block's independent branches are spread over
 
 struct Op {
@@ -310,6 +315,8 @@ struct Op {
     void* out = nullptr;
     const float* bias = nullptr;
     int H = 0, W = 0, C = 0, OH = 0, OW = 0, out_ld = 0, out_off = 0;
+    int reverse = 0;                     // walk the tensor from its end (FTF_REVERSE, measurement)
+    int first = 0, count = 0;            // count > 0: the op covers images [first, first + count) of the batch only (Impl::split_early_layers)
     std::string tag;                     // layer name(s) for the FTF_TIMELINE dump
 };
 
@@ -462,17 +469,60 @@ struct InceptionV3::Impl {
             ops.push_back(op);
             return;
         }
-        plan_info.emplace_back();
-        PlanInfo& pi = plan_info.back();
-        pi.g = g; pi.segs = segs; pi.sm = share();
-        rc = conv_tc_plan_set(g, segs.data(), (int)segs.size(), pi.sm, &pi.set, err, kPlanTune);
-        if (rc) return;
-        plans.push_back(pi.set.cands[pi.set.chosen]);
-        Op op{}; op.type = Op::kConv; op.lane = cur_lane; op.plan = (int)plans.size() - 1;
+        Op op{}; op.type = Op::kConv; op.lane = cur_lane;
         op.tag = br[0].name + (br.size() > 1 ? "+" + std::to_string(br.size() - 1) : std::string()) + " " + std::to_string(kh) + "x" + std::to_string(kw) +
                  " " + std::to_string(in.c) + "->" + std::to_string(total) + " @" + std::to_string(OH);
-        plan_info.back().tag = op.tag;
+        if (defer_plans) {        // planned per group of images by split_early_layers
+            deferred.push_back(Deferred{g, segs, OH, OW});
+            op.plan = -(int)deferred.size();
+            ops.push_back(op);
+            return;
+        }
+        op.plan = add_plan(g, segs, share(), op.tag);
+        if (rc) return;
         ops.push_back(op);
+    }
+    int add_plan(const ConvGeometry& g, const std::vector<ConvSegment>& segs, int sm, const std::string& tag) {
+        plan_info.emplace_back();
+        PlanInfo& pi = plan_info.back();
+        pi.g = g; pi.segs = segs; pi.sm = sm; pi.tag = tag;
+        rc = conv_tc_plan_set(g, segs.data(), (int)segs.size(), pi.sm, &pi.set, err, kPlanTune);
+        if (rc) return -1;
+        plans.push_back(pi.set.cands[pi.set.chosen]);
+        return (int)plans.size() - 1;
+    }
+    // The layers between the first convolution and Mixed_5b move 1.2 GB per 64 images through tensors of 44-177 MB each: run
+    // layer by layer over the whole batch, every one of them reads its input from HBM because the producer's output no longer
+    // is in the 126 MB L2 when the consumer gets to it.  Here the ops [begin, end) are re-emitted group by group: all of these
+    // layers for images [0, sub), then for [sub, 2 sub), ... -- a group's tensors (44 MB at most for 16 images) are still in
+    // L2 when the next layer reads them.  Same kernels, same tensors, same bits; a layer's plan is made for `sub` images and
+    // its tensor maps start at the group's first image.
+    struct Deferred { ConvGeometry g; std::vector<ConvSegment> segs; int OH, OW; };
+    std::vector<Deferred> deferred;
+    bool defer_plans = false;
+    void split_early_layers(size_t begin, int sub) {
+        if (rc) return;
+        std::vector<Op> layer_ops(ops.begin() + begin, ops.end());
+        ops.resize(begin);
+        for (int first = 0; first < max_batch && !rc; first += sub) {
+            const int count = std::min(sub, max_batch - first);
+            for (const Op& lo : layer_ops) {
+                Op o = lo;
+                o.first = first; o.count = count;
+                if (o.type == Op::kConv) {
+                    const Deferred& d = deferred[-lo.plan - 1];
+                    ConvGeometry g = d.g;
+                    g.in = (const char*)g.in + (size_t)first * g.H * g.W * g.in_ld * 2;
+                    g.n_max = count;
+                    std::vector<ConvSegment> segs = d.segs;
+                    for (auto& sg : segs) sg.out = (char*)sg.out + (size_t)first * d.OH * d.OW * sg.ld * ((sg.flags & kSegF32) ? 4 : 2);
+                    o.plan = add_plan(g, segs, sms, lo.tag);
+                    if (rc) return;
+                }
+                ops.push_back(o);
+            }
+        }
+        deferred.clear();
     }
     // SMs a convolution may plan for.  The layers of the 17x17 and 8x8 blocks are single-wave kernels whose time is the
     // serial fill -> MMA -> epilogue chain of one tile, and a kernel that spreads over all SMs leaves no room for the
@@ -520,7 +570,7 @@ struct InceptionV3::Impl {
         cur_lane = 0; conv_to(blk + ".branch5x5_2", t5, 64, 5, 5, 1, 2, 2, &out, 64);
         cur_lane = 1; Act u = conv(blk + ".branch3x3dbl_2", t3, 96, 3, 3, 1, 1, 1);
         conv_to(blk + ".branch3x3dbl_3", u, 96, 3, 3, 1, 1, 1, &out, 128);
-        cur_lane = 2; emit_pools();
+        cur_lane = pool_last ? 0 : 2; emit_pools();
         join(0b0110);
         named[blk] = out;
         return out;
@@ -533,7 +583,7 @@ struct InceptionV3::Impl {
         cur_lane = 1; Act t = conv(blk + ".branch3x3dbl_1", x, 64, 1, 1, 1, 0, 0);
         Act u = conv(blk + ".branch3x3dbl_2", t, 96, 3, 3, 1, 1, 1);
         conv_to(blk + ".branch3x3dbl_3", u, 96, 3, 3, 2, 0, 0, &out, 384);
-        cur_lane = 2; maxpool_to(x, &out, 480);
+        cur_lane = pool_last ? 0 : 2; maxpool_to(x, &out, 480);
         join(0b0110);
         named[blk] = out;
         return out;
@@ -554,7 +604,7 @@ struct InceptionV3::Impl {
         Act d4 = conv(blk + ".branch7x7dbl_4", d3, c7, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7dbl_5", d4, 192, 1, 7, 1, 0, 3, &out, 384);
         sm_share_den = 1;
-        cur_lane = 2; emit_pools();
+        cur_lane = pool_last ? 0 : 2; emit_pools();
         join(0b0110);
         named[blk] = out;
         return out;
@@ -572,7 +622,7 @@ struct InceptionV3::Impl {
         Act s3 = conv(blk + ".branch7x7x3_3", s2, 192, 7, 1, 1, 3, 0);
         conv_to(blk + ".branch7x7x3_4", s3, 192, 3, 3, 2, 0, 0, &out, 320);
         sm_share_den = 1;
-        cur_lane = 2; maxpool_to(x, &out, 512);
+        cur_lane = pool_last ? 0 : 2; maxpool_to(x, &out, 512);
         join(0b0110);
         named[blk] = out;
         return out;
@@ -593,7 +643,7 @@ struct InceptionV3::Impl {
         conv_to(blk + ".branch3x3dbl_3a", u, 384, 1, 3, 1, 0, 1, &out, 1088);
         conv_to(blk + ".branch3x3dbl_3b", u, 384, 3, 1, 1, 1, 0, &out, 1472);
         sm_share_den = 1;
-        cur_lane = 3; emit_pools();
+        cur_lane = pool_last ? 0 : 3; emit_pools();
         join(0b1110);
         named[blk] = out;
         return out;
@@ -631,6 +681,10 @@ struct InceptionV3::Impl {
             Op o{}; o.type = Op::kStem; o.in = image.p; o.out = a1.p; o.H = 299; o.W = 299; o.OH = 149; o.OW = 149; ops.push_back(o);
             named["Conv2d_1a_3x3"] = a1;
         }
+        // images per group of the early layers (see split_early_layers); FTF_EARLY_GROUP=0: whole batch, layer by layer
+        const int early_group = f32 ? 0 : (getenv("FTF_EARLY_GROUP") ? atoi(getenv("FTF_EARLY_GROUP")) : kEarlyGroup);
+        const size_t early_begin = ops.size();
+        defer_plans = early_group > 0 && early_group < max_batch;
         Act a2 = conv("Conv2d_2a_3x3", a1, 32, 3, 3, 1, 0, 0);
         Act a3 = conv("Conv2d_2b_3x3", a2, 64, 3, 3, 1, 1, 1);
         Act p1 = act(73, 73, 64);
@@ -641,6 +695,7 @@ struct InceptionV3::Impl {
         Act p2 = act(35, 35, 192);
         maxpool_to(a5, &p2, 0);
         named["pool2"] = p2;
+        if (defer_plans) { defer_plans = false; split_early_layers(early_begin, early_group); if (rc) return; }
         Act x = block_a("Mixed_5b", p2, 32);
         x = block_a("Mixed_5c", x, 64);
         x = block_a("Mixed_5d", x, 64);
@@ -704,6 +759,8 @@ struct InceptionV3::Impl {
     int logits_ld = 0;
     // CTAs per SM of a pooling kernel on a branch stream (beside convolutions): see pools.cu.  FTF_BRANCH_POOL_CTAS overrides (measurement).
     int branch_pool_ctas = getenv("FTF_BRANCH_POOL_CTAS") ? atoi(getenv("FTF_BRANCH_POOL_CTAS")) : 16;
+    int conv_priority = 0;          // launch priority of the convolutions (create(): the device's highest; FTF_CONV_PRIORITY=0 for none)
+    bool pool_last = getenv("FTF_POOL_LAST") != nullptr;        // measurement switch: a block's pool kernel behind the convolutions of its shortest branch (lane 0)
     bool pool_first = getenv("FTF_POOL_FIRST") != nullptr;      // measurement switch: issue a block's pool kernel before its convolutions
     int refine(std::string* e);
 };
@@ -824,8 +881,22 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
         // second build takes over the first one's kernel choices anyway
         static std::mutex build_mu;
         std::lock_guard<std::mutex> lock(build_mu);
+        {
+            int least = 0, greatest = 0;
+            if (cudaDeviceGetStreamPriorityRange(&least, &greatest) != cudaSuccess) { cudaGetLastError(); greatest = 0; }
+            const char* pe = getenv("FTF_CONV_PRIORITY");
+            m.conv_priority = pe ? atoi(pe) : greatest;
+        }
         m.build();
         if (m.rc) return m.rc;
+        if (const char* rv = getenv("FTF_REVERSE")) {      // measurement switch: op indices (as in the FTF_TIMELINE table) to walk backwards
+            for (const char* q = rv; *q;) {
+                const int i = atoi(q);
+                if (i >= 0 && i < (int)m.ops.size()) m.ops[i].reverse = 1;
+                while (*q && *q != ',') ++q;
+                if (*q) ++q;
+            }
+        }
         static const bool no_refine = getenv("FTF_NO_REFINE") != nullptr;      // measurement switch: isolated timing only
         if (!no_refine) { const int rr = m.refine(err); if (rr) return rr; }
     }
@@ -847,10 +918,12 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
 // Enqueues every op of the network for nb images: lane 0 on `s`, the other lanes on the net's own streams,
 // fenced by events at each block's fork and join (the same calls record a graph when `s` is being captured).
 // ops [first, last) are enqueued; the stem convolution (op 0) reads `image`, the caller's batch, where it lies.
-static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* err, const void* image, int image_dtype, size_t first, size_t last) {
+static int run_ops(InceptionV3::Impl& m, int nb_all, cudaStream_t s, std::string* err, const void* image, int image_dtype, size_t first, size_t last) {
     auto stream_of = [&](int lane) { return lane == 0 ? s : m.lane_stream[lane]; };
     for (size_t oi = first; oi < last; ++oi) {
         const Op& op = m.ops[oi];
+        const int nb = op.count > 0 ? std::max(0, std::min(op.count, nb_all - op.first)) : nb_all;     // this op's images
+        if (nb == 0 && op.count > 0) continue;
         cudaStream_t st = stream_of(op.lane);
         unsigned long long* tl = m.tl_dev ? m.tl_dev + 4 * oi : nullptr;
         switch (op.type) {
@@ -891,7 +964,14 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
             break;
         }
         case Op::kConv: {
-            const int rc = conv_tc_launch(m.plans[op.plan], nb, st, err, tl);
+            // Convolutions outrank the pooling kernel of a sibling branch.  A pool kernel has thousands of short CTAs of which
+            // only a few fit on an SM beside a convolution's CTA, so most of them are still pending when a branch's first
+            // convolution ends; at equal priority the block scheduler hands the freed SMs to those older pending CTAs first and
+            // the branch's NEXT convolution (200 KB of shared memory: it needs the whole SM) started only when the pool kernel
+            // had drained -- 8 us late in every 17x17 block, on the block's critical path.
+            launch_priority() = m.conv_priority;
+            const int rc = conv_tc_launch(m.plans[op.plan], nb, st, err, tl, op.reverse);
+            launch_priority() = 0;
             if (rc) return rc;
             break;
         }
@@ -902,8 +982,10 @@ static int run_ops(InceptionV3::Impl& m, int nb, cudaStream_t s, std::string* er
             break;
         }
         case Op::kMaxPool: {
+            const char* in = (const char*)op.in + (size_t)op.first * op.H * op.W * op.C * 2;             // first > 0 in the bf16 mode only
+            char* out = (char*)op.out + (size_t)op.first * op.OH * op.OW * op.out_ld * 2;
             const int rc = m.f32 ? f32::launch_maxpool3x3s2((const float*)op.in, (float*)op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err)
-                                 : launch_maxpool3x3s2(op.in, op.out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl, op.lane ? m.branch_pool_ctas : 16);
+                                 : launch_maxpool3x3s2(in, out, nb, op.H, op.W, op.C, op.out_ld, op.out_off, st, err, tl, op.lane ? m.branch_pool_ctas : 16, op.reverse);
             if (rc) return rc;
             break;
         }

@@ -180,6 +180,44 @@ def test_pool_kernels_match_oracle(dev, oracle):
     assert np.all(np.abs(g - want) <= np.abs(want) * 2.0 ** -8 + 1e-6)
 
 
+@pytest.mark.parametrize("shape", [(2, 147, 147, 64), (2, 71, 71, 192), (1, 35, 35, 288), (2, 17, 17, 768), (3, 9, 13, 40), (1, 3, 3, 32), (2, 20, 6, 64)])
+def test_maxpool_exact_on_every_tile_shape(dev, oracle, shape):
+    """K4 on the Inception pool shapes (TMA-tiled kernel: 64- and 32-channel chunks, tiles that overhang the output grid) and on
+    a channel count that falls back to the one-thread-per-output kernel; exact, written into a concat slice."""
+    import torch
+    rng = np.random.default_rng(sum(shape))
+    n, H, W, C = shape
+    x = _bf16(oracle, rng.standard_normal(shape))
+    OH, OW = (H - 3) // 2 + 1, (W - 3) // 2 + 1
+    out = torch.full((n, OH, OW, C + 16), -7.0, dtype=torch.bfloat16, device="cuda")
+    dev.maxpool3x3s2(_to_bf16_cuda(x), out=out, out_off=8)
+    win = np.lib.stride_tricks.sliding_window_view(x, (3, 3), axis=(1, 2))[:, ::2, ::2]
+    got = out.float().cpu().numpy()
+    assert np.array_equal(got[..., 8:8 + C], win.max(axis=(-1, -2)))
+    assert np.all(got[..., :8] == -7.0) and np.all(got[..., 8 + C:] == -7.0)
+
+
+@pytest.mark.parametrize("shape", [(1, 1, 1, 32), (1, 3, 5, 32), (2, 35, 35, 32), (1, 8, 8, 192), (2, 17, 17, 64), (1, 13, 9, 64)])
+def test_pool_branch_sums_taps_in_row_major_order(dev, oracle, shape):
+    """K5 alone, bit for bit: with identity 1x1 weights the pre-activation IS the input, and the kernel must add the nine taps
+    row-major in fp32 (zero for taps outside the image), times 1/9, plus bias, ReLU, one bf16 rounding -- whatever the strip
+    of rows a thread walks (strips of 6 or 4 rows; heights that are no multiple of either)."""
+    import torch
+    rng = np.random.default_rng(sum(shape))
+    n, H, W, C = shape
+    x = _bf16(oracle, rng.standard_normal(shape))
+    b = rng.uniform(-0.1, 0.1, C).astype(np.float32)
+    got = dev.pool_branch(_to_bf16_cuda(x), _to_bf16_cuda(np.eye(C, dtype=np.float32)), torch.from_numpy(b).cuda())
+    padded = np.pad(x, ((0, 0), (1, 1), (1, 1), (0, 0)))
+    s = np.zeros(shape, np.float32)
+    for ky in range(3):
+        for kx in range(3):
+            s = s + padded[:, ky:ky + H, kx:kx + W, :]
+    want = np.maximum(s * np.float32(1.0 / 9.0) + b, np.float32(0.0))
+    want_bf16 = torch.from_numpy(want).to(torch.bfloat16)
+    assert torch.equal(got.cpu(), want_bf16)
+
+
 @pytest.fixture(scope="module")
 def label_runner(ftf):
     r = ftf.Runner("builtin:inception_v3", None, None, ftf.default_config(max_batch=4, top_k=5, num_classes=1000, seed=2024))

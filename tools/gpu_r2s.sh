@@ -1,0 +1,19 @@
+#!/bin/bash
+set -u
+cd "$(dirname "$0")/.."
+O=gpurun_out; mkdir -p $O
+timeout 900 python -m pytest tests/test_gpu_conv.py tests/test_gpu_label_batch64.py -x -q -m gpu -k "pool or network or batch_64 or layer" > $O/r2s_tests.log 2>&1; tail -3 $O/r2s_tests.log
+run() {  # name, env...
+  name=$1; shift
+  env FTF_CONV_PLAN_FILE=$O/r2s_plan.txt "$@" FTF_TIMELINE=8 timeout 300 python bench.py --quick --steps 30 --warmup 3 > $O/r2s_$name.json 2> $O/r2s_$name.txt
+  python - "$name" <<'PY'
+import json,sys
+b=json.loads(open('gpurun_out/r2s_%s.json'%sys.argv[1]).read().strip().splitlines()[-1]); print(sys.argv[1], 'ms_per_step', round(b['ms_per_step'],4), 'value', round(b['value']), 'launches', b.get('gpu_launches'))
+PY
+  grep maxpool $O/r2s_$name.txt | head -4
+}
+run tma A=1
+run notma FTF_POOL_NO_TMA=1
+run tma2 A=1
+run tma_g16 FTF_EARLY_GROUP=16 FTF_CONV_PLAN_FILE=$O/r2s_plan16.txt
+echo done

@@ -1,0 +1,42 @@
+#!/usr/bin/env python
+"""Compact CSV of the metrics the design notes quote, from an .ncu-rep (one row per captured launch).
+
+usage: python tools/ncu_summary.py gpurun_out/x.ncu-rep profiles/r02_ncu_x.csv
+"""
+import csv
+import subprocess
+import sys
+
+METRICS = [
+    "Kernel Name", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+    "launch__shared_mem_per_block_dynamic", "launch__occupancy_limit_registers", "launch__waves_per_multiprocessor",
+    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "dram__throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct", "lts__t_bytes.sum",
+    "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_active",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed", "sm__inst_executed_pipe_uniform.sum",
+    "sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_tensor_op_hmma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__inst_executed_pipe_tensor.sum", "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__cycles_active.avg", "sm__cycles_elapsed.max",
+    "smsp__average_warp_latency_issue_stalled_long_scoreboard.ratio", "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+    "smsp__thread_inst_executed_per_inst_executed.ratio",
+]
+
+
+def main():
+    rep, out = sys.argv[1], sys.argv[2]
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    head, units, body = rows[0], rows[1], rows[2:]
+    cols = [head.index(m) for m in METRICS if m in head]
+    with open(out, "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow([head[c] for c in cols])
+        w.writerow([units[c] for c in cols])
+        for r in body:
+            w.writerow([r[c] for c in cols])
+    print(out, len(body), "launches,", len(cols), "metrics")
+
+
+if __name__ == "__main__":
+    main()
