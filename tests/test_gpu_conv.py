@@ -197,7 +197,7 @@ def test_maxpool_exact_on_every_tile_shape(dev, oracle, shape):
     assert np.all(got[..., :8] == -7.0) and np.all(got[..., 8 + C:] == -7.0)
 
 
-@pytest.mark.parametrize("shape", [(1, 1, 1, 32), (1, 3, 5, 32), (2, 35, 35, 32), (1, 8, 8, 192), (2, 17, 17, 64), (1, 13, 9, 64)])
+@pytest.mark.parametrize("shape", [(1, 1, 1, 32), (1, 3, 5, 32), (2, 35, 35, 32), (1, 8, 8, 192), (2, 17, 17, 64), (1, 13, 9, 64), (2, 6, 7, 48), (1, 40, 40, 32)])
 def test_pool_branch_sums_taps_in_row_major_order(dev, oracle, shape):
     """K5 alone, bit for bit: with identity 1x1 weights the pre-activation IS the input, and the kernel must add the nine taps
     row-major in fp32 (zero for taps outside the image), times 1/9, plus bias, ReLU, one bf16 rounding -- whatever the strip
