@@ -162,6 +162,7 @@ stem_conv3x3s2(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, int 
 // then reads back its own row (tcgen05.ld), adds the bias, applies ReLU and stores its pixel's 32 channels as 64 bytes.
 // The direct-FMA kernel this replaces (864 FMAs per pixel) was bound by the CUDA cores at twice the layer's HBM time.
 // ------------------------------------------------------------------------------------------------
+constexpr int kStemCtas = 6;             // CTAs per SM of the stem kernel (85 registers each with the next tile's loads in flight)
 struct StemTcParams {
     float bias[32];
 };
@@ -171,8 +172,14 @@ __device__ __forceinline__ uint32_t stem_pack(float a, float b) {
 }
 __device__ __forceinline__ float stem_raw(const __nv_bfloat16* p) { return __bfloat162float(*p); }
 __device__ __forceinline__ float stem_raw(const float* p) { return __ldg(p); }
+__device__ __forceinline__ __nv_bfloat16 stem_fetch(const __nv_bfloat16* p) { return *p; }
+__device__ __forceinline__ float stem_fetch(const float* p) { return __ldg(p); }
+__device__ __forceinline__ __nv_bfloat16 stem_zero(__nv_bfloat16) { return __float2bfloat16(0.0f); }
+__device__ __forceinline__ float stem_zero(float) { return 0.0f; }
+__device__ __forceinline__ float stem_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ float stem_f(float v) { return v; }
 template <typename TIn>
-__global__ void __launch_bounds__(128, 8)
+__global__ void __launch_bounds__(128, kStemCtas)
 stem_conv_tc(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, const __nv_bfloat16* __restrict__ w32 /* [32 cout][32 k] */,
              int n, int H, int W, int OH, int OW, const __grid_constant__ StemTcParams prm, unsigned long long* tl) {
     __shared__ __align__(1024) uint8_t a_s[128 * 64];
@@ -207,31 +214,40 @@ stem_conv_tc(const TIn* __restrict__ in, __nv_bfloat16* __restrict__ out, const 
     // Persistent: TMEM is allocated once per CTA (allocations on an SM are serialised; one per 128-pixel tile made them
     // the kernel's critical path) and the CTA walks tiles blockIdx.x, blockIdx.x + gridDim.x, ...; eight CTAs per SM
     // overlap one another's gather, MMA and store phases.
+    // The 27 loads of the NEXT tile are issued before this tile's MMA and epilogue and consumed at the top of the next
+    // iteration: a CTA has two tiles' worth of loads in flight instead of one serial load -> MMA -> store chain per tile.
+    TIn raw[27];
+    auto gather = [&](long long tile_) {
+        const long long pix_ = tile_ * 128 + t;
+        if (tile_ < tiles && pix_ < total) {
+            const int img = (int)(pix_ / (OH * OW));
+            const int rem = (int)(pix_ - (long long)img * OH * OW);
+            const int oy = rem / OW, ox = rem - oy * OW;
+            const TIn* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
+#pragma unroll
+            for (int ky = 0; ky < 3; ++ky)
+#pragma unroll
+                for (int i = 0; i < 9; ++i) raw[ky * 9 + i] = stem_fetch(base + (size_t)ky * W * 3 + i);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 27; ++i) raw[i] = stem_zero(raw[i]);
+        }
+    };
+    gather(blockIdx.x);
     for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
         const long long pix = tile * 128 + t;
         const bool live = pix < total;
         {
             uint32_t kw[16];                       // 32 bf16: k = ky*9 + kx*3 + c for k < 27, zeros behind
 #pragma unroll
-            for (int i = 0; i < 16; ++i) kw[i] = 0u;
-            if (live) {
-                const int img = (int)(pix / (OH * OW));
-                const int rem = (int)(pix - (long long)img * OH * OW);
-                const int oy = rem / OW, ox = rem - oy * OW;
-                const TIn* base = in + (((size_t)img * H + 2 * oy) * W + 2 * ox) * 3;
-                float v[28];
-#pragma unroll
-                for (int ky = 0; ky < 3; ++ky)
-#pragma unroll
-                    for (int i = 0; i < 9; ++i) v[ky * 9 + i] = stem_raw(base + (size_t)ky * W * 3 + i);
-                v[27] = 0.0f;
-#pragma unroll
-                for (int i = 0; i < 14; ++i) kw[i] = stem_pack(v[2 * i], v[2 * i + 1]);      // RNE to bf16, as a cast pass would
-            }
+            for (int i = 0; i < 13; ++i) kw[i] = stem_pack(stem_f(raw[2 * i]), stem_f(raw[2 * i + 1]));      // RNE to bf16, as a cast pass would
+            kw[13] = stem_pack(stem_f(raw[26]), 0.0f);
+            kw[14] = 0u; kw[15] = 0u;
 #pragma unroll
             for (int j = 0; j < 4; ++j)
                 *reinterpret_cast<uint4*>(a_s + t * 64 + ((j ^ ((t >> 1) & 3)) << 4)) = make_uint4(kw[4 * j], kw[4 * j + 1], kw[4 * j + 2], kw[4 * j + 3]);
         }
+        gather(tile + gridDim.x);
         ptx::fence_proxy_async();                  // the tensor core reads shared memory through the async proxy
         ptx::tc_fence_before();
         __syncthreads();                           // (also: every thread has read the previous tile's accumulator)
@@ -943,7 +959,8 @@ static int run_ops(InceptionV3::Impl& m, int nb_all, cudaStream_t s, std::string
             const long long pix = (long long)nb * op.OH * op.OW;
             static const bool direct = getenv("FTF_STEM_DIRECT") != nullptr;      // measurement switch: the CUDA-core kernel
             if (!direct) {
-                const long long tiles = (pix + 127) / 128, cap = (long long)m.sms * 8;
+                static const int stem_ctas = getenv("FTF_STEM_CTAS") ? std::max(1, std::min(kStemCtas, atoi(getenv("FTF_STEM_CTAS")))) : kStemCtas;    // measurement switch
+                const long long tiles = (pix + 127) / 128, cap = (long long)m.sms * stem_ctas;
                 const unsigned grid = (unsigned)(tiles < cap ? tiles : cap);
                 if (image_dtype == FTF_FLOAT)
                     FTF_CUDA(launch_pdl(stem_conv_tc<float>, dim3(grid), dim3(128), 0, st, (const float*)image,
