@@ -366,7 +366,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__
             const int m_grp = item_ / p.n_tiles, n_tile = item_ - m_grp * p.n_tiles;
             const int m_tile = kPair ? 2 * m_grp + rank : m_grp;
             const long long m = (long long)m_tile * kBlockM + row;
-            const bool row_ok = m < p.M;                               // also false for the surplus CTA of an odd last pair
+            const bool row_ok = m < p.M && !p.dbg_no_store;            // also false for the surplus CTA of an odd last pair
             timed_wait(&tmem_full[acc], acc_phase, prof, &w_epi);
             ptx::tc_fence_after();
             const uint32_t t_row = tmem_base + (uint32_t)(acc * 256) + ((uint32_t)(e * 32) << 16);
@@ -783,6 +783,8 @@ int launch(const ConvPlan& plan, int n, cudaStream_t s, std::string* err, unsign
     ConvParams p = plan.p;
     p.tl = tl;
     p.reverse = reverse;
+    static const bool no_store = getenv("FTF_EPI_NO_STORE") != nullptr;
+    p.dbg_no_store = no_store;
     p.M = n * p.OH * p.OW;
     if (p.M <= 0) return FTF_OK;
     p.m_tiles = (p.M + kBlockM - 1) / kBlockM;

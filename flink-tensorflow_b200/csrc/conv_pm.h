@@ -33,6 +33,7 @@ struct ConvParams {
     int pair;                   // 1: CTA-pair kernel (cta_group::2): tiles of 256 pixels, each CTA holds block_n/2 weight rows
     int wide_stores;            // 1: every segment's rows and channel offset are 32-byte aligned (256-bit epilogue stores)
     int ksteps_last;            // K=16 steps holding real channels in the LAST channel chunk (the all-zero rest is skipped)
+    int dbg_no_store;           // measurement only (FTF_EPI_NO_STORE): the im2col kernel's epilogue computes but does not store
     int reverse;                // 1: walk the tiles from the last image to the first (see InceptionV3: the consumer of a tensor larger than L2's share
                                 // walks it in the opposite direction of its producer, so that it starts on what is still cached)
     unsigned long long* prof;   // diagnostic cycle counters (FTF_CONV_PROFILE=1), else NULL
