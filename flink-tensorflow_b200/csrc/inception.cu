@@ -775,7 +775,7 @@ struct InceptionV3::Impl {
     int logits_ld = 0;
     // CTAs per SM of a pooling kernel on a branch stream (beside convolutions): see pools.cu.  FTF_BRANCH_POOL_CTAS overrides (measurement).
     int branch_pool_ctas = getenv("FTF_BRANCH_POOL_CTAS") ? atoi(getenv("FTF_BRANCH_POOL_CTAS")) : 16;
-    int conv_priority = 0;          // launch priority of the convolutions (create(): the device's highest; FTF_CONV_PRIORITY=0 for none)
+    int conv_priority = 0;          // launch priority of the convolutions (0: none; FTF_CONV_PRIORITY, a measurement switch)
     bool pool_last = getenv("FTF_POOL_LAST") != nullptr;        // measurement switch: a block's pool kernel behind the convolutions of its shortest branch (lane 0)
     bool pool_first = getenv("FTF_POOL_FIRST") != nullptr;      // measurement switch: issue a block's pool kernel before its convolutions
     int refine(std::string* e);
@@ -901,7 +901,7 @@ int InceptionV3::create(int device, int num_classes, uint64_t seed, int max_batc
             int least = 0, greatest = 0;
             if (cudaDeviceGetStreamPriorityRange(&least, &greatest) != cudaSuccess) { cudaGetLastError(); greatest = 0; }
             const char* pe = getenv("FTF_CONV_PRIORITY");
-            m.conv_priority = pe ? atoi(pe) : greatest;
+            m.conv_priority = pe ? std::max(greatest, std::min(least, atoi(pe))) : 0;
         }
         m.build();
         if (m.rc) return m.rc;
@@ -981,11 +981,11 @@ static int run_ops(InceptionV3::Impl& m, int nb_all, cudaStream_t s, std::string
             break;
         }
         case Op::kConv: {
-            // Convolutions outrank the pooling kernel of a sibling branch.  A pool kernel has thousands of short CTAs of which
-            // only a few fit on an SM beside a convolution's CTA, so most of them are still pending when a branch's first
-            // convolution ends; at equal priority the block scheduler hands the freed SMs to those older pending CTAs first and
-            // the branch's NEXT convolution (200 KB of shared memory: it needs the whole SM) started only when the pool kernel
-            // had drained -- 8 us late in every 17x17 block, on the block's critical path.
+            // FTF_CONV_PRIORITY=<p> (measurement switch): convolutions launched at a higher priority than the pool kernel of the
+            // sibling branch.  A branch's next convolution (200 KB of shared memory: it needs a whole SM) starts late while a pool
+            // kernel has CTAs pending, because those slip onto every SM a finished convolution frees.  With priority the block
+            // scheduler prefers the convolution's CTAs and the gap shrinks from 8 to 4-5 us (a pool CTA already on the SM still has
+            // to finish), but the step time did not move (1.306 / 1.307 ms), so the default is no priority.
             launch_priority() = m.conv_priority;
             const int rc = conv_tc_launch(m.plans[op.plan], nb, st, err, tl, op.reverse);
             launch_priority() = 0;

@@ -1,7 +1,7 @@
 // pools.cu -- K4 max pool 3x3/s2, K5 (average pool 3x3/s1 + bias + ReLU) on a 1x1-convolution pre-activation,
 // K6 global average pool.  The pooling nodes of the frozen Inception graph the reference runs
-// (flink-tensorflow-examples/.../inception/InceptionModel.scala:58-67).  All HBM-bound: 16-byte accesses along
-// the channel dimension, outputs written straight into the channel slice of the block's concat tensor.
+// (flink-tensorflow-examples/.../inception/InceptionModel.scala:58-67).  Inputs staged tile by tile with TMA (K4, K5), 16-byte
+// accesses along the channel dimension, outputs written straight into the channel slice of the block's concat tensor.
 #include "pools.h"
 #include "ptx.cuh"
 #include <cuda.h>
@@ -255,15 +255,13 @@ global_avgpool(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__
 
 }  // namespace
 
-// ctas_per_sm: 16 fills an otherwise idle GPU; a pooling kernel that runs BESIDE tensor-core convolutions (the pool branch of
-// an Inception block, on its own stream) is launched with 1: a convolution CTA needs three quarters of an SM's registers, and
-// a pool kernel with thousands of small CTAs floods every SM a convolution has just left, so that the next convolution's CTAs
-// wait for the flood to drain (measured: 7-9 us per block boundary in the 17x17 blocks).
-// An SM's split between L1 and shared memory is fixed while any CTA runs on it.  A pooling kernel that asks for no shared
-// memory gets SMs configured for a large L1, and a convolution CTA (200 KB of shared memory) cannot start on such an SM until
-// every pool CTA has left it -- nor can a pool CTA join an SM a convolution has configured.  Measured in the Inception blocks:
-// the convolutions behind a pool kernel on a sibling stream started only when the pool kernel had finished, 7-15 us late per
-// block.  Asking for the maximum shared-memory carve-out gives both kinds of kernel the same configuration, so they share SMs.
+// The one-thread-per-output kernels (channel counts the tiled kernels do not take): ctas_per_sm caps their grid (16 fills an
+// otherwise idle GPU; FTF_BRANCH_POOL_CTAS for the pool of an Inception branch, a measurement switch).
+// An SM's split between L1 and shared memory is fixed while any CTA runs on it.  A kernel that asks for no shared memory
+// gets SMs configured for a large L1, and a convolution CTA (200 KB of shared memory) cannot start on such an SM until every
+// pool CTA has left it; asking for the maximum shared-memory carve-out gives both kinds of kernel the same configuration.
+// What remains, whatever the pool kernel looks like: a convolution CTA needs a whole SM, so the next
+// convolution of a sibling branch starts only when the pool CTAs that slipped onto a freed SM have left it.
 template <typename K>
 static void prefer_max_smem(K kernel) {
     cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
