@@ -154,7 +154,8 @@ __device__ __forceinline__ void epilogue_chunk_seg(const ConvParams& p, const Co
     if (row_ok) {
         // A thread owns a row, so the 32 lanes of a store instruction hit 32 different cache lines and the LSU spends a tag
         // lookup per lane whatever the width: 256-bit stores (one full 32-byte sector per lane) halve the instruction count
-        // of the 1x1 layers' epilogue, which is what bounds them.  p.wide_stores: every segment keeps 32-byte alignment.
+        // of the epilogue.  With them the stores cost what their bytes cost (FTF_EPI_NO_STORE: the 1x1 layers of the 35x35 blocks
+        // write 38-47 MB and run 5-7 us faster without their stores).  p.wide_stores: every segment keeps 32-byte alignment.
         const size_t off = (size_t)m * sg.ld + sg.coff + (gc - sg.col_begin);
         if (sg.flags & kSegF32) {
             float* o = (float*)sg.out + off;

@@ -416,3 +416,23 @@ def test_fp32_compute_mode_matches_the_fp32_oracle(ftf, oracle):
         assert np.abs(got - want).max() <= 1e-4 * np.abs(want).max()
     finally:
         r2.close()
+
+
+def test_early_layers_in_groups_of_images_give_the_same_bits(ftf, monkeypatch):
+    """FTF_EARLY_GROUP=<n> (a measurement switch): the layers ahead of Mixed_5b run group by group of n images
+    instead of layer by layer over the batch.  Same kernels on the same tensors: logits bit for bit those of the default order,
+    also for a batch that ends inside a group."""
+    x = np.random.default_rng(77).standard_normal((20, 299, 299, 3)).astype(np.float32)
+    outs = []
+    for group in (None, "8"):
+        if group is None:
+            monkeypatch.delenv("FTF_EARLY_GROUP", raising=False)
+        else:
+            monkeypatch.setenv("FTF_EARLY_GROUP", group)
+        r = ftf.Runner("builtin:inception_v3", None, None, ftf.default_config(max_batch=24, top_k=5, num_classes=1000, seed=2024))
+        try:
+            outs.append([r.run({"inputs": ftf.TensorValue.from_array(x[:n])}, ["logits"])["logits"].to_array() for n in (20, 11, 3)])
+        finally:
+            r.close()
+    for a, b in zip(*outs):
+        assert np.array_equal(a, b)
