@@ -44,6 +44,14 @@ struct Slot {
     std::vector<uint64_t> tags;
     std::vector<std::chrono::steady_clock::time_point> t_submit;
     int64_t emitted = 0;
+    // record uploads not yet handed to the copy engine: consecutive records that lie back to back in one pinned allocation (or
+    // in the slot's own staging) and go to consecutive places of d_in are uploaded by ONE copy (see flush_upload in runner.cu)
+    const uint8_t* pend_src = nullptr;
+    size_t pend_off = 0, pend_bytes = 0;      // place in d_in and payload bytes of the run
+    size_t pend_rec = 0, pend_stride = 0;     // bytes of one record; distance of consecutive payloads in host memory (0: one record so far)
+    int64_t pend_n = 0;
+    cudaEvent_t up_done = nullptr;     // behind the slot's last record upload
+    bool up_inflight = false;
     uint32_t downloaded = 0;           // bit j: output j of the batch in flight was copied to h_out[j]
     std::vector<int32_t> rec_status;   // per record of a finished batch of JPEG files: FTF_OK or what was wrong with the file
     // records that arrive as JPEG files (the reference's ImageFileTensor): decoder state of this slot (it stages the

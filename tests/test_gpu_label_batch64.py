@@ -123,6 +123,30 @@ def _stream_records(ftf, runner, recs, how):
             ring[i * rec_bytes:(i + 1) * rec_bytes] = a.reshape(-1).view(np.uint8)
             tensors.append(FtfTensor(code, a.ndim, dims, p + i * rec_bytes, rec_bytes))
         free = lambda: lib.ftf_host_free(p)
+    elif how == "mixed":
+        # runs of records back to back in one pinned allocation (uploaded by one merged copy), records in a second allocation in
+        # reverse order (never mergeable), single-record allocations, and pageable payloads in between (staged by the runner)
+        pa, pb = lib.ftf_host_alloc(n * rec_bytes), lib.ftf_host_alloc(n * rec_bytes)
+        assert pa and pb
+        singles = []
+        for i, a in enumerate(recs):
+            raw = np.ascontiguousarray(a).reshape(-1).view(np.uint8)
+            if i % 7 == 0:
+                bcopy = raw.copy()
+                keep.append(bcopy)
+                addr = bcopy.ctypes.data
+            elif i % 7 in (1, 2, 3):
+                addr = pa + i * rec_bytes
+            elif i % 7 in (4, 5):
+                addr = pb + (n - 1 - i) * rec_bytes
+            else:
+                addr = lib.ftf_host_alloc(rec_bytes)
+                assert addr
+                singles.append(addr)
+            if i % 7:
+                np.ctypeslib.as_array(C.cast(addr, C.POINTER(C.c_uint8)), shape=(rec_bytes,))[:] = raw
+            tensors.append(FtfTensor(code, a.ndim, dims, addr, rec_bytes))
+        free = lambda: [lib.ftf_host_free(q) for q in [pa, pb] + singles]
     elif how == "pageable":
         for a in recs:
             b = np.ascontiguousarray(a).reshape(-1).view(np.uint8).copy()
@@ -169,7 +193,7 @@ def _stream_records(ftf, runner, recs, how):
     return got
 
 
-@pytest.mark.parametrize("how", ["pinned", "pageable", "wire"])
+@pytest.mark.parametrize("how", ["pinned", "pageable", "wire", "mixed"])
 def test_label_records_through_submit_poll(ftf, oracle, net64, how):
     """builtin:inception_v3 behind the 1-in/1-out map: three full micro-batches and a short one, every record's logits and
     top-5 bit-equal to the blocking call on the same records, in submission order; a sample checked against the oracle."""

@@ -62,6 +62,21 @@ def main():
                 print(f"copy size {size / 2**20:8.2f} MiB x {n:5d}: per rank [{per}] GB/s, all ranks together {rates.sum().item():6.1f} GB/s")
         else:
             print(f"copy size {size / 2**20:8.2f} MiB x {n:5d}: {rate:6.1f} GB/s  (host issue {t_issue / n * 1e6:6.1f} us per copy)")
+    if world == 1:
+        # the same record-sized copies spread over several streams (copy engines): does the per-copy gap overlap?
+        size = 1072812
+        n = total // size
+        for k in (1, 2, 3, 4):
+            streams = [torch.cuda.Stream() for _ in range(k)]
+            for rep in range(2):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for i in range(n):
+                    with torch.cuda.stream(streams[i % k]):
+                        dev[i * size:(i + 1) * size].copy_(host[i * size:(i + 1) * size], non_blocking=True)
+                torch.cuda.synchronize()
+                dt = time.perf_counter() - t0
+            print(f"copy size {size / 2**20:8.2f} MiB x {n:5d} over {k} stream(s): {n * size / dt / 1e9:6.1f} GB/s")
     if world > 1:
         dist.destroy_process_group()
 
