@@ -261,7 +261,7 @@ def pinned_array(lib, np, nbytes, dtype):
     return p, np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(nbytes,)).view(dtype)
 
 
-def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_label", sync=None, wire=False, offered_rate=None):
+def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_label", sync=None, wire=False, offered_rate=None, max_batch=None):
     """Records through ftf_submit/ftf_poll at saturation (micro-batches of 64, 2 ms deadline); latency = submit -> result
     polled.  kind "normalize_label": BASELINE config 5 on one GPU, raw 640x480 RGB records (normalise -> Inception-v3 ->
     top-5 on the device).  kind "inception": config 4's records, normalised 299x299x3 fp32 images (Inception-v3 -> top-5),
@@ -269,9 +269,10 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
     wire: every record sits in the pinned ring as a TensorValue wire image (TensorValue.java:142-187) and is decoded in place
     (ftf_tv_decode, no copy) before it is submitted.  offered_rate: records/s the source emits (None = saturation)."""
     from flink_tensorflow_b200.host import _as_ftf, FtfTensor, _check
-    cfg = ftf.default_config(device=device, max_batch=INC["batch"], max_delay_us=2000, top_k=INC["top_k"], out_h=299, out_w=299,
+    max_batch = max_batch or INC["batch"]
+    cfg = ftf.default_config(device=device, max_batch=max_batch, max_delay_us=2000, top_k=INC["top_k"], out_h=299, out_w=299,
                              mean=128.0, scale=128.0, num_classes=INC["classes"], seed=INC["seed"])
-    n_buf = 4 * INC["batch"]                                   # records stay untouched until polled: a ring of pinned payloads
+    n_buf = 4 * max_batch                                   # records stay untouched until polled: a ring of pinned payloads
     if kind == "jpeg_label":
         # BASELINE config 5 with the records the reference's source emits: image FILES (ImageInputFormat.scala:63-80 reads the
         # file, ImageFileTensor wraps its bytes), here 640x480 baseline JPEGs as 0-D STRING tensors in pinned memory
@@ -324,7 +325,9 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
                 _check(lib.ftf_tv_decode(wire_ptrs[slot], wlen, C.byref(decoded), dims_buf), r.handle)
                 rc = lib.ftf_submit(r.handle, i, C.byref(decoded))
             else:
+                t_in = time.perf_counter()
                 rc = lib.ftf_submit(r.handle, i, C.byref(recs[slot]))
+                in_submit[0] += time.perf_counter() - t_in
             if rc != 8:                                        # RESOURCE_EXHAUSTED: every slot holds undelivered results
                 _check(rc, r.handle)
                 return
@@ -342,6 +345,7 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
             checksum[0] += C.cast(outs[2 * q].data, C.POINTER(C.c_int32))[0]
         done += n_ready.value
     checksum = [0]
+    in_submit = [0.0]                                        # seconds the source thread spends inside ftf_submit
     # warm-up (graph capture, allocations)
     n_warm = 4 * INC["batch"]                                # every slot has run once before the clock starts
     for i in range(n_warm):
@@ -355,6 +359,7 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
         drain(True)
     done = 0
     checksum[0] = 0
+    in_submit[0] = 0.0
     if sync:
         sync()
     r2 = r.stats()
@@ -381,10 +386,10 @@ def streaming_bench(ftf, lib, np, device, n_records=64 * 40, kind="normalize_lab
         lib.ftf_host_free(wire_p)
     return {"records_per_s": n_records / dt, "offered_records_per_s": offered_rate,
             "record_format": "TensorValue wire image, decoded in place" if wire else ("JPEG file as a 0-D STRING tensor" if kind == "jpeg_label" else "raw tensor"), "records": n_records, "latency_us_p50": st["queue_latency_us_p50"],
-            "latency_us_p99": st["queue_latency_us_p99"], "max_batch": INC["batch"], "max_delay_us": 2000,
+            "latency_us_p99": st["queue_latency_us_p99"], "max_batch": max_batch, "max_delay_us": 2000,
             "h2d_bytes_per_record": rec_bytes, "d2h_bytes_per_record": 2 * INC["top_k"] * 4, "pipeline": pipeline, "seconds": dt,
             "api": "ftf_submit/ftf_poll, pinned record payloads", "launches": int(st["kernel_launches"] - r2["kernel_launches"]),
-            "checksum": int(checksum[0])}
+            "checksum": int(checksum[0]), "host_us_in_submit_per_record": None if wire else round(in_submit[0] / n_records * 1e6, 2)}
 
 
 def blocking_two_subtasks(ftf, lib, np, device, seconds=1.5):

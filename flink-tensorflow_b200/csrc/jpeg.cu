@@ -22,6 +22,10 @@
 #include "runner.h"
 #include <string.h>
 #include <algorithm>
+#include <condition_variable>
+#include <deque>
+#include <mutex>
+#include <thread>
 
 using namespace ftf;
 using namespace ftf::jpeg;
@@ -246,6 +250,40 @@ struct ftf_jpeg_batch {
     int max_blocks = 0, max_groups = 0, max_chunks = 1;
     bool decoded = false, attr_set = false, committed = false;
     Parsed parsed;                        // scratch of batch_add
+    // Staging (the one host pass over the compressed bytes: unstuff, split at restart markers, copy into pinned memory) costs
+    // 12 us per 77 KB file -- two thirds of what the submitting thread spends per record.  For files whose bytes the caller
+    // leaves alone until the result is out (may_defer) it runs on a worker thread of the batch, into a region of h_scan
+    // reserved by the submitting thread; batch_commit waits for the worker.  Segments are kept per file and put in image order
+    // at commit, so the batch is laid out exactly as if everything had been staged in place.
+    struct StageTask { const uint8_t* file; int64_t len; Parsed parsed; ImageDesc im; int image; size_t dst_off; };
+    std::deque<std::vector<Segment>> file_segs;     // per image (a deque: the worker holds references while images are added)
+    std::vector<std::thread> workers;   // kStageWorkers of them, started with the first deferred file
+    std::mutex mu;
+    std::condition_variable cv_work, cv_idle;
+    std::deque<StageTask> tasks;
+    int outstanding = 0;
+    bool stop = false, stage_failed = false;
+    void worker_loop() {
+        std::unique_lock<std::mutex> lock(mu);
+        for (;;) {
+            cv_work.wait(lock, [&] { return stop || !tasks.empty(); });
+            if (stop) return;                   // whatever is still queued is dropped: its buffers may be gone
+            StageTask t = std::move(tasks.front());
+            tasks.pop_front();
+            std::vector<Segment>& out = file_segs[(size_t)t.image];
+            uint8_t* dst = (uint8_t*)h_scan.p + t.dst_off;
+            lock.unlock();
+            bool truncated = false;
+            stage_scan(t.file, t.len, t.parsed, t.im, t.image, dst, (int64_t)t.dst_off, &out, &truncated);
+            lock.lock();
+            if (truncated) stage_failed = true;
+            if (--outstanding == 0) cv_idle.notify_all();
+        }
+    }
+    void wait_staged() {
+        std::unique_lock<std::mutex> lock(mu);
+        cv_idle.wait(lock, [&] { return outstanding == 0; });
+    }
 };
 
 namespace {
@@ -303,6 +341,11 @@ extern "C" int ftf_jpeg_batch_create(int32_t device, ftf_jpeg_batch** out) {
 extern "C" void ftf_jpeg_batch_destroy(ftf_jpeg_batch* b) {
     if (!b) return;
     cudaSetDevice(b->device);
+    if (!b->workers.empty()) {
+        { std::lock_guard<std::mutex> lock(b->mu); b->stop = true; }
+        b->cv_work.notify_all();
+        for (auto& t : b->workers) t.join();
+    }
     if (b->done) { cudaEventSynchronize(b->done); cudaEventDestroy(b->done); }
     for (Buf* f : {&b->h_scan, &b->h_meta, &b->h_status, &b->d_scan, &b->d_meta, &b->d_coef, &b->d_dc, &b->d_planes, &b->d_status})
         f->free_now();
@@ -320,6 +363,8 @@ int batch_begin(ftf_jpeg_batch* b) {
     FTF_CUDA(cudaSetDevice(b->device), &b->err);
     // the previous batch's uploads and kernels may still be reading the staging buffers
     FTF_CUDA(cudaEventSynchronize(b->done), &b->err);
+    b->wait_staged();                      // an abandoned batch may still have files on their way into h_scan
+    b->file_segs.clear(); b->stage_failed = false;
     b->images.clear(); b->segments.clear(); b->tables.clear(); b->specs.clear(); b->quants.clear();
     b->decoded = false; b->committed = false;
     b->coef_elems = 0; b->plane_bytes = 0; b->rgb_bytes = 0; b->dc_elems = 0; b->max_blocks = 0; b->max_groups = 0;
@@ -327,7 +372,7 @@ int batch_begin(ftf_jpeg_batch* b) {
     return FTF_OK;
 }
 
-int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* height, int32_t* width, int64_t* rgb_offset) {
+int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* height, int32_t* width, int64_t* rgb_offset, bool may_defer) {
     Parsed& p = b->parsed;
     p = Parsed();
     std::string perr;
@@ -347,8 +392,9 @@ int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* heig
     const int64_t coef0 = b->coef_elems, plane0 = b->plane_bytes, dc0 = b->dc_elems, rgb0 = b->rgb_bytes;
     const int blocks0 = b->max_blocks, groups0 = b->max_groups;
     // room in the pinned staging buffer (grown with its contents kept; sized generously so that this is rare)
-    const size_t need = b->scan_bytes + (size_t)stage_bound(len, p, im);
+    const size_t need = b->scan_bytes + align_up((size_t)stage_bound(len, p, im), 16);
     if (need > b->h_scan.cap) {
+        b->wait_staged();                  // the worker writes into the buffer that is about to move
         Buf bigger;
         bigger.host = true;
         if ((rc = bigger.ensure(std::max<size_t>(need * 2, 8u << 20), &b->err))) return rc;
@@ -387,26 +433,58 @@ int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* heig
     const int groups = ((im.width + 7) >> 3) * im.height;
     if (groups > b->max_groups) b->max_groups = groups;
     // the one host pass over the compressed bytes: unstuff + split at restart markers + copy into pinned memory
-    const size_t first_seg = b->segments.size();
+    {
+        std::lock_guard<std::mutex> lock(b->mu);
+        b->file_segs.emplace_back();
+    }
+    // A file that ends with its end-of-image marker cannot turn out truncated (the scan below stops at a marker at the
+    // latest there), so nothing about it can be refused any more: its staging may run behind the caller's back.
+    if (may_defer && len >= 2 && file[len - 2] == 0xFF && file[len - 1] == 0xD9) {
+        if (b->workers.empty()) {
+            // two threads keep up with a submitting thread that spends 4 us per record on everything else (12 us of staging per
+            // 77 KB file); FTF_JPEG_STAGE_THREADS: measurement switch
+            static const int n_workers = getenv("FTF_JPEG_STAGE_THREADS") ? std::max(1, std::min(8, atoi(getenv("FTF_JPEG_STAGE_THREADS")))) : 2;
+            for (int k = 0; k < n_workers; ++k) b->workers.emplace_back([b] { b->worker_loop(); });
+        }
+        {
+            std::lock_guard<std::mutex> lock(b->mu);
+            b->tasks.push_back(ftf_jpeg_batch::StageTask{file, len, p, im, i, b->scan_bytes});
+            b->outstanding += 1;
+        }
+        b->cv_work.notify_one();
+        b->scan_bytes += align_up((size_t)stage_bound(len, p, im), 16);      // reserved (the kernels read whole aligned words); the staged streams are a little shorter
+        b->images.push_back(im);
+        return FTF_OK;
+    }
     bool truncated = false;
-    const size_t staged = (size_t)stage_scan(file, len, p, im, i, (uint8_t*)b->h_scan.p + b->scan_bytes, (int64_t)b->scan_bytes, &b->segments, &truncated);
+    std::vector<Segment>& segs = b->file_segs.back();              // (references into a deque stay valid)
+    const size_t staged = (size_t)stage_scan(file, len, p, im, i, (uint8_t*)b->h_scan.p + b->scan_bytes, (int64_t)b->scan_bytes, &segs, &truncated);
     if (truncated) {
         // the reference's graph leaves DecodeJpeg's try_recover_truncated at false (GraphBuilder.java:41-47 sets channels
         // only): TF refuses a file that ends before its end-of-image marker instead of padding it
-        b->segments.resize(first_seg);
+        { std::lock_guard<std::mutex> lock(b->mu); b->file_segs.pop_back(); }
         b->coef_elems = coef0; b->plane_bytes = plane0; b->dc_elems = dc0; b->rgb_bytes = rgb0;
         b->max_blocks = blocks0; b->max_groups = groups0;
         return bfail(b, FTF_INVALID_ARGUMENT, "image " + std::to_string(i) + ": DecodeJpeg: invalid JPEG data (the file ends inside the scan)");
     }
     b->scan_bytes += staged;
-    for (size_t k = first_seg; k < b->segments.size(); ++k)
-        if (b->segments[k].n_chunks > b->max_chunks) b->max_chunks = b->segments[k].n_chunks;
     b->images.push_back(im);
     return FTF_OK;
 }
 
+void batch_wait_staged(ftf_jpeg_batch* b) { if (b) b->wait_staged(); }
+
 int batch_commit(ftf_jpeg_batch* b, cudaStream_t st) {
     const size_t n = b->images.size();
+    b->wait_staged();
+    if (b->stage_failed) return bfail(b, FTF_INTERNAL, "DecodeJpeg: a deferred file turned out truncated");
+    b->segments.clear();
+    b->max_chunks = 1;
+    for (const auto& fs : b->file_segs)
+        for (const Segment& sg : fs) {
+            b->segments.push_back(sg);
+            if (sg.n_chunks > b->max_chunks) b->max_chunks = sg.n_chunks;
+        }
     if (n == 0) { b->committed = true; return FTF_OK; }
     int rc;
     b->off_seg = align_up(n * sizeof(ImageDesc), 16);
@@ -439,9 +517,9 @@ extern "C" int ftf_jpeg_batch_load(ftf_jpeg_batch* b, int32_t n, const uint8_t* 
     if (n < 0 || (n > 0 && (!files || !lens))) return bfail(b, FTF_INVALID_ARGUMENT, "ftf_jpeg_batch_load: null argument");
     int rc = batch_begin(b);
     for (int i = 0; i < n && rc == FTF_OK; ++i)
-        rc = batch_add(b, files[i], lens[i], heights ? heights + i : nullptr, widths ? widths + i : nullptr, rgb_offsets ? rgb_offsets + i : nullptr);
+        rc = batch_add(b, files[i], lens[i], heights ? heights + i : nullptr, widths ? widths + i : nullptr, rgb_offsets ? rgb_offsets + i : nullptr, /*may_defer=*/true);
     if (rc == FTF_OK) rc = batch_commit(b, (cudaStream_t)stream);
-    if (rc) { b->images.clear(); b->segments.clear(); }
+    if (rc) { b->wait_staged(); b->images.clear(); b->segments.clear(); }      // (the caller's buffers are his again on return)
     return rc;
 }
 

@@ -61,7 +61,11 @@ struct CUstream_st;
 namespace ftf {
 namespace jpeg {
 int batch_begin(ftf_jpeg_batch* b);
-int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* height, int32_t* width, int64_t* rgb_offset);
+// may_defer: the caller leaves the file's bytes alone until the batch has been committed (batch_commit waits); they may then be
+// staged by the batch's worker thread while the caller goes on.
+int batch_add(ftf_jpeg_batch* b, const uint8_t* file, int64_t len, int32_t* height, int32_t* width, int64_t* rgb_offset, bool may_defer = false);
 int batch_commit(ftf_jpeg_batch* b, CUstream_st* stream);
+// Returns when no deferred file is being read any more (a caller that gives up on a batch and takes its buffers back).
+void batch_wait_staged(ftf_jpeg_batch* b);
 }  // namespace jpeg
 }  // namespace ftf

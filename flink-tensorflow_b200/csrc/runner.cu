@@ -263,10 +263,12 @@ int files_begin(ftf_runner* r, Slot& s) {
     s.joff.clear(); s.jh.clear(); s.jw.clear();
     return FTF_OK;
 }
-int files_add(ftf_runner* r, Slot& s, const uint8_t* file, int64_t len) {
+// stable: the caller leaves the file's bytes alone until the batch has been uploaded (a blocking call's inputs; a streamed record
+// in pinned memory, which stays untouched until its result has been polled): its staging may run on the batch's worker thread
+int files_add(ftf_runner* r, Slot& s, const uint8_t* file, int64_t len, bool stable) {
     int32_t h = 0, w = 0;
     int64_t off = 0;
-    const int rc = jpeg::batch_add(s.jpeg, file, len, &h, &w, &off);
+    const int rc = jpeg::batch_add(s.jpeg, file, len, &h, &w, &off, stable);
     if (rc) return fail(r, rc, ftf_jpeg_batch_error(s.jpeg));
     s.joff.push_back(off); s.jh.push_back(h); s.jw.push_back(w);
     return FTF_OK;
@@ -289,8 +291,9 @@ int files_launch(ftf_runner* r, Slot& s) {
 }
 int decode_files(ftf_runner* r, Slot& s, int n, const uint8_t* const* files, const int64_t* lens) {
     int rc = files_begin(r, s);
-    for (int i = 0; i < n && !rc; ++i) rc = files_add(r, s, files[i], lens[i]);
+    for (int i = 0; i < n && !rc; ++i) rc = files_add(r, s, files[i], lens[i], /*stable=*/true);
     if (!rc) rc = files_launch(r, s);
+    if (rc) jpeg::batch_wait_staged(s.jpeg);      // the inputs are the caller's again when this returns
     return rc;
 }
 
@@ -798,7 +801,7 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
         return fail(r, FTF_INVALID_ARGUMENT, "records of one micro-batch must share one format (raw RGB or JPEG files)");
     if (file) {
         if (s.n == 0 && (rc = files_begin(r, s))) return rc;
-        if ((rc = files_add(r, s, file, file_len))) return rc;      // header trouble: the record joins no batch
+        if ((rc = files_add(r, s, file, file_len, pinned(rec->data)))) return rc;      // header trouble: the record joins no batch
         s.files_n += 1;
         s.tags.push_back(tag);
         s.t_submit.push_back(std::chrono::steady_clock::now());

@@ -33,5 +33,21 @@ def main():
         print(f"{n:4d} files: {ms * 1e3:8.1f} us per decode, {ms * 1e3 / n:6.2f} us per file, {n / ms:8.1f} k files/s")
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and len(sys.argv) == 1:
     main()
+
+
+def streaming():
+    """The same files as records through ftf_submit/ftf_poll on builtin:normalize_label, micro-batches of 64 and of 256."""
+    import ctypes as C  # noqa: F401
+    ftf = ftf_loader.load()
+    lib = ftf._abi.load_library()
+    for mb in (64, 128, 256):
+        res = bench.streaming_bench(ftf, lib, np, 0, n_records=mb * 40, kind="jpeg_label", max_batch=mb)
+        print(f"micro-batches of {mb:3d} JPEG records: {res['records_per_s']:9.0f} records/s, "
+              f"p50 {res['latency_us_p50'] / 1e3:.2f} ms, p99 {res['latency_us_p99'] / 1e3:.2f} ms, {res['host_us_in_submit_per_record']} us per record inside ftf_submit "
+              f"of {1e6 / res['records_per_s']:.1f} us per record")
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "streaming":
+    streaming()
