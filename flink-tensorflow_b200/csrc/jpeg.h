@@ -55,7 +55,7 @@ int64_t stage_scan(const uint8_t* d, int64_t n, const Parsed& p, const ImageDesc
 
 // The pieces of ftf_jpeg_batch_load, for callers that receive their files one at a time (ftf_submit): a file is parsed
 // and staged when it arrives, the batch is uploaded when it closes.  batch_add copies what it needs: the caller's buffer
-// is free again when it returns.
+// is free again when it returns (unless the caller allows the staging to be deferred, see may_defer).
 struct ftf_jpeg_batch;
 struct CUstream_st;
 namespace ftf {
