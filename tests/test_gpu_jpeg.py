@@ -1,6 +1,7 @@
 """DecodeJpeg on the GPU (J1-J3, csrc/jpeg.cu) through the C ABI: bit-exact against the libjpeg-turbo fixtures and the
 oracle, alone and in front of the normalisation and labeling models.  Needs a B200 (-m gpu)."""
 import io
+import ctypes as C
 import os
 
 import numpy as np
@@ -320,3 +321,49 @@ def test_files_and_decoded_pixels_label_alike(ftf, oracle):
     assert np.array_equal(_bits(a["logits"].to_array()), _bits(b["logits"].to_array()))
     assert np.array_equal(a["top_k_indices"].to_array(), b["top_k_indices"].to_array())
     r.close()
+
+
+def test_file_records_in_pinned_memory_are_staged_behind_the_callers_back(ftf, oracle, cases):
+    """JPEG records whose bytes lie in ftf_host_alloc memory are unstuffed by the slot's worker threads while the caller submits
+    the next ones (pageable payloads are staged inside ftf_submit).  Both kinds in one micro-batch, a file with restart markers,
+    one that does not end with its EOI marker (never deferred), many batches back to back: order kept, values equal the oracle's."""
+    from flink_tensorflow_b200.host import FtfTensor, _check
+    lib = ftf._abi.load_library()
+    rng = np.random.default_rng(31)
+    base = [_jpeg(_photo(rng, 120, 160), quality=80) for _ in range(5)]
+    base += [cases["420_rst_rows"][0], cases["444_rst_blocks"][0]]          # restart intervals: several segments per file
+    base.append(base[1] + b"\x00\x00")          # trailing bytes behind EOI: staged in place
+    files = [base[i % len(base)] for i in range(90)]
+    blobs = [ftf.bytes_to_tensor(f).buffer for f in files]
+    stride = (max(b.nbytes for b in blobs) + 255) // 256 * 256
+    p = lib.ftf_host_alloc(len(files) * stride)
+    assert p
+    ring = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(len(files) * stride,))
+    cfg = ftf.default_config(max_batch=16, max_delay_us=100000, out_h=32, out_w=24, mean=117.0, scale=1.0)
+    r = ftf.Runner("builtin:image_normalization", None, None, cfg)
+    res = []
+    try:
+        for i, b in enumerate(blobs):
+            if i % 5 == 4:                      # a pageable payload between the pinned ones
+                t = FtfTensor(ftf.DataType.STRING, 0, None, b.ctypes.data, b.nbytes)
+            else:
+                ring[i * stride:i * stride + b.nbytes] = b
+                t = FtfTensor(ftf.DataType.STRING, 0, None, p + i * stride, b.nbytes)
+            while True:
+                rc = lib.ftf_submit(r.handle, 700 + i, C.byref(t))
+                if rc != ftf._abi.RESOURCE_EXHAUSTED:
+                    _check(rc, r.handle)
+                    break
+                res += r.poll(block=True)
+        r.flush()
+        while len(res) < len(files):
+            res += r.poll(block=True)
+    finally:
+        r.close()
+        lib.ftf_host_free(p)
+    assert [t for t, _ in res] == list(range(700, 700 + len(files)))
+    want = {}
+    for (_, tv), f in zip(res, files):
+        if f not in want:
+            want[f] = oracle.resize_bilinear_norm_u8(oracle.jpeg_decode(f)[None], 32, 24, 117.0, 1.0)[0]
+        assert np.array_equal(_bits(tv.to_array()), _bits(want[f]))
