@@ -506,7 +506,7 @@ def per_record_leg(ftf, lib, np, local_rank, lab, seconds=2.0):
     r.close()
     lat = np.sort(np.array(lat)) * 1e6
     out["half_plus_two"] = {"calls_per_s": i / dt, "latency_us_p50": float(lat[len(lat) // 2]), "latency_us_p99": float(lat[int(len(lat) * 0.99)]),
-                            "calls": i, "wrong_answers": int(wrong), "api": "one serialized tf.Example per ftf_run on regress_x_to_y (parse, upload, K1, download)"}
+                            "calls": i, "wrong_answers": int(wrong), "api": "one serialized tf.Example per ftf_run on regress_x_to_y (parse, K1 on the mapped pinned buffers: no copies)"}
     # one image per label call on the batch-64 runner (a batch of one replays the 8-image graph bucket)
     nb = 299 * 299 * 3 * 4
     p, hx = pinned_array(lib, np, nb, np.float32)

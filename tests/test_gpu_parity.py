@@ -360,3 +360,23 @@ def test_mini_cluster_subtasks(ftf, oracle, model_dir):
     outs = [ftf.MiniCluster(p, n_gpus).run(recs, lambda dev: ftf.HalfPlusTwo(model_dir, device=dev), fun)
             for p in (1, 4)]
     assert outs[0] == outs[1] == oracle.affine_f32(xs, 0.5, 2.0).tolist()
+
+
+@pytest.mark.parametrize("n", [1, 2, 4095, 4096, 4097, 9000])
+def test_small_affine_calls_run_on_the_pinned_buffers_themselves(ftf, oracle, model_dir, n):
+    """Up to 16 KB a blocking affine call makes no copies: K1 reads the pinned input and writes the pinned output (mapped host
+    memory).  Same bits either side of that limit, edge values included, and repeated calls do not see one another's data."""
+    model = ftf.HalfPlusTwo(model_dir)
+    model.open()
+    try:
+        rng = np.random.default_rng(n)
+        for rep in range(3):
+            xs = rng.uniform(-1e6, 1e6, n).astype(np.float32)
+            xs[:min(n, 6)] = np.array([np.nan, np.inf, -np.inf, 1e-42, -0.0, 3.4e38], np.float32)[:min(n, 6)]
+            with model.serving_default(ftf.TensorValue.from_array(xs.reshape(-1, 1))) as y:
+                assert y.shape == (n, 1)
+                got, want = y.to_array().ravel(), oracle.affine_f32(xs, 0.5, 2.0)
+                nan = np.isnan(want)
+                assert np.array_equal(nan, np.isnan(got)) and np.array_equal(_bits(got)[~nan], _bits(want)[~nan])
+    finally:
+        model.close()
