@@ -546,6 +546,8 @@ extern "C" int ftf_jpeg_batch_decode_dev(ftf_jpeg_batch* b, uint8_t* rgb_out, in
     // CTA size: one thread per chunk up to 1024; up to 640 threads the kernel is built for two CTAs per SM (48 registers)
     int threads = (b->max_chunks + 31) / 32 * 32;
     threads = threads > 1024 ? 1024 : threads;
+    static const int thread_cap = getenv("FTF_JPEG_THREADS") ? atoi(getenv("FTF_JPEG_THREADS")) / 32 * 32 : 0;      // measurement switch
+    if (thread_cap >= 32 && threads > thread_cap) threads = thread_cap;
     const size_t hsm = (size_t)threads * kHuffSmemPerThread;
     if (!b->attr_set) {                  // once per batch object: the attribute belongs to the function on this device
         FTF_CUDA(cudaFuncSetAttribute(jpeg_huffman_kernel<640, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 640 * (int)kHuffSmemPerThread), &b->err);
