@@ -22,8 +22,9 @@ import org.apache.flink.types.VersionMismatchException;
  * {@code 8 * rank} and drops the rank and length integers, so a record copied between operators without being
  * deserialised is corrupt.  {@link #copy(DataInputView, DataOutputView)} below forwards the whole image.
  *
- * <p>Payloads are read into pinned direct buffers from {@link Native#hostAlloc}, so a deserialised record can be handed
- * to {@link Native#submit} and uploaded in place (no staging copy in the runner).
+ * <p>Payloads are read into consecutive slices of a {@link PinnedArena} (one ring of {@link Native#hostAlloc} memory per
+ * task thread), so a deserialised record can be handed to {@link Native#submit} and uploaded in place (no staging copy in
+ * the runner), and the uploads of records that arrive one after the other are merged into one copy.
  *
  * <p>SOURCE ONLY: not compiled in this repository's environment (no JDK).
  */
@@ -31,11 +32,25 @@ public final class TensorValueSerializer extends TypeSerializer<TensorValue> {
 	private static final long serialVersionUID = 1L;
 	private static final byte VERSION_1 = 0x1;
 
-	private final boolean pinned;
+	private final long arenaBytes;
+	private transient PinnedArena arena;
 
-	/** @param pinned read payloads into pinned direct buffers (for operators that feed a B200 runner). */
-	public TensorValueSerializer(boolean pinned) {
-		this.pinned = pinned;
+	/**
+	 * @param arenaBytes size of the pinned ring payloads are read into (for operators that feed a B200 runner; it must hold
+	 *        every record that can be in flight, see {@link PinnedArena}); 0: plain direct buffers.
+	 */
+	public TensorValueSerializer(long arenaBytes) {
+		this.arenaBytes = arenaBytes;
+	}
+
+	private ByteBuffer payloadBuffer(int nbytes) {
+		if (arenaBytes <= 0 || nbytes == 0) {
+			return ByteBuffer.allocateDirect(nbytes);
+		}
+		if (arena == null) {
+			arena = new PinnedArena(arenaBytes);
+		}
+		return arena.allocate(nbytes);
 	}
 
 	@Override
@@ -45,7 +60,7 @@ public final class TensorValueSerializer extends TypeSerializer<TensorValue> {
 
 	@Override
 	public TypeSerializer<TensorValue> duplicate() {
-		return this;
+		return new TensorValueSerializer(arenaBytes);   // a ring per task thread
 	}
 
 	@Override
@@ -90,8 +105,7 @@ public final class TensorValueSerializer extends TypeSerializer<TensorValue> {
 			shape[i] = source.readLong();
 		}
 		int nbytes = source.readInt();
-		ByteBuffer payload = (pinned && nbytes > 0 ? Native.hostAlloc(nbytes) : ByteBuffer.allocateDirect(nbytes))
-			.order(ByteOrder.nativeOrder());
+		ByteBuffer payload = payloadBuffer(nbytes).order(ByteOrder.nativeOrder());
 		byte[] chunk = new byte[Math.min(Math.max(nbytes, 1), 1 << 16)];
 		for (int done = 0; done < nbytes; ) {
 			int n = Math.min(chunk.length, nbytes - done);
@@ -128,7 +142,7 @@ public final class TensorValueSerializer extends TypeSerializer<TensorValue> {
 
 	@Override
 	public boolean equals(Object obj) {
-		return obj instanceof TensorValueSerializer && ((TensorValueSerializer) obj).pinned == pinned;
+		return obj instanceof TensorValueSerializer && ((TensorValueSerializer) obj).arenaBytes == arenaBytes;
 	}
 
 	@Override
@@ -138,6 +152,6 @@ public final class TensorValueSerializer extends TypeSerializer<TensorValue> {
 
 	@Override
 	public int hashCode() {
-		return TensorValueSerializer.class.hashCode() + (pinned ? 1 : 0);
+		return TensorValueSerializer.class.hashCode() + Long.hashCode(arenaBytes);
 	}
 }
