@@ -858,6 +858,7 @@ extern "C" int ftf_submit(ftf_runner* r, uint64_t tag, const ftf_tensor* rec) {
             const cudaError_t q = cudaEventQuery(s.up_done);
             if (q == cudaSuccess) s.up_inflight = false;
             else if (q != cudaErrorNotReady) { r->dead = true; return cuda_fail(q, "record upload", &r->err); }
+            else cudaGetLastError();           // "not ready" is an answer, not an error to be found by a later check
         }
         if ((go || !s.up_inflight) && (rc = flush_upload(r, s))) return rc;
         r->stats.h2d_bytes += bytes;
