@@ -709,6 +709,7 @@ def run_ours(args):
     for _ in range(Wm):
         step()
     barrier()
+    launches0 = lib.ftf_launch_count()          # kernels of the timed steps only (not model set-up, plan-time timing or warm-up)
     # FTF_BENCH_CUDA_PROFILER=1: bracket the timed region with cudaProfilerStart/Stop, so that
     # `ncu --profile-from-start off` lists exactly the launches of the timed steps (not the plan-time tuning launches)
     prof_range = os.environ.get("FTF_BENCH_CUDA_PROFILER") == "1"
