@@ -631,7 +631,9 @@ int plan(const ConvGeometry& g, const ConvSegment* segs, int n_seg, int sm_count
     static const bool allow_kc32 = !(getenv("FTF_NO_KC32") && getenv("FTF_NO_KC32")[0] == '1');
     const double kFill = 36.0, kFixed = 2500.0;
     // experiment switches: force the number of N tiles / halo sub-tiles the shape search may pick
-    const int force_nt = getenv("FTF_PM_NT") ? atoi(getenv("FTF_PM_NT")) : 0, force_S = halo_S ? halo_S : (getenv("FTF_PM_S") ? atoi(getenv("FTF_PM_S")) : 0),
+    const int want_nt = getenv("FTF_PM_NT") ? atoi(getenv("FTF_PM_NT")) : 0;
+    const int force_nt = want_nt >= (g.Cout + 255) / 256 && want_nt <= (g.Cout + 31) / 32 ? want_nt : 0;     // only where the layer has that many N tiles
+    const int force_S = halo_S ? halo_S : (getenv("FTF_PM_S") ? atoi(getenv("FTF_PM_S")) : 0),
               force_grp = getenv("FTF_PM_BGROUP") ? atoi(getenv("FTF_PM_BGROUP")) : 0;
     const long long kSmem = 208 * 1024;
     double best = -1.0;
